@@ -1,0 +1,105 @@
+/* rpvg_b200 — C ABI of the B200-native inference hot path of rpvg (everything inside PathEstimator::estimate()).
+ *
+ * Plain C, plain pointers and sizes, no C++/torch types. Every function returns RPVG_B200_OK (0) or a negative
+ * status; rpvg_b200_last_error(ctx) gives the message. Nothing here falls back to the CPU: without a CUDA device
+ * rpvg_b200_create fails and every other entry point needs a ctx.
+ *
+ * Citations "rpvg:<file>:<line>" name the reference code (jonassibbesen/rpvg @ b4d1bdc2) that an entry point replaces.
+ *
+ * Data layout ("cluster arena"): a batch of mutually independent path clusters (rpvg:src/main.cpp:829 treats them as
+ * independent work items), flattened as one CSR over read classes:
+ *   cluster c owns read classes [read_offset[c], read_offset[c+1]) and paths (matrix columns) [path_offset[c], path_offset[c+1]);
+ *   read class r owns entries [row_ptr[r], row_ptr[r+1]); entry e says "path col[e] (cluster-local index) has probability prob[e]".
+ * This is rpvg's vector<ReadPathProbabilities> (rpvg:src/read_path_probabilities.hpp:19-44) with each
+ * pair<double, vector<uint32_t>> expanded to one entry per path id and the entries of a read class sorted by path index
+ * (strictly ascending: a path occurs at most once per read class), i.e. the non-zeros of the dense row that
+ * constructProbabilityMatrix would write (rpvg:src/path_estimator.cpp:55-77).
+ */
+#ifndef RPVG_B200_H
+#define RPVG_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RPVG_B200_OK 0
+#define RPVG_B200_ERR_INVALID -1  /* bad argument / malformed arena */
+#define RPVG_B200_ERR_CUDA -2     /* CUDA runtime error (message has the cudaError string) */
+#define RPVG_B200_ERR_NO_DEVICE -3
+#define RPVG_B200_ERR_LIMIT -4    /* a size is beyond what an entry point supports */
+
+typedef struct rpvg_b200_ctx rpvg_b200_ctx;     /* per (process, device): stream, scratch pools */
+typedef struct rpvg_b200_batch rpvg_b200_batch; /* a cluster arena resident in HBM + its results */
+
+typedef struct {
+    uint32_t n_clusters;
+    const uint64_t * read_offset; /* [n_clusters + 1] */
+    const uint64_t * path_offset; /* [n_clusters + 1] */
+    const uint64_t * row_ptr;     /* [n_reads + 1], n_reads = read_offset[n_clusters] */
+    const uint32_t * col;         /* [nnz], nnz = row_ptr[n_reads] */
+    const double * prob;          /* [nnz]  ReadPathProbabilities::pathProbs() values */
+    const double * noise;         /* [n_reads] ReadPathProbabilities::noiseProb() */
+    const uint32_t * count;       /* [n_reads] ReadPathProbabilities::readCount() */
+} rpvg_b200_clusters;
+
+/* The knobs of PathAbundanceEstimator (rpvg:src/path_abundance_estimator.hpp:22, .cpp:10-14). */
+typedef struct {
+    uint32_t max_em_its;       /* --max-em-its, default 10000 (rpvg:src/main.cpp:416) */
+    double max_rel_em_conv;    /* --max-rel-em-conv, default 0.001 (rpvg:src/main.cpp:417) */
+    uint32_t min_em_conv_its;  /* 10   (rpvg:src/path_abundance_estimator.cpp:10) */
+    double min_em_abundance;   /* 1e-8 (rpvg:src/path_abundance_estimator.cpp:11) */
+} rpvg_b200_em_params;
+
+void rpvg_b200_em_params_default(rpvg_b200_em_params * params);
+
+/* ---- context ---- */
+
+/* device: CUDA ordinal. stream: a cudaStream_t the caller owns (all work of this ctx is enqueued on it), or NULL to
+ * let the ctx create its own non-blocking stream. One ctx per host thread that calls in (rpvg calls estimate() from
+ * OpenMP threads, rpvg:src/main.cpp:829-830,977); a ctx is not re-entrant. */
+int rpvg_b200_create(int device, void * stream, rpvg_b200_ctx ** out_ctx);
+void rpvg_b200_destroy(rpvg_b200_ctx * ctx);
+const char * rpvg_b200_last_error(const rpvg_b200_ctx * ctx);
+const char * rpvg_b200_version(void);
+/* Number of kernel launches this ctx has enqueued so far (for bench.py's gpu_launches). */
+uint64_t rpvg_b200_launch_count(const rpvg_b200_ctx * ctx);
+
+/* ---- transcripts model: matrix build + EM ----
+ * Replaces, for a batch of clusters, the body of PathAbundanceEstimator::estimate
+ * (rpvg:src/path_abundance_estimator.cpp:18-33): constructProbabilityMatrix (rpvg:src/path_estimator.cpp:55-77),
+ * addNoiseAndNormalizeProbabilityMatrix (:156-166) and EMAbundanceEstimator (rpvg:src/path_abundance_estimator.cpp:47-114).
+ * Host pointers in and out; includes the H2D and D2H copies and a stream synchronize.
+ *   abundances  [n_paths]    PathClusterEstimates::abundances of every cluster, concatenated (read counts; 0 below min_em_abundance)
+ *   noise_count [n_clusters] PathClusterEstimates::noise_count
+ *   total_count [n_clusters] PathClusterEstimates::total_count
+ *   iterations  [n_clusters] EM iterations executed (may be NULL)
+ * Clusters without read classes get zeros (rpvg:src/path_abundance_estimator.cpp:20-22). */
+int rpvg_b200_em_abundances(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * clusters, const rpvg_b200_em_params * params,
+                            double * abundances, double * noise_count, double * total_count, uint32_t * iterations);
+
+/* The same in three steps, for callers that keep the arena resident in HBM (bench.py times step 2 alone):
+ * 1. upload: H2D copy of the arena on the ctx stream (returns when the copies have completed, so the host buffers may be
+ *    reused; pinned host memory makes the copies run at full PCIe rate).
+ * 2. em:     matrix build (row normalisation + noise column + column-major index) and EM; asynchronous.
+ * 3. download: D2H of the results + synchronize. */
+int rpvg_b200_batch_upload(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * clusters, rpvg_b200_batch ** out_batch);
+int rpvg_b200_batch_em(rpvg_b200_ctx * ctx, rpvg_b200_batch * batch, const rpvg_b200_em_params * params);
+int rpvg_b200_batch_download(rpvg_b200_ctx * ctx, rpvg_b200_batch * batch, double * abundances, double * noise_count, double * total_count, uint32_t * iterations);
+void rpvg_b200_batch_free(rpvg_b200_ctx * ctx, rpvg_b200_batch * batch);
+
+/* Sum over clusters of nnz_c (path non-zeros + one noise entry per read class) x iterations_c of the last
+ * rpvg_b200_batch_em on this batch, and the algorithmic bytes it moved (12 nnz_path + 20 M + 16 (N+1) per
+ * cluster per iteration). Valid after rpvg_b200_batch_download. */
+int rpvg_b200_batch_em_work(rpvg_b200_ctx * ctx, rpvg_b200_batch * batch, double * nnz_iterations, double * algorithmic_bytes);
+
+/* Device time (CUDA events on the ctx stream) of the two phases of the last rpvg_b200_batch_em on this batch:
+ * matrix build (normalise + column-major index) and the EM kernels. Blocks until that work has finished. */
+int rpvg_b200_batch_em_timings(rpvg_b200_ctx * ctx, rpvg_b200_batch * batch, float * build_ms, float * em_ms);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif

@@ -1,0 +1,194 @@
+"""ctypes view of librpvg_b200.so (include/rpvg_b200.h) for the Python test and bench drivers.
+
+The product is the C ABI; this file only marshals numpy / pinned buffers into it. There is no fallback: if the shared
+library is missing or no CUDA device is present, every entry point raises.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from .arena import ClusterArena
+
+_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "librpvg_b200.so")
+_lib = None
+
+
+class RpvgB200Error(RuntimeError):
+    pass
+
+
+class Clusters(C.Structure):
+    _fields_ = [
+        ("n_clusters", C.c_uint32),
+        ("read_offset", C.c_void_p),
+        ("path_offset", C.c_void_p),
+        ("row_ptr", C.c_void_p),
+        ("col", C.c_void_p),
+        ("prob", C.c_void_p),
+        ("noise", C.c_void_p),
+        ("count", C.c_void_p),
+    ]
+
+
+class EmParams(C.Structure):
+    _fields_ = [
+        ("max_em_its", C.c_uint32),
+        ("max_rel_em_conv", C.c_double),
+        ("min_em_conv_its", C.c_uint32),
+        ("min_em_abundance", C.c_double),
+    ]
+
+
+def library_path() -> str:
+    return _LIB_PATH
+
+
+def lib():
+    """Load librpvg_b200.so (built in-tree by ``__graft_entry__.build()`` / rpvg_b200/csrc/Makefile)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB_PATH):
+            raise RpvgB200Error(f"{_LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                                "(there is no CPU fallback for the CUDA extension)")
+        l = C.CDLL(_LIB_PATH)
+        l.rpvg_b200_version.restype = C.c_char_p
+        l.rpvg_b200_last_error.restype = C.c_char_p
+        l.rpvg_b200_last_error.argtypes = [C.c_void_p]
+        l.rpvg_b200_launch_count.restype = C.c_uint64
+        l.rpvg_b200_launch_count.argtypes = [C.c_void_p]
+        l.rpvg_b200_create.argtypes = [C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]
+        l.rpvg_b200_destroy.argtypes = [C.c_void_p]
+        l.rpvg_b200_em_params_default.argtypes = [C.POINTER(EmParams)]
+        l.rpvg_b200_em_abundances.argtypes = [C.c_void_p, C.POINTER(Clusters), C.POINTER(EmParams)] + [C.c_void_p] * 4
+        l.rpvg_b200_batch_upload.argtypes = [C.c_void_p, C.POINTER(Clusters), C.POINTER(C.c_void_p)]
+        l.rpvg_b200_batch_em.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(EmParams)]
+        l.rpvg_b200_batch_download.argtypes = [C.c_void_p, C.c_void_p] + [C.c_void_p] * 4
+        l.rpvg_b200_batch_em_work.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        l.rpvg_b200_batch_em_timings.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+        l.rpvg_b200_batch_free.argtypes = [C.c_void_p, C.c_void_p]
+        _lib = l
+    return _lib
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data
+    return a.data_ptr()  # torch tensor (pinned host memory)
+
+
+def clusters_struct(arena) -> Clusters:
+    """``arena`` is a ClusterArena (numpy) or any object with the same attribute names holding torch CPU tensors."""
+    s = Clusters()
+    s.n_clusters = len(arena.read_offset) - 1
+    s.read_offset = _ptr(arena.read_offset)
+    s.path_offset = _ptr(arena.path_offset)
+    s.row_ptr = _ptr(arena.row_ptr)
+    s.col = _ptr(arena.col)
+    s.prob = _ptr(arena.prob)
+    s.noise = _ptr(arena.noise)
+    s.count = _ptr(arena.count)
+    return s
+
+
+def default_em_params(max_em_its=10000, max_rel_em_conv=0.001) -> EmParams:
+    p = EmParams()
+    lib().rpvg_b200_em_params_default(C.byref(p))
+    p.max_em_its = max_em_its
+    p.max_rel_em_conv = max_rel_em_conv
+    return p
+
+
+class Context:
+    """One ``rpvg_b200_ctx``: a device and the stream all of its work is enqueued on."""
+
+    def __init__(self, device: int = 0, stream: int | None = None):
+        self._h = C.c_void_p()
+        status = lib().rpvg_b200_create(device, C.c_void_p(stream) if stream else None, C.byref(self._h))
+        if status != 0:
+            self._h = C.c_void_p()
+            raise RpvgB200Error(f"rpvg_b200_create(device={device}) failed with status {status}: "
+                                "a CUDA device is required (no CPU fallback)")
+
+    def close(self):
+        if self._h:
+            lib().rpvg_b200_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, status: int):
+        if status != 0:
+            raise RpvgB200Error(f"status {status}: {lib().rpvg_b200_last_error(self._h).decode()}")
+
+    @property
+    def launches(self) -> int:
+        return int(lib().rpvg_b200_launch_count(self._h))
+
+    # -- transcripts model --------------------------------------------------------------------------------------------
+    def em_abundances(self, arena: ClusterArena, params: EmParams | None = None):
+        """rpvg_b200_em_abundances: host in, host out. Returns (abundances, noise_count, total_count, iterations)."""
+        params = params or default_em_params()
+        Cn = arena.n_clusters
+        abundances = np.empty(arena.n_paths, dtype=np.float64)
+        noise_count = np.empty(Cn, dtype=np.float64)
+        total_count = np.empty(Cn, dtype=np.float64)
+        iterations = np.empty(Cn, dtype=np.uint32)
+        cl = clusters_struct(arena)
+        self._check(lib().rpvg_b200_em_abundances(self._h, C.byref(cl), C.byref(params), abundances.ctypes.data,
+                                                  noise_count.ctypes.data, total_count.ctypes.data, iterations.ctypes.data))
+        return abundances, noise_count, total_count, iterations
+
+    def upload(self, arena) -> "Batch":
+        cl = clusters_struct(arena)
+        h = C.c_void_p()
+        self._check(lib().rpvg_b200_batch_upload(self._h, C.byref(cl), C.byref(h)))
+        return Batch(self, h)
+
+
+class Batch:
+    """A cluster arena resident in HBM (``rpvg_b200_batch``)."""
+
+    def __init__(self, ctx: Context, handle):
+        self.ctx = ctx
+        self._h = handle
+
+    def em(self, params: EmParams | None = None):
+        params = params or default_em_params()
+        self.ctx._check(lib().rpvg_b200_batch_em(self.ctx._h, self._h, C.byref(params)))
+
+    def download(self, abundances, noise_count, total_count, iterations):
+        self.ctx._check(lib().rpvg_b200_batch_download(self.ctx._h, self._h, _ptr(abundances), _ptr(noise_count),
+                                                       _ptr(total_count), _ptr(iterations)))
+
+    def em_work(self) -> tuple[float, float]:
+        """(sum nnz_c x iterations_c, algorithmic bytes) of the last em()."""
+        work, nbytes = C.c_double(), C.c_double()
+        self.ctx._check(lib().rpvg_b200_batch_em_work(self.ctx._h, self._h, C.byref(work), C.byref(nbytes)))
+        return work.value, nbytes.value
+
+    def em_timings(self) -> tuple[float, float]:
+        """(build_ms, em_ms): device time of the matrix build and of the EM kernels of the last em()."""
+        build, em = C.c_float(), C.c_float()
+        self.ctx._check(lib().rpvg_b200_batch_em_timings(self.ctx._h, self._h, C.byref(build), C.byref(em)))
+        return build.value, em.value
+
+    def free(self):
+        if self._h:
+            lib().rpvg_b200_batch_free(self.ctx._h, self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass

@@ -1,0 +1,94 @@
+// Shared declarations of librpvg_b200.so (sm_100a only).
+#pragma once
+
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "rpvg_b200.h"
+
+struct rpvg_b200_ctx {
+
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    int num_sms = 148;
+    int max_smem_optin = 0;
+    uint64_t launches = 0;
+    std::string error;
+};
+
+inline int rpvgFail(rpvg_b200_ctx * ctx, int status, const std::string & message) {
+
+    if (ctx) { ctx->error = message; }
+    return status;
+}
+
+#define RPVG_CUDA(ctx, call)                                                                                     \
+    do {                                                                                                         \
+        cudaError_t rpvg_cuda_err = (call);                                                                      \
+        if (rpvg_cuda_err != cudaSuccess) {                                                                      \
+            return rpvgFail((ctx), RPVG_B200_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(rpvg_cuda_err)); \
+        }                                                                                                        \
+    } while (0)
+
+// Launch bookkeeping: bench.py reports gpu_launches from this counter.
+#define RPVG_LAUNCHED(ctx)                                                                                       \
+    do {                                                                                                         \
+        (ctx)->launches++;                                                                                       \
+        cudaError_t rpvg_launch_err = cudaGetLastError();                                                        \
+        if (rpvg_launch_err != cudaSuccess) {                                                                    \
+            return rpvgFail((ctx), RPVG_B200_ERR_CUDA, std::string("kernel launch: ") + cudaGetErrorString(rpvg_launch_err)); \
+        }                                                                                                        \
+    } while (0)
+
+// Device error flags a kernel may raise (checked at download).
+enum : uint32_t {
+    RPVG_DEV_ERR_COL_RANGE = 1u,   // col[e] >= N_c
+    RPVG_DEV_ERR_COL_ORDER = 2u,   // entries of a read class not strictly ascending by path index
+    RPVG_DEV_ERR_VALUE = 4u        // non-finite or negative probability
+};
+
+#ifdef __CUDACC__
+
+__device__ __forceinline__ double warpSum(double v) {
+
+    #pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        v += __shfl_xor_sync(0xffffffffu, v, off);
+    }
+    return v;
+}
+
+// Deterministic block-wide sum (fixed tree). scratch: >= 32 doubles of shared memory. All threads get the result.
+__device__ __forceinline__ double blockSum(double v, double * scratch) {
+
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int num_warps = (blockDim.x + 31) >> 5;
+
+    v = warpSum(v);
+    __syncthreads();   // scratch may still be read from a previous call
+    if (lane == 0) { scratch[warp] = v; }
+    __syncthreads();
+
+    double r = (lane < num_warps) ? scratch[lane] : 0.0;
+    r = warpSum(r);
+    return r;
+}
+
+// First cluster c with offset[c + 1] > idx (offset non-decreasing, offset[n] > idx).
+__device__ __forceinline__ uint32_t clusterOf(const uint64_t * __restrict__ offset, uint32_t n, uint64_t idx) {
+
+    uint32_t lo = 0, hi = n;
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (__ldg(offset + mid + 1) > idx) { hi = mid; } else { lo = mid + 1; }
+    }
+    return lo;
+}
+
+#endif

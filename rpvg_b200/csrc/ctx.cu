@@ -1,0 +1,84 @@
+// Context management of librpvg_b200.so.
+
+#include "common.cuh"
+
+extern "C" {
+
+const char * rpvg_b200_version(void) {
+
+    return "rpvg_b200 0.1 (sm_100a)";
+}
+
+int rpvg_b200_create(int device, void * stream, rpvg_b200_ctx ** out_ctx) {
+
+    if (!out_ctx) { return RPVG_B200_ERR_INVALID; }
+    *out_ctx = nullptr;
+
+    int count = 0;
+    cudaError_t err = cudaGetDeviceCount(&count);
+
+    // No device, no library: there is no CPU fallback behind this ABI.
+    if (err != cudaSuccess || count == 0) { return RPVG_B200_ERR_NO_DEVICE; }
+    if (device < 0 || device >= count) { return RPVG_B200_ERR_INVALID; }
+
+    if (cudaSetDevice(device) != cudaSuccess) { return RPVG_B200_ERR_CUDA; }
+
+    auto * ctx = new rpvg_b200_ctx();
+    ctx->device = device;
+
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) {
+        delete ctx;
+        return RPVG_B200_ERR_CUDA;
+    }
+
+    ctx->num_sms = prop.multiProcessorCount;
+    ctx->max_smem_optin = static_cast<int>(prop.sharedMemPerBlockOptin);
+
+    if (stream) {
+
+        ctx->stream = static_cast<cudaStream_t>(stream);
+        ctx->own_stream = false;
+
+    } else {
+
+        if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) {
+            delete ctx;
+            return RPVG_B200_ERR_CUDA;
+        }
+        ctx->own_stream = true;
+    }
+
+    // Keep freed batch memory in the pool: batches of similar size follow each other.
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+        uint64_t threshold = UINT64_MAX;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold);
+    }
+
+    *out_ctx = ctx;
+    return RPVG_B200_OK;
+}
+
+void rpvg_b200_destroy(rpvg_b200_ctx * ctx) {
+
+    if (!ctx) { return; }
+
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    if (ctx->own_stream) { cudaStreamDestroy(ctx->stream); }
+
+    delete ctx;
+}
+
+const char * rpvg_b200_last_error(const rpvg_b200_ctx * ctx) {
+
+    return ctx ? ctx->error.c_str() : "no context (is a CUDA device present?)";
+}
+
+uint64_t rpvg_b200_launch_count(const rpvg_b200_ctx * ctx) {
+
+    return ctx ? ctx->launches : 0;
+}
+
+}

@@ -1,0 +1,123 @@
+"""Parity of the CUDA EM path (through the C ABI) with the CPU oracle, transcripts model.
+
+Tolerances are north_star's: per-path read counts within 1e-6 relative, identical set of paths above the min-abundance
+threshold; here additionally identical EM iteration counts (same stopping iteration).
+"""
+
+import numpy as np
+import pytest
+
+from rpvg_b200 import capi, synth
+from rpvg_b200.arena import ClusterArena, concat
+from oracle import loader
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-6
+
+
+def check_against_port(ctx, arena, params=None, **port_kwargs):
+    abundances, noise_count, total_count, iterations = ctx.em_abundances(arena, params)
+    o_ab, o_noise, o_total, o_its, _ = loader.port_em_abundances(arena, **port_kwargs)
+
+    assert np.array_equal(total_count, o_total)
+    assert np.array_equal(abundances == 0, o_ab == 0), "set of paths above min_em_abundance differs"
+    nz = o_ab != 0
+    if nz.any():
+        rel = np.max(np.abs(abundances[nz] - o_ab[nz]) / o_ab[nz])
+        assert rel < REL_TOL, rel
+    assert np.allclose(noise_count, o_noise, rtol=REL_TOL, atol=1e-9)
+    flips = int(np.sum(iterations != o_its))
+    assert flips == 0, f"{flips} clusters stopped on a different EM iteration than the oracle"
+    # writer invariant (rpvg:src/threaded_output_writer.cpp:327-328): abundance_sum + noise_count ~ total_count
+    for c in range(arena.n_clusters):
+        p0, p1 = int(arena.path_offset[c]), int(arena.path_offset[c + 1])
+        if total_count[c] > 0:
+            assert abs(abundances[p0:p1].sum() + noise_count[c] - total_count[c]) <= 1e-9 * total_count[c]
+    return abundances, noise_count, total_count, iterations
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_em_matches_oracle_small_clusters(ctx, seed):
+    arena = synth.transcripts_arena(seed=seed, n_paths=3000, n_reads=15000, n_max=300)
+    check_against_port(ctx, arena)
+
+
+def test_em_matches_oracle_mixed_sizes(ctx):
+    arena = synth.transcripts_arena(seed=5, n_paths=20000, n_reads=100000, n_max=2000)
+    check_against_port(ctx, arena)
+
+
+def test_em_matches_reference_estimator(ctx, reference):
+    """Same clusters through the reference's own PathAbundanceEstimator::estimate (oracle/_ref)."""
+    arena = synth.transcripts_arena(seed=9, n_paths=1500, n_reads=8000, n_max=150)
+    abundances, noise_count, total_count, _ = ctx.em_abundances(arena)
+    _, results = loader.harness_estimate_batch(reference, loader.make_config(loader.MODEL_TRANSCRIPTS), arena)
+    for c, res in enumerate(results):
+        p0, p1 = int(arena.path_offset[c]), int(arena.path_offset[c + 1])
+        mine, ref = abundances[p0:p1], res["abundances"]
+        assert np.array_equal(mine == 0, ref == 0)
+        nz = ref != 0
+        if nz.any():
+            assert np.max(np.abs(mine[nz] - ref[nz]) / ref[nz]) < REL_TOL
+        assert abs(noise_count[c] - res["noise_count"]) <= REL_TOL * max(1.0, res["total_count"])
+        assert total_count[c] == res["total_count"]
+        assert res["sets"] == [(j,) for j in range(p1 - p0)]
+
+
+def test_em_parameters_are_honoured(ctx):
+    arena = synth.transcripts_arena(seed=4, n_paths=1000, n_reads=5000, n_max=100)
+    params = capi.default_em_params(max_em_its=7, max_rel_em_conv=0.01)
+    _, _, _, its = check_against_port(ctx, arena, params, max_em_its=7, max_rel_em_conv=0.01)
+    assert its.max() <= 7
+
+
+def test_edge_cases(ctx):
+    """Empty cluster (no read classes), noise-only read classes, single path, single read class."""
+    read_offset = np.array([0, 0, 2, 3, 5], dtype=np.uint64)
+    path_offset = np.array([0, 3, 5, 6, 8], dtype=np.uint64)
+    # cluster 0: empty; cluster 1: one noise-only row + one normal row; cluster 2: single path; cluster 3: two rows
+    row_ptr = np.array([0, 0, 2, 3, 4, 6], dtype=np.uint64)
+    col = np.array([0, 1, 0, 0, 0, 1], dtype=np.uint32)
+    prob = np.array([0.3, 0.6, 0.9, 0.5, 0.2, 0.7], dtype=np.float64)
+    noise = np.array([1.0, 0.1, 0.1, 0.5, 0.1], dtype=np.float64)
+    count = np.array([3, 5, 7, 1, 4000000000], dtype=np.uint32)
+    arena = ClusterArena(read_offset, path_offset, row_ptr, col, prob, noise, count)
+    abundances, noise_count, total_count, iterations = check_against_port(ctx, arena)
+    assert iterations[0] == 0 and total_count[0] == 0 and np.all(abundances[:3] == 0)
+    assert total_count[3] == 4000000001.0
+
+
+def test_malformed_arena_is_rejected(ctx):
+    arena = synth.transcripts_arena(seed=4, n_paths=200, n_reads=1000, n_max=50)
+    bad = ClusterArena(arena.read_offset, arena.path_offset, arena.row_ptr, arena.col.copy(), arena.prob, arena.noise, arena.count)
+    bad.col[0] = 10 ** 6
+    with pytest.raises(capi.RpvgB200Error, match="out of range"):
+        ctx.em_abundances(bad)
+    # the context stays usable
+    check_against_port(ctx, arena)
+
+
+def test_full_size_properties(ctx):
+    """Config 2 at full size (1M read classes, 200k paths): properties that need no oracle run —
+    mass conservation per cluster, determinism (two runs bit-identical), and permutation of clusters."""
+    arena = synth.transcripts_arena()
+    a1 = ctx.em_abundances(arena)
+    a2 = ctx.em_abundances(arena)
+    for x, y in zip(a1, a2):
+        assert np.array_equal(x, y), "EM is not run-to-run deterministic"
+    abundances, noise_count, total_count, iterations = a1
+    sums = np.add.reduceat(abundances, arena.path_offset[:-1].astype(np.int64))
+    assert np.allclose(sums + noise_count, total_count, rtol=1e-9)
+    counts = np.add.reduceat(arena.count.astype(np.float64), arena.read_offset[:-1].astype(np.int64))
+    assert np.array_equal(counts, total_count)
+    assert iterations.min() >= 10 and iterations.max() <= 10000
+    # cluster order must not matter: reverse the batch
+    rev = arena.select(list(range(arena.n_clusters - 1, -1, -1))[:500])
+    r_ab, r_noise, _, r_its = ctx.em_abundances(rev)
+    for k in range(500):
+        c = arena.n_clusters - 1 - k
+        p0, p1 = int(arena.path_offset[c]), int(arena.path_offset[c + 1])
+        q0, q1 = int(rev.path_offset[k]), int(rev.path_offset[k + 1])
+        assert np.array_equal(r_ab[q0:q1], abundances[p0:p1])
+        assert r_its[k] == iterations[c]
