@@ -213,7 +213,10 @@ def main():
     out_its = torch.empty(arena.n_clusters, dtype=torch.int32).pin_memory()
     d2h_bytes = out_ab.numel() * 8 + out_noise.numel() * 8 + out_total.numel() * 8 + out_its.numel() * 4
 
-    stream = torch.cuda.current_stream()
+    # a dedicated (non-default) stream shared by torch (events, L2 flush) and the library (kernels, copies)
+    stream = torch.cuda.Stream()
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
     ctx = capi.Context(local_rank, stream.cuda_stream)
     params = capi.default_em_params()
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")
