@@ -19,7 +19,16 @@ struct rpvg_b200_ctx {
     int max_smem_optin = 0;
     uint64_t launches = 0;
     std::string error;
+
+    // EM launch machinery (em.cu): side streams for concurrent bins, largest thread-block cluster this device accepts
+    std::vector<cudaStream_t> side_streams;
+    std::vector<cudaEvent_t> join_events;
+    cudaEvent_t fork_event = nullptr;
+    uint32_t max_group_size = 1;
 };
+
+// em.cu: sets the kernel attributes of the EM kernels and probes the largest usable thread-block cluster.
+int rpvgEmInit(rpvg_b200_ctx * ctx);
 
 inline int rpvgFail(rpvg_b200_ctx * ctx, int status, const std::string & message) {
 
@@ -49,7 +58,8 @@ inline int rpvgFail(rpvg_b200_ctx * ctx, int status, const std::string & message
 enum : uint32_t {
     RPVG_DEV_ERR_COL_RANGE = 1u,   // col[e] >= N_c
     RPVG_DEV_ERR_COL_ORDER = 2u,   // entries of a read class not strictly ascending by path index
-    RPVG_DEV_ERR_VALUE = 4u        // non-finite or negative probability
+    RPVG_DEV_ERR_VALUE = 4u,       // non-finite or negative probability
+    RPVG_DEV_ERR_CAPACITY = 8u     // internal: a slice outgrew its scratch area
 };
 
 #ifdef __CUDACC__

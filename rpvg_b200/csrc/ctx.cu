@@ -56,6 +56,30 @@ int rpvg_b200_create(int device, void * stream, rpvg_b200_ctx ** out_ctx) {
         cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold);
     }
 
+    // side streams: the first few have high priority (large thread-block clusters are launched there)
+    int prio_low = 0, prio_high = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_low, &prio_high);
+
+    for (int k = 0; k < 8; ++k) {
+
+        cudaStream_t side = nullptr;
+        cudaEvent_t join = nullptr;
+
+        if (cudaStreamCreateWithPriority(&side, cudaStreamNonBlocking, k < 3 ? prio_high : prio_low) != cudaSuccess ||
+            cudaEventCreateWithFlags(&join, cudaEventDisableTiming) != cudaSuccess) {
+            rpvg_b200_destroy(ctx);
+            return RPVG_B200_ERR_CUDA;
+        }
+
+        ctx->side_streams.push_back(side);
+        ctx->join_events.push_back(join);
+    }
+
+    if (cudaEventCreateWithFlags(&ctx->fork_event, cudaEventDisableTiming) != cudaSuccess || rpvgEmInit(ctx) != RPVG_B200_OK) {
+        rpvg_b200_destroy(ctx);
+        return RPVG_B200_ERR_CUDA;
+    }
+
     *out_ctx = ctx;
     return RPVG_B200_OK;
 }
@@ -66,6 +90,12 @@ void rpvg_b200_destroy(rpvg_b200_ctx * ctx) {
 
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    for (auto side: ctx->side_streams) {
+        cudaStreamSynchronize(side);
+        cudaStreamDestroy(side);
+    }
+    for (auto ev: ctx->join_events) { cudaEventDestroy(ev); }
+    if (ctx->fork_event) { cudaEventDestroy(ctx->fork_event); }
     if (ctx->own_stream) { cudaStreamDestroy(ctx->stream); }
 
     delete ctx;

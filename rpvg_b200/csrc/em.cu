@@ -10,22 +10,24 @@
 //   CSR  : row_ptr[u64], col[u32], val[f64]        one entry per (read class, path) non-zero, normalised
 //   CSC  : col_ptr[u64], csc_row[u32], csc_val[f64] the same non-zeros ordered by (global path, read class)
 //   rows : noise[f64], cnt[f64]                     the noise column is dense and kept apart
+//   scratch                                         per-CTA work area of the EM kernel (em_sell.cuh)
 // The reference is dense and column-major; here the matrix is sparse in both orientations so that the E-step (row sums)
 // and the M-step (column sums) are both gathers with a fixed summation order: no atomics, results are run-to-run
 // deterministic, which matters because the stopping rule is a 1e-3 step test while parity is 1e-6.
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <numeric>
 
 #include <cub/device/device_radix_sort.cuh>
 
 #include "common.cuh"
+#include "em_kernels.cuh"
+#include "em_sell.cuh"
 
 namespace {
-
-constexpr int kEmThreads = 256;
 
 struct DevicePool {
 
@@ -60,6 +62,18 @@ struct rpvg_b200_batch {
     std::vector<uint64_t> h_cluster_nnz;   // path non-zeros per cluster
     std::vector<uint32_t> h_iterations;
 
+    // launch plan of the EM: clusters binned by thread-block-cluster size, shared-memory tier and index width
+    struct EmBin {
+        uint32_t group_size;   // CTAs per path cluster; 0 = fallback kernel (one CTA, everything in global memory)
+        uint32_t threads;
+        uint32_t smem;
+        uint32_t index_bytes;  // 2 or 4
+        uint32_t first;        // offset into d_order / d_group_scratch / d_group_cta_bytes
+        uint32_t count;
+    };
+    std::vector<EmBin> bins;
+    uint64_t scratch_bytes = 0;
+
     DevicePool pool;
 
     // inputs
@@ -71,6 +85,8 @@ struct rpvg_b200_batch {
     double * d_noise = nullptr;
     uint32_t * d_count = nullptr;
     uint32_t * d_order = nullptr;
+    uint64_t * d_group_scratch = nullptr;
+    uint64_t * d_group_cta_bytes = nullptr;
 
     // built
     double * d_val = nullptr;
@@ -88,8 +104,9 @@ struct rpvg_b200_batch {
     int sort_bits = 32;
 
     // EM state + results
-    double * d_abund = nullptr;   // [n_paths + n_clusters]: per cluster N_c + 1 relative abundances (noise last)
-    double * d_w = nullptr;       // [n_reads]
+    double * d_abund = nullptr;   // fallback kernel only: per cluster N_c + 1 relative abundances (noise last)
+    double * d_w = nullptr;       // fallback kernel only
+    unsigned char * d_scratch = nullptr;
     double * d_abundances = nullptr;
     double * d_noise_count = nullptr;
     double * d_total_count = nullptr;
@@ -187,155 +204,233 @@ __global__ void gatherColumnsKernel(uint64_t nnz, const uint32_t * __restrict__ 
     csc_val[k] = val[e];
 }
 
-// ---- EM: one CTA per cluster, all iterations inside the kernel ------------------------------------------------------
-struct EmArgs {
+uint32_t envKnob(const char * name, uint32_t fallback) {
 
-    const uint32_t * order;
-    const uint64_t * read_offset;
-    const uint64_t * path_offset;
-    const uint64_t * row_ptr;
-    const uint32_t * col;
-    const double * val;
-    const double * noise;
-    const double * cnt;
-    const uint64_t * col_ptr;
-    const uint32_t * csc_row;
-    const double * csc_val;
-    double * abund;
-    double * w;
-    double * abundances;
-    double * noise_count;
-    double * total_count;
-    uint32_t * iterations;
-    rpvg_b200_em_params params;
+    const char * v = std::getenv(name);
+    return (v && *v) ? static_cast<uint32_t>(std::strtoul(v, nullptr, 10)) : fallback;
+}
+
+constexpr uint32_t kSmemTiers[] = {8 * 1024, 24 * 1024, 56 * 1024, 108 * 1024, 216 * 1024};
+constexpr uint32_t kTierThreads[] = {64, 128, 256, 512, 512};
+constexpr int kNumTiers = 5;
+constexpr uint32_t kStaticSmemReserve = 8 * 1024;   // static shared memory of emSellKernel<512> + slack
+
+struct GroupPlan {
+
+    uint32_t cluster;
+    uint64_t weight;
+    int bin;              // sort key: group size (descending), tier (descending), index width
+    uint64_t cta_bytes;   // scratch bytes per CTA
 };
 
-__global__ void __launch_bounds__(kEmThreads) emClusterKernel(const EmArgs args) {
+// Bins the clusters of a batch into launches. Within a bin, largest first, like the reference's schedule
+// (rpvg:src/main.cpp:827): the hardware block scheduler then hands the long-running clusters out first.
+void planEmLaunches(const rpvg_b200_ctx * ctx, rpvg_b200_batch * b, std::vector<uint32_t> * order, std::vector<uint64_t> * group_scratch,
+                    std::vector<uint64_t> * group_cta_bytes) {
 
-    __shared__ double red[32];
+    // weight (entries + rows) one CTA should own; above it a cluster is split over 2, 4, 8, 16 CTAs
+    const uint32_t slice_weight = std::max(64u, envKnob("RPVG_B200_EM_SLICE_WEIGHT", 6000));
+    const uint32_t max_group = std::min(ctx->max_group_size, std::max(1u, envKnob("RPVG_B200_EM_MAX_GROUP", kMaxGroupSize)));
+    const uint32_t smem_cap = std::min<uint32_t>(kSmemTiers[kNumTiers - 1], static_cast<uint32_t>(ctx->max_smem_optin) - kStaticSmemReserve);
 
-    const int tid = threadIdx.x;
-    const int lane = tid & 31;
-    const int warp = tid >> 5;
-    constexpr int num_warps = kEmThreads / 32;
+    std::vector<GroupPlan> items(b->n_clusters);
 
-    const uint32_t c = args.order[blockIdx.x];
+    // bin index = ((4 - log2 group) * tiers + (tiers - 1 - tier)) * 2 + (index_bytes == 4); last bin = fallback
+    const int fallback_bin = 5 * kNumTiers * 2;
 
-    const uint64_t r0 = args.read_offset[c];
-    const uint32_t M = static_cast<uint32_t>(args.read_offset[c + 1] - r0);
-    const uint64_t p0 = args.path_offset[c];
-    const uint32_t N = static_cast<uint32_t>(args.path_offset[c + 1] - p0);
+    for (uint32_t c = 0; c < b->n_clusters; ++c) {
 
-    double * abundances = args.abundances + p0;
+        const uint64_t M = b->h_read_offset[c + 1] - b->h_read_offset[c];
+        const uint64_t N = b->h_path_offset[c + 1] - b->h_path_offset[c];
+        const uint64_t Zc = b->h_cluster_nnz[c];
+        const uint64_t weight = Zc + M;
 
-    if (M == 0) {
+        uint32_t group = 1;
+        while (group < max_group && weight > static_cast<uint64_t>(slice_weight) * group) { group *= 2; }
 
-        for (uint32_t j = tid; j < N; j += kEmThreads) { abundances[j] = 0; }
+        // bounds of one slice (slices are cut at equal weight)
+        const uint64_t m_b = std::min(M, weight / group + 2);
+        const uint64_t z_b = std::min(Zc, weight / group + std::min(N, Zc) + 2);
+        const uint64_t index_bytes = (N + 1 < 65536 && m_b < 65536) ? 2 : 4;
 
-        if (tid == 0) {
-            args.noise_count[c] = 0;
-            args.total_count[c] = 0;
-            args.iterations[c] = 0;
-        }
-        return;
-    }
+        const bool multi = group > 1;
+        const uint64_t fixed = sellRound16(8 * (N + 1)) * (multi ? 2 : 1);
 
-    const uint64_t * row_ptr = args.row_ptr + r0;
-    const double * noise = args.noise + r0;
-    const double * cnt = args.cnt + r0;
-    const uint64_t * col_ptr = args.col_ptr + p0;
+        GroupPlan plan;
+        plan.cluster = c;
+        plan.weight = weight;
+        plan.bin = fallback_bin;
+        plan.cta_bytes = 0;
 
-    double * a = args.abund + p0 + c;   // N + 1 relative abundances, noise last
-    double * w = args.w + r0;
+        if (fixed + 4096 <= smem_cap) {
 
-    double count_sum = 0;
-    for (uint32_t i = tid; i < M; i += kEmThreads) { count_sum += cnt[i]; }
-    const double total = blockSum(count_sum, red);
+            const uint64_t need_typical = sellSmemBytes(m_b, z_b, N, index_bytes, multi, false);
+            const uint64_t need_worst = sellSmemBytes(m_b, z_b, N, index_bytes, multi, true);
 
-    // rpvg:src/path_abundance_estimator.cpp:54 — single-precision quotient widened to double.
-    const double a_init = static_cast<double>(1 / static_cast<float>(N + 1));
-    for (uint32_t j = tid; j <= N; j += kEmThreads) { a[j] = a_init; }
-    __syncthreads();
-
-    const double conv = args.params.max_rel_em_conv;
-    const double min_abundance = args.params.min_em_abundance;
-
-    uint32_t conv_its = 0;
-    uint32_t it = 0;
-
-    while (it < args.params.max_em_its) {
-
-        // E-step: w_i = count_i / sum_j p_ij a_j (noise column last, as in the dense left-to-right row sum).
-        const double a_noise = a[N];
-        double noise_acc = 0;
-
-        for (uint32_t i = tid; i < M; i += kEmThreads) {
-
-            const uint64_t e1 = row_ptr[i + 1];
-            double s = 0;
-            for (uint64_t e = row_ptr[i]; e < e1; ++e) { s += args.val[e] * a[args.col[e]]; }
-            s += noise[i] * a_noise;
-
-            const double wi = cnt[i] / s;
-            w[i] = wi;
-            noise_acc += noise[i] * wi;
-        }
-
-        const double noise_g = blockSum(noise_acc, red);
-
-        // M-step: a_j <- a_j * sum_i p_ij w_i / total, one warp per column.
-        bool ok = true;
-
-        for (uint32_t j = warp; j < N; j += num_warps) {
-
-            const uint64_t k1 = col_ptr[j + 1];
-            double g = 0;
-            for (uint64_t k = col_ptr[j] + lane; k < k1; k += 32) { g += args.csc_val[k] * w[args.csc_row[k]]; }
-            g = warpSum(g);
-
-            if (lane == 0) {
-                const double a_old = a[j];
-                const double a_new = (a_old * g) / total;
-                a[j] = a_new;
-                if (a_new >= min_abundance && fabs(a_new - a_old) / a_new > conv) { ok = false; }
+            int tier_typical = kNumTiers - 1;
+            for (int t = 0; t < kNumTiers; ++t) {
+                if (need_typical <= std::min(kSmemTiers[t], smem_cap)) { tier_typical = t; break; }
             }
+
+            int tier_worst = kNumTiers;
+            for (int t = 0; t < kNumTiers; ++t) {
+                if (need_worst <= std::min(kSmemTiers[t], smem_cap)) { tier_worst = t; break; }
+            }
+
+            // one tier up buys the guarantee that nothing spills; beyond that the slice is given scratch for its entries
+            int tier = tier_typical;
+            bool with_entries = true;
+            if (tier_worst < kNumTiers && tier_worst <= tier_typical + 1) {
+                tier = tier_worst;
+                with_entries = false;
+            }
+
+            int group_log2 = 0;
+            while ((1u << group_log2) < group) { group_log2++; }
+
+            plan.bin = ((4 - group_log2) * kNumTiers + (kNumTiers - 1 - tier)) * 2 + (index_bytes == 4 ? 1 : 0);
+            plan.cta_bytes = sellScratchBytes(m_b, z_b, N, index_bytes, with_entries);
         }
 
-        if (tid == 0) {
-            const double a_new = (a_noise * noise_g) / total;
-            a[N] = a_new;
-            if (a_new >= min_abundance && fabs(a_new - a_noise) / a_new > conv) { ok = false; }
-        }
-
-        ++it;
-
-        if (__syncthreads_and(ok)) {
-            if (++conv_its == args.params.min_em_conv_its) { break; }
-        } else {
-            conv_its = 0;
-        }
+        items[c] = plan;
     }
 
-    // rpvg:src/path_abundance_estimator.cpp:100-113
-    double noise_part = 0;
-    for (uint32_t j = tid; j < N; j += kEmThreads) {
+    std::stable_sort(items.begin(), items.end(), [](const GroupPlan & x, const GroupPlan & y) {
+        if (x.bin != y.bin) { return x.bin < y.bin; }
+        return x.weight > y.weight;
+    });
 
-        const double aj = a[j];
-        if (aj < min_abundance) {
-            noise_part += aj * total;
-            abundances[j] = 0;
-        } else {
-            abundances[j] = aj * total;
+    order->resize(b->n_clusters);
+    group_scratch->resize(b->n_clusters);
+    group_cta_bytes->resize(b->n_clusters);
+    b->bins.clear();
+    b->scratch_bytes = 0;
+
+    for (uint32_t k = 0; k < items.size(); ++k) {
+
+        (*order)[k] = items[k].cluster;
+
+        if (k == 0 || items[k].bin != items[k - 1].bin) {
+
+            rpvg_b200_batch::EmBin bin;
+            bin.first = k;
+            bin.count = 0;
+
+            if (items[k].bin == fallback_bin) {
+
+                bin.group_size = 0;
+                bin.threads = kEmThreads;
+                bin.smem = 0;
+                bin.index_bytes = 4;
+
+            } else {
+
+                const int code = items[k].bin / 2;
+                const int tier = kNumTiers - 1 - (code % kNumTiers);
+
+                bin.group_size = 1u << (4 - code / kNumTiers);
+                bin.index_bytes = (items[k].bin & 1) ? 4 : 2;
+                bin.smem = std::min(kSmemTiers[tier], smem_cap);
+                bin.threads = kTierThreads[tier];
+
+                // instantiations that exist: one CTA {64,128,256,512} x u16; groups {256,512} x u16; 512 x u32
+                if (bin.index_bytes == 4) { bin.threads = 512; }
+                if (bin.group_size > 1) { bin.threads = std::max(bin.threads, 256u); }
+            }
+
+            b->bins.push_back(bin);
         }
+
+        b->bins.back().count++;
+
+        const uint64_t group_bytes = items[k].cta_bytes * std::max(1u, b->bins.back().group_size);
+        (*group_scratch)[k] = b->scratch_bytes;
+        (*group_cta_bytes)[k] = items[k].cta_bytes;
+        b->scratch_bytes += group_bytes;
+    }
+}
+
+template <int THREADS, bool MULTI, typename IndexT>
+cudaError_t launchSell(const SellArgs & sa, uint32_t group_size, uint32_t n_groups, cudaStream_t stream) {
+
+    cudaLaunchConfig_t config = {};
+    config.gridDim = dim3(n_groups * group_size, 1, 1);
+    config.blockDim = dim3(THREADS, 1, 1);
+    config.dynamicSmemBytes = sa.smem_bytes;
+    config.stream = stream;
+
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = group_size;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    config.attrs = attr;
+    config.numAttrs = MULTI ? 1 : 0;
+
+    return cudaLaunchKernelEx(&config, emSellKernel<THREADS, MULTI, IndexT>, sa);
+}
+
+cudaError_t launchSellBin(const SellArgs & sa, const rpvg_b200_batch::EmBin & bin, cudaStream_t stream) {
+
+    const bool multi = bin.group_size > 1;
+
+    if (bin.index_bytes == 4) {
+        return multi ? launchSell<512, true, uint32_t>(sa, bin.group_size, bin.count, stream)
+                     : launchSell<512, false, uint32_t>(sa, 1, bin.count, stream);
     }
 
-    const double low_sum = blockSum(noise_part, red);
-
-    if (tid == 0) {
-        args.noise_count[c] = low_sum + a[N] * total;
-        args.total_count[c] = total;
-        args.iterations[c] = it;
+    if (multi) {
+        return bin.threads == 256 ? launchSell<256, true, uint16_t>(sa, bin.group_size, bin.count, stream)
+                                  : launchSell<512, true, uint16_t>(sa, bin.group_size, bin.count, stream);
     }
+
+    switch (bin.threads) {
+        case 64: return launchSell<64, false, uint16_t>(sa, 1, bin.count, stream);
+        case 128: return launchSell<128, false, uint16_t>(sa, 1, bin.count, stream);
+        case 256: return launchSell<256, false, uint16_t>(sa, 1, bin.count, stream);
+        default: return launchSell<512, false, uint16_t>(sa, 1, bin.count, stream);
+    }
+}
+
+template <int THREADS, bool MULTI, typename IndexT>
+cudaError_t configureSell(const rpvg_b200_ctx * ctx, uint32_t * max_group) {
+
+    const int smem_cap = std::min<int>(kSmemTiers[kNumTiers - 1], ctx->max_smem_optin - static_cast<int>(kStaticSmemReserve));
+
+    cudaError_t err = cudaFuncSetAttribute(emSellKernel<THREADS, MULTI, IndexT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap);
+    if (err != cudaSuccess || !MULTI) { return err; }
+
+    err = cudaFuncSetAttribute(emSellKernel<THREADS, MULTI, IndexT>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    if (err != cudaSuccess) { return err; }
+
+    // largest thread-block cluster that can be co-scheduled with the biggest shared-memory tier
+    uint32_t group = kMaxGroupSize;
+
+    while (group > 1) {
+
+        cudaLaunchConfig_t config = {};
+        config.gridDim = dim3(group, 1, 1);
+        config.blockDim = dim3(THREADS, 1, 1);
+        config.dynamicSmemBytes = smem_cap;
+
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = group;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        config.attrs = attr;
+        config.numAttrs = 1;
+
+        int num_clusters = 0;
+        err = cudaOccupancyMaxActiveClusters(&num_clusters, emSellKernel<THREADS, MULTI, IndexT>, &config);
+        if (err == cudaSuccess && num_clusters > 0) { break; }
+
+        cudaGetLastError();
+        group /= 2;
+    }
+
+    *max_group = std::min(*max_group, group);
+    return cudaSuccess;
 }
 
 int checkClusters(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl) {
@@ -367,6 +462,24 @@ int checkClusters(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl) {
     return RPVG_B200_OK;
 }
 
+}
+
+int rpvgEmInit(rpvg_b200_ctx * ctx) {
+
+    uint32_t max_group = kMaxGroupSize;
+    uint32_t unused = kMaxGroupSize;
+
+    RPVG_CUDA(ctx, (configureSell<64, false, uint16_t>(ctx, &unused)));
+    RPVG_CUDA(ctx, (configureSell<128, false, uint16_t>(ctx, &unused)));
+    RPVG_CUDA(ctx, (configureSell<256, false, uint16_t>(ctx, &unused)));
+    RPVG_CUDA(ctx, (configureSell<512, false, uint16_t>(ctx, &unused)));
+    RPVG_CUDA(ctx, (configureSell<512, false, uint32_t>(ctx, &unused)));
+    RPVG_CUDA(ctx, (configureSell<256, true, uint16_t>(ctx, &max_group)));
+    RPVG_CUDA(ctx, (configureSell<512, true, uint16_t>(ctx, &max_group)));
+    RPVG_CUDA(ctx, (configureSell<512, true, uint32_t>(ctx, &max_group)));
+
+    ctx->max_group_size = max_group;
+    return RPVG_B200_OK;
 }
 
 extern "C" {
@@ -409,15 +522,10 @@ int rpvg_b200_batch_upload(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, r
         b->h_cluster_nnz[c] = hi - lo;
     }
 
-    // Largest first, like the reference's schedule (rpvg:src/main.cpp:827): the hardware block scheduler then hands the
-    // long-running clusters out first.
-    std::vector<uint32_t> order(cl->n_clusters);
-    std::iota(order.begin(), order.end(), 0u);
-    std::stable_sort(order.begin(), order.end(), [&](uint32_t x, uint32_t y) {
-        const uint64_t cx = b->h_cluster_nnz[x] + (b->h_read_offset[x + 1] - b->h_read_offset[x]);
-        const uint64_t cy = b->h_cluster_nnz[y] + (b->h_read_offset[y + 1] - b->h_read_offset[y]);
-        return cx > cy;
-    });
+    std::vector<uint32_t> order;
+    std::vector<uint64_t> group_scratch;
+    std::vector<uint64_t> group_cta_bytes;
+    planEmLaunches(ctx, b, &order, &group_scratch, &group_cta_bytes);
 
     const uint64_t C = b->n_clusters, R = b->n_reads, P = b->n_paths, Z = b->nnz;
 
@@ -429,10 +537,12 @@ int rpvg_b200_batch_upload(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, r
 
     size_t bytes = 0;
     bytes += 2 * padded<uint64_t>(C + 1) + padded<uint64_t>(R + 1) + padded<uint32_t>(Z) + padded<double>(Z) + padded<double>(R) + padded<uint32_t>(R) + padded<uint32_t>(C);
+    bytes += 2 * padded<uint64_t>(C);
     bytes += padded<double>(Z) + padded<double>(R) + 5 * padded<uint32_t>(Z) + padded<uint64_t>(P + 1) + padded<uint32_t>(Z) + padded<double>(Z);
     bytes += ((b->sort_temp_bytes + 255) & ~size_t(255));
     bytes += padded<double>(P + C) + padded<double>(R) + padded<double>(P) + 2 * padded<double>(C) + padded<uint32_t>(C) + padded<uint32_t>(1);
-    bytes += 4096;
+    bytes += ((b->scratch_bytes + 255) & ~size_t(255));
+    bytes += 8192;
 
     cudaError_t err = cudaMallocAsync(reinterpret_cast<void **>(&b->pool.base), bytes, ctx->stream);
     if (err != cudaSuccess) {
@@ -450,6 +560,8 @@ int rpvg_b200_batch_upload(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, r
     b->d_noise = pool.take<double>(R);
     b->d_count = pool.take<uint32_t>(R);
     b->d_order = pool.take<uint32_t>(C);
+    b->d_group_scratch = pool.take<uint64_t>(C);
+    b->d_group_cta_bytes = pool.take<uint64_t>(C);
     b->d_val = pool.take<double>(Z);
     b->d_cnt = pool.take<double>(R);
     b->d_entry_row = pool.take<uint32_t>(Z);
@@ -468,6 +580,7 @@ int rpvg_b200_batch_upload(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, r
     b->d_total_count = pool.take<double>(C);
     b->d_iterations = pool.take<uint32_t>(C);
     b->d_error = pool.take<uint32_t>(1);
+    b->d_scratch = pool.take<unsigned char>(b->scratch_bytes);
 
     if (pool.used > pool.size) {
         cudaFreeAsync(pool.base, ctx->stream);
@@ -494,8 +607,10 @@ int rpvg_b200_batch_upload(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, r
     RPVG_UPLOAD(b->d_prob, cl->prob, Z, double)
     RPVG_UPLOAD(b->d_noise, cl->noise, R, double)
     RPVG_UPLOAD(b->d_count, cl->count, R, uint32_t)
-    // order is a small temporary host vector: the copy must finish before it goes out of scope
+    // the plan vectors are temporaries: the synchronize below keeps them alive long enough
     RPVG_UPLOAD(b->d_order, order.data(), C, uint32_t)
+    RPVG_UPLOAD(b->d_group_scratch, group_scratch.data(), C, uint64_t)
+    RPVG_UPLOAD(b->d_group_cta_bytes, group_cta_bytes.data(), C, uint64_t)
     #undef RPVG_UPLOAD
 
     err = cudaStreamSynchronize(s);
@@ -539,7 +654,7 @@ int rpvg_b200_batch_em(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const rpvg_b200
         size_t temp_bytes = b->sort_temp_bytes;
         RPVG_CUDA(ctx, cub::DeviceRadixSort::SortPairs(b->d_sort_temp, temp_bytes, b->d_key_in, b->d_key_out, b->d_idx_in, b->d_idx_out,
                                                        static_cast<int>(b->nnz), 0, b->sort_bits, s));
-        ctx->launches += static_cast<uint64_t>((b->sort_bits + 7) / 8) * 3;   // library launches, counted approximately
+        ctx->launches += 2 + static_cast<uint64_t>((b->sort_bits + 7) / 8);   // histogram, scan and one pass per 8 key bits
     }
 
     {
@@ -573,12 +688,59 @@ int rpvg_b200_batch_em(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const rpvg_b200
     args.noise_count = b->d_noise_count;
     args.total_count = b->d_total_count;
     args.iterations = b->d_iterations;
+    args.error = b->d_error;
     args.params = *params;
 
     RPVG_CUDA(ctx, cudaEventRecord(b->ev_built, s));
 
-    emClusterKernel<<<b->n_clusters, kEmThreads, 0, s>>>(args);
-    RPVG_LAUNCHED(ctx);
+    // Bins run concurrently on the ctx's side streams (fork after the build, join before ev_done); the bins of large
+    // groups go first and on high-priority streams so that they get whole GPCs before the small ones fill the rest.
+    RPVG_CUDA(ctx, cudaEventRecord(ctx->fork_event, s));
+
+    const bool debug = std::getenv("RPVG_B200_DEBUG") != nullptr;
+
+    for (size_t k = 0; k < b->bins.size(); ++k) {
+
+        const auto & bin = b->bins[k];
+        if (debug) {
+            fprintf(stderr, "[rpvg_b200] em bin %zu: group %u threads %u smem %u index %u clusters %u (max group %u, scratch %.1f MB)\n", k, bin.group_size,
+                    bin.threads, bin.smem, bin.index_bytes, bin.count, ctx->max_group_size, b->scratch_bytes / 1e6);
+        }
+
+        cudaStream_t bs = ctx->side_streams[k % ctx->side_streams.size()];
+        RPVG_CUDA(ctx, cudaStreamWaitEvent(bs, ctx->fork_event, 0));
+
+        if (bin.group_size == 0) {
+
+            EmArgs fallback_args = args;
+            fallback_args.order = b->d_order + bin.first;
+            emClusterKernel<<<bin.count, kEmThreads, 0, bs>>>(fallback_args);
+            RPVG_LAUNCHED(ctx);
+
+        } else {
+
+            SellArgs sa;
+            sa.em = args;
+            sa.group_cluster = b->d_order + bin.first;
+            sa.group_scratch = b->d_group_scratch + bin.first;
+            sa.group_cta_bytes = b->d_group_cta_bytes + bin.first;
+            sa.scratch = b->d_scratch;
+            sa.smem_bytes = bin.smem;
+
+            const cudaError_t launch_err = launchSellBin(sa, bin, bs);
+
+            if (launch_err != cudaSuccess) {
+                return rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("emSellKernel launch (group ") + std::to_string(bin.group_size) + ", threads " +
+                                std::to_string(bin.threads) + ", smem " + std::to_string(bin.smem) + "): " + cudaGetErrorString(launch_err));
+            }
+            RPVG_LAUNCHED(ctx);
+        }
+    }
+
+    for (size_t k = 0; k < std::min(b->bins.size(), ctx->side_streams.size()); ++k) {
+        RPVG_CUDA(ctx, cudaEventRecord(ctx->join_events[k], ctx->side_streams[k]));
+        RPVG_CUDA(ctx, cudaStreamWaitEvent(s, ctx->join_events[k], 0));
+    }
 
     RPVG_CUDA(ctx, cudaEventRecord(b->ev_done, s));
 
@@ -605,6 +767,10 @@ int rpvg_b200_batch_download(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, double * 
     RPVG_CUDA(ctx, cudaStreamSynchronize(s));
 
     if (iterations) { std::memcpy(iterations, b->h_iterations.data(), b->n_clusters * sizeof(uint32_t)); }
+
+    if (dev_error & RPVG_DEV_ERR_CAPACITY) {
+        return rpvgFail(ctx, RPVG_B200_ERR_LIMIT, "internal: a cluster slice outgrew its scratch area (please report; RPVG_B200_EM_SLICE_WEIGHT changes the slicing)");
+    }
 
     if (dev_error) {
 

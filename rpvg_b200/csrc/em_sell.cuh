@@ -1,0 +1,783 @@
+// emSellKernel — the EM kernel proper (sm_100a).
+//
+// One thread-block cluster of S CTAs (S = 1, 2, 4, 8, 16) per path cluster; read classes (rows) are split into S
+// slices of equal weight. In its prologue every CTA re-lays its slice out as two sliced-ELL structures, one per
+// orientation, built so that the inner loops of both EM steps are the same branch-free, bank-conflict-free loop:
+//
+//   chunk = 32 lane slots; a row (column) of the chunk owns L = 1..32 adjacent lanes (L chosen from its length so a
+//   chunk is ~5-8 steps deep); entry t of that row sits at [chunk_off + (t / L) * 32 + first_lane + (t % L)].
+//   Rows (columns) are ordered by length (stable bucket sort) so rows sharing a chunk have near-equal length; padding
+//   entries are (value 0, index 0) and need no predicate.
+//
+// E-step: warp per row chunk  : acc = sum val * a[col]; reduce over L lanes; w_row = count / (acc + noise * a_noise)
+// M-step: warp per column chunk: acc = sum val * w[row]; reduce over L lanes; partial column sum g[col] (S > 1) or the
+//         abundance update itself (S = 1).
+// S > 1: reduce-scatter + all-gather of the N + 1 column sums over distributed shared memory, two cluster barriers per
+//        iteration; S = 1: two block barriers per iteration (the second one carries the convergence vote).
+//
+// The slice lives in shared memory as far as it fits (vectors first, then column chunks, then row chunks); chunks
+// that do not fit are streamed from a global scratch area with coalesced 128-byte warp loads ("hybrid residency").
+// Everything is deterministic: fixed slices, stable sorts, fixed summation trees, no atomics.
+#pragma once
+
+#include <cooperative_groups.h>
+
+#include "common.cuh"
+#include "em_kernels.cuh"
+
+struct SellArgs {
+
+    EmArgs em;
+    const uint32_t * group_cluster;    // [n_groups] path cluster of each thread-block cluster
+    const uint64_t * group_scratch;    // [n_groups] byte offset of the group's scratch area in `scratch`
+    const uint64_t * group_cta_bytes;  // [n_groups] scratch bytes each CTA of the group owns
+    unsigned char * scratch;
+    uint32_t smem_bytes;               // dynamic shared memory per CTA of this launch
+};
+
+struct SellChunk {
+
+    uint32_t off;     // first entry slot (multiple of 32)
+    uint32_t first;   // first row (column) of the chunk, in sorted order
+    uint16_t count;   // rows (columns) in the chunk, <= 32 >> l2
+    uint8_t l2;       // log2(lanes per row)
+    uint8_t pad;
+    uint32_t width;   // steps
+};
+
+constexpr uint32_t kSellBuckets = 64;
+
+// Length bucket: exact up to 32, then one bucket per power of two.
+__host__ __device__ __forceinline__ uint32_t sellBucket(uint32_t len) {
+
+    if (len <= 32) { return len; }
+    uint32_t lg = 0;
+    uint32_t v = len - 1;
+    while (v >>= 1) { lg++; }   // floor(log2(len - 1)) >= 5
+    return 32 + (lg - 4);
+}
+
+__host__ __device__ __forceinline__ uint32_t sellBucketUpper(uint32_t bucket) {
+
+    return bucket <= 32 ? bucket : (1u << (bucket - 32 + 5));
+}
+
+// log2 of the lanes a row of (at most) this length gets: about 8 entries per lane, 1..32 lanes.
+__host__ __device__ __forceinline__ uint32_t sellLanesLog2(uint32_t len_upper) {
+
+    const uint32_t want = (len_upper + 7) / 8;
+    uint32_t l2 = 0;
+    while (l2 < 5 && (1u << l2) < want) { l2++; }
+    return l2;
+}
+
+// Entry slots one orientation of a slice occupies (z entries in n rows): worst case and what is typical after sorting.
+__host__ __device__ inline uint64_t sellSlotsWorst(uint64_t z, uint64_t n) { return 4 * z + 32 * n + 320; }
+__host__ __device__ inline uint64_t sellSlotsTypical(uint64_t z, uint64_t n) { return z + z / 4 + 2 * n + 128; }
+
+__host__ __device__ inline uint64_t sellRound16(uint64_t bytes) { return (bytes + 15) & ~uint64_t(15); }
+
+// Shared-memory need of one CTA: m rows, z entries, N columns (worst: upper bound; otherwise the expected need).
+__host__ __device__ inline uint64_t sellSmemBytes(uint64_t m, uint64_t z, uint64_t N, uint64_t index_bytes, bool multi, bool worst) {
+
+    const uint64_t fixed = sellRound16(8 * (N + 1)) * (multi ? 2 : 1);
+    const uint64_t vectors = 3 * sellRound16(8 * (m + 1));
+    const uint64_t chunks = worst ? 16 * (m + N + 130) : 16 * ((m + N) / 8 + 140);
+    const uint64_t col_id = sellRound16(index_bytes * (N + 1));
+    const uint64_t slots = worst ? sellSlotsWorst(z, m) + sellSlotsWorst(z, N) : sellSlotsTypical(z, m) + sellSlotsTypical(z, N);
+    return fixed + vectors + chunks + col_id + (8 + index_bytes) * slots + 256;
+}
+
+// Global scratch one CTA owns: prologue temporaries, everything that may spill out of shared memory and, when
+// with_entries, the worst-case entry arrays.
+__host__ __device__ inline uint64_t sellScratchBytes(uint64_t m, uint64_t z, uint64_t N, uint64_t index_bytes, bool with_entries) {
+
+    const uint64_t temps = 2 * sellRound16(4 * (m + 1)) + 4 * sellRound16(4 * (N + 1));
+    const uint64_t vectors = 3 * sellRound16(8 * (m + 1));
+    const uint64_t chunks = 16 * (m + N + 130);
+    const uint64_t col_id = sellRound16(index_bytes * (N + 1));
+    const uint64_t entries = with_entries ? (8 + index_bytes) * (sellSlotsWorst(z, m) + sellSlotsWorst(z, N)) + 128 : 64;
+    return ((temps + vectors + chunks + col_id + entries + 1023) / 1024) * 1024;
+}
+
+template <int THREADS>
+struct SellSort {
+
+    // shared state of the stable bucket sort (static shared memory)
+    uint32_t hist[THREADS / 32][kSellBuckets];
+    uint32_t bucket_total[kSellBuckets];
+    uint32_t bucket_start[kSellBuckets];    // start of each bucket in sorted (descending length) order
+    uint32_t chunk_base[kSellBuckets + 1];  // first chunk of each bucket
+};
+
+// Stable sort of n items by descending bucket. len(i) gives the length of item i. Writes pos[i] = sorted position and
+// src[sorted position] = i. Warps own contiguous item ranges, so ties keep their original order.
+template <int THREADS, typename LenFn>
+__device__ void sellStableSort(SellSort<THREADS> & st, const uint32_t n, LenFn len, uint32_t * pos, uint32_t * src) {
+
+    constexpr uint32_t W = THREADS / 32;
+    const uint32_t tid = threadIdx.x;
+    const uint32_t lane = tid & 31;
+    const uint32_t warp = tid >> 5;
+
+    for (uint32_t k = tid; k < W * kSellBuckets; k += THREADS) { (&st.hist[0][0])[k] = 0; }
+    __syncthreads();
+
+    const uint32_t per_warp = (((n + W - 1) / W) + 31) & ~31u;
+    const uint32_t begin = min(n, warp * per_warp);
+    const uint32_t end = min(n, begin + per_warp);
+
+    for (uint32_t i0 = begin; i0 < end; i0 += 32) {
+
+        const uint32_t i = i0 + lane;
+        const uint32_t b = (i < end) ? sellBucket(len(i)) : 0xffffffffu;
+        const uint32_t same = __match_any_sync(0xffffffffu, b);
+
+        if (i < end && (same & ((1u << lane) - 1)) == 0) { st.hist[warp][b] += __popc(same); }
+        __syncwarp();
+    }
+
+    __syncthreads();
+
+    if (tid < kSellBuckets) {
+        uint32_t total = 0;
+        for (uint32_t w = 0; w < W; ++w) {
+            const uint32_t h = st.hist[w][tid];
+            st.hist[w][tid] = total;    // exclusive over warps
+            total += h;
+        }
+        st.bucket_total[tid] = total;
+    }
+
+    __syncthreads();
+
+    if (tid == 0) {
+        uint32_t run = 0;
+        for (int b = kSellBuckets - 1; b >= 0; --b) {
+            st.bucket_start[b] = run;
+            run += st.bucket_total[b];
+        }
+    }
+
+    __syncthreads();
+
+    for (uint32_t i0 = begin; i0 < end; i0 += 32) {
+
+        const uint32_t i = i0 + lane;
+        const uint32_t b = (i < end) ? sellBucket(len(i)) : 0xffffffffu;
+        const uint32_t same = __match_any_sync(0xffffffffu, b);
+        const uint32_t before = __popc(same & ((1u << lane) - 1));
+
+        if (i < end) {
+            const uint32_t p = st.bucket_start[b] + st.hist[warp][b] + before;
+            pos[i] = p;
+            src[p] = i;
+        }
+        __syncwarp();
+        if (i < end && before == 0) { st.hist[warp][b] += __popc(same); }
+        __syncwarp();
+    }
+
+    __syncthreads();
+}
+
+// Number of chunks sellMakeChunks will form for the items just sorted (same walk, nothing written).
+template <int THREADS>
+__device__ uint32_t sellCountChunks(SellSort<THREADS> & st, const uint32_t n) {
+
+    if (threadIdx.x == 0) {
+
+        uint32_t p = 0;
+        uint32_t k = 0;
+        int b = kSellBuckets - 1;
+
+        while (p < n) {
+            while (st.bucket_start[b] + st.bucket_total[b] <= p) { --b; }
+            p += min(32u >> sellLanesLog2(sellBucketUpper(b)), n - p);
+            ++k;
+        }
+
+        st.chunk_base[1] = k;
+    }
+
+    __syncthreads();
+    return st.chunk_base[1];
+}
+
+// Chunk descriptors for items already sorted by descending bucket: a chunk takes the next 32 >> l2 items, l2 from the
+// bucket of its first (longest) item. Returns the number of chunks; total_slots receives the number of entry slots.
+template <int THREADS, typename LenFn>
+__device__ uint32_t sellMakeChunks(SellSort<THREADS> & st, const uint32_t n, LenFn len, const uint32_t * src, SellChunk * chunks, uint32_t * scan_tmp, uint32_t * total_slots) {
+
+    const uint32_t tid = threadIdx.x;
+    const uint32_t lane = tid & 31;
+    const uint32_t warp = tid >> 5;
+
+    if (tid == 0) {
+
+        uint32_t p = 0;
+        uint32_t k = 0;
+        int b = kSellBuckets - 1;
+
+        while (p < n) {
+
+            while (st.bucket_start[b] + st.bucket_total[b] <= p) { --b; }
+
+            const uint32_t l2 = sellLanesLog2(sellBucketUpper(b));
+            const uint32_t count = min(32u >> l2, n - p);
+
+            SellChunk ch;
+            ch.off = 0;
+            ch.first = p;
+            ch.count = static_cast<uint16_t>(count);
+            ch.l2 = static_cast<uint8_t>(l2);
+            ch.pad = 0;
+            ch.width = 0;
+            chunks[k] = ch;
+
+            p += count;
+            ++k;
+        }
+
+        st.chunk_base[0] = k;
+    }
+
+    __syncthreads();
+
+    const uint32_t n_chunks = st.chunk_base[0];
+
+    for (uint32_t k = tid; k < n_chunks; k += THREADS) {
+
+        const uint32_t first = chunks[k].first;
+        const uint32_t count = chunks[k].count;
+        const uint32_t l2 = chunks[k].l2;
+
+        uint32_t max_len = 0;
+        for (uint32_t r = 0; r < count; ++r) { max_len = max(max_len, len(src[first + r])); }
+
+        chunks[k].width = (max_len + (1u << l2) - 1) >> l2;
+    }
+
+    __syncthreads();
+
+    // exclusive scan of width * 32 over the chunks (block-wide, chunked per thread)
+    const uint32_t per_thread = (n_chunks + THREADS - 1) / THREADS;
+    const uint32_t k_begin = min(n_chunks, tid * per_thread);
+    const uint32_t k_end = min(n_chunks, k_begin + per_thread);
+
+    uint32_t local = 0;
+    for (uint32_t k = k_begin; k < k_end; ++k) { local += chunks[k].width * 32; }
+
+    uint32_t incl = local;
+    #pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const uint32_t up = __shfl_up_sync(0xffffffffu, incl, off);
+        if (lane >= off) { incl += up; }
+    }
+    if (lane == 31) { scan_tmp[warp] = incl; }
+    __syncthreads();
+
+    uint32_t warp_base = 0;
+    for (uint32_t w = 0; w < warp; ++w) { warp_base += scan_tmp[w]; }
+
+    uint32_t offset = warp_base + incl - local;
+    for (uint32_t k = k_begin; k < k_end; ++k) {
+        chunks[k].off = offset;
+        offset += chunks[k].width * 32;
+    }
+
+    if (tid == THREADS - 1) { *total_slots = offset; }
+    __syncthreads();
+
+    return n_chunks;
+}
+
+// Bump allocator over the CTA's dynamic shared memory with overflow into its global scratch area.
+struct SellArena {
+
+    unsigned char * smem;
+    uint64_t smem_left;
+    unsigned char * gmem;
+    uint64_t gmem_left;
+    bool overflow;
+
+    __device__ __forceinline__ void * take(uint64_t bytes, bool allow_smem, bool * in_smem) {
+
+        bytes = (bytes + 15) & ~uint64_t(15);
+
+        if (allow_smem && bytes <= smem_left) {
+            void * p = smem;
+            smem += bytes;
+            smem_left -= bytes;
+            if (in_smem) { *in_smem = true; }
+            return p;
+        }
+
+        if (in_smem) { *in_smem = false; }
+        if (bytes > gmem_left) {
+            overflow = true;
+            return gmem;   // never dereferenced: the kernel bails out on overflow
+        }
+
+        void * p = gmem;
+        gmem += bytes;
+        gmem_left -= bytes;
+        return p;
+    }
+};
+
+template <typename IndexT>
+struct SellSide {
+
+    const SellChunk * chunks;
+    uint32_t n_chunks;
+    uint32_t n_resident;         // chunks [0, n_resident) have their entries in shared memory
+    uint32_t resident_slots;     // entry slots of the resident chunks
+    const double * val_s;        // resident entries
+    const IndexT * idx_s;
+    const double * val_g;        // streamed entries (indexed by slot - resident_slots)
+    const IndexT * idx_g;
+};
+
+template <int THREADS, bool MULTI, typename IndexT>
+__global__ void __launch_bounds__(THREADS) emSellKernel(const SellArgs sa) {
+
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+
+    __shared__ double red[32];
+    __shared__ uint32_t conv_flags[kMaxGroupSize];
+    __shared__ uint32_t scan_tmp[THREADS / 32];
+    __shared__ uint32_t shared_u32[4];
+    __shared__ SellSort<THREADS> sort_state;
+
+    const EmArgs & args = sa.em;
+
+    cg::cluster_group cluster = cg::this_cluster();
+    const uint32_t S = MULTI ? cluster.num_blocks() : 1;
+    const uint32_t rank = MULTI ? cluster.block_rank() : 0;
+
+    const uint32_t tid = threadIdx.x;
+    const uint32_t lane = tid & 31;
+    const uint32_t warp = tid >> 5;
+    constexpr uint32_t num_warps = THREADS / 32;
+
+    if (*args.error) { return; }   // malformed arena: indices cannot be trusted (uniform over the whole grid)
+
+    const uint32_t group = blockIdx.x / S;
+    const uint32_t c = sa.group_cluster[group];
+
+    const uint64_t r0 = args.read_offset[c];
+    const uint32_t M = static_cast<uint32_t>(args.read_offset[c + 1] - r0);
+    const uint64_t p0 = args.path_offset[c];
+    const uint32_t N = static_cast<uint32_t>(args.path_offset[c + 1] - p0);
+
+    if (M == 0) {   // rpvg:src/path_abundance_estimator.cpp:20-22 — only the reset runs
+
+        for (uint32_t j = rank * THREADS + tid; j < N; j += S * THREADS) { args.abundances[p0 + j] = 0; }
+
+        if (rank == 0 && tid == 0) {
+            args.noise_count[c] = 0;
+            args.total_count[c] = 0;
+            args.iterations[c] = 0;
+        }
+        return;
+    }
+
+    const uint64_t * row_ptr = args.row_ptr + r0;
+    const uint64_t e_cluster = row_ptr[0];
+    const uint64_t Z = row_ptr[M] - e_cluster;
+
+    // ---- this CTA's slice of read classes: equal weight (entries + rows) per CTA
+    uint32_t bounds[2];
+    #pragma unroll
+    for (int b = 0; b < 2; ++b) {
+
+        const uint32_t r = rank + b;
+        if (r == 0) { bounds[b] = 0; continue; }
+        if (r >= S) { bounds[b] = M; continue; }
+
+        const uint64_t target = ((Z + M) * r) / S;
+        uint32_t lo = 0, hi = M;
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if ((row_ptr[mid] - e_cluster) + mid >= target) { hi = mid; } else { lo = mid + 1; }
+        }
+        bounds[b] = lo;
+    }
+
+    const uint32_t i0 = bounds[0];
+    const uint32_t m = bounds[1] - i0;
+    const uint64_t e_slice = row_ptr[i0];
+
+    // columns (noise included as column N) this CTA reduces and owns in the finalisation
+    const uint32_t jc0 = static_cast<uint32_t>((static_cast<uint64_t>(N + 1) * rank) / S);
+    const uint32_t jc1 = static_cast<uint32_t>((static_cast<uint64_t>(N + 1) * (rank + 1)) / S);
+
+    // ---- memory: shared first, scratch for what does not fit
+    SellArena arena;
+    arena.smem = smem_raw;
+    arena.smem_left = sa.smem_bytes;
+    arena.gmem = sa.scratch + sa.group_scratch[group] + static_cast<uint64_t>(rank) * sa.group_cta_bytes[group];
+    arena.gmem_left = sa.group_cta_bytes[group];
+    arena.overflow = false;
+
+    // a and g come first so that they sit at the same offsets in every CTA of the group (remote access); the host only
+    // sends a cluster here when they fit
+    double * a = static_cast<double *>(arena.take(8ull * (N + 1), true, nullptr));
+    double * g = MULTI ? static_cast<double *>(arena.take(8ull * (N + 1), true, nullptr)) : nullptr;
+
+    // prologue temporaries (global scratch only)
+    uint32_t * row_pos = static_cast<uint32_t *>(arena.take(4ull * (m + 1), false, nullptr));
+    uint32_t * row_src = static_cast<uint32_t *>(arena.take(4ull * (m + 1), false, nullptr));
+    uint32_t * cstart = static_cast<uint32_t *>(arena.take(4ull * (N + 1), false, nullptr));
+    uint32_t * clen = static_cast<uint32_t *>(arena.take(4ull * (N + 1), false, nullptr));
+    uint32_t * col_pos = static_cast<uint32_t *>(arena.take(4ull * (N + 1), false, nullptr));
+    uint32_t * col_src = static_cast<uint32_t *>(arena.take(4ull * (N + 1), false, nullptr));
+
+    // per-row vectors in sorted order
+    double * w = static_cast<double *>(arena.take(8ull * (m + 1), true, nullptr));
+    double * noise = static_cast<double *>(arena.take(8ull * (m + 1), true, nullptr));
+    double * cnt = static_cast<double *>(arena.take(8ull * (m + 1), true, nullptr));
+
+    // ---- total read count: every CTA sums all rows in the same order, so all agree bit for bit
+    double count_sum = 0;
+    for (uint32_t i = tid; i < M; i += THREADS) { count_sum += args.cnt[r0 + i]; }
+    const double total = blockSum(count_sum, red);
+
+    // ---- rows: sort by length, chunk, fill
+    auto row_len = [&](uint32_t i) { return static_cast<uint32_t>(row_ptr[i0 + i + 1] - row_ptr[i0 + i]); };
+    sellStableSort<THREADS>(sort_state, m, row_len, row_pos, row_src);
+
+    const uint32_t row_chunk_bound = sellCountChunks<THREADS>(sort_state, m);
+
+    SellChunk * row_chunks = static_cast<SellChunk *>(arena.take(sizeof(SellChunk) * (row_chunk_bound + 1), true, nullptr));
+    const uint32_t n_row_chunks = sellMakeChunks<THREADS>(sort_state, m, row_len, row_src, row_chunks, scan_tmp, &shared_u32[0]);
+    const uint32_t row_slots = shared_u32[0];
+
+    for (uint32_t p = tid; p < m; p += THREADS) {
+        const uint32_t i = row_src[p];
+        noise[p] = args.noise[r0 + i0 + i];
+        cnt[p] = args.cnt[r0 + i0 + i];
+    }
+
+    // ---- columns: range of this slice inside each column of the column-major arrays (rows ascend within a column)
+    {
+        const uint64_t * col_ptr = args.col_ptr + p0;
+        const uint32_t i1 = i0 + m;
+
+        for (uint32_t j = tid; j < N; j += THREADS) {
+
+            const uint64_t k_begin = col_ptr[j];
+            const uint64_t k_end = col_ptr[j + 1];
+
+            uint64_t lo = k_begin, hi = k_end;
+            while (lo < hi) {
+                const uint64_t mid = (lo + hi) >> 1;
+                if (__ldg(args.csc_row + mid) >= i0) { hi = mid; } else { lo = mid + 1; }
+            }
+            const uint64_t first = lo;
+
+            hi = k_end;
+            while (lo < hi) {
+                const uint64_t mid = (lo + hi) >> 1;
+                if (__ldg(args.csc_row + mid) >= i1) { hi = mid; } else { lo = mid + 1; }
+            }
+
+            cstart[j] = static_cast<uint32_t>(first);
+            clen[j] = static_cast<uint32_t>(lo - first);
+        }
+    }
+
+    __syncthreads();
+
+    auto col_len = [&](uint32_t j) { return clen[j]; };
+    sellStableSort<THREADS>(sort_state, N, col_len, col_pos, col_src);
+
+    const uint32_t col_chunk_bound = sellCountChunks<THREADS>(sort_state, N);
+
+    SellChunk * col_chunks = static_cast<SellChunk *>(arena.take(sizeof(SellChunk) * (col_chunk_bound + 1), true, nullptr));
+    const uint32_t n_col_chunks = sellMakeChunks<THREADS>(sort_state, N, col_len, col_src, col_chunks, scan_tmp, &shared_u32[1]);
+    const uint32_t col_slots = shared_u32[1];
+
+    // column ids in sorted order (kept for the whole kernel)
+    IndexT * col_id = static_cast<IndexT *>(arena.take(sizeof(IndexT) * (N + 1), true, nullptr));
+    for (uint32_t p = tid; p < N; p += THREADS) { col_id[p] = static_cast<IndexT>(col_src[p]); }
+
+    // ---- entry arrays: column side first (it also carries the update), then row side; whole chunks only
+    auto place = [&](const SellChunk * chunks, uint32_t n_chunks, uint32_t slots, SellSide<IndexT> * side) {
+
+        // largest prefix of chunks whose entries fit in what is left of shared memory
+        const uint64_t per_slot = 8 + sizeof(IndexT);
+        const uint64_t budget_slots = arena.smem_left > 64 ? (arena.smem_left - 64) / per_slot : 0;
+
+        uint32_t n_res = n_chunks;
+        uint32_t res_slots = slots;
+
+        if (slots > budget_slots) {
+            uint32_t lo = 0, hi = n_chunks;   // first chunk whose end exceeds the budget
+            while (lo < hi) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if (static_cast<uint64_t>(chunks[mid].off) + chunks[mid].width * 32 > budget_slots) { hi = mid; } else { lo = mid + 1; }
+            }
+            n_res = lo;
+            res_slots = (n_res < n_chunks) ? chunks[n_res].off : slots;
+        }
+
+        side->chunks = chunks;
+        side->n_chunks = n_chunks;
+        side->n_resident = n_res;
+        side->resident_slots = res_slots;
+        side->val_s = static_cast<double *>(arena.take(8ull * res_slots, true, nullptr));
+        side->idx_s = static_cast<IndexT *>(arena.take(sizeof(IndexT) * static_cast<uint64_t>(res_slots), true, nullptr));
+        side->val_g = static_cast<double *>(arena.take(8ull * (slots - res_slots), false, nullptr));
+        side->idx_g = static_cast<IndexT *>(arena.take(sizeof(IndexT) * static_cast<uint64_t>(slots - res_slots), false, nullptr));
+    };
+
+    SellSide<IndexT> cols, rows;
+    place(col_chunks, n_col_chunks, col_slots, &cols);
+    place(row_chunks, n_row_chunks, row_slots, &rows);
+
+    // capacity check, uniform over the group: every CTA publishes its flag before anyone proceeds
+    if (MULTI) {
+        if (tid == 0) { conv_flags[0] = 0; }
+        cluster.sync();
+        if (arena.overflow && tid == 0) {
+            for (uint32_t s = 0; s < S; ++s) { *(cluster.map_shared_rank(conv_flags, s)) = 1; }
+            printf("[rpvg_b200] capacity: cluster %u rank %u/%u M %u N %u m %u row_slots %u col_slots %u chunks %u/%u cta_bytes %llu smem %u\n", c, rank, S, M, N, m,
+                   row_slots, col_slots, n_row_chunks, n_col_chunks, static_cast<unsigned long long>(sa.group_cta_bytes[group]), sa.smem_bytes);
+        }
+        cluster.sync();
+        if (conv_flags[0]) {
+            if (rank == 0 && tid == 0) { atomicOr(const_cast<uint32_t *>(args.error), RPVG_DEV_ERR_CAPACITY); }
+            return;
+        }
+    } else if (arena.overflow) {
+        if (tid == 0) {
+            atomicOr(const_cast<uint32_t *>(args.error), RPVG_DEV_ERR_CAPACITY);
+            printf("[rpvg_b200] capacity: cluster %u M %u N %u m %u row_slots %u col_slots %u chunks %u/%u cta_bytes %llu smem %u\n", c, M, N, m, row_slots, col_slots,
+                   n_row_chunks, n_col_chunks, static_cast<unsigned long long>(sa.group_cta_bytes[group]), sa.smem_bytes);
+        }
+        return;
+    }
+
+    // ---- fill: one warp per chunk
+    auto fill = [&](const SellSide<IndexT> & side, auto entry_range, auto entry_value, auto entry_index, const uint32_t * src) {
+
+        for (uint32_t k = warp; k < side.n_chunks; k += num_warps) {
+
+            const SellChunk ch = side.chunks[k];
+            const uint32_t lanes = 1u << ch.l2;
+            const uint32_t r = lane >> ch.l2;
+            const uint32_t sub = lane & (lanes - 1);
+
+            const bool res = k < side.n_resident;
+            double * val = const_cast<double *>(res ? side.val_s + ch.off : side.val_g + (ch.off - side.resident_slots));
+            IndexT * idx = const_cast<IndexT *>(res ? side.idx_s + ch.off : side.idx_g + (ch.off - side.resident_slots));
+
+            uint64_t base = 0;
+            uint32_t len = 0;
+            if (r < ch.count) { entry_range(src[ch.first + r], &base, &len); }
+
+            for (uint32_t t = 0; t < ch.width; ++t) {
+
+                const uint32_t e = t * lanes + sub;
+                double v = 0;
+                IndexT x = 0;
+                if (e < len) {
+                    v = entry_value(base + e);
+                    x = static_cast<IndexT>(entry_index(base + e));
+                }
+                val[t * 32 + lane] = v;
+                idx[t * 32 + lane] = x;
+            }
+        }
+    };
+
+    fill(rows,
+         [&](uint32_t i, uint64_t * base, uint32_t * len) { *base = row_ptr[i0 + i]; *len = static_cast<uint32_t>(row_ptr[i0 + i + 1] - *base); },
+         [&](uint64_t e) { return args.val[e]; },
+         [&](uint64_t e) { return args.col[e]; },
+         row_src);
+
+    fill(cols,
+         [&](uint32_t j, uint64_t * base, uint32_t * len) { *base = cstart[j]; *len = clen[j]; },
+         [&](uint64_t k) { return args.csc_val[k]; },
+         [&](uint64_t k) { return row_pos[args.csc_row[k] - i0]; },
+         col_src);
+
+    // rpvg:src/path_abundance_estimator.cpp:54 — single-precision quotient widened to double
+    const double a_init = static_cast<double>(1 / static_cast<float>(N + 1));
+    for (uint32_t j = tid; j <= N; j += THREADS) { a[j] = a_init; }
+
+    if (MULTI) { cluster.sync(); } else { __syncthreads(); }
+
+    const double conv = args.params.max_rel_em_conv;
+    const double min_abundance = args.params.min_em_abundance;
+    const double inv_total = 1.0 / total;
+
+    uint32_t conv_its = 0;
+    uint32_t it = 0;
+
+    while (it < args.params.max_em_its) {
+
+        // ---- E-step over the slice: w_i = count_i / sum_j p_ij a_j
+        const double a_noise = a[N];
+        double noise_acc = 0;
+
+        for (uint32_t k = warp; k < rows.n_chunks; k += num_warps) {
+
+            const SellChunk ch = rows.chunks[k];
+            const bool res = k < rows.n_resident;
+            const double * val = (res ? rows.val_s + ch.off : rows.val_g + (ch.off - rows.resident_slots)) + lane;
+            const IndexT * idx = (res ? rows.idx_s + ch.off : rows.idx_g + (ch.off - rows.resident_slots)) + lane;
+
+            double acc = 0;
+            #pragma unroll 4
+            for (uint32_t t = 0; t < ch.width; ++t) { acc += val[t * 32] * a[idx[t * 32]]; }
+
+            for (uint32_t off = (1u << ch.l2) >> 1; off > 0; off >>= 1) { acc += __shfl_xor_sync(0xffffffffu, acc, off); }
+
+            const uint32_t r = lane >> ch.l2;
+            if ((lane & ((1u << ch.l2) - 1)) == 0 && r < ch.count) {
+                const uint32_t p = ch.first + r;
+                const double nz = noise[p];
+                const double wv = cnt[p] / (acc + nz * a_noise);
+                w[p] = wv;
+                noise_acc += nz * wv;
+            }
+        }
+
+        // noise column: per-warp partials now, combined in a fixed order after the barrier
+        noise_acc = warpSum(noise_acc);
+        if (lane == 0) { red[warp] = noise_acc; }
+        if (MULTI && tid < S) { conv_flags[tid] = 1; }
+
+        __syncthreads();
+
+        // ---- M-step over the slice: column sums (and, with one CTA, the abundance update itself)
+        bool ok = true;
+
+        for (uint32_t k = warp; k < cols.n_chunks; k += num_warps) {
+
+            const SellChunk ch = cols.chunks[k];
+            const bool res = k < cols.n_resident;
+            const double * val = (res ? cols.val_s + ch.off : cols.val_g + (ch.off - cols.resident_slots)) + lane;
+            const IndexT * idx = (res ? cols.idx_s + ch.off : cols.idx_g + (ch.off - cols.resident_slots)) + lane;
+
+            double acc = 0;
+            #pragma unroll 4
+            for (uint32_t t = 0; t < ch.width; ++t) { acc += val[t * 32] * w[idx[t * 32]]; }
+
+            for (uint32_t off = (1u << ch.l2) >> 1; off > 0; off >>= 1) { acc += __shfl_xor_sync(0xffffffffu, acc, off); }
+
+            const uint32_t r = lane >> ch.l2;
+            if ((lane & ((1u << ch.l2) - 1)) == 0 && r < ch.count) {
+
+                const uint32_t j = col_id[ch.first + r];
+
+                if (MULTI) {
+                    g[j] = acc;
+                } else {
+                    const double a_old = a[j];
+                    const double a_new = (a_old * acc) * inv_total;
+                    a[j] = a_new;
+                    if (a_new >= min_abundance && fabs(a_new - a_old) > conv * a_new) { ok = false; }
+                }
+            }
+        }
+
+        if (tid == THREADS - 1) {
+
+            double noise_g = 0;
+            #pragma unroll
+            for (uint32_t wi = 0; wi < num_warps; ++wi) { noise_g += red[wi]; }
+
+            if (MULTI) {
+                g[N] = noise_g;
+            } else {
+                const double a_new = (a_noise * noise_g) * inv_total;
+                a[N] = a_new;
+                if (a_new >= min_abundance && fabs(a_new - a_noise) > conv * a_new) { ok = false; }
+            }
+        }
+
+        ++it;
+
+        if constexpr (!MULTI) {
+
+            if (__syncthreads_and(ok)) {
+                if (++conv_its == args.params.min_em_conv_its) { break; }
+            } else {
+                conv_its = 0;
+            }
+
+        } else {
+
+            cluster.sync();
+
+            // reduce-scatter + all-gather over the group: this CTA owns columns [jc0, jc1)
+            for (uint32_t j = jc0 + tid; j < jc1; j += THREADS) {
+
+                double part[kMaxGroupSize];
+                #pragma unroll
+                for (uint32_t s = 0; s < kMaxGroupSize; ++s) { part[s] = (s < S) ? *(cluster.map_shared_rank(g, s) + j) : 0.0; }
+
+                double sum = 0;
+                #pragma unroll
+                for (uint32_t s = 0; s < kMaxGroupSize; ++s) { sum += part[s]; }
+
+                const double a_old = a[j];
+                const double a_new = (a_old * sum) * inv_total;
+                if (a_new >= min_abundance && fabs(a_new - a_old) > conv * a_new) { ok = false; }
+
+                #pragma unroll
+                for (uint32_t s = 0; s < kMaxGroupSize; ++s) {
+                    if (s < S) { *(cluster.map_shared_rank(a, s) + j) = a_new; }
+                }
+            }
+
+            // convergence vote: flags were set to 1 before the block barrier above; a failing warp clears this CTA's
+            // flag in every CTA of the group
+            if (__any_sync(0xffffffffu, !ok) && lane == 0) {
+                for (uint32_t s = 0; s < S; ++s) { *(cluster.map_shared_rank(conv_flags, s) + rank) = 0; }
+            }
+
+            cluster.sync();
+
+            bool all_ok = true;
+            for (uint32_t s = 0; s < S; ++s) { all_ok = all_ok && (conv_flags[s] != 0); }
+
+            if (all_ok) {
+                if (++conv_its == args.params.min_em_conv_its) { break; }
+            } else {
+                conv_its = 0;
+            }
+        }
+    }
+
+    // rpvg:src/path_abundance_estimator.cpp:100-113; every CTA holds the full abundance vector
+    for (uint32_t j = jc0 + tid; j < min(jc1, N); j += THREADS) {
+        const double aj = a[j];
+        args.abundances[p0 + j] = (aj < min_abundance) ? 0 : aj * total;
+    }
+
+    if (rank == 0) {
+
+        double noise_part = 0;
+        for (uint32_t j = tid; j < N; j += THREADS) {
+            const double aj = a[j];
+            if (aj < min_abundance) { noise_part += aj * total; }
+        }
+
+        const double low_sum = blockSum(noise_part, red);
+
+        if (tid == 0) {
+            args.noise_count[c] = low_sum + a[N] * total;
+            args.total_count[c] = total;
+            args.iterations[c] = it;
+        }
+    }
+
+    // no CTA may exit while a peer can still touch its shared memory
+    if (MULTI) { cluster.sync(); }
+}
