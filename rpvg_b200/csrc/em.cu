@@ -22,6 +22,7 @@
 #include <numeric>
 
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 
 #include "common.cuh"
 #include "em_kernels.cuh"
@@ -88,7 +89,20 @@ struct rpvg_b200_batch {
     uint64_t * d_group_scratch = nullptr;
     uint64_t * d_group_cta_bytes = nullptr;
 
-    // built
+    // built: read classes re-ordered by first path (sorted CSR), then the column-major copy
+    uint64_t * d_rowkey_in = nullptr;
+    uint64_t * d_rowkey_out = nullptr;
+    uint32_t * d_rowid_in = nullptr;
+    uint32_t * d_perm = nullptr;            // sorted position -> original read class
+    uint64_t * d_sorted_len = nullptr;
+    uint64_t * d_sorted_row_ptr = nullptr;
+    uint32_t * d_sorted_col = nullptr;
+    double * d_sorted_noise = nullptr;
+    void * d_rowsort_temp = nullptr;
+    size_t rowsort_temp_bytes = 0;
+    void * d_scan_temp = nullptr;
+    size_t scan_temp_bytes = 0;
+    int rowsort_bits = 64;
     double * d_val = nullptr;
     double * d_cnt = nullptr;
     uint32_t * d_entry_row = nullptr;
@@ -123,26 +137,63 @@ struct rpvg_b200_batch {
 
 namespace {
 
-// ---- build: one thread per read class -------------------------------------------------------------------------------
+// ---- build ----------------------------------------------------------------------------------------------------------
+// The read classes of a cluster are re-ordered by their first (lowest) path index: EM does not care about the order of
+// read classes, and with this order a contiguous slice of them touches a narrow band of paths, which keeps the
+// cross-CTA exchange of the EM kernel short (em_sell.cuh). Sort key: (cluster, first path); empty read classes last.
+__global__ void rowKeysKernel(uint32_t n_clusters, uint64_t n_reads, const uint64_t * __restrict__ read_offset, const uint64_t * __restrict__ row_ptr,
+                              const uint32_t * __restrict__ col, uint64_t * __restrict__ key, uint32_t * __restrict__ row_id) {
+
+    const uint64_t r = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (r >= n_reads) { return; }
+
+    const uint32_t c = clusterOf(read_offset, n_clusters, r);
+    const uint32_t first = (row_ptr[r + 1] > row_ptr[r]) ? col[row_ptr[r]] : 0xffffffffu;
+
+    key[r] = (static_cast<uint64_t>(c) << 32) | first;
+    row_id[r] = static_cast<uint32_t>(r);
+}
+
+// Length of every read class in sorted order (one extra zero at the end so that the scan yields n_reads + 1 offsets).
+__global__ void sortedLengthsKernel(uint64_t n_reads, const uint32_t * __restrict__ perm, const uint64_t * __restrict__ row_ptr, uint64_t * __restrict__ len) {
+
+    const uint64_t p = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (p > n_reads) { return; }
+
+    uint64_t l = 0;
+    if (p < n_reads) {
+        const uint32_t r = perm[p];
+        l = row_ptr[r + 1] - row_ptr[r];
+    }
+    len[p] = l;
+}
+
+// One thread per read class (sorted position p, original row perm[p]).
 // Row normalisation exactly as the reference orders it: v = p / rowsum (left-to-right sum over ascending path index,
 // which is what the dense row-wise sum does since zeros add nothing), then v * (1 - noise), NaN -> 0.
 __global__ void buildRowsKernel(uint32_t n_clusters, uint64_t n_reads,
                                 const uint64_t * __restrict__ read_offset, const uint64_t * __restrict__ path_offset,
                                 const uint64_t * __restrict__ row_ptr, const uint32_t * __restrict__ col,
                                 const double * __restrict__ prob, const double * __restrict__ noise, const uint32_t * __restrict__ count,
+                                const uint32_t * __restrict__ perm, const uint64_t * __restrict__ sorted_row_ptr,
+                                uint32_t * __restrict__ sorted_col, double * __restrict__ sorted_noise,
                                 double * __restrict__ val, double * __restrict__ cnt, uint32_t * __restrict__ entry_row,
                                 uint32_t * __restrict__ key, uint32_t * __restrict__ idx, uint32_t * __restrict__ error) {
 
-    const uint64_t r = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
-    if (r >= n_reads) { return; }
+    const uint64_t p = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (p >= n_reads) { return; }
 
-    const uint32_t c = clusterOf(read_offset, n_clusters, r);
+    const uint64_t r = perm[p];
+
+    // sorting keeps clusters contiguous, so position p lies in the same cluster's range as row r
+    const uint32_t c = clusterOf(read_offset, n_clusters, p);
     const uint64_t path_base = path_offset[c];
     const uint64_t num_paths = path_offset[c + 1] - path_base;
-    const uint32_t local_row = static_cast<uint32_t>(r - read_offset[c]);
+    const uint32_t local_row = static_cast<uint32_t>(p - read_offset[c]);
 
     const uint64_t e0 = row_ptr[r];
     const uint64_t e1 = row_ptr[r + 1];
+    const uint64_t out = sorted_row_ptr[p];
 
     double row_sum = 0;
     uint32_t err = 0;
@@ -168,13 +219,18 @@ __global__ void buildRowsKernel(uint32_t n_clusters, uint64_t n_reads,
         double v = (prob[e] / row_sum) * scale;
         if (isnan(v)) { v = 0; }
 
-        val[e] = v;
-        entry_row[e] = local_row;
-        key[e] = static_cast<uint32_t>(path_base + min(static_cast<uint64_t>(col[e]), num_paths - 1));
-        idx[e] = static_cast<uint32_t>(e);
+        const uint64_t o = out + (e - e0);
+        const uint32_t j = static_cast<uint32_t>(min(static_cast<uint64_t>(col[e]), num_paths - 1));
+
+        val[o] = v;
+        sorted_col[o] = j;
+        entry_row[o] = local_row;
+        key[o] = static_cast<uint32_t>(path_base + j);
+        idx[o] = static_cast<uint32_t>(o);
     }
 
-    cnt[r] = static_cast<double>(count[r]);
+    sorted_noise[p] = noise[r];
+    cnt[p] = static_cast<double>(count[r]);
 
     if (err) { atomicOr(error, err); }
 }
@@ -535,7 +591,16 @@ int rpvg_b200_batch_upload(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, r
     cub::DeviceRadixSort::SortPairs(nullptr, b->sort_temp_bytes, static_cast<uint32_t *>(nullptr), static_cast<uint32_t *>(nullptr),
                                     static_cast<uint32_t *>(nullptr), static_cast<uint32_t *>(nullptr), static_cast<int>(Z), 0, b->sort_bits, ctx->stream);
 
+    b->rowsort_bits = 33;
+    while ((uint64_t(1) << (b->rowsort_bits - 32)) < C && b->rowsort_bits < 64) { b->rowsort_bits++; }
+
+    cub::DeviceRadixSort::SortPairs(nullptr, b->rowsort_temp_bytes, static_cast<uint64_t *>(nullptr), static_cast<uint64_t *>(nullptr),
+                                    static_cast<uint32_t *>(nullptr), static_cast<uint32_t *>(nullptr), static_cast<int>(R), 0, b->rowsort_bits, ctx->stream);
+    cub::DeviceScan::ExclusiveSum(nullptr, b->scan_temp_bytes, static_cast<uint64_t *>(nullptr), static_cast<uint64_t *>(nullptr), static_cast<int>(R + 1), ctx->stream);
+
     size_t bytes = 0;
+    bytes += 4 * padded<uint64_t>(R + 1) + 2 * padded<uint32_t>(R) + padded<uint32_t>(Z) + padded<double>(R);
+    bytes += ((b->rowsort_temp_bytes + 255) & ~size_t(255)) + ((b->scan_temp_bytes + 255) & ~size_t(255));
     bytes += 2 * padded<uint64_t>(C + 1) + padded<uint64_t>(R + 1) + padded<uint32_t>(Z) + padded<double>(Z) + padded<double>(R) + padded<uint32_t>(R) + padded<uint32_t>(C);
     bytes += 2 * padded<uint64_t>(C);
     bytes += padded<double>(Z) + padded<double>(R) + 5 * padded<uint32_t>(Z) + padded<uint64_t>(P + 1) + padded<uint32_t>(Z) + padded<double>(Z);
@@ -562,6 +627,16 @@ int rpvg_b200_batch_upload(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, r
     b->d_order = pool.take<uint32_t>(C);
     b->d_group_scratch = pool.take<uint64_t>(C);
     b->d_group_cta_bytes = pool.take<uint64_t>(C);
+    b->d_rowkey_in = pool.take<uint64_t>(R + 1);
+    b->d_rowkey_out = pool.take<uint64_t>(R + 1);
+    b->d_rowid_in = pool.take<uint32_t>(R);
+    b->d_perm = pool.take<uint32_t>(R);
+    b->d_sorted_len = pool.take<uint64_t>(R + 1);
+    b->d_sorted_row_ptr = pool.take<uint64_t>(R + 1);
+    b->d_sorted_col = pool.take<uint32_t>(Z);
+    b->d_sorted_noise = pool.take<double>(R);
+    b->d_rowsort_temp = pool.take<char>(b->rowsort_temp_bytes);
+    b->d_scan_temp = pool.take<char>(b->scan_temp_bytes);
     b->d_val = pool.take<double>(Z);
     b->d_cnt = pool.take<double>(R);
     b->d_entry_row = pool.take<uint32_t>(Z);
@@ -644,9 +719,31 @@ int rpvg_b200_batch_em(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const rpvg_b200
     if (b->n_reads > 0) {
 
         const unsigned grid = static_cast<unsigned>((b->n_reads + 255) / 256);
-        buildRowsKernel<<<grid, 256, 0, s>>>(b->n_clusters, b->n_reads, b->d_read_offset, b->d_path_offset, b->d_row_ptr, b->d_col, b->d_prob,
-                                             b->d_noise, b->d_count, b->d_val, b->d_cnt, b->d_entry_row, b->d_key_in, b->d_idx_in, b->d_error);
+        const unsigned grid1 = static_cast<unsigned>((b->n_reads + 1 + 255) / 256);
+
+        rowKeysKernel<<<grid, 256, 0, s>>>(b->n_clusters, b->n_reads, b->d_read_offset, b->d_row_ptr, b->d_col, b->d_rowkey_in, b->d_rowid_in);
         RPVG_LAUNCHED(ctx);
+
+        size_t temp_bytes = b->rowsort_temp_bytes;
+        RPVG_CUDA(ctx, cub::DeviceRadixSort::SortPairs(b->d_rowsort_temp, temp_bytes, b->d_rowkey_in, b->d_rowkey_out, b->d_rowid_in, b->d_perm,
+                                                       static_cast<int>(b->n_reads), 0, b->rowsort_bits, s));
+        ctx->launches += 2 + static_cast<uint64_t>((b->rowsort_bits + 7) / 8);
+
+        sortedLengthsKernel<<<grid1, 256, 0, s>>>(b->n_reads, b->d_perm, b->d_row_ptr, b->d_sorted_len);
+        RPVG_LAUNCHED(ctx);
+
+        temp_bytes = b->scan_temp_bytes;
+        RPVG_CUDA(ctx, cub::DeviceScan::ExclusiveSum(b->d_scan_temp, temp_bytes, b->d_sorted_len, b->d_sorted_row_ptr, static_cast<int>(b->n_reads + 1), s));
+        ctx->launches += 2;
+
+        buildRowsKernel<<<grid, 256, 0, s>>>(b->n_clusters, b->n_reads, b->d_read_offset, b->d_path_offset, b->d_row_ptr, b->d_col, b->d_prob,
+                                             b->d_noise, b->d_count, b->d_perm, b->d_sorted_row_ptr, b->d_sorted_col, b->d_sorted_noise,
+                                             b->d_val, b->d_cnt, b->d_entry_row, b->d_key_in, b->d_idx_in, b->d_error);
+        RPVG_LAUNCHED(ctx);
+
+    } else {
+
+        RPVG_CUDA(ctx, cudaMemsetAsync(b->d_sorted_row_ptr, 0, sizeof(uint64_t), s));
     }
 
     if (b->nnz > 0) {
@@ -674,10 +771,10 @@ int rpvg_b200_batch_em(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const rpvg_b200
     args.order = b->d_order;
     args.read_offset = b->d_read_offset;
     args.path_offset = b->d_path_offset;
-    args.row_ptr = b->d_row_ptr;
-    args.col = b->d_col;
+    args.row_ptr = b->d_sorted_row_ptr;
+    args.col = b->d_sorted_col;
     args.val = b->d_val;
-    args.noise = b->d_noise;
+    args.noise = b->d_sorted_noise;
     args.cnt = b->d_cnt;
     args.col_ptr = b->d_col_ptr;
     args.csc_row = b->d_csc_row;

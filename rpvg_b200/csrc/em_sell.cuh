@@ -20,6 +20,8 @@
 // Everything is deterministic: fixed slices, stable sorts, fixed summation trees, no atomics.
 #pragma once
 
+#include <type_traits>
+
 #include <cooperative_groups.h>
 
 #include "common.cuh"
@@ -85,7 +87,8 @@ __host__ __device__ inline uint64_t sellSmemBytes(uint64_t m, uint64_t z, uint64
     const uint64_t chunks = worst ? 16 * (m + N + 130) : 16 * ((m + N) / 8 + 140);
     const uint64_t col_id = sellRound16(index_bytes * (N + 1));
     const uint64_t slots = worst ? sellSlotsWorst(z, m) + sellSlotsWorst(z, N) : sellSlotsTypical(z, m) + sellSlotsTypical(z, N);
-    return fixed + vectors + chunks + col_id + (8 + index_bytes) * slots + 256;
+    const uint64_t masks = multi ? sellRound16(2 * (N + 2)) : 0;
+    return fixed + vectors + chunks + col_id + masks + (8 + index_bytes) * slots + 256;
 }
 
 // Global scratch one CTA owns: prologue temporaries, everything that may spill out of shared memory and, when
@@ -97,7 +100,8 @@ __host__ __device__ inline uint64_t sellScratchBytes(uint64_t m, uint64_t z, uin
     const uint64_t chunks = 16 * (m + N + 130);
     const uint64_t col_id = sellRound16(index_bytes * (N + 1));
     const uint64_t entries = with_entries ? (8 + index_bytes) * (sellSlotsWorst(z, m) + sellSlotsWorst(z, N)) + 128 : 64;
-    return ((temps + vectors + chunks + col_id + entries + 1023) / 1024) * 1024;
+    const uint64_t masks = sellRound16(2 * (N + 2));
+    return ((temps + vectors + chunks + col_id + masks + entries + 1023) / 1024) * 1024;
 }
 
 template <int THREADS>
@@ -339,6 +343,232 @@ struct SellSide {
     const IndexT * idx_g;
 };
 
+template <typename IndexT>
+struct SellLoop {
+
+    double * a;
+    double * g;
+    double * w;
+    const double * noise;
+    const double * cnt;
+    const IndexT * col_id;
+    const uint16_t * owned_mask;
+    SellSide<IndexT> rows;
+    SellSide<IndexT> cols;
+};
+
+// 1 / x to within an ulp or two: hardware seed (20 bits) and two Newton steps. The E-step divides once per read class;
+// an IEEE division would be a dependent chain four times as long on the critical path of every iteration.
+__device__ __forceinline__ double sellReciprocal(double x) {
+
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    double e = fma(-x, r, 1.0);
+    r = fma(r, e, r);
+    e = fma(-x, r, 1.0);
+    r = fma(r, e, r);
+    return r;
+}
+
+// sum over the 1 << l2 adjacent lanes that share a row (column)
+__device__ __forceinline__ double sellLaneSum(double acc, uint32_t l2) {
+
+    if (l2 > 0) { acc += __shfl_xor_sync(0xffffffffu, acc, 1); }
+    if (l2 > 1) { acc += __shfl_xor_sync(0xffffffffu, acc, 2); }
+    if (l2 > 2) { acc += __shfl_xor_sync(0xffffffffu, acc, 4); }
+    if (l2 > 3) { acc += __shfl_xor_sync(0xffffffffu, acc, 8); }
+    if (l2 > 4) { acc += __shfl_xor_sync(0xffffffffu, acc, 16); }
+    return acc;
+}
+
+// chunk handled by `warp` in round q: rounds alternate direction so that the chunk widths (descending) even out
+__device__ __forceinline__ uint32_t sellChunkOfRound(uint32_t q, uint32_t warp, uint32_t num_warps) {
+
+    return q * num_warps + ((q & 1) ? (num_warps - 1 - warp) : warp);
+}
+
+// The EM iterations of one CTA (see the header comment of this file). Returns the number of iterations executed.
+template <int THREADS, bool MULTI, bool ALL_SHARED, typename IndexT>
+__device__ __forceinline__ uint32_t emSellIterate(const SellLoop<IndexT> & lp, const rpvg_b200_em_params & params, const uint32_t N, const uint32_t S, const uint32_t rank,
+                                                  const uint32_t jc0, const uint32_t jc1, const double total, double * red, uint32_t * conv_flags) {
+
+    cg::cluster_group cluster = cg::this_cluster();
+
+    const uint32_t tid = threadIdx.x;
+    const uint32_t lane = tid & 31;
+    const uint32_t warp = tid >> 5;
+    constexpr uint32_t num_warps = THREADS / 32;
+
+    double * a = lp.a;
+    double * g = lp.g;
+    double * w = lp.w;
+
+    const double conv = params.max_rel_em_conv;
+    const double min_abundance = params.min_em_abundance;
+    const double inv_total = 1.0 / total;
+
+    const uint32_t row_rounds = (lp.rows.n_chunks + num_warps - 1) / num_warps;
+    const uint32_t col_rounds = (lp.cols.n_chunks + num_warps - 1) / num_warps;
+
+    uint32_t conv_its = 0;
+    uint32_t it = 0;
+
+    while (it < params.max_em_its) {
+
+        // ---- E-step over the slice: w_i = count_i / sum_j p_ij a_j
+        const double a_noise = a[N];
+        double noise_acc = 0;
+
+        #pragma unroll 1
+        for (uint32_t q = 0; q < row_rounds; ++q) {
+
+            const uint32_t k = sellChunkOfRound(q, warp, num_warps);
+            if (k >= lp.rows.n_chunks) { continue; }
+
+            const SellChunk ch = lp.rows.chunks[k];
+            const uint32_t r = lane >> ch.l2;
+            const bool head = (lane & ((1u << ch.l2) - 1)) == 0 && r < ch.count;
+            const uint32_t p = ch.first + r;
+
+            double nz = 0, ct = 0;
+            if (head) {
+                nz = lp.noise[p];
+                ct = lp.cnt[p];
+            }
+
+            const bool res = ALL_SHARED || k < lp.rows.n_resident;
+            const double * val = (res ? lp.rows.val_s + ch.off : lp.rows.val_g + (ch.off - lp.rows.resident_slots)) + lane;
+            const IndexT * idx = (res ? lp.rows.idx_s + ch.off : lp.rows.idx_g + (ch.off - lp.rows.resident_slots)) + lane;
+
+            double acc = 0;
+            #pragma unroll 4
+            for (uint32_t t = 0; t < ch.width; ++t) { acc = fma(val[t * 32], a[idx[t * 32]], acc); }
+
+            acc = sellLaneSum(acc, ch.l2);
+
+            if (head) {
+                const double wv = ct * sellReciprocal(fma(nz, a_noise, acc));
+                w[p] = wv;
+                noise_acc = fma(nz, wv, noise_acc);
+            }
+        }
+
+        // noise column: per-warp partials now, combined in a fixed order after the barrier
+        noise_acc = warpSum(noise_acc);
+        if (lane == 0) { red[warp] = noise_acc; }
+        if (MULTI && tid < S) { conv_flags[tid] = 1; }
+
+        __syncthreads();
+
+        // ---- M-step over the slice: column sums (and, with one CTA, the abundance update itself)
+        bool ok = true;
+
+        #pragma unroll 1
+        for (uint32_t q = 0; q < col_rounds; ++q) {
+
+            const uint32_t k = sellChunkOfRound(q, warp, num_warps);
+            if (k >= lp.cols.n_chunks) { continue; }
+
+            const SellChunk ch = lp.cols.chunks[k];
+            const uint32_t r = lane >> ch.l2;
+            const bool head = (lane & ((1u << ch.l2) - 1)) == 0 && r < ch.count;
+
+            uint32_t j = 0;
+            double a_old = 0;
+            if (head) {
+                j = lp.col_id[ch.first + r];
+                if (!MULTI) { a_old = a[j]; }
+            }
+
+            const bool res = ALL_SHARED || k < lp.cols.n_resident;
+            const double * val = (res ? lp.cols.val_s + ch.off : lp.cols.val_g + (ch.off - lp.cols.resident_slots)) + lane;
+            const IndexT * idx = (res ? lp.cols.idx_s + ch.off : lp.cols.idx_g + (ch.off - lp.cols.resident_slots)) + lane;
+
+            double acc = 0;
+            #pragma unroll 4
+            for (uint32_t t = 0; t < ch.width; ++t) { acc = fma(val[t * 32], w[idx[t * 32]], acc); }
+
+            acc = sellLaneSum(acc, ch.l2);
+
+            if (head) {
+                if (MULTI) {
+                    g[j] = acc;
+                } else {
+                    const double a_new = (a_old * acc) * inv_total;
+                    a[j] = a_new;
+                    if (a_new >= min_abundance && fabs(a_new - a_old) > conv * a_new) { ok = false; }
+                }
+            }
+        }
+
+        if (tid == THREADS - 1) {
+
+            double noise_g = 0;
+            #pragma unroll
+            for (uint32_t wi = 0; wi < num_warps; ++wi) { noise_g += red[wi]; }
+
+            if (MULTI) {
+                g[N] = noise_g;
+            } else {
+                const double a_new = (a_noise * noise_g) * inv_total;
+                a[N] = a_new;
+                if (a_new >= min_abundance && fabs(a_new - a_noise) > conv * a_new) { ok = false; }
+            }
+        }
+
+        ++it;
+
+        if constexpr (!MULTI) {
+
+            if (__syncthreads_and(ok)) {
+                if (++conv_its == params.min_em_conv_its) { break; }
+            } else {
+                conv_its = 0;
+            }
+
+        } else {
+
+            cluster.sync();
+
+            // reduce-scatter + all-gather over the group, restricted to the CTAs that hold the column: this CTA owns
+            // columns [jc0, jc1); partial sums are added in ascending CTA order
+            for (uint32_t j = jc0 + tid; j < jc1; j += THREADS) {
+
+                const uint32_t mask = lp.owned_mask[j - jc0];
+
+                double sum = 0;
+                for (uint32_t mm = mask; mm; mm &= mm - 1) { sum += *(cluster.map_shared_rank(g, __ffs(mm) - 1) + j); }
+
+                const double a_old = a[j];
+                const double a_new = (a_old * sum) * inv_total;
+                if (a_new >= min_abundance && fabs(a_new - a_old) > conv * a_new) { ok = false; }
+
+                a[j] = a_new;
+                for (uint32_t mm = mask & ~(1u << rank); mm; mm &= mm - 1) { *(cluster.map_shared_rank(a, __ffs(mm) - 1) + j) = a_new; }
+            }
+
+            // convergence vote: flags were set to 1 before the block barrier above; a failing warp clears this CTA's
+            // flag in every CTA of the group
+            if (__any_sync(0xffffffffu, !ok) && lane == 0) {
+                for (uint32_t s = 0; s < S; ++s) { *(cluster.map_shared_rank(conv_flags, s) + rank) = 0; }
+            }
+
+            cluster.sync();
+
+            bool all_ok = true;
+            for (uint32_t s = 0; s < S; ++s) { all_ok = all_ok && (conv_flags[s] != 0); }
+
+            if (all_ok) {
+                if (++conv_its == params.min_em_conv_its) { break; }
+            } else {
+                conv_its = 0;
+            }
+        }
+    }
+
+    return it;
+}
+
 template <int THREADS, bool MULTI, typename IndexT>
 __global__ void __launch_bounds__(THREADS) emSellKernel(const SellArgs sa) {
 
@@ -346,6 +576,7 @@ __global__ void __launch_bounds__(THREADS) emSellKernel(const SellArgs sa) {
 
     __shared__ double red[32];
     __shared__ uint32_t conv_flags[kMaxGroupSize];
+    __shared__ double final_part[kMaxGroupSize];
     __shared__ uint32_t scan_tmp[THREADS / 32];
     __shared__ uint32_t shared_u32[4];
     __shared__ SellSort<THREADS> sort_state;
@@ -490,6 +721,34 @@ __global__ void __launch_bounds__(THREADS) emSellKernel(const SellArgs sa) {
 
     __syncthreads();
 
+    // ---- which CTAs of the group hold entries of each column this CTA owns: only those take part in the column's
+    // reduction and need its abundance. With read classes ordered by their first path (em.cu) a slice touches a band of
+    // columns, so most masks have one or two bits.
+    uint16_t * owned_mask = nullptr;
+
+    if (MULTI) {
+
+        owned_mask = static_cast<uint16_t *>(arena.take(2ull * (jc1 - jc0 + 1), true, nullptr));
+
+        unsigned char * present = reinterpret_cast<unsigned char *>(g);   // g is not in use yet
+        for (uint32_t j = tid; j < N; j += THREADS) { present[j] = clen[j] > 0; }
+
+        cluster.sync();
+
+        for (uint32_t j = jc0 + tid; j < jc1; j += THREADS) {
+
+            uint32_t mask = 0;
+            if (j == N) {
+                mask = (1u << S) - 1;   // the noise column concerns everyone
+            } else {
+                for (uint32_t s = 0; s < S; ++s) { mask |= static_cast<uint32_t>(*(reinterpret_cast<unsigned char *>(cluster.map_shared_rank(g, s)) + j)) << s; }
+            }
+            owned_mask[j - jc0] = static_cast<uint16_t>(mask);
+        }
+
+        cluster.sync();   // g may be overwritten from here on
+    }
+
     auto col_len = [&](uint32_t j) { return clen[j]; };
     sellStableSort<THREADS>(sort_state, N, col_len, col_pos, col_src);
 
@@ -611,171 +870,96 @@ __global__ void __launch_bounds__(THREADS) emSellKernel(const SellArgs sa) {
 
     if (MULTI) { cluster.sync(); } else { __syncthreads(); }
 
-    const double conv = args.params.max_rel_em_conv;
-    const double min_abundance = args.params.min_em_abundance;
-    const double inv_total = 1.0 / total;
+    // ---- EM iterations. When everything this CTA touches sits in shared memory the loop runs on pointers the compiler
+    // can prove to be shared (plain LDS/STS); otherwise on generic pointers (hybrid residency).
+    SellLoop<IndexT> loop;
+    loop.a = a;
+    loop.g = g;
+    loop.w = w;
+    loop.noise = noise;
+    loop.cnt = cnt;
+    loop.col_id = col_id;
+    loop.owned_mask = owned_mask;
+    loop.rows = rows;
+    loop.cols = cols;
 
-    uint32_t conv_its = 0;
-    uint32_t it = 0;
+    const unsigned char * smem_end = smem_raw + sa.smem_bytes;
+    auto in_shared = [&](const void * ptr) {
+        const unsigned char * q = static_cast<const unsigned char *>(ptr);
+        return ptr == nullptr || (q >= smem_raw && q < smem_end);
+    };
 
-    while (it < args.params.max_em_its) {
+    const bool all_shared = in_shared(a) && in_shared(g) && in_shared(w) && in_shared(noise) && in_shared(cnt) && in_shared(col_id) && in_shared(owned_mask) &&
+                            in_shared(rows.chunks) && in_shared(cols.chunks) && rows.n_resident == rows.n_chunks && cols.n_resident == cols.n_chunks;
 
-        // ---- E-step over the slice: w_i = count_i / sum_j p_ij a_j
-        const double a_noise = a[N];
-        double noise_acc = 0;
+    const double total_count = total;
+    uint32_t it;
 
-        for (uint32_t k = warp; k < rows.n_chunks; k += num_warps) {
+    if (all_shared) {
 
-            const SellChunk ch = rows.chunks[k];
-            const bool res = k < rows.n_resident;
-            const double * val = (res ? rows.val_s + ch.off : rows.val_g + (ch.off - rows.resident_slots)) + lane;
-            const IndexT * idx = (res ? rows.idx_s + ch.off : rows.idx_g + (ch.off - rows.resident_slots)) + lane;
+        auto rebase = [&](auto * ptr) {
+            using T = std::remove_pointer_t<decltype(ptr)>;
+            if (ptr == nullptr) { return static_cast<T *>(nullptr); }
+            const uint32_t off = static_cast<uint32_t>(reinterpret_cast<const unsigned char *>(ptr) - smem_raw);
+            return reinterpret_cast<T *>(smem_raw + off);
+        };
 
-            double acc = 0;
-            #pragma unroll 4
-            for (uint32_t t = 0; t < ch.width; ++t) { acc += val[t * 32] * a[idx[t * 32]]; }
+        SellLoop<IndexT> fast = loop;
+        fast.a = rebase(loop.a);
+        fast.g = rebase(loop.g);
+        fast.w = rebase(loop.w);
+        fast.noise = rebase(loop.noise);
+        fast.cnt = rebase(loop.cnt);
+        fast.col_id = rebase(loop.col_id);
+        fast.owned_mask = rebase(loop.owned_mask);
+        fast.rows.chunks = rebase(loop.rows.chunks);
+        fast.rows.val_s = rebase(loop.rows.val_s);
+        fast.rows.idx_s = rebase(loop.rows.idx_s);
+        fast.cols.chunks = rebase(loop.cols.chunks);
+        fast.cols.val_s = rebase(loop.cols.val_s);
+        fast.cols.idx_s = rebase(loop.cols.idx_s);
 
-            for (uint32_t off = (1u << ch.l2) >> 1; off > 0; off >>= 1) { acc += __shfl_xor_sync(0xffffffffu, acc, off); }
+        it = emSellIterate<THREADS, MULTI, true, IndexT>(fast, args.params, N, S, rank, jc0, jc1, total_count, red, conv_flags);
 
-            const uint32_t r = lane >> ch.l2;
-            if ((lane & ((1u << ch.l2) - 1)) == 0 && r < ch.count) {
-                const uint32_t p = ch.first + r;
-                const double nz = noise[p];
-                const double wv = cnt[p] / (acc + nz * a_noise);
-                w[p] = wv;
-                noise_acc += nz * wv;
-            }
-        }
+    } else {
 
-        // noise column: per-warp partials now, combined in a fixed order after the barrier
-        noise_acc = warpSum(noise_acc);
-        if (lane == 0) { red[warp] = noise_acc; }
-        if (MULTI && tid < S) { conv_flags[tid] = 1; }
-
-        __syncthreads();
-
-        // ---- M-step over the slice: column sums (and, with one CTA, the abundance update itself)
-        bool ok = true;
-
-        for (uint32_t k = warp; k < cols.n_chunks; k += num_warps) {
-
-            const SellChunk ch = cols.chunks[k];
-            const bool res = k < cols.n_resident;
-            const double * val = (res ? cols.val_s + ch.off : cols.val_g + (ch.off - cols.resident_slots)) + lane;
-            const IndexT * idx = (res ? cols.idx_s + ch.off : cols.idx_g + (ch.off - cols.resident_slots)) + lane;
-
-            double acc = 0;
-            #pragma unroll 4
-            for (uint32_t t = 0; t < ch.width; ++t) { acc += val[t * 32] * w[idx[t * 32]]; }
-
-            for (uint32_t off = (1u << ch.l2) >> 1; off > 0; off >>= 1) { acc += __shfl_xor_sync(0xffffffffu, acc, off); }
-
-            const uint32_t r = lane >> ch.l2;
-            if ((lane & ((1u << ch.l2) - 1)) == 0 && r < ch.count) {
-
-                const uint32_t j = col_id[ch.first + r];
-
-                if (MULTI) {
-                    g[j] = acc;
-                } else {
-                    const double a_old = a[j];
-                    const double a_new = (a_old * acc) * inv_total;
-                    a[j] = a_new;
-                    if (a_new >= min_abundance && fabs(a_new - a_old) > conv * a_new) { ok = false; }
-                }
-            }
-        }
-
-        if (tid == THREADS - 1) {
-
-            double noise_g = 0;
-            #pragma unroll
-            for (uint32_t wi = 0; wi < num_warps; ++wi) { noise_g += red[wi]; }
-
-            if (MULTI) {
-                g[N] = noise_g;
-            } else {
-                const double a_new = (a_noise * noise_g) * inv_total;
-                a[N] = a_new;
-                if (a_new >= min_abundance && fabs(a_new - a_noise) > conv * a_new) { ok = false; }
-            }
-        }
-
-        ++it;
-
-        if constexpr (!MULTI) {
-
-            if (__syncthreads_and(ok)) {
-                if (++conv_its == args.params.min_em_conv_its) { break; }
-            } else {
-                conv_its = 0;
-            }
-
-        } else {
-
-            cluster.sync();
-
-            // reduce-scatter + all-gather over the group: this CTA owns columns [jc0, jc1)
-            for (uint32_t j = jc0 + tid; j < jc1; j += THREADS) {
-
-                double part[kMaxGroupSize];
-                #pragma unroll
-                for (uint32_t s = 0; s < kMaxGroupSize; ++s) { part[s] = (s < S) ? *(cluster.map_shared_rank(g, s) + j) : 0.0; }
-
-                double sum = 0;
-                #pragma unroll
-                for (uint32_t s = 0; s < kMaxGroupSize; ++s) { sum += part[s]; }
-
-                const double a_old = a[j];
-                const double a_new = (a_old * sum) * inv_total;
-                if (a_new >= min_abundance && fabs(a_new - a_old) > conv * a_new) { ok = false; }
-
-                #pragma unroll
-                for (uint32_t s = 0; s < kMaxGroupSize; ++s) {
-                    if (s < S) { *(cluster.map_shared_rank(a, s) + j) = a_new; }
-                }
-            }
-
-            // convergence vote: flags were set to 1 before the block barrier above; a failing warp clears this CTA's
-            // flag in every CTA of the group
-            if (__any_sync(0xffffffffu, !ok) && lane == 0) {
-                for (uint32_t s = 0; s < S; ++s) { *(cluster.map_shared_rank(conv_flags, s) + rank) = 0; }
-            }
-
-            cluster.sync();
-
-            bool all_ok = true;
-            for (uint32_t s = 0; s < S; ++s) { all_ok = all_ok && (conv_flags[s] != 0); }
-
-            if (all_ok) {
-                if (++conv_its == args.params.min_em_conv_its) { break; }
-            } else {
-                conv_its = 0;
-            }
-        }
+        it = emSellIterate<THREADS, MULTI, false, IndexT>(loop, args.params, N, S, rank, jc0, jc1, total_count, red, conv_flags);
     }
 
-    // rpvg:src/path_abundance_estimator.cpp:100-113; every CTA holds the full abundance vector
+    const double min_abundance = args.params.min_em_abundance;
+
+
+    // rpvg:src/path_abundance_estimator.cpp:100-113; every CTA finalises the columns it owns
+    double noise_part = 0;
     for (uint32_t j = jc0 + tid; j < min(jc1, N); j += THREADS) {
         const double aj = a[j];
-        args.abundances[p0 + j] = (aj < min_abundance) ? 0 : aj * total;
+        if (aj < min_abundance) {
+            noise_part += aj * total;
+            args.abundances[p0 + j] = 0;
+        } else {
+            args.abundances[p0 + j] = aj * total;
+        }
     }
 
-    if (rank == 0) {
+    const double low_sum = blockSum(noise_part, red);
 
-        double noise_part = 0;
-        for (uint32_t j = tid; j < N; j += THREADS) {
-            const double aj = a[j];
-            if (aj < min_abundance) { noise_part += aj * total; }
+    if (MULTI) {
+        if (tid == 0) { *(cluster.map_shared_rank(final_part, 0) + rank) = low_sum; }
+        cluster.sync();
+    }
+
+    if (rank == 0 && tid == 0) {
+
+        double low_total = low_sum;
+        if (MULTI) {
+            low_total = 0;
+            for (uint32_t s = 0; s < S; ++s) { low_total += final_part[s]; }
         }
 
-        const double low_sum = blockSum(noise_part, red);
-
-        if (tid == 0) {
-            args.noise_count[c] = low_sum + a[N] * total;
-            args.total_count[c] = total;
-            args.iterations[c] = it;
-        }
+        // the noise column is owned by the last CTA of the group; every CTA holds its value
+        args.noise_count[c] = low_total + a[N] * total;
+        args.total_count[c] = total;
+        args.iterations[c] = it;
     }
 
     // no CTA may exit while a peer can still touch its shared memory
