@@ -13,7 +13,7 @@ import numpy as np
 
 from .arena import ClusterArena
 
-_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "librpvg_b200.so")
+_LIB_PATH = os.environ.get("RPVG_B200_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "librpvg_b200.so")
 _lib = None
 
 

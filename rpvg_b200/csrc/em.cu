@@ -269,7 +269,7 @@ uint32_t envKnob(const char * name, uint32_t fallback) {
 constexpr uint32_t kSmemTiers[] = {8 * 1024, 24 * 1024, 56 * 1024, 108 * 1024, 216 * 1024};
 constexpr uint32_t kTierThreads[] = {64, 128, 256, 512, 512};
 constexpr int kNumTiers = 5;
-constexpr uint32_t kStaticSmemReserve = 8 * 1024;   // static shared memory of emSellKernel<512> + slack
+constexpr uint32_t kStaticSmemReserve = 12 * 1024;   // static shared memory of emSellKernel<512> + slack
 
 struct GroupPlan {
 
@@ -285,7 +285,8 @@ void planEmLaunches(const rpvg_b200_ctx * ctx, rpvg_b200_batch * b, std::vector<
                     std::vector<uint64_t> * group_cta_bytes) {
 
     // weight (entries + rows) one CTA should own; above it a cluster is split over 2, 4, 8, 16 CTAs
-    const uint32_t slice_weight = std::max(64u, envKnob("RPVG_B200_EM_SLICE_WEIGHT", 6000));
+    const uint32_t slice_weight = std::max(64u, envKnob("RPVG_B200_EM_SLICE_WEIGHT", 8000));
+    const uint32_t big_threads = envKnob("RPVG_B200_EM_BIG_THREADS", 512);
     const uint32_t max_group = std::min(ctx->max_group_size, std::max(1u, envKnob("RPVG_B200_EM_MAX_GROUP", kMaxGroupSize)));
     const uint32_t smem_cap = std::min<uint32_t>(kSmemTiers[kNumTiers - 1], static_cast<uint32_t>(ctx->max_smem_optin) - kStaticSmemReserve);
 
@@ -389,7 +390,8 @@ void planEmLaunches(const rpvg_b200_ctx * ctx, rpvg_b200_batch * b, std::vector<
                 bin.smem = std::min(kSmemTiers[tier], smem_cap);
                 bin.threads = kTierThreads[tier];
 
-                // instantiations that exist: one CTA {64,128,256,512} x u16; groups {256,512} x u16; 512 x u32
+                // instantiations that exist: one CTA {64,128,256,512,1024} x u16; groups {256,512,1024} x u16; 512 x u32
+                if (tier == kNumTiers - 1) { bin.threads = (big_threads == 1024) ? 1024 : 512; }
                 if (bin.index_bytes == 4) { bin.threads = 512; }
                 if (bin.group_size > 1) { bin.threads = std::max(bin.threads, 256u); }
             }
@@ -436,14 +438,16 @@ cudaError_t launchSellBin(const SellArgs & sa, const rpvg_b200_batch::EmBin & bi
     }
 
     if (multi) {
-        return bin.threads == 256 ? launchSell<256, true, uint16_t>(sa, bin.group_size, bin.count, stream)
-                                  : launchSell<512, true, uint16_t>(sa, bin.group_size, bin.count, stream);
+        if (bin.threads == 256) { return launchSell<256, true, uint16_t>(sa, bin.group_size, bin.count, stream); }
+        if (bin.threads == 1024) { return launchSell<1024, true, uint16_t>(sa, bin.group_size, bin.count, stream); }
+        return launchSell<512, true, uint16_t>(sa, bin.group_size, bin.count, stream);
     }
 
     switch (bin.threads) {
         case 64: return launchSell<64, false, uint16_t>(sa, 1, bin.count, stream);
         case 128: return launchSell<128, false, uint16_t>(sa, 1, bin.count, stream);
         case 256: return launchSell<256, false, uint16_t>(sa, 1, bin.count, stream);
+        case 1024: return launchSell<1024, false, uint16_t>(sa, 1, bin.count, stream);
         default: return launchSell<512, false, uint16_t>(sa, 1, bin.count, stream);
     }
 }
@@ -533,6 +537,8 @@ int rpvgEmInit(rpvg_b200_ctx * ctx) {
     RPVG_CUDA(ctx, (configureSell<256, true, uint16_t>(ctx, &max_group)));
     RPVG_CUDA(ctx, (configureSell<512, true, uint16_t>(ctx, &max_group)));
     RPVG_CUDA(ctx, (configureSell<512, true, uint32_t>(ctx, &max_group)));
+    RPVG_CUDA(ctx, (configureSell<1024, false, uint16_t>(ctx, &unused)));
+    RPVG_CUDA(ctx, (configureSell<1024, true, uint16_t>(ctx, &max_group)));
 
     ctx->max_group_size = max_group;
     return RPVG_B200_OK;

@@ -64,10 +64,10 @@ __host__ __device__ __forceinline__ uint32_t sellBucketUpper(uint32_t bucket) {
     return bucket <= 32 ? bucket : (1u << (bucket - 32 + 5));
 }
 
-// log2 of the lanes a row of (at most) this length gets: about 8 entries per lane, 1..32 lanes.
-__host__ __device__ __forceinline__ uint32_t sellLanesLog2(uint32_t len_upper) {
+// log2 of the lanes a row of (at most) this length gets: about `depth` entries per lane, 1..32 lanes.
+__host__ __device__ __forceinline__ uint32_t sellLanesLog2(uint32_t len_upper, uint32_t depth) {
 
-    const uint32_t want = (len_upper + 7) / 8;
+    const uint32_t want = (len_upper + depth - 1) / depth;
     uint32_t l2 = 0;
     while (l2 < 5 && (1u << l2) < want) { l2++; }
     return l2;
@@ -186,8 +186,16 @@ __device__ void sellStableSort(SellSort<THREADS> & st, const uint32_t n, LenFn l
 }
 
 // Number of chunks sellMakeChunks will form for the items just sorted (same walk, nothing written).
+// Entries per lane a side with z entries aims for: chunks cost ~100 instructions on top of ~6 per step, so they should
+// be as deep as the warp count allows (about two rounds of chunks per warp), but at least 8 and at most 64 steps.
+__host__ __device__ __forceinline__ uint32_t sellDepth(uint32_t z, uint32_t num_warps) {
+
+    const uint32_t d = (2 * z) / (32 * num_warps);
+    return d < 8 ? 8 : (d > 64 ? 64 : d);
+}
+
 template <int THREADS>
-__device__ uint32_t sellCountChunks(SellSort<THREADS> & st, const uint32_t n) {
+__device__ uint32_t sellCountChunks(SellSort<THREADS> & st, const uint32_t n, const uint32_t depth) {
 
     if (threadIdx.x == 0) {
 
@@ -197,7 +205,7 @@ __device__ uint32_t sellCountChunks(SellSort<THREADS> & st, const uint32_t n) {
 
         while (p < n) {
             while (st.bucket_start[b] + st.bucket_total[b] <= p) { --b; }
-            p += min(32u >> sellLanesLog2(sellBucketUpper(b)), n - p);
+            p += min(32u >> sellLanesLog2(sellBucketUpper(b), depth), n - p);
             ++k;
         }
 
@@ -211,7 +219,7 @@ __device__ uint32_t sellCountChunks(SellSort<THREADS> & st, const uint32_t n) {
 // Chunk descriptors for items already sorted by descending bucket: a chunk takes the next 32 >> l2 items, l2 from the
 // bucket of its first (longest) item. Returns the number of chunks; total_slots receives the number of entry slots.
 template <int THREADS, typename LenFn>
-__device__ uint32_t sellMakeChunks(SellSort<THREADS> & st, const uint32_t n, LenFn len, const uint32_t * src, SellChunk * chunks, uint32_t * scan_tmp, uint32_t * total_slots) {
+__device__ uint32_t sellMakeChunks(SellSort<THREADS> & st, const uint32_t n, const uint32_t depth, LenFn len, const uint32_t * src, SellChunk * chunks, uint32_t * scan_tmp, uint32_t * total_slots) {
 
     const uint32_t tid = threadIdx.x;
     const uint32_t lane = tid & 31;
@@ -227,7 +235,7 @@ __device__ uint32_t sellMakeChunks(SellSort<THREADS> & st, const uint32_t n, Len
 
             while (st.bucket_start[b] + st.bucket_total[b] <= p) { --b; }
 
-            const uint32_t l2 = sellLanesLog2(sellBucketUpper(b));
+            const uint32_t l2 = sellLanesLog2(sellBucketUpper(b), depth);
             const uint32_t count = min(32u >> l2, n - p);
 
             SellChunk ch;
@@ -387,6 +395,14 @@ __device__ __forceinline__ uint32_t sellChunkOfRound(uint32_t q, uint32_t warp, 
     return q * num_warps + ((q & 1) ? (num_warps - 1 - warp) : warp);
 }
 
+#ifdef RPVG_B200_EM_TRACE
+#define SELL_TRACE_DECL long long trace_t = clock64(); long long trace_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#define SELL_TRACE(k) { const long long trace_now = clock64(); trace_acc[k] += trace_now - trace_t; trace_t = trace_now; }
+#else
+#define SELL_TRACE_DECL
+#define SELL_TRACE(k)
+#endif
+
 // The EM iterations of one CTA (see the header comment of this file). Returns the number of iterations executed.
 template <int THREADS, bool MULTI, bool ALL_SHARED, typename IndexT>
 __device__ __forceinline__ uint32_t emSellIterate(const SellLoop<IndexT> & lp, const rpvg_b200_em_params & params, const uint32_t N, const uint32_t S, const uint32_t rank,
@@ -412,6 +428,8 @@ __device__ __forceinline__ uint32_t emSellIterate(const SellLoop<IndexT> & lp, c
 
     uint32_t conv_its = 0;
     uint32_t it = 0;
+
+    SELL_TRACE_DECL
 
     while (it < params.max_em_its) {
 
@@ -453,12 +471,16 @@ __device__ __forceinline__ uint32_t emSellIterate(const SellLoop<IndexT> & lp, c
             }
         }
 
+        SELL_TRACE(0)
+
         // noise column: per-warp partials now, combined in a fixed order after the barrier
         noise_acc = warpSum(noise_acc);
         if (lane == 0) { red[warp] = noise_acc; }
         if (MULTI && tid < S) { conv_flags[tid] = 1; }
 
         __syncthreads();
+
+        SELL_TRACE(1)
 
         // ---- M-step over the slice: column sums (and, with one CTA, the abundance update itself)
         bool ok = true;
@@ -518,9 +540,14 @@ __device__ __forceinline__ uint32_t emSellIterate(const SellLoop<IndexT> & lp, c
 
         ++it;
 
+        SELL_TRACE(2)
+
         if constexpr (!MULTI) {
 
-            if (__syncthreads_and(ok)) {
+            const int block_ok = __syncthreads_and(ok);
+            SELL_TRACE(3)
+
+            if (block_ok) {
                 if (++conv_its == params.min_em_conv_its) { break; }
             } else {
                 conv_its = 0;
@@ -530,14 +557,30 @@ __device__ __forceinline__ uint32_t emSellIterate(const SellLoop<IndexT> & lp, c
 
             cluster.sync();
 
+            SELL_TRACE(3)
+
             // reduce-scatter + all-gather over the group, restricted to the CTAs that hold the column: this CTA owns
-            // columns [jc0, jc1); partial sums are added in ascending CTA order
-            for (uint32_t j = jc0 + tid; j < jc1; j += THREADS) {
+            // columns [jc0, jc1); partial sums are added in ascending CTA order. The noise column (owned by the last
+            // CTA, held by everyone) is reduced by one warp, a lane per CTA, so that its S remote loads overlap.
+            const uint32_t jc1_paths = min(jc1, N);
+
+            for (uint32_t j = jc0 + tid; j < jc1_paths; j += THREADS) {
 
                 const uint32_t mask = lp.owned_mask[j - jc0];
-
                 double sum = 0;
-                for (uint32_t mm = mask; mm; mm &= mm - 1) { sum += *(cluster.map_shared_rank(g, __ffs(mm) - 1) + j); }
+
+                if (__popc(mask) <= 2) {
+
+                    for (uint32_t mm = mask; mm; mm &= mm - 1) { sum += *(cluster.map_shared_rank(g, __ffs(mm) - 1) + j); }
+
+                } else {
+
+                    double part[kMaxGroupSize];
+                    #pragma unroll
+                    for (uint32_t s = 0; s < kMaxGroupSize; ++s) { part[s] = ((mask >> s) & 1u) ? *(cluster.map_shared_rank(g, s) + j) : 0.0; }
+                    #pragma unroll
+                    for (uint32_t s = 0; s < kMaxGroupSize; ++s) { sum += part[s]; }
+                }
 
                 const double a_old = a[j];
                 const double a_new = (a_old * sum) * inv_total;
@@ -547,13 +590,27 @@ __device__ __forceinline__ uint32_t emSellIterate(const SellLoop<IndexT> & lp, c
                 for (uint32_t mm = mask & ~(1u << rank); mm; mm &= mm - 1) { *(cluster.map_shared_rank(a, __ffs(mm) - 1) + j) = a_new; }
             }
 
-            // convergence vote: flags were set to 1 before the block barrier above; a failing warp clears this CTA's
-            // flag in every CTA of the group
-            if (__any_sync(0xffffffffu, !ok) && lane == 0) {
-                for (uint32_t s = 0; s < S; ++s) { *(cluster.map_shared_rank(conv_flags, s) + rank) = 0; }
+            if (jc1 == N + 1 && warp == num_warps - 1) {
+
+                double part = (lane < S) ? *(cluster.map_shared_rank(g, lane) + N) : 0.0;
+                part = warpSum(part);
+
+                const double a_new = (a_noise * part) * inv_total;
+                if (a_new >= min_abundance && fabs(a_new - a_noise) > conv * a_new) { ok = false; }
+
+                if (lane < S) { *(cluster.map_shared_rank(a, lane) + N) = a_new; }
             }
 
+            // convergence vote: flags were set to 1 before the block barrier above; a CTA in which any column failed
+            // clears its flag in every CTA of the group
+            SELL_TRACE(4)
+
+            const int cta_failed = __syncthreads_or(!ok);
+            if (cta_failed && tid < S) { *(cluster.map_shared_rank(conv_flags, tid) + rank) = 0; }
+
             cluster.sync();
+
+            SELL_TRACE(5)
 
             bool all_ok = true;
             for (uint32_t s = 0; s < S; ++s) { all_ok = all_ok && (conv_flags[s] != 0); }
@@ -565,6 +622,13 @@ __device__ __forceinline__ uint32_t emSellIterate(const SellLoop<IndexT> & lp, c
             }
         }
     }
+
+#ifdef RPVG_B200_EM_TRACE
+    if (lane == 0 && (warp == 0 || warp == num_warps - 1) && (rank == 0 || rank == S - 1) && it > 50) {
+        printf("[trace] rank %u/%u warp %u its %u N %u chunks %u/%u cycles/it: E %lld | bar %lld | M %lld | sync1 %lld | reduce %lld | sync2 %lld\n", rank, S, warp, it, N,
+               lp.rows.n_chunks, lp.cols.n_chunks, trace_acc[0] / it, trace_acc[1] / it, trace_acc[2] / it, trace_acc[3] / it, trace_acc[4] / it, trace_acc[5] / it);
+    }
+#endif
 
     return it;
 }
@@ -679,10 +743,13 @@ __global__ void __launch_bounds__(THREADS) emSellKernel(const SellArgs sa) {
     auto row_len = [&](uint32_t i) { return static_cast<uint32_t>(row_ptr[i0 + i + 1] - row_ptr[i0 + i]); };
     sellStableSort<THREADS>(sort_state, m, row_len, row_pos, row_src);
 
-    const uint32_t row_chunk_bound = sellCountChunks<THREADS>(sort_state, m);
+    const uint32_t z_slice = static_cast<uint32_t>(row_ptr[i0 + m] - e_slice);
+    const uint32_t depth = sellDepth(z_slice, num_warps);
+
+    const uint32_t row_chunk_bound = sellCountChunks<THREADS>(sort_state, m, depth);
 
     SellChunk * row_chunks = static_cast<SellChunk *>(arena.take(sizeof(SellChunk) * (row_chunk_bound + 1), true, nullptr));
-    const uint32_t n_row_chunks = sellMakeChunks<THREADS>(sort_state, m, row_len, row_src, row_chunks, scan_tmp, &shared_u32[0]);
+    const uint32_t n_row_chunks = sellMakeChunks<THREADS>(sort_state, m, depth, row_len, row_src, row_chunks, scan_tmp, &shared_u32[0]);
     const uint32_t row_slots = shared_u32[0];
 
     for (uint32_t p = tid; p < m; p += THREADS) {
@@ -752,15 +819,20 @@ __global__ void __launch_bounds__(THREADS) emSellKernel(const SellArgs sa) {
     auto col_len = [&](uint32_t j) { return clen[j]; };
     sellStableSort<THREADS>(sort_state, N, col_len, col_pos, col_src);
 
-    const uint32_t col_chunk_bound = sellCountChunks<THREADS>(sort_state, N);
+    // Only the columns with entries in this slice get chunks (empty ones sort last). A column that is empty in every
+    // slice has no read class behind it: its abundance is 0 from the first update on (a_j * 0 / total), which is what it
+    // is set to — with one CTA right away (nothing ever reads it), with several by the reduction (mask 0, sum 0).
+    const uint32_t n_cols_present = N - sort_state.bucket_total[0];
+
+    const uint32_t col_chunk_bound = sellCountChunks<THREADS>(sort_state, n_cols_present, depth);
 
     SellChunk * col_chunks = static_cast<SellChunk *>(arena.take(sizeof(SellChunk) * (col_chunk_bound + 1), true, nullptr));
-    const uint32_t n_col_chunks = sellMakeChunks<THREADS>(sort_state, N, col_len, col_src, col_chunks, scan_tmp, &shared_u32[1]);
+    const uint32_t n_col_chunks = sellMakeChunks<THREADS>(sort_state, n_cols_present, depth, col_len, col_src, col_chunks, scan_tmp, &shared_u32[1]);
     const uint32_t col_slots = shared_u32[1];
 
     // column ids in sorted order (kept for the whole kernel)
-    IndexT * col_id = static_cast<IndexT *>(arena.take(sizeof(IndexT) * (N + 1), true, nullptr));
-    for (uint32_t p = tid; p < N; p += THREADS) { col_id[p] = static_cast<IndexT>(col_src[p]); }
+    IndexT * col_id = static_cast<IndexT *>(arena.take(sizeof(IndexT) * (n_cols_present + 1), true, nullptr));
+    for (uint32_t p = tid; p < n_cols_present; p += THREADS) { col_id[p] = static_cast<IndexT>(col_src[p]); }
 
     // ---- entry arrays: column side first (it also carries the update), then row side; whole chunks only
     auto place = [&](const SellChunk * chunks, uint32_t n_chunks, uint32_t slots, SellSide<IndexT> * side) {
@@ -866,7 +938,7 @@ __global__ void __launch_bounds__(THREADS) emSellKernel(const SellArgs sa) {
 
     // rpvg:src/path_abundance_estimator.cpp:54 — single-precision quotient widened to double
     const double a_init = static_cast<double>(1 / static_cast<float>(N + 1));
-    for (uint32_t j = tid; j <= N; j += THREADS) { a[j] = a_init; }
+    for (uint32_t j = tid; j <= N; j += THREADS) { a[j] = (MULTI || j == N || clen[j] > 0) ? a_init : 0.0; }
 
     if (MULTI) { cluster.sync(); } else { __syncthreads(); }
 

@@ -26,9 +26,12 @@ for t in targets:
         batch = ctx.upload(sub)
         batch.em()
         batch.em()
-        ab = np.empty(sub.n_paths); nz = np.empty(1); tc = np.empty(1); its = np.empty(1, dtype=np.uint32)
+        ab = np.empty(sub.n_paths); nz = np.empty(1); tc = np.empty(1); its = np.empty(1, dtype=np.uint32); its1 = np.empty(1, dtype=np.uint32)
         batch.download(ab, nz, tc, its)
         _, em_ms = batch.em_timings()
+        batch.em(capi.default_em_params(max_em_its=1))
+        batch.download(ab, nz, tc, its1)
+        _, pro_ms = batch.em_timings()
         batch.free()
-        line += f"  S={group}: {em_ms:.2f} ms / {int(its[0])} its = {1e3 * em_ms / max(1, int(its[0])):.2f} us"
+        line += f"  S={group}: {em_ms:.2f} ms (prologue {pro_ms:.2f}) / {int(its[0])} its = {1e3 * (em_ms - pro_ms) / max(1, int(its[0])):.2f} us"
     print(line, flush=True)
