@@ -297,7 +297,7 @@ def main():
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                         "ms_per_step": max_e2e_ms / args.steps},
                 "gpu_launches": int(launches),
-                "roofline": {"bound": "hbm", "kernel": "emClusterKernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "roofline": {"bound": "hbm", "kernel": "emSellKernel (all bins, concurrent streams)", "achieved": achieved, "peak": peak, "unit": "GB/s",
                              "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                              "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": em_ms_mean, "build_ms": float(np.mean(build_ms)),
                              "kernel_share_of_step": em_ms_mean / (max_ms / args.steps)},
