@@ -18,6 +18,7 @@
 #ifndef RPVG_B200_H
 #define RPVG_B200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -97,6 +98,27 @@ int rpvg_b200_batch_em_work(rpvg_b200_ctx * ctx, rpvg_b200_batch * batch, double
 /* Device time (CUDA events on the ctx stream) of the two phases of the last rpvg_b200_batch_em on this batch:
  * matrix build (normalise + column-major index) and the EM kernels. Blocks until that work has finished. */
 int rpvg_b200_batch_em_timings(rpvg_b200_ctx * ctx, rpvg_b200_batch * batch, float * build_ms, float * em_ms);
+
+/* ---- EM of one cluster for callers that must not allocate ----
+ * No counterpart in the reference (rpvg runs on the host and allocates freely); it exists for callers of this library
+ * that cannot call cudaMalloc while they run: code under a fixed device-memory budget sized at start-up, real-time
+ * loops, or hosts living inside another framework's allocator. Unlike every other entry point it allocates nothing
+ * (no cudaMalloc/cudaFree/cudaMallocAsync, no allocating library call): inputs and outputs are DEVICE pointers owned by
+ * the caller and the kernel's work area is a fixed 4 MiB array inside the library's device image (held by every GPU that
+ * loads the library until exit).
+ *   limit   : 8 * (nnz + 2 * (n_paths + 1)) <= 4 MiB, else RPVG_B200_ERR_LIMIT (message in error_message) and no launch.
+ *   inputs  : one cluster in the arena layout above: d_row_ptr[n_reads + 1] (entry offsets, any base), d_col/d_prob
+ *             indexed by those offsets, d_noise[n_reads], d_count[n_reads]; nnz = d_row_ptr[n_reads] - d_row_ptr[0].
+ *   outputs : d_abundances[n_paths], d_noise_count[1], d_total_count[1], d_iterations[1] (0xffffffff = a path index was
+ *             out of range). The kernel is enqueued on `stream` (a cudaStream_t, NULL = default stream); the call does
+ *             not synchronize. Same semantics as rpvg_b200_em_abundances for one cluster, equal to it up to rounding.
+ *   sharing : all calls on a device use the same work area and find the previous call's contents in it (the kernel clears
+ *             what it accumulates into); calls whose kernels could overlap on the GPU race — serialise them per device.
+ *   set-up  : the first call on a device resolves the work area's device address; make it before any stream capture. */
+int rpvg_b200_em_cluster_noalloc(int device, void * stream, uint32_t n_reads, uint32_t n_paths, uint64_t nnz, const uint64_t * d_row_ptr,
+                                 const uint32_t * d_col, const double * d_prob, const double * d_noise, const uint32_t * d_count,
+                                 const rpvg_b200_em_params * params, double * d_abundances, double * d_noise_count, double * d_total_count,
+                                 uint32_t * d_iterations, char * error_message, size_t error_message_len);
 
 #ifdef __cplusplus
 }

@@ -70,6 +70,8 @@ def lib():
         l.rpvg_b200_batch_em_work.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         l.rpvg_b200_batch_em_timings.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]
         l.rpvg_b200_batch_free.argtypes = [C.c_void_p, C.c_void_p]
+        l.rpvg_b200_em_cluster_noalloc.argtypes = ([C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint64] + [C.c_void_p] * 5 + [C.POINTER(EmParams)] +
+                                                   [C.c_void_p] * 4 + [C.c_char_p, C.c_size_t])
         _lib = l
     return _lib
 
@@ -192,3 +194,13 @@ class Batch:
             self.free()
         except Exception:
             pass
+
+
+def em_cluster_noalloc(device, stream, n_reads, n_paths, nnz, d_row_ptr, d_col, d_prob, d_noise, d_count, params, d_abundances, d_noise_count,
+                       d_total_count, d_iterations):
+    """rpvg_b200_em_cluster_noalloc: every pointer argument is a device address (int) owned by the caller; nothing is
+    allocated. Returns (status, message)."""
+    message = C.create_string_buffer(512)
+    status = lib().rpvg_b200_em_cluster_noalloc(device, C.c_void_p(stream) if stream else None, n_reads, n_paths, nnz, d_row_ptr, d_col, d_prob, d_noise,
+                                                d_count, C.byref(params), d_abundances, d_noise_count, d_total_count, d_iterations, message, len(message))
+    return status, message.value.decode()
