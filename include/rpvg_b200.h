@@ -99,6 +99,28 @@ int rpvg_b200_batch_em_work(rpvg_b200_ctx * ctx, rpvg_b200_batch * batch, double
  * matrix build (normalise + column-major index) and the EM kernels. Blocks until that work has finished. */
 int rpvg_b200_batch_em_timings(rpvg_b200_ctx * ctx, rpvg_b200_batch * batch, float * build_ms, float * em_ms);
 
+/* ---- haplotype models: log-likelihoods of path-group sets ----
+ * The O(#sets x #read classes) core of calculatePathGroupPosteriorsFull (rpvg:src/path_estimator.cpp:332-377),
+ * calculatePathGroupPosteriorsBounded (:379-473) and of the conditional distributions of
+ * estimatePathGroupPosteriorsGibbs (:527-555): for every set s of group_size paths of its problem (cluster)
+ *   loglik[s] = sum_r counts[r] * log(noise[r] + sum_{p in s} matrix[r, p] / group_size).
+ * Log frequencies, log(numPermutations), the log-sum-exp and Bounded's sequential pruning are O(#sets) and stay with the
+ * caller (rpvg_b200/host does them in the reference's order). Host pointers in and out. */
+typedef struct {
+    uint32_t n_problems;
+    const uint64_t * row_offset;    /* [n_problems + 1] read classes of problem p */
+    const uint64_t * path_offset;   /* [n_problems + 1] paths (matrix columns) of problem p */
+    const uint64_t * matrix_offset; /* [n_problems + 1] into matrix; problem p owns rows_p x paths_p doubles, column-major */
+    const uint64_t * set_offset;    /* [n_problems + 1] sets of problem p */
+    const double * matrix;
+    const double * noise;           /* [rows] */
+    const double * counts;          /* [rows] read counts (as doubles: collapsed classes carry sums) */
+    uint32_t group_size;            /* ploidy k, 1..8 */
+    const uint32_t * sets;          /* [n_sets * group_size] problem-local path indices */
+} rpvg_b200_loglik_problems;
+
+int rpvg_b200_group_loglik(rpvg_b200_ctx * ctx, const rpvg_b200_loglik_problems * problems, double * loglik);
+
 /* ---- EM of one cluster for callers that must not allocate ----
  * No counterpart in the reference (rpvg runs on the host and allocates freely); it exists for callers of this library
  * that cannot call cudaMalloc while they run: code under a fixed device-memory budget sized at start-up, real-time

@@ -1,0 +1,167 @@
+// Log-likelihoods of path-group sets (haplotype combinations) — the `log`-bound core of the haplotype models.
+//
+// Reference semantics restated (never its code): for a set s of k paths,
+//   LL_s = sum_r count_r * log(noise_r + sum_{p in s} P[r, p] / k)
+// (rpvg:src/path_estimator.cpp:354-361 Full, :424-440 Bounded, :527-545 Gibbs). The per-set terms that do not touch the
+// matrix (log frequencies, log numPermutations, the log-sum-exp normalisation, Bounded's sequential pruning) stay on the
+// host side of the ABI (rpvg_b200/host), in the reference's own order, because they are O(#sets), not O(#sets x M).
+//
+// Layout: problems (clusters) concatenated; per problem a dense column-major matrix rows x paths, as the reference holds
+// it, plus noise[rows] and counts[rows]. One warp per set: lanes stride the rows (coalesced column reads, the columns of a
+// problem are shared by all of its sets and stay in L2/L1), fp64 log, fixed summation tree (deterministic).
+// Bound: fp64 ALU / log throughput, not HBM.
+
+#include <cmath>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int kLoglikThreads = 256;
+constexpr uint32_t kMaxGroupSizeLoglik = 8;
+
+struct LoglikArgs {
+
+    uint32_t n_problems;
+    uint32_t group_size;
+    uint64_t n_sets;
+    const uint64_t * row_offset;
+    const uint64_t * path_offset;
+    const uint64_t * matrix_offset;
+    const uint64_t * set_offset;
+    const double * matrix;
+    const double * noise;
+    const double * counts;
+    const uint32_t * sets;
+    double * loglik;
+};
+
+__global__ void __launch_bounds__(kLoglikThreads) groupLoglikKernel(const LoglikArgs args) {
+
+    const uint32_t lane = threadIdx.x & 31;
+    const uint64_t set = (blockIdx.x * static_cast<uint64_t>(kLoglikThreads) + threadIdx.x) >> 5;
+    if (set >= args.n_sets) { return; }
+
+    const uint32_t p = clusterOf(args.set_offset, args.n_problems, set);
+    const uint64_t r0 = args.row_offset[p];
+    const uint32_t rows = static_cast<uint32_t>(args.row_offset[p + 1] - r0);
+    const double * matrix = args.matrix + args.matrix_offset[p];
+    const double * noise = args.noise + r0;
+    const double * counts = args.counts + r0;
+
+    const uint32_t k = args.group_size;
+    const double group_size = static_cast<double>(k);
+
+    const double * cols[kMaxGroupSizeLoglik];
+    #pragma unroll
+    for (uint32_t q = 0; q < kMaxGroupSizeLoglik; ++q) {
+        cols[q] = (q < k) ? matrix + static_cast<uint64_t>(args.sets[set * k + q]) * rows : matrix;
+    }
+
+    double acc = 0;
+
+    for (uint32_t r = lane; r < rows; r += 32) {
+
+        // noise + col_1 / k + col_2 / k + ... in the reference's order
+        double prob = noise[r];
+        #pragma unroll
+        for (uint32_t q = 0; q < kMaxGroupSizeLoglik; ++q) {
+            if (q < k) { prob += cols[q][r] / group_size; }
+        }
+        acc += counts[r] * log(prob);
+    }
+
+    acc = warpSum(acc);
+    if (lane == 0) { args.loglik[set] = acc; }
+}
+
+}
+
+extern "C" int rpvg_b200_group_loglik(rpvg_b200_ctx * ctx, const rpvg_b200_loglik_problems * pr, double * loglik) {
+
+    if (!ctx || !pr || !loglik) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "NULL argument"); }
+    if (pr->n_problems == 0) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "no problems"); }
+    if (pr->group_size == 0 || pr->group_size > kMaxGroupSizeLoglik) { return rpvgFail(ctx, RPVG_B200_ERR_LIMIT, "group_size must be 1..8"); }
+
+    const uint32_t P = pr->n_problems;
+    const uint64_t R = pr->row_offset[P];
+    const uint64_t Mx = pr->matrix_offset[P];
+    const uint64_t S = pr->set_offset[P];
+
+    if (S == 0) { return RPVG_B200_OK; }
+
+    for (uint32_t p = 0; p < P; ++p) {
+        const uint64_t rows = pr->row_offset[p + 1] - pr->row_offset[p];
+        const uint64_t paths = pr->path_offset[p + 1] - pr->path_offset[p];
+        if (pr->matrix_offset[p + 1] - pr->matrix_offset[p] != rows * paths) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "matrix_offset does not match rows x paths"); }
+        if (rows >= 0xffffffffull) { return rpvgFail(ctx, RPVG_B200_ERR_LIMIT, "too many rows in one problem"); }
+    }
+
+    RPVG_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+
+    auto pad = [](size_t b) { return (b + 255) & ~size_t(255); };
+    const size_t bytes = 4 * pad(8 * (P + 1)) + pad(8 * Mx) + 2 * pad(8 * R) + pad(4 * S * pr->group_size) + pad(8 * S) + 1024;
+
+    char * base = nullptr;
+    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&base), bytes, s));
+
+    size_t used = 0;
+    auto take = [&](size_t b) { char * q = base + used; used += pad(b); return q; };
+
+    uint64_t * d_row_offset = reinterpret_cast<uint64_t *>(take(8 * (P + 1)));
+    uint64_t * d_path_offset = reinterpret_cast<uint64_t *>(take(8 * (P + 1)));
+    uint64_t * d_matrix_offset = reinterpret_cast<uint64_t *>(take(8 * (P + 1)));
+    uint64_t * d_set_offset = reinterpret_cast<uint64_t *>(take(8 * (P + 1)));
+    double * d_matrix = reinterpret_cast<double *>(take(8 * Mx));
+    double * d_noise = reinterpret_cast<double *>(take(8 * R));
+    double * d_counts = reinterpret_cast<double *>(take(8 * R));
+    uint32_t * d_sets = reinterpret_cast<uint32_t *>(take(4 * S * pr->group_size));
+    double * d_loglik = reinterpret_cast<double *>(take(8 * S));
+
+    int status = RPVG_B200_OK;
+    cudaError_t err = cudaSuccess;
+
+    #define RPVG_H2D(dst, src, n)                                                                                  \
+        if (err == cudaSuccess && (n) > 0) { err = cudaMemcpyAsync((dst), (src), (n), cudaMemcpyHostToDevice, s); }
+
+    RPVG_H2D(d_row_offset, pr->row_offset, 8 * (P + 1))
+    RPVG_H2D(d_path_offset, pr->path_offset, 8 * (P + 1))
+    RPVG_H2D(d_matrix_offset, pr->matrix_offset, 8 * (P + 1))
+    RPVG_H2D(d_set_offset, pr->set_offset, 8 * (P + 1))
+    RPVG_H2D(d_matrix, pr->matrix, 8 * Mx)
+    RPVG_H2D(d_noise, pr->noise, 8 * R)
+    RPVG_H2D(d_counts, pr->counts, 8 * R)
+    RPVG_H2D(d_sets, pr->sets, 4 * S * pr->group_size)
+    #undef RPVG_H2D
+
+    if (err == cudaSuccess) {
+
+        LoglikArgs args;
+        args.n_problems = P;
+        args.group_size = pr->group_size;
+        args.n_sets = S;
+        args.row_offset = d_row_offset;
+        args.path_offset = d_path_offset;
+        args.matrix_offset = d_matrix_offset;
+        args.set_offset = d_set_offset;
+        args.matrix = d_matrix;
+        args.noise = d_noise;
+        args.counts = d_counts;
+        args.sets = d_sets;
+        args.loglik = d_loglik;
+
+        const uint64_t blocks = (S * 32 + kLoglikThreads - 1) / kLoglikThreads;
+        groupLoglikKernel<<<static_cast<unsigned>(blocks), kLoglikThreads, 0, s>>>(args);
+        ctx->launches++;
+        err = cudaGetLastError();
+    }
+
+    if (err == cudaSuccess) { err = cudaMemcpyAsync(loglik, d_loglik, 8 * S, cudaMemcpyDeviceToHost, s); }
+    if (err == cudaSuccess) { err = cudaStreamSynchronize(s); }
+
+    if (err != cudaSuccess) { status = rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("rpvg_b200_group_loglik: ") + cudaGetErrorString(err)); }
+
+    cudaFreeAsync(base, s);
+    return status;
+}

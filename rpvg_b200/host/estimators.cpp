@@ -1,0 +1,406 @@
+// Host side of the drop-in estimators: flattening, the O(#sets) combinatorics in the reference's order, calls into the
+// C ABI. No numerical work over the data happens here; without a GPU threadContext() aborts (rpvg's own error style:
+// asserts are live, rpvg:CMakeLists.txt:180).
+
+#include "estimators.hpp"
+
+#include <algorithm>
+#include <cassert>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <iostream>
+#include <limits>
+#include <numeric>
+
+#include "rpvg_b200.h"
+
+namespace {
+
+// rpvg:src/utils.hpp:300-302
+inline double add_log(double log_x, double log_y) {
+
+    return log_x > log_y ? log_x + log1p(exp(log_y - log_x)) : log_y + log1p(exp(log_x - log_y));
+}
+
+// rpvg:src/utils.hpp:95-117 — kept as it is (not the multinomial coefficient for k >= 4)
+inline uint32_t numPermutations(vector<uint32_t> values) {
+
+    assert(!values.empty());
+    if (values.size() == 1) { return 1; }
+
+    sort(values.begin(), values.end());
+
+    uint32_t num_unique_values = 1;
+    for (size_t i = 1; i < values.size(); ++i) {
+        if (values.at(i - 1) != values.at(i)) { num_unique_values++; }
+    }
+
+    return (tgamma(values.size() + 1) / tgamma(values.size() - num_unique_values + 2));
+}
+
+// rpvg:src/path_estimator.cpp:315-330
+vector<double> calcPathLogFrequences(const vector<uint32_t> & path_counts) {
+
+    uint32_t count_sum = accumulate(path_counts.begin(), path_counts.end(), 0);
+    assert(count_sum > 0);
+
+    vector<double> path_log_freqs;
+    path_log_freqs.reserve(path_counts.size());
+
+    for (auto & count: path_counts) {
+        assert(count > 0);
+        path_log_freqs.emplace_back(log(count / static_cast<double>(count_sum)));
+    }
+
+    return path_log_freqs;
+}
+
+void generateGroupsRecursive(vector<vector<uint32_t> > * sets, const uint32_t num_components, const uint32_t group_size, vector<uint32_t> cur_group) {
+
+    if (cur_group.size() < group_size) {
+
+        const uint32_t start_idx = cur_group.empty() ? 0 : cur_group.back();
+
+        for (uint32_t i = start_idx; i < num_components; ++i) {
+            vector<uint32_t> new_group = cur_group;
+            new_group.push_back(i);
+            generateGroupsRecursive(sets, num_components, group_size, new_group);
+        }
+
+    } else {
+
+        sets->emplace_back(cur_group);
+    }
+}
+
+[[noreturn]] void fatal(rpvg_b200_ctx * ctx, const char * what) {
+
+    cerr << "ERROR: rpvg_b200 " << what << ": " << rpvg_b200_last_error(ctx) << endl;
+    abort();
+}
+
+[[noreturn]] void notBuiltYet(const char * what) {
+
+    cerr << "ERROR: rpvg_b200 does not provide " << what << " on the GPU yet, and it has no CPU fallback" << endl;
+    abort();
+}
+
+// sum_r count_r log(noise_r + sum_p col_p / k) for each set, on the device
+vector<double> deviceLogLikelihoods(rpvg_b200_ctx * ctx, const vector<double> & matrix, const vector<double> & noise, const vector<double> & counts,
+                                    const uint32_t num_paths, const uint32_t group_size, const vector<uint32_t> & flat_sets) {
+
+    const uint64_t rows = noise.size();
+    const uint64_t n_sets = flat_sets.size() / group_size;
+
+    const uint64_t row_offset[2] = {0, rows};
+    const uint64_t path_offset[2] = {0, num_paths};
+    const uint64_t matrix_offset[2] = {0, rows * num_paths};
+    const uint64_t set_offset[2] = {0, n_sets};
+
+    rpvg_b200_loglik_problems problems;
+    problems.n_problems = 1;
+    problems.row_offset = row_offset;
+    problems.path_offset = path_offset;
+    problems.matrix_offset = matrix_offset;
+    problems.set_offset = set_offset;
+    problems.matrix = matrix.data();
+    problems.noise = noise.data();
+    problems.counts = counts.data();
+    problems.group_size = group_size;
+    problems.sets = flat_sets.data();
+
+    vector<double> loglik(n_sets, 0);
+    if (n_sets > 0 && rpvg_b200_group_loglik(ctx, &problems, loglik.data()) != RPVG_B200_OK) { fatal(ctx, "rpvg_b200_group_loglik"); }
+
+    return loglik;
+}
+
+}
+
+#ifndef RPVG_B200_WITH_RPVG_HEADERS
+
+void PathClusterEstimates::resetEstimates(uint32_t num_components, const uint32_t group_size) {
+
+    path_group_sets.clear();
+
+    posteriors.clear();
+    abundances.clear();
+
+    noise_count = 0;
+    total_count = 0;
+
+    gibbs_read_count_samples.clear();
+
+    if (group_size > 0) {
+
+        generateGroupsRecursive(&path_group_sets, num_components, group_size, vector<uint32_t>());
+
+        posteriors = vector<double>(path_group_sets.size(), 0);
+        abundances = vector<double>(path_group_sets.size() * group_size, 0);
+    }
+}
+
+#endif
+
+PathEstimator::PathEstimator(const double prob_precision_in) : prob_precision(prob_precision_in) {}
+
+rpvg_b200_ctx * PathEstimator::threadContext() {
+
+    thread_local rpvg_b200_ctx * ctx = nullptr;
+
+    if (!ctx) {
+
+        const char * device = getenv("RPVG_B200_DEVICE");
+        const int status = rpvg_b200_create(device ? atoi(device) : 0, nullptr, &ctx);
+
+        if (status != RPVG_B200_OK) {
+            cerr << "ERROR: rpvg_b200_create failed with status " << status << " (a CUDA device is required; there is no CPU fallback)" << endl;
+            abort();
+        }
+    }
+
+    return ctx;
+}
+
+void PathEstimator::denseMatrix(vector<double> * matrix, vector<double> * noise, vector<double> * counts, const vector<ReadPathProbabilities> & cluster_probs, const uint32_t num_paths) {
+
+    const size_t rows = cluster_probs.size();
+
+    matrix->assign(rows * num_paths, 0);
+    noise->resize(rows);
+    counts->resize(rows);
+
+    for (size_t i = 0; i < rows; ++i) {
+
+        for (auto & path_probs: cluster_probs.at(i).pathProbs()) {
+            for (auto & path: path_probs.second) {
+                assert(path < num_paths);
+                (*matrix)[static_cast<size_t>(path) * rows + i] = path_probs.first;
+            }
+        }
+
+        (*noise)[i] = cluster_probs.at(i).noiseProb();
+        (*counts)[i] = cluster_probs.at(i).readCount();
+    }
+}
+
+void PathEstimator::calculatePathGroupPosteriorsFull(PathClusterEstimates * path_cluster_estimates, const vector<double> & matrix, const vector<double> & noise, const vector<double> & counts, const uint32_t num_paths, const vector<uint32_t> & path_counts, const uint32_t group_size) const {
+
+    assert(!noise.empty());
+    assert(group_size > 0);
+
+    auto path_log_freqs = calcPathLogFrequences(path_counts);
+
+    path_cluster_estimates->resetEstimates(num_paths, group_size);
+
+    vector<uint32_t> flat_sets;
+    flat_sets.reserve(path_cluster_estimates->path_group_sets.size() * group_size);
+    for (auto & group_set: path_cluster_estimates->path_group_sets) { flat_sets.insert(flat_sets.end(), group_set.begin(), group_set.end()); }
+
+    auto loglik = deviceLogLikelihoods(threadContext(), matrix, noise, counts, num_paths, group_size, flat_sets);
+
+    double sum_log_posterior = numeric_limits<double>::lowest();
+
+    for (uint32_t i = 0; i < path_cluster_estimates->path_group_sets.size(); ++i) {
+
+        path_cluster_estimates->posteriors.at(i) = loglik.at(i);
+
+        for (auto & path_idx: path_cluster_estimates->path_group_sets.at(i)) { path_cluster_estimates->posteriors.at(i) += path_log_freqs.at(path_idx); }
+
+        path_cluster_estimates->posteriors.at(i) += log(numPermutations(path_cluster_estimates->path_group_sets.at(i)));
+        sum_log_posterior = add_log(sum_log_posterior, path_cluster_estimates->posteriors.at(i));
+    }
+
+    for (size_t i = 0; i < path_cluster_estimates->posteriors.size(); ++i) {
+        path_cluster_estimates->posteriors.at(i) = exp(path_cluster_estimates->posteriors.at(i) - sum_log_posterior);
+    }
+}
+
+void PathEstimator::calculatePathGroupPosteriorsBounded(PathClusterEstimates * path_cluster_estimates, const vector<double> & matrix, const vector<double> & noise, const vector<double> & counts, const uint32_t num_paths, const vector<uint32_t> & path_counts, const uint32_t group_size, const double min_rel_likelihood) const {
+
+    assert(group_size == 2);
+
+    const double min_log_likelihood_diff = log(min_rel_likelihood);
+    auto path_log_freqs = calcPathLogFrequences(path_counts);
+
+    path_cluster_estimates->resetEstimates(0, 0);
+
+    PathClusterEstimates marginal_path_cluster_estimates;
+    calculatePathGroupPosteriorsFull(&marginal_path_cluster_estimates, matrix, noise, counts, num_paths, path_counts, 1);
+
+    vector<pair<double, uint32_t> > marginal_posteriors;
+    marginal_posteriors.reserve(marginal_path_cluster_estimates.posteriors.size());
+
+    for (size_t i = 0; i < marginal_path_cluster_estimates.posteriors.size(); ++i) {
+        marginal_posteriors.emplace_back(marginal_path_cluster_estimates.posteriors.at(i), marginal_path_cluster_estimates.path_group_sets.at(i).front());
+    }
+
+    sort(marginal_posteriors.rbegin(), marginal_posteriors.rend());
+
+    // Every pair (i, j >= i) in the reference's enumeration order is evaluated on the device; the reference's pruning
+    // (per-first-path upper bound, running maximum) is then replayed over the finished values. A pair the bound would
+    // have skipped has a log-likelihood below the bound, so the replay drops it as well: the list comes out the same.
+    vector<uint32_t> flat_sets;
+    flat_sets.reserve(static_cast<size_t>(num_paths) * (num_paths + 1));
+
+    for (uint32_t i = 0; i < marginal_posteriors.size(); ++i) {
+        for (uint32_t j = i; j < marginal_posteriors.size(); ++j) {
+            flat_sets.push_back(marginal_posteriors.at(i).second);
+            flat_sets.push_back(marginal_posteriors.at(j).second);
+        }
+    }
+
+    auto loglik = deviceLogLikelihoods(threadContext(), matrix, noise, counts, num_paths, group_size, flat_sets);
+
+    vector<double> log_likelihoods;
+    double max_log_likelihood = numeric_limits<double>::lowest();
+
+    size_t pair_idx = 0;
+
+    for (uint32_t i = 0; i < marginal_posteriors.size(); ++i) {
+
+        const uint32_t first_path_idx = marginal_posteriors.at(i).second;
+
+        for (uint32_t j = i; j < marginal_posteriors.size(); ++j, ++pair_idx) {
+
+            const uint32_t second_path_idx = marginal_posteriors.at(j).second;
+
+            double log_likelihood = loglik.at(pair_idx);
+            log_likelihood += path_log_freqs.at(first_path_idx) + path_log_freqs.at(second_path_idx) + log(numPermutations(vector<uint32_t>({first_path_idx, second_path_idx})));
+
+            if (log_likelihood - max_log_likelihood < min_log_likelihood_diff) { continue; }
+
+            log_likelihoods.emplace_back(log_likelihood);
+            max_log_likelihood = max(max_log_likelihood, log_likelihood);
+            path_cluster_estimates->path_group_sets.emplace_back(vector<uint32_t>({first_path_idx, second_path_idx}));
+        }
+    }
+
+    double sum_log_posterior = numeric_limits<double>::lowest();
+
+    for (size_t i = 0; i < log_likelihoods.size(); ++i) {
+
+        if (log_likelihoods.at(i) - max_log_likelihood < min_log_likelihood_diff) { log_likelihoods.at(i) = numeric_limits<double>::lowest(); }
+        sum_log_posterior = add_log(sum_log_posterior, log_likelihoods.at(i));
+    }
+
+    for (auto & ll: log_likelihoods) { path_cluster_estimates->posteriors.emplace_back(exp(ll - sum_log_posterior)); }
+}
+
+// ---- transcripts -----------------------------------------------------------------------------------------------------
+
+PathAbundanceEstimator::PathAbundanceEstimator(const uint32_t max_em_its_in, const double max_rel_em_conv_in, const uint32_t num_gibbs_samples_in, const uint32_t gibbs_thin_its_in, const double prob_precision) : PathEstimator(prob_precision), max_em_its(max_em_its_in), max_rel_em_conv(max_rel_em_conv_in), num_gibbs_samples(num_gibbs_samples_in), gibbs_thin_its(gibbs_thin_its_in) {}
+
+void PathAbundanceEstimator::estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng) {
+
+    path_cluster_estimates->resetEstimates(path_cluster_estimates->paths.size(), 1);
+
+    if (cluster_probs.empty()) { return; }
+
+    // the cluster as a one-cluster arena: entries of a read class sorted by path index
+    vector<uint64_t> read_offset = {0, cluster_probs.size()};
+    vector<uint64_t> path_offset = {0, path_cluster_estimates->paths.size()};
+    vector<uint64_t> row_ptr = {0};
+    vector<uint32_t> col, count;
+    vector<double> prob, noise;
+    vector<pair<uint32_t, double> > row;
+
+    for (auto & read_probs: cluster_probs) {
+
+        row.clear();
+        for (auto & path_probs: read_probs.pathProbs()) {
+            for (auto & path: path_probs.second) { row.emplace_back(path, path_probs.first); }
+        }
+        sort(row.begin(), row.end());
+
+        for (auto & entry: row) {
+            col.push_back(entry.first);
+            prob.push_back(entry.second);
+        }
+
+        row_ptr.push_back(col.size());
+        noise.push_back(read_probs.noiseProb());
+        count.push_back(read_probs.readCount());
+    }
+
+    rpvg_b200_clusters clusters = {1, read_offset.data(), path_offset.data(), row_ptr.data(), col.data(), prob.data(), noise.data(), count.data()};
+
+    rpvg_b200_em_params params;
+    rpvg_b200_em_params_default(&params);
+    params.max_em_its = max_em_its;
+    params.max_rel_em_conv = max_rel_em_conv;
+
+    auto * ctx = threadContext();
+
+    if (rpvg_b200_em_abundances(ctx, &clusters, &params, path_cluster_estimates->abundances.data(), &path_cluster_estimates->noise_count, &path_cluster_estimates->total_count, nullptr) != RPVG_B200_OK) {
+        fatal(ctx, "rpvg_b200_em_abundances");
+    }
+
+    if (num_gibbs_samples > 0) { notBuiltYet("the Gibbs read-count sampler (--num-gibbs-samples)"); }
+}
+
+MinimumPathAbundanceEstimator::MinimumPathAbundanceEstimator(const uint32_t max_em_its, const double max_rel_em_conv, const uint32_t num_gibbs_samples, const uint32_t gibbs_thin_its, const double prob_precision) : PathAbundanceEstimator(max_em_its, max_rel_em_conv, num_gibbs_samples, gibbs_thin_its, prob_precision) {}
+
+void MinimumPathAbundanceEstimator::estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng) {
+
+    notBuiltYet("the strains model (MinimumPathAbundanceEstimator)");
+}
+
+NestedPathAbundanceEstimator::NestedPathAbundanceEstimator(const uint32_t group_size_in, const double min_hap_prob_in, const bool infer_collapsed_in, const bool use_group_post_gibbs_in, const uint32_t max_em_its, const double max_rel_em_conv, const uint32_t num_gibbs_samples, const uint32_t gibbs_thin_its, const double prob_precision) : PathAbundanceEstimator(max_em_its, max_rel_em_conv, num_gibbs_samples, gibbs_thin_its, prob_precision), group_size(group_size_in), min_hap_prob(min_hap_prob_in), infer_collapsed(infer_collapsed_in), use_group_post_gibbs(use_group_post_gibbs_in) {}
+
+void NestedPathAbundanceEstimator::estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng) {
+
+    notBuiltYet("the haplotype-transcripts model (NestedPathAbundanceEstimator)");
+}
+
+// ---- haplotypes ------------------------------------------------------------------------------------------------------
+
+static const double min_rel_likelihood = 1e-8;   // rpvg:src/path_posterior_estimator.cpp:5
+
+PathPosteriorEstimator::PathPosteriorEstimator(const double prob_precision) : PathEstimator(prob_precision) {}
+
+void PathPosteriorEstimator::estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng) {
+
+    path_cluster_estimates->resetEstimates(path_cluster_estimates->paths.size(), 1);
+
+    if (cluster_probs.empty()) { return; }
+
+    vector<double> matrix, noise, counts;
+    denseMatrix(&matrix, &noise, &counts, cluster_probs, path_cluster_estimates->paths.size());
+
+    vector<uint32_t> path_counts;
+    for (auto & path: path_cluster_estimates->paths) { path_counts.emplace_back(path.source_count); }
+
+    calculatePathGroupPosteriorsFull(path_cluster_estimates, matrix, noise, counts, path_cluster_estimates->paths.size(), path_counts, 1);
+}
+
+PathGroupPosteriorEstimator::PathGroupPosteriorEstimator(const uint32_t group_size_in, const bool use_group_post_gibbs_in, const double prob_precision) : PathPosteriorEstimator(prob_precision), group_size(group_size_in), use_group_post_gibbs(use_group_post_gibbs_in) {}
+
+void PathGroupPosteriorEstimator::estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng) {
+
+    path_cluster_estimates->resetEstimates(0, 0);
+
+    if (cluster_probs.empty()) { return; }
+
+    const uint32_t num_paths = path_cluster_estimates->paths.size();
+
+    vector<double> matrix, noise, counts;
+    denseMatrix(&matrix, &noise, &counts, cluster_probs, num_paths);
+
+    vector<uint32_t> path_counts;
+    for (auto & path: path_cluster_estimates->paths) { path_counts.emplace_back(path.source_count); }
+
+    if (use_group_post_gibbs) {
+
+        notBuiltYet("the haplotype Gibbs sampler (--use-hap-gibbs)");
+
+    } else if (group_size == 2) {
+
+        calculatePathGroupPosteriorsBounded(path_cluster_estimates, matrix, noise, counts, num_paths, path_counts, group_size, min_rel_likelihood);
+
+    } else {
+
+        calculatePathGroupPosteriorsFull(path_cluster_estimates, matrix, noise, counts, num_paths, path_counts, group_size);
+    }
+}

@@ -1,0 +1,209 @@
+// rpvg_b200 host side: drop-in estimator classes with the reference's names, constructor and estimate() signatures
+// (rpvg:src/path_estimator.hpp:16-49, path_abundance_estimator.hpp:18-79, path_posterior_estimator.hpp:18-42), so that
+// rpvg:src/main.cpp:766-788,977 compiles unchanged. Everything O(data) runs on the GPU through the C ABI
+// (include/rpvg_b200.h); what stays here is the O(#sets) combinatorics whose order is observable in the output.
+//
+// Inside rpvg's tree, compile with -DRPVG_B200_WITH_RPVG_HEADERS: the value types then come from rpvg's own headers.
+// Stand-alone (this repository's tests) the same public types are declared below.
+#ifndef RPVG_B200_HOST_ESTIMATORS_HPP
+#define RPVG_B200_HOST_ESTIMATORS_HPP
+
+#include <cstdint>
+#include <random>
+#include <string>
+#include <utility>
+#include <vector>
+
+#ifdef RPVG_B200_WITH_RPVG_HEADERS
+
+#include "path_cluster_estimates.hpp"
+#include "read_path_probabilities.hpp"
+
+#else
+
+#if __has_include("sparsepp/spp.h")
+#include "sparsepp/spp.h"
+#define RPVG_B200_HAVE_SPARSEPP 1
+namespace rpvg_b200_host {
+template <class K> using hash_set = spp::sparse_hash_set<K>;
+template <class K, class V> using hash_map = spp::sparse_hash_map<K, V>;
+}
+#else
+#include <unordered_map>
+#include <unordered_set>
+namespace rpvg_b200_host {
+template <class K> using hash_set = std::unordered_set<K>;
+template <class K, class V> using hash_map = std::unordered_map<K, V>;
+}
+#endif
+
+using namespace std;
+
+// rpvg:src/path_cluster_estimates.hpp:14-32
+struct PathInfo {
+
+    string name;
+    uint32_t group_id;
+
+    uint32_t source_count;
+    rpvg_b200_host::hash_set<uint32_t> source_ids;
+
+    uint32_t length;
+    double effective_length;
+
+    PathInfo(const string & name_in) : name(name_in), group_id(0), source_count(1), length(0), effective_length(0) {}
+};
+
+// rpvg:src/path_cluster_estimates.hpp:34-42
+struct CountSamples {
+
+    vector<uint32_t> path_ids;
+
+    vector<double> noise_samples;
+    vector<double> abundance_samples;
+};
+
+// rpvg:src/path_cluster_estimates.hpp:44-110
+struct PathClusterEstimates {
+
+    vector<PathInfo> paths;
+
+    vector<vector<uint32_t> > path_group_sets;
+
+    vector<double> posteriors;
+    vector<double> abundances;
+
+    double noise_count;
+    double total_count;
+
+    vector<CountSamples> gibbs_read_count_samples;
+
+    PathClusterEstimates() : noise_count(0), total_count(0) {}
+
+    // all size-k multisets of {0..n-1} in lexicographic order; posteriors and abundances zeroed
+    void resetEstimates(uint32_t num_components, const uint32_t group_size);
+};
+
+// rpvg:src/read_path_probabilities.hpp:19-44 (the record; addPathProbs stays in rpvg)
+class ReadPathProbabilities {
+
+    public:
+
+        ReadPathProbabilities() : read_count(0), noise_prob(1), prob_precision(0) {}
+        ReadPathProbabilities(const uint32_t read_count_in, const double prob_precision_in) : read_count(read_count_in), noise_prob(1), prob_precision(prob_precision_in) {}
+
+        uint32_t readCount() const { return read_count; }
+        double noiseProb() const { return noise_prob; }
+        const vector<pair<double, vector<uint32_t> > > & pathProbs() const { return path_probs; }
+
+        void addReadCount(const uint32_t read_count_in) { read_count += read_count_in; }
+
+    private:
+
+        uint32_t read_count;
+        double noise_prob;
+        vector<pair<double, vector<uint32_t> > > path_probs;
+
+        double prob_precision;
+};
+
+#endif
+
+struct rpvg_b200_ctx;
+
+class PathEstimator {
+
+    public:
+
+        PathEstimator(const double prob_precision_in);
+        virtual ~PathEstimator() {};
+
+        virtual void estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng) = 0;
+
+    protected:
+
+        const double prob_precision;
+
+        // One context per calling thread: estimate() is re-entrant on a shared object (rpvg:src/main.cpp:829-830).
+        static rpvg_b200_ctx * threadContext();
+
+        // Dense column-major matrix as constructProbabilityMatrix leaves it (rpvg:src/path_estimator.cpp:55-77).
+        static void denseMatrix(vector<double> * matrix, vector<double> * noise, vector<double> * counts, const vector<ReadPathProbabilities> & cluster_probs, const uint32_t num_paths);
+
+        // rpvg:src/path_estimator.cpp:332-377 / 379-473 with the log-likelihoods computed on the device.
+        void calculatePathGroupPosteriorsFull(PathClusterEstimates * path_cluster_estimates, const vector<double> & matrix, const vector<double> & noise, const vector<double> & counts, const uint32_t num_paths, const vector<uint32_t> & path_counts, const uint32_t group_size) const;
+        void calculatePathGroupPosteriorsBounded(PathClusterEstimates * path_cluster_estimates, const vector<double> & matrix, const vector<double> & noise, const vector<double> & counts, const uint32_t num_paths, const vector<uint32_t> & path_counts, const uint32_t group_size, const double min_rel_likelihood) const;
+};
+
+class PathAbundanceEstimator : public PathEstimator {
+
+    public:
+
+        PathAbundanceEstimator(const uint32_t max_em_its_in, const double max_rel_em_conv_in, const uint32_t num_gibbs_samples_in, const uint32_t gibbs_thin_its_in, const double prob_precision);
+        virtual ~PathAbundanceEstimator() {};
+
+        void estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng);
+
+    protected:
+
+        const uint32_t max_em_its;
+        const double max_rel_em_conv;
+
+        const uint32_t num_gibbs_samples;
+        const uint32_t gibbs_thin_its;
+};
+
+class MinimumPathAbundanceEstimator : public PathAbundanceEstimator {
+
+    public:
+
+        MinimumPathAbundanceEstimator(const uint32_t max_em_its, const double max_rel_em_conv, const uint32_t num_gibbs_samples, const uint32_t gibbs_thin_its, const double prob_precision);
+        ~MinimumPathAbundanceEstimator() {};
+
+        void estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng);
+};
+
+class NestedPathAbundanceEstimator : public PathAbundanceEstimator {
+
+    public:
+
+        NestedPathAbundanceEstimator(const uint32_t group_size_in, const double min_hap_prob_in, const bool infer_collapsed_in, const bool use_group_post_gibbs_in, const uint32_t max_em_its, const double max_rel_em_conv, const uint32_t num_gibbs_samples, const uint32_t gibbs_thin_its, const double prob_precision);
+        ~NestedPathAbundanceEstimator() {};
+
+        void estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng);
+
+    private:
+
+        const uint32_t group_size;
+        const double min_hap_prob;
+
+        const bool infer_collapsed;
+        const bool use_group_post_gibbs;
+};
+
+class PathPosteriorEstimator : public PathEstimator {
+
+    public:
+
+        PathPosteriorEstimator(const double prob_precision);
+        virtual ~PathPosteriorEstimator() {};
+
+        void estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng);
+};
+
+class PathGroupPosteriorEstimator : public PathPosteriorEstimator {
+
+    public:
+
+        PathGroupPosteriorEstimator(const uint32_t group_size_in, const bool use_group_post_gibbs_in, const double prob_precision);
+        ~PathGroupPosteriorEstimator() {};
+
+        void estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng);
+
+    private:
+
+        const uint32_t group_size;
+        const bool use_group_post_gibbs;
+};
+
+#endif

@@ -33,3 +33,15 @@ def reference():
     if not loader.reference_available():
         pytest.skip("oracle/_ref not built (needs /root/reference at build time)")
     return loader.reference()
+
+
+@pytest.fixture(scope="session")
+def b200_harness():
+    """tests/harness/estimator_harness.cpp compiled against this repository's drop-in estimator classes."""
+    from oracle import loader
+    path = os.path.join(ROOT, "tests", "_build", "libharness_b200.so")
+    if not os.path.exists(path):
+        pytest.fail(f"{path} is missing: run __graft_entry__.build()")
+    lib = loader.load_harness(path)
+    assert lib.harness_impl_name() == b"rpvg_b200"
+    return lib
