@@ -121,6 +121,30 @@ typedef struct {
 
 int rpvg_b200_group_loglik(rpvg_b200_ctx * ctx, const rpvg_b200_loglik_problems * problems, double * loglik);
 
+/* ---- read-class collapse ----
+ * rowSortProbabilityMatrix + readCollapseProbabilityMatrix (rpvg:src/path_estimator.cpp:13-31,197-259) for a batch of
+ * problems: rows of a normalised probability matrix (sparse: entries with problem-local column indices ascending, an
+ * absent column is 0; the noise column is the separate per-row value, compared last) are sorted with the reference's
+ * tolerance comparator and merged greedily against the running representative (all columns within prob_precision).
+ * Exact: the partition of rows into classes, the class counts and the class order.
+ *   row_class   [n_rows]       class (index in output order, within its problem) of every input row; may be NULL
+ *   n_classes   [n_problems]
+ *   class_rep   [>= sum n_classes] input row whose values the class keeps (classes of problem p start at the sum of
+ *               n_classes over earlier problems); may be NULL. Capacity n_rows always suffices.
+ *   class_count [>= sum n_classes] summed read counts; may be NULL */
+typedef struct {
+    uint32_t n_problems;
+    const uint64_t * row_offset; /* [n_problems + 1] */
+    const uint64_t * row_ptr;    /* [n_rows + 1] */
+    const uint32_t * col;
+    const double * val;
+    const double * noise;        /* [n_rows] */
+    const double * count;        /* [n_rows] */
+} rpvg_b200_collapse_problems;
+
+int rpvg_b200_collapse(rpvg_b200_ctx * ctx, const rpvg_b200_collapse_problems * problems, double prob_precision, uint32_t * row_class, uint32_t * n_classes,
+                       uint32_t * class_rep, double * class_count);
+
 /* ---- EM of one cluster for callers that must not allocate ----
  * No counterpart in the reference (rpvg runs on the host and allocates freely); it exists for callers of this library
  * that cannot call cudaMalloc while they run: code under a fixed device-memory budget sized at start-up, real-time

@@ -43,6 +43,10 @@ class EmParams(C.Structure):
     ]
 
 
+class CollapseProblems(C.Structure):
+    _fields_ = [("n_problems", C.c_uint32)] + [(n, C.c_void_p) for n in ("row_offset", "row_ptr", "col", "val", "noise", "count")]
+
+
 def library_path() -> str:
     return _LIB_PATH
 
@@ -70,6 +74,7 @@ def lib():
         l.rpvg_b200_batch_em_work.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         l.rpvg_b200_batch_em_timings.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]
         l.rpvg_b200_batch_free.argtypes = [C.c_void_p, C.c_void_p]
+        l.rpvg_b200_collapse.argtypes = [C.c_void_p, C.POINTER(CollapseProblems), C.c_double] + [C.c_void_p] * 4
         l.rpvg_b200_em_cluster_noalloc.argtypes = ([C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint64] + [C.c_void_p] * 5 + [C.POINTER(EmParams)] +
                                                    [C.c_void_p] * 4 + [C.c_char_p, C.c_size_t])
         _lib = l
@@ -149,6 +154,25 @@ class Context:
         self._check(lib().rpvg_b200_em_abundances(self._h, C.byref(cl), C.byref(params), abundances.ctypes.data,
                                                   noise_count.ctypes.data, total_count.ctypes.data, iterations.ctypes.data))
         return abundances, noise_count, total_count, iterations
+
+    def collapse(self, row_offset, row_ptr, col, val, noise, count, prob_precision=1e-8):
+        """rpvg_b200_collapse on numpy arrays. Returns (row_class, n_classes, class_rep, class_count)."""
+        row_offset = np.ascontiguousarray(row_offset, dtype=np.uint64)
+        row_ptr = np.ascontiguousarray(row_ptr, dtype=np.uint64)
+        col = np.ascontiguousarray(col, dtype=np.uint32)
+        val = np.ascontiguousarray(val, dtype=np.float64)
+        noise = np.ascontiguousarray(noise, dtype=np.float64)
+        count = np.ascontiguousarray(count, dtype=np.float64)
+        P, R = len(row_offset) - 1, int(row_offset[-1])
+        row_class = np.zeros(R, dtype=np.uint32)
+        n_classes = np.zeros(P, dtype=np.uint32)
+        class_rep = np.zeros(max(R, 1), dtype=np.uint32)
+        class_count = np.zeros(max(R, 1), dtype=np.float64)
+        pr = CollapseProblems(P, row_offset.ctypes.data, row_ptr.ctypes.data, col.ctypes.data, val.ctypes.data, noise.ctypes.data, count.ctypes.data)
+        self._check(lib().rpvg_b200_collapse(self._h, C.byref(pr), prob_precision, row_class.ctypes.data, n_classes.ctypes.data, class_rep.ctypes.data,
+                                             class_count.ctypes.data))
+        total = int(n_classes.sum())
+        return row_class, n_classes, class_rep[:total], class_count[:total]
 
     def upload(self, arena) -> "Batch":
         cl = clusters_struct(arena)
