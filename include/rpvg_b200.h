@@ -145,6 +145,32 @@ typedef struct {
 int rpvg_b200_collapse(rpvg_b200_ctx * ctx, const rpvg_b200_collapse_problems * problems, double prob_precision, uint32_t * row_class, uint32_t * n_classes,
                        uint32_t * class_rep, double * class_count);
 
+/* ---- EM on path subsets: the many small EMs of the haplotype-transcripts model, the restricted EM of the strains model ----
+ * For every subset s of the paths of cluster subset_cluster[s]: constructPartialProbabilityMatrix
+ * (rpvg:src/path_estimator.cpp:79-113), addNoiseAndNormalizeProbabilityMatrix (:156-166), readCollapseProbabilityMatrix
+ * (:219-259) and EMAbundanceEstimator (rpvg:src/path_abundance_estimator.cpp:47-114) — the body of the loop over sampled
+ * haplotype combinations at rpvg:src/path_abundance_estimator.cpp:625-671 (and of :260-269 for the minimum path cover) —
+ * for all subsets of all clusters in one batched device pipeline. Host pointers in and out.
+ *   abundances  [sum |subset|]  per subset path, in subset order (read counts; 0 below min_em_abundance)
+ *   noise_count, total_count [n_subsets]; iterations [n_subsets] (may be NULL)
+ *   n_classes   [n_subsets] read classes left after the collapse (may be NULL) */
+typedef struct {
+    uint32_t n_subsets;
+    const uint32_t * subset_cluster; /* [n_subsets] cluster of the arena each subset restricts */
+    const uint64_t * subset_offset;  /* [n_subsets + 1] into subset_paths */
+    const uint32_t * subset_paths;   /* cluster-local path indices, strictly ascending within a subset (duplicates removed) */
+} rpvg_b200_subsets;
+
+int rpvg_b200_subset_em(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * clusters, const rpvg_b200_subsets * subsets, const rpvg_b200_em_params * params,
+                        double prob_precision, double * abundances, double * noise_count, double * total_count, uint32_t * iterations, uint32_t * n_classes);
+
+/* ---- strains model: greedy weighted minimum path cover ----
+ * The cover construction of MinimumPathAbundanceEstimator::estimate (rpvg:src/path_abundance_estimator.cpp:229-251:
+ * cover = the non-zero pattern, read counts zeroed for noise-only read classes, weight_j = -sum_i log(p_ij) count_i) and
+ * weightedMinimumPathCover (:297-340) for every cluster of the arena. in_cover [n_paths]: 1 for the paths picked.
+ * (A cluster with one path gets {0}; a cluster whose read classes are all noise-only gets the empty cover.) */
+int rpvg_b200_path_cover(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * clusters, uint8_t * in_cover);
+
 /* ---- EM of one cluster for callers that must not allocate ----
  * No counterpart in the reference (rpvg runs on the host and allocates freely); it exists for callers of this library
  * that cannot call cudaMalloc while they run: code under a fixed device-memory budget sized at start-up, real-time

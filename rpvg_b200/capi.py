@@ -47,6 +47,10 @@ class CollapseProblems(C.Structure):
     _fields_ = [("n_problems", C.c_uint32)] + [(n, C.c_void_p) for n in ("row_offset", "row_ptr", "col", "val", "noise", "count")]
 
 
+class Subsets(C.Structure):
+    _fields_ = [("n_subsets", C.c_uint32), ("subset_cluster", C.c_void_p), ("subset_offset", C.c_void_p), ("subset_paths", C.c_void_p)]
+
+
 def library_path() -> str:
     return _LIB_PATH
 
@@ -75,6 +79,8 @@ def lib():
         l.rpvg_b200_batch_em_timings.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]
         l.rpvg_b200_batch_free.argtypes = [C.c_void_p, C.c_void_p]
         l.rpvg_b200_collapse.argtypes = [C.c_void_p, C.POINTER(CollapseProblems), C.c_double] + [C.c_void_p] * 4
+        l.rpvg_b200_subset_em.argtypes = [C.c_void_p, C.POINTER(Clusters), C.POINTER(Subsets), C.POINTER(EmParams), C.c_double] + [C.c_void_p] * 5
+        l.rpvg_b200_path_cover.argtypes = [C.c_void_p, C.POINTER(Clusters), C.c_void_p]
         l.rpvg_b200_em_cluster_noalloc.argtypes = ([C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint64] + [C.c_void_p] * 5 + [C.POINTER(EmParams)] +
                                                    [C.c_void_p] * 4 + [C.c_char_p, C.c_size_t])
         _lib = l
@@ -173,6 +179,32 @@ class Context:
                                              class_count.ctypes.data))
         total = int(n_classes.sum())
         return row_class, n_classes, class_rep[:total], class_count[:total]
+
+    def subset_em(self, arena, subset_cluster, subsets, params: EmParams | None = None, prob_precision=1e-8):
+        """rpvg_b200_subset_em. ``subsets`` is a list of ascending path-index lists, ``subset_cluster[s]`` the cluster of subset s.
+        Returns (list of abundance arrays, noise_count, total_count, iterations, n_classes)."""
+        params = params or default_em_params()
+        S = len(subsets)
+        subset_cluster = np.ascontiguousarray(subset_cluster, dtype=np.uint32)
+        subset_offset = np.zeros(S + 1, dtype=np.uint64)
+        subset_offset[1:] = np.cumsum([len(x) for x in subsets])
+        subset_paths = np.ascontiguousarray(np.concatenate([np.asarray(x, dtype=np.uint32) for x in subsets]), dtype=np.uint32)
+        abundances = np.zeros(int(subset_offset[-1]), dtype=np.float64)
+        noise_count = np.zeros(S); total_count = np.zeros(S)
+        iterations = np.zeros(S, dtype=np.uint32); n_classes = np.zeros(S, dtype=np.uint32)
+        cl = clusters_struct(arena)
+        ss = Subsets(S, subset_cluster.ctypes.data, subset_offset.ctypes.data, subset_paths.ctypes.data)
+        self._check(lib().rpvg_b200_subset_em(self._h, C.byref(cl), C.byref(ss), C.byref(params), prob_precision, abundances.ctypes.data, noise_count.ctypes.data,
+                                              total_count.ctypes.data, iterations.ctypes.data, n_classes.ctypes.data))
+        parts = [abundances[int(subset_offset[s]):int(subset_offset[s + 1])] for s in range(S)]
+        return parts, noise_count, total_count, iterations, n_classes
+
+    def path_cover(self, arena):
+        """rpvg_b200_path_cover: boolean array [n_paths], True for the paths of the greedy weighted minimum cover."""
+        in_cover = np.zeros(arena.n_paths, dtype=np.uint8)
+        cl = clusters_struct(arena)
+        self._check(lib().rpvg_b200_path_cover(self._h, C.byref(cl), in_cover.ctypes.data))
+        return in_cover.astype(bool)
 
     def upload(self, arena) -> "Batch":
         cl = clusters_struct(arena)

@@ -78,7 +78,7 @@ constexpr int kCollapseSortThreads = 512;
 
 // One CTA per problem: bitonic network (all compare-exchanges ascending, so the virtual +inf padding above n stays put)
 // over sorted[s0, s1), which holds the problem's row ids on entry.
-__global__ void __launch_bounds__(kCollapseSortThreads) collapseSortKernel(const CollapseRows rows, uint32_t * __restrict__ sorted) {
+static __global__ void __launch_bounds__(kCollapseSortThreads) collapseSortKernel(const CollapseRows rows, uint32_t * __restrict__ sorted) {
 
     const uint32_t p = blockIdx.x;
     const uint64_t s0 = rows.problem_row_offset[p];
@@ -148,7 +148,7 @@ __device__ __forceinline__ bool collapseWithinPrecision(const CollapseRows & row
 
 // One thread per problem. sorted[] holds the row ids of every problem in sorted order (problems contiguous).
 // Writes, per sorted position: class index within its problem; per problem: number of classes.
-__global__ void collapseScanKernel(const CollapseRows rows, const uint32_t * __restrict__ sorted, const double prob_precision,
+static __global__ void collapseScanKernel(const CollapseRows rows, const uint32_t * __restrict__ sorted, const double prob_precision,
                                    uint32_t * __restrict__ sorted_class, uint32_t * __restrict__ n_classes) {
 
     const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
@@ -176,7 +176,7 @@ __global__ void collapseScanKernel(const CollapseRows rows, const uint32_t * __r
 
 // Per sorted position: scatter to per-row class ids, mark representatives, add the counts up per class (in sorted
 // order, by the thread of the representative, so the sum order is fixed).
-__global__ void collapseClassesKernel(const CollapseRows rows, const uint32_t * __restrict__ sorted, const uint32_t * __restrict__ sorted_class,
+static __global__ void collapseClassesKernel(const CollapseRows rows, const uint32_t * __restrict__ sorted, const uint32_t * __restrict__ sorted_class,
                                       const uint64_t * __restrict__ class_offset, uint32_t * __restrict__ row_class, uint32_t * __restrict__ class_rep,
                                       double * __restrict__ class_count) {
 

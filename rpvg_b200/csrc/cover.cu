@@ -1,0 +1,271 @@
+// rpvg_b200_path_cover — the greedy weighted minimum path cover of the strains model, for a batch of clusters.
+//
+// Reference semantics restated (never its code): MinimumPathAbundanceEstimator::estimate builds
+//   cover[i][j]  = read class i has path j,
+//   count_i      = read count, 0 when noise_i == 1 under doubleCompare,
+//   weight_j     = - sum_i log(p_ij) * count_i                      (rpvg:src/path_abundance_estimator.cpp:229-251)
+// and weightedMinimumPathCover (:297-340) picks, while any uncovered count is > 0, the FIRST path with the strictly
+// largest (sum of uncovered counts it covers) / weight_j, then zeroes the read classes it covers; one path -> {0}.
+//
+// Device: entries sorted by (global path, read class) with a stable radix sort, so that a column's weight is summed in
+// read-class order like the reference does; one CTA per cluster runs the pick loop: a warp per column for the covered
+// counts (integers, exact in fp64), a block arg-max that prefers the lower index among equal scores, a pass over the
+// picked column to zero its rows. No atomics, deterministic.
+
+#include <cfloat>
+#include <vector>
+
+#include <cub/device/device_radix_sort.cuh>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int kCoverThreads = 256;
+
+__global__ void coverRowsKernel(uint32_t n_clusters, uint64_t n_reads, const uint64_t * __restrict__ read_offset, const uint64_t * __restrict__ path_offset,
+                                const uint64_t * __restrict__ row_ptr, const uint32_t * __restrict__ col, const double * __restrict__ noise,
+                                const uint32_t * __restrict__ count, uint32_t * __restrict__ key, uint32_t * __restrict__ idx, uint32_t * __restrict__ entry_row,
+                                double * __restrict__ cnt, uint32_t * __restrict__ error) {
+
+    const uint64_t r = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (r >= n_reads) { return; }
+
+    const uint32_t c = clusterOf(read_offset, n_clusters, r);
+    const uint64_t base = path_offset[c];
+    const uint64_t num_paths = path_offset[c + 1] - base;
+
+    for (uint64_t e = row_ptr[r]; e < row_ptr[r + 1]; ++e) {
+
+        uint32_t j = col[e];
+        if (j >= num_paths) {
+            atomicOr(error, RPVG_DEV_ERR_COL_RANGE);
+            j = 0;
+        }
+        key[e] = static_cast<uint32_t>(base + j);
+        idx[e] = static_cast<uint32_t>(e);
+        entry_row[e] = static_cast<uint32_t>(r);
+    }
+
+    // doubleCompare(noise, 1): rpvg:src/utils.hpp:87-93
+    const double nz = noise[r];
+    const bool is_noise = (nz == 1.0) || (fabs(nz - 1.0) < fabs(fmin(nz, 1.0)) * (DBL_EPSILON * 100));
+    cnt[r] = is_noise ? 0.0 : static_cast<double>(count[r]);
+}
+
+__global__ void coverColumnPointerKernel(uint64_t n_paths, uint64_t nnz, const uint32_t * __restrict__ sorted_key, uint64_t * __restrict__ col_ptr) {
+
+    const uint64_t j = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (j > n_paths) { return; }
+
+    uint64_t lo = 0, hi = nnz;
+    while (lo < hi) {
+        const uint64_t mid = (lo + hi) >> 1;
+        if (__ldg(sorted_key + mid) >= j) { hi = mid; } else { lo = mid + 1; }
+    }
+    col_ptr[j] = lo;
+}
+
+// thread per path: weight in read-class order; rows of the column
+__global__ void coverWeightsKernel(uint64_t n_paths, const uint64_t * __restrict__ col_ptr, const uint32_t * __restrict__ sorted_idx, const uint32_t * __restrict__ entry_row,
+                                   const double * __restrict__ prob, const double * __restrict__ cnt, uint32_t * __restrict__ csc_row, double * __restrict__ weight) {
+
+    const uint64_t j = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (j >= n_paths) { return; }
+
+    double w = 0;
+    for (uint64_t k = col_ptr[j]; k < col_ptr[j + 1]; ++k) {
+        const uint32_t e = sorted_idx[k];
+        const uint32_t r = entry_row[e];
+        csc_row[k] = r;
+        w += log(prob[e]) * cnt[r];
+    }
+    weight[j] = w * -1;
+}
+
+// one CTA per cluster
+__global__ void __launch_bounds__(kCoverThreads) coverKernel(const uint64_t * __restrict__ read_offset, const uint64_t * __restrict__ path_offset,
+                                                             const uint64_t * __restrict__ col_ptr, const uint32_t * __restrict__ csc_row,
+                                                             const double * __restrict__ weight, double * uncovered, uint8_t * __restrict__ in_cover,
+                                                             const uint32_t * __restrict__ error) {
+
+    __shared__ double best_score[kCoverThreads / 32];
+    __shared__ uint32_t best_index[kCoverThreads / 32];
+    __shared__ int pick_shared;
+
+    if (*error) { return; }
+
+    const uint32_t c = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int num_warps = kCoverThreads / 32;
+
+    const uint64_t r0 = read_offset[c], r1 = read_offset[c + 1];
+    const uint64_t p0 = path_offset[c];
+    const uint32_t N = static_cast<uint32_t>(path_offset[c + 1] - p0);
+
+    for (uint32_t j = tid; j < N; j += kCoverThreads) { in_cover[p0 + j] = 0; }
+
+    if (r1 == r0) { return; }   // the reference does not get here without read classes
+
+    if (N == 1) {
+        if (tid == 0) { in_cover[p0] = 1; }
+        return;
+    }
+
+    __syncthreads();
+
+    for (uint32_t pick_round = 0; pick_round < N; ++pick_round) {
+
+        // while (uncovered_read_counts.maxCoeff() > 0)
+        int any = 0;
+        for (uint64_t r = r0 + tid; r < r1; r += kCoverThreads) { any |= uncovered[r] > 0; }
+        if (!__syncthreads_or(any)) { break; }
+
+        double score = 0;            // strictly-greater-than-0 is what the reference's scan starts from
+        uint32_t index = 0xffffffffu;
+
+        for (uint32_t j = warp; j < N; j += num_warps) {
+
+            double covered = 0;
+            for (uint64_t k = col_ptr[p0 + j] + lane; k < col_ptr[p0 + j + 1]; k += 32) { covered += uncovered[csc_row[k]]; }
+            covered = warpSum(covered);   // integers: exact, order does not matter
+
+            const double s = covered / weight[p0 + j];
+            if (s > score) {   // ascending j per warp: the first maximum of this warp's columns stays
+                score = s;
+                index = j;
+            }
+        }
+
+        if (lane == 0) {
+            best_score[warp] = score;
+            best_index[warp] = index;
+        }
+        __syncthreads();
+
+        if (tid == 0) {
+            double s = 0;
+            uint32_t best = 0xffffffffu;
+            for (int wi = 0; wi < num_warps; ++wi) {
+                if (best_index[wi] != 0xffffffffu && (best_score[wi] > s || (best_score[wi] == s && best_index[wi] < best))) {
+                    s = best_score[wi];
+                    best = best_index[wi];
+                }
+            }
+            pick_shared = static_cast<int>(best);
+        }
+        __syncthreads();
+
+        const uint32_t pick = static_cast<uint32_t>(pick_shared);
+        if (pick == 0xffffffffu) { break; }   // the reference asserts here (no positive score)
+
+        if (tid == 0) { in_cover[p0 + pick] = 1; }
+        for (uint64_t k = col_ptr[p0 + pick] + tid; k < col_ptr[p0 + pick + 1]; k += kCoverThreads) { uncovered[csc_row[k]] = 0; }
+        __syncthreads();
+    }
+}
+
+}
+
+extern "C" int rpvg_b200_path_cover(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, uint8_t * in_cover) {
+
+    if (!ctx || !cl || !in_cover) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "NULL argument"); }
+    if (cl->n_clusters == 0) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "no clusters"); }
+
+    const uint32_t C = cl->n_clusters;
+    const uint64_t R = cl->read_offset[C];
+    const uint64_t P = cl->path_offset[C];
+    const uint64_t Z = R > 0 ? cl->row_ptr[R] : 0;
+
+    if (P >= 0xffffffffull || Z >= 0xffffffffull || R >= 0xffffffffull) { return rpvgFail(ctx, RPVG_B200_ERR_LIMIT, "batch too large (paths, read classes, entries below 2^32)"); }
+
+    RPVG_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+
+    int sort_bits = 1;
+    while ((uint64_t(1) << sort_bits) < P + 1 && sort_bits < 32) { sort_bits++; }
+
+    size_t sort_bytes = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, static_cast<uint32_t *>(nullptr), static_cast<uint32_t *>(nullptr), static_cast<uint32_t *>(nullptr),
+                                    static_cast<uint32_t *>(nullptr), static_cast<int>(Z), 0, sort_bits, s);
+
+    auto pad = [](size_t b) { return (b + 255) & ~size_t(255); };
+    const size_t bytes = 2 * pad(8 * (C + 1)) + pad(8 * (R + 1)) + pad(4 * Z) + pad(8 * Z) + pad(8 * R) + pad(4 * R) + 6 * pad(4 * Z) + pad(8 * R) + pad(8 * (P + 1)) +
+                         pad(8 * P) + pad(P) + pad(sort_bytes) + 1024;
+
+    char * base = nullptr;
+    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&base), bytes, s));
+
+    size_t used = 0;
+    auto take = [&](size_t b) { char * q = base + used; used += pad(b); return q; };
+
+    uint64_t * d_read_offset = reinterpret_cast<uint64_t *>(take(8 * (C + 1)));
+    uint64_t * d_path_offset = reinterpret_cast<uint64_t *>(take(8 * (C + 1)));
+    uint64_t * d_row_ptr = reinterpret_cast<uint64_t *>(take(8 * (R + 1)));
+    uint32_t * d_col = reinterpret_cast<uint32_t *>(take(4 * Z));
+    double * d_prob = reinterpret_cast<double *>(take(8 * Z));
+    double * d_noise = reinterpret_cast<double *>(take(8 * R));
+    uint32_t * d_count = reinterpret_cast<uint32_t *>(take(4 * R));
+    uint32_t * d_key_in = reinterpret_cast<uint32_t *>(take(4 * Z));
+    uint32_t * d_key_out = reinterpret_cast<uint32_t *>(take(4 * Z));
+    uint32_t * d_idx_in = reinterpret_cast<uint32_t *>(take(4 * Z));
+    uint32_t * d_idx_out = reinterpret_cast<uint32_t *>(take(4 * Z));
+    uint32_t * d_entry_row = reinterpret_cast<uint32_t *>(take(4 * Z));
+    uint32_t * d_csc_row = reinterpret_cast<uint32_t *>(take(4 * Z));
+    double * d_cnt = reinterpret_cast<double *>(take(8 * R));
+    uint64_t * d_col_ptr = reinterpret_cast<uint64_t *>(take(8 * (P + 1)));
+    double * d_weight = reinterpret_cast<double *>(take(8 * P));
+    uint8_t * d_in_cover = reinterpret_cast<uint8_t *>(take(P));
+    void * d_sort_temp = take(sort_bytes);
+    uint32_t * d_error = reinterpret_cast<uint32_t *>(take(4));
+
+    cudaError_t err = cudaSuccess;
+    int status = RPVG_B200_OK;
+
+    #define RPVG_STEP(call) if (err == cudaSuccess) { err = (call); }
+    #define RPVG_H2D(dst, src, n) if (err == cudaSuccess && (n) > 0) { err = cudaMemcpyAsync((dst), (src), (n), cudaMemcpyHostToDevice, s); }
+
+    RPVG_H2D(d_read_offset, cl->read_offset, 8 * (C + 1))
+    RPVG_H2D(d_path_offset, cl->path_offset, 8 * (C + 1))
+    RPVG_H2D(d_row_ptr, cl->row_ptr, 8 * (R + 1))
+    RPVG_H2D(d_col, cl->col, 4 * Z)
+    RPVG_H2D(d_prob, cl->prob, 8 * Z)
+    RPVG_H2D(d_noise, cl->noise, 8 * R)
+    RPVG_H2D(d_count, cl->count, 4 * R)
+    RPVG_STEP(cudaMemsetAsync(d_error, 0, 4, s))
+
+    if (err == cudaSuccess && R > 0) {
+        coverRowsKernel<<<static_cast<unsigned>((R + 255) / 256), 256, 0, s>>>(C, R, d_read_offset, d_path_offset, d_row_ptr, d_col, d_noise, d_count, d_key_in, d_idx_in,
+                                                                               d_entry_row, d_cnt, d_error);
+        ctx->launches++;
+        err = cudaGetLastError();
+    }
+
+    if (err == cudaSuccess && Z > 0) {
+        size_t temp = sort_bytes;
+        err = cub::DeviceRadixSort::SortPairs(d_sort_temp, temp, d_key_in, d_key_out, d_idx_in, d_idx_out, static_cast<int>(Z), 0, sort_bits, s);
+        ctx->launches += 2 + (sort_bits + 7) / 8;
+    }
+
+    if (err == cudaSuccess) {
+        coverColumnPointerKernel<<<static_cast<unsigned>((P + 1 + 255) / 256), 256, 0, s>>>(P, Z, d_key_out, d_col_ptr);
+        coverWeightsKernel<<<static_cast<unsigned>((P + 255) / 256), 256, 0, s>>>(P, d_col_ptr, d_idx_out, d_entry_row, d_prob, d_cnt, d_csc_row, d_weight);
+        coverKernel<<<C, kCoverThreads, 0, s>>>(d_read_offset, d_path_offset, d_col_ptr, d_csc_row, d_weight, d_cnt, d_in_cover, d_error);
+        ctx->launches += 3;
+        err = cudaGetLastError();
+    }
+
+    uint32_t dev_error = 0;
+    RPVG_STEP(cudaMemcpyAsync(in_cover, d_in_cover, P, cudaMemcpyDeviceToHost, s))
+    RPVG_STEP(cudaMemcpyAsync(&dev_error, d_error, 4, cudaMemcpyDeviceToHost, s))
+    RPVG_STEP(cudaStreamSynchronize(s))
+
+    #undef RPVG_STEP
+    #undef RPVG_H2D
+
+    if (err != cudaSuccess) { status = rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("rpvg_b200_path_cover: ") + cudaGetErrorString(err)); }
+    else if (dev_error) { status = rpvgFail(ctx, RPVG_B200_ERR_INVALID, "malformed cluster arena: path index out of range"); }
+
+    cudaFreeAsync(base, s);
+    return status;
+}

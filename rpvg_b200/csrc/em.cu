@@ -27,113 +27,7 @@
 #include "common.cuh"
 #include "em_kernels.cuh"
 #include "em_sell.cuh"
-
-namespace {
-
-struct DevicePool {
-
-    // One cudaMallocAsync region, carved in 256-byte aligned pieces.
-    char * base = nullptr;
-    size_t size = 0;
-    size_t used = 0;
-
-    template <typename T>
-    T * take(size_t n) {
-        used = (used + 255) & ~size_t(255);
-        T * p = reinterpret_cast<T *>(base + used);
-        used += n * sizeof(T);
-        return p;
-    }
-};
-
-template <typename T>
-size_t padded(size_t n) { return ((n * sizeof(T)) + 255) & ~size_t(255); }
-
-}
-
-struct rpvg_b200_batch {
-
-    uint32_t n_clusters = 0;
-    uint64_t n_reads = 0;
-    uint64_t n_paths = 0;
-    uint64_t nnz = 0;
-
-    std::vector<uint64_t> h_read_offset;
-    std::vector<uint64_t> h_path_offset;
-    std::vector<uint64_t> h_cluster_nnz;   // path non-zeros per cluster
-    std::vector<uint32_t> h_iterations;
-
-    // launch plan of the EM: clusters binned by thread-block-cluster size, shared-memory tier and index width
-    struct EmBin {
-        uint32_t group_size;   // CTAs per path cluster; 0 = fallback kernel (one CTA, everything in global memory)
-        uint32_t threads;
-        uint32_t smem;
-        uint32_t index_bytes;  // 2 or 4
-        uint32_t first;        // offset into d_order / d_group_scratch / d_group_cta_bytes
-        uint32_t count;
-    };
-    std::vector<EmBin> bins;
-    uint64_t scratch_bytes = 0;
-
-    DevicePool pool;
-
-    // inputs
-    uint64_t * d_read_offset = nullptr;
-    uint64_t * d_path_offset = nullptr;
-    uint64_t * d_row_ptr = nullptr;
-    uint32_t * d_col = nullptr;
-    double * d_prob = nullptr;
-    double * d_noise = nullptr;
-    uint32_t * d_count = nullptr;
-    uint32_t * d_order = nullptr;
-    uint64_t * d_group_scratch = nullptr;
-    uint64_t * d_group_cta_bytes = nullptr;
-
-    // built: read classes re-ordered by first path (sorted CSR), then the column-major copy
-    uint64_t * d_rowkey_in = nullptr;
-    uint64_t * d_rowkey_out = nullptr;
-    uint32_t * d_rowid_in = nullptr;
-    uint32_t * d_perm = nullptr;            // sorted position -> original read class
-    uint64_t * d_sorted_len = nullptr;
-    uint64_t * d_sorted_row_ptr = nullptr;
-    uint32_t * d_sorted_col = nullptr;
-    double * d_sorted_noise = nullptr;
-    void * d_rowsort_temp = nullptr;
-    size_t rowsort_temp_bytes = 0;
-    void * d_scan_temp = nullptr;
-    size_t scan_temp_bytes = 0;
-    int rowsort_bits = 64;
-    double * d_val = nullptr;
-    double * d_cnt = nullptr;
-    uint32_t * d_entry_row = nullptr;
-    uint32_t * d_key_in = nullptr;
-    uint32_t * d_key_out = nullptr;
-    uint32_t * d_idx_in = nullptr;
-    uint32_t * d_idx_out = nullptr;
-    uint64_t * d_col_ptr = nullptr;
-    uint32_t * d_csc_row = nullptr;
-    double * d_csc_val = nullptr;
-    void * d_sort_temp = nullptr;
-    size_t sort_temp_bytes = 0;
-    int sort_bits = 32;
-
-    // EM state + results
-    double * d_abund = nullptr;   // fallback kernel only: per cluster N_c + 1 relative abundances (noise last)
-    double * d_w = nullptr;       // fallback kernel only
-    unsigned char * d_scratch = nullptr;
-    double * d_abundances = nullptr;
-    double * d_noise_count = nullptr;
-    double * d_total_count = nullptr;
-    uint32_t * d_iterations = nullptr;
-    uint32_t * d_error = nullptr;
-
-    bool have_results = false;
-
-    // device timestamps around the two phases of rpvg_b200_batch_em (bench.py's roofline numbers)
-    cudaEvent_t ev_start = nullptr;
-    cudaEvent_t ev_built = nullptr;
-    cudaEvent_t ev_done = nullptr;
-};
+#include "em_batch.cuh"
 
 namespace {
 
@@ -178,7 +72,8 @@ __global__ void buildRowsKernel(uint32_t n_clusters, uint64_t n_reads,
                                 const uint32_t * __restrict__ perm, const uint64_t * __restrict__ sorted_row_ptr,
                                 uint32_t * __restrict__ sorted_col, double * __restrict__ sorted_noise,
                                 double * __restrict__ val, double * __restrict__ cnt, uint32_t * __restrict__ entry_row,
-                                uint32_t * __restrict__ key, uint32_t * __restrict__ idx, uint32_t * __restrict__ error) {
+                                uint32_t * __restrict__ key, uint32_t * __restrict__ idx, uint32_t * __restrict__ error,
+                                const double * __restrict__ count_f64, const int prenormalised) {
 
     const uint64_t p = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
     if (p >= n_reads) { return; }
@@ -216,8 +111,11 @@ __global__ void buildRowsKernel(uint32_t n_clusters, uint64_t n_reads,
 
     for (uint64_t e = e0; e < e1; ++e) {
 
-        double v = (prob[e] / row_sum) * scale;
-        if (isnan(v)) { v = 0; }
+        double v = prob[e];
+        if (!prenormalised) {
+            v = (v / row_sum) * scale;
+            if (isnan(v)) { v = 0; }
+        }
 
         const uint64_t o = out + (e - e0);
         const uint32_t j = static_cast<uint32_t>(min(static_cast<uint64_t>(col[e]), num_paths - 1));
@@ -230,7 +128,7 @@ __global__ void buildRowsKernel(uint32_t n_clusters, uint64_t n_reads,
     }
 
     sorted_noise[p] = noise[r];
-    cnt[p] = static_cast<double>(count[r]);
+    cnt[p] = prenormalised ? count_f64[r] : static_cast<double>(count[r]);
 
     if (err) { atomicOr(error, err); }
 }
@@ -544,45 +442,25 @@ int rpvgEmInit(rpvg_b200_ctx * ctx) {
     return RPVG_B200_OK;
 }
 
-extern "C" {
+int rpvgBatchCreate(rpvg_b200_ctx * ctx, uint32_t n_clusters, const uint64_t * read_offset, const uint64_t * path_offset, const uint64_t * cluster_nnz,
+                    bool prenormalised, rpvg_b200_batch ** out_batch) {
 
-void rpvg_b200_em_params_default(rpvg_b200_em_params * params) {
-
-    params->max_em_its = 10000;
-    params->max_rel_em_conv = 0.001;
-    params->min_em_conv_its = 10;
-    params->min_em_abundance = 1e-8;
-}
-
-int rpvg_b200_batch_upload(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, rpvg_b200_batch ** out_batch) {
-
-    if (!ctx || !out_batch) { return RPVG_B200_ERR_INVALID; }
     *out_batch = nullptr;
-
-    int status = checkClusters(ctx, cl);
-    if (status != RPVG_B200_OK) { return status; }
 
     RPVG_CUDA(ctx, cudaSetDevice(ctx->device));
 
     auto * b = new rpvg_b200_batch();
-    b->n_clusters = cl->n_clusters;
-    b->n_reads = cl->read_offset[cl->n_clusters];
-    b->n_paths = cl->path_offset[cl->n_clusters];
-    b->nnz = cl->row_ptr[b->n_reads];
+    b->n_clusters = n_clusters;
+    b->n_reads = read_offset[n_clusters];
+    b->n_paths = path_offset[n_clusters];
+    b->prenormalised = prenormalised;
 
-    b->h_read_offset.assign(cl->read_offset, cl->read_offset + cl->n_clusters + 1);
-    b->h_path_offset.assign(cl->path_offset, cl->path_offset + cl->n_clusters + 1);
-    b->h_cluster_nnz.resize(cl->n_clusters);
+    b->h_read_offset.assign(read_offset, read_offset + n_clusters + 1);
+    b->h_path_offset.assign(path_offset, path_offset + n_clusters + 1);
+    b->h_cluster_nnz.assign(cluster_nnz, cluster_nnz + n_clusters);
 
-    for (uint32_t c = 0; c < cl->n_clusters; ++c) {
-        const uint64_t lo = cl->row_ptr[cl->read_offset[c]];
-        const uint64_t hi = cl->row_ptr[cl->read_offset[c + 1]];
-        if (hi < lo) {
-            delete b;
-            return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "row_ptr must be non-decreasing");
-        }
-        b->h_cluster_nnz[c] = hi - lo;
-    }
+    b->nnz = 0;
+    for (uint32_t c = 0; c < n_clusters; ++c) { b->nnz += cluster_nnz[c]; }
 
     std::vector<uint32_t> order;
     std::vector<uint64_t> group_scratch;
@@ -613,7 +491,7 @@ int rpvg_b200_batch_upload(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, r
     bytes += ((b->sort_temp_bytes + 255) & ~size_t(255));
     bytes += padded<double>(P + C) + padded<double>(R) + padded<double>(P) + 2 * padded<double>(C) + padded<uint32_t>(C) + padded<uint32_t>(1);
     bytes += ((b->scratch_bytes + 255) & ~size_t(255));
-    bytes += 8192;
+    bytes += padded<double>(R) + 8192;
 
     cudaError_t err = cudaMallocAsync(reinterpret_cast<void **>(&b->pool.base), bytes, ctx->stream);
     if (err != cudaSuccess) {
@@ -630,6 +508,7 @@ int rpvg_b200_batch_upload(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, r
     b->d_prob = pool.take<double>(Z);
     b->d_noise = pool.take<double>(R);
     b->d_count = pool.take<uint32_t>(R);
+    b->d_count_f64 = pool.take<double>(R);
     b->d_order = pool.take<uint32_t>(C);
     b->d_group_scratch = pool.take<uint64_t>(C);
     b->d_group_cta_bytes = pool.take<uint64_t>(C);
@@ -681,13 +560,8 @@ int rpvg_b200_batch_upload(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, r
             }                                                                                                       \
         }
 
-    RPVG_UPLOAD(b->d_read_offset, cl->read_offset, C + 1, uint64_t)
-    RPVG_UPLOAD(b->d_path_offset, cl->path_offset, C + 1, uint64_t)
-    RPVG_UPLOAD(b->d_row_ptr, cl->row_ptr, R + 1, uint64_t)
-    RPVG_UPLOAD(b->d_col, cl->col, Z, uint32_t)
-    RPVG_UPLOAD(b->d_prob, cl->prob, Z, double)
-    RPVG_UPLOAD(b->d_noise, cl->noise, R, double)
-    RPVG_UPLOAD(b->d_count, cl->count, R, uint32_t)
+    RPVG_UPLOAD(b->d_read_offset, read_offset, C + 1, uint64_t)
+    RPVG_UPLOAD(b->d_path_offset, path_offset, C + 1, uint64_t)
     // the plan vectors are temporaries: the synchronize below keeps them alive long enough
     RPVG_UPLOAD(b->d_order, order.data(), C, uint32_t)
     RPVG_UPLOAD(b->d_group_scratch, group_scratch.data(), C, uint64_t)
@@ -699,6 +573,57 @@ int rpvg_b200_batch_upload(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, r
         cudaFreeAsync(pool.base, s);
         delete b;
         return rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("upload synchronize: ") + cudaGetErrorString(err));
+    }
+
+    *out_batch = b;
+    return RPVG_B200_OK;
+}
+
+extern "C" {
+
+void rpvg_b200_em_params_default(rpvg_b200_em_params * params) {
+
+    params->max_em_its = 10000;
+    params->max_rel_em_conv = 0.001;
+    params->min_em_conv_its = 10;
+    params->min_em_abundance = 1e-8;
+}
+
+int rpvg_b200_batch_upload(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, rpvg_b200_batch ** out_batch) {
+
+    if (!ctx || !out_batch) { return RPVG_B200_ERR_INVALID; }
+    *out_batch = nullptr;
+
+    int status = checkClusters(ctx, cl);
+    if (status != RPVG_B200_OK) { return status; }
+
+    std::vector<uint64_t> cluster_nnz(cl->n_clusters);
+
+    for (uint32_t c = 0; c < cl->n_clusters; ++c) {
+        const uint64_t lo = cl->row_ptr[cl->read_offset[c]];
+        const uint64_t hi = cl->row_ptr[cl->read_offset[c + 1]];
+        if (hi < lo) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "row_ptr must be non-decreasing"); }
+        cluster_nnz[c] = hi - lo;
+    }
+
+    rpvg_b200_batch * b = nullptr;
+    status = rpvgBatchCreate(ctx, cl->n_clusters, cl->read_offset, cl->path_offset, cluster_nnz.data(), false, &b);
+    if (status != RPVG_B200_OK) { return status; }
+
+    const uint64_t R = b->n_reads, Z = b->nnz;
+    cudaStream_t s = ctx->stream;
+    cudaError_t err = cudaSuccess;
+
+    if (err == cudaSuccess) { err = cudaMemcpyAsync(b->d_row_ptr, cl->row_ptr, (R + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, s); }
+    if (err == cudaSuccess && Z > 0) { err = cudaMemcpyAsync(b->d_col, cl->col, Z * sizeof(uint32_t), cudaMemcpyHostToDevice, s); }
+    if (err == cudaSuccess && Z > 0) { err = cudaMemcpyAsync(b->d_prob, cl->prob, Z * sizeof(double), cudaMemcpyHostToDevice, s); }
+    if (err == cudaSuccess && R > 0) { err = cudaMemcpyAsync(b->d_noise, cl->noise, R * sizeof(double), cudaMemcpyHostToDevice, s); }
+    if (err == cudaSuccess && R > 0) { err = cudaMemcpyAsync(b->d_count, cl->count, R * sizeof(uint32_t), cudaMemcpyHostToDevice, s); }
+    if (err == cudaSuccess) { err = cudaStreamSynchronize(s); }
+
+    if (err != cudaSuccess) {
+        rpvg_b200_batch_free(ctx, b);
+        return rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("arena upload: ") + cudaGetErrorString(err));
     }
 
     *out_batch = b;
@@ -744,7 +669,7 @@ int rpvg_b200_batch_em(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const rpvg_b200
 
         buildRowsKernel<<<grid, 256, 0, s>>>(b->n_clusters, b->n_reads, b->d_read_offset, b->d_path_offset, b->d_row_ptr, b->d_col, b->d_prob,
                                              b->d_noise, b->d_count, b->d_perm, b->d_sorted_row_ptr, b->d_sorted_col, b->d_sorted_noise,
-                                             b->d_val, b->d_cnt, b->d_entry_row, b->d_key_in, b->d_idx_in, b->d_error);
+                                             b->d_val, b->d_cnt, b->d_entry_row, b->d_key_in, b->d_idx_in, b->d_error, b->d_count_f64, b->prenormalised ? 1 : 0);
         RPVG_LAUNCHED(ctx);
 
     } else {

@@ -86,6 +86,45 @@ void generateGroupsRecursive(vector<vector<uint32_t> > * sets, const uint32_t nu
     abort();
 }
 
+// One cluster as a one-cluster arena: every pair<double, vector<uint32_t>> expanded, entries of a read class sorted by path.
+struct FlatCluster {
+
+    vector<uint64_t> read_offset, path_offset, row_ptr;
+    vector<uint32_t> col, count;
+    vector<double> prob, noise;
+
+    FlatCluster(const vector<ReadPathProbabilities> & cluster_probs, const uint32_t num_paths) {
+
+        read_offset = {0, cluster_probs.size()};
+        path_offset = {0, num_paths};
+        row_ptr = {0};
+
+        vector<pair<uint32_t, double> > row;
+
+        for (auto & read_probs: cluster_probs) {
+
+            row.clear();
+            for (auto & path_probs: read_probs.pathProbs()) {
+                for (auto & path: path_probs.second) { row.emplace_back(path, path_probs.first); }
+            }
+            sort(row.begin(), row.end());
+
+            for (auto & entry: row) {
+                col.push_back(entry.first);
+                prob.push_back(entry.second);
+            }
+
+            row_ptr.push_back(col.size());
+            noise.push_back(read_probs.noiseProb());
+            count.push_back(read_probs.readCount());
+        }
+    }
+
+    rpvg_b200_clusters view() const {
+        return rpvg_b200_clusters{1, read_offset.data(), path_offset.data(), row_ptr.data(), col.data(), prob.data(), noise.data(), count.data()};
+    }
+};
+
 // sum_r count_r log(noise_r + sum_p col_p / k) for each set, on the device
 vector<double> deviceLogLikelihoods(rpvg_b200_ctx * ctx, const vector<double> & matrix, const vector<double> & noise, const vector<double> & counts,
                                     const uint32_t num_paths, const uint32_t group_size, const vector<uint32_t> & flat_sets) {
@@ -298,33 +337,8 @@ void PathAbundanceEstimator::estimate(PathClusterEstimates * path_cluster_estima
 
     if (cluster_probs.empty()) { return; }
 
-    // the cluster as a one-cluster arena: entries of a read class sorted by path index
-    vector<uint64_t> read_offset = {0, cluster_probs.size()};
-    vector<uint64_t> path_offset = {0, path_cluster_estimates->paths.size()};
-    vector<uint64_t> row_ptr = {0};
-    vector<uint32_t> col, count;
-    vector<double> prob, noise;
-    vector<pair<uint32_t, double> > row;
-
-    for (auto & read_probs: cluster_probs) {
-
-        row.clear();
-        for (auto & path_probs: read_probs.pathProbs()) {
-            for (auto & path: path_probs.second) { row.emplace_back(path, path_probs.first); }
-        }
-        sort(row.begin(), row.end());
-
-        for (auto & entry: row) {
-            col.push_back(entry.first);
-            prob.push_back(entry.second);
-        }
-
-        row_ptr.push_back(col.size());
-        noise.push_back(read_probs.noiseProb());
-        count.push_back(read_probs.readCount());
-    }
-
-    rpvg_b200_clusters clusters = {1, read_offset.data(), path_offset.data(), row_ptr.data(), col.data(), prob.data(), noise.data(), count.data()};
+    const FlatCluster flat(cluster_probs, path_cluster_estimates->paths.size());
+    rpvg_b200_clusters clusters = flat.view();
 
     rpvg_b200_em_params params;
     rpvg_b200_em_params_default(&params);
@@ -344,7 +358,51 @@ MinimumPathAbundanceEstimator::MinimumPathAbundanceEstimator(const uint32_t max_
 
 void MinimumPathAbundanceEstimator::estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng) {
 
-    notBuiltYet("the strains model (MinimumPathAbundanceEstimator)");
+    const uint32_t num_paths = path_cluster_estimates->paths.size();
+    path_cluster_estimates->resetEstimates(num_paths, 1);
+
+    if (cluster_probs.empty()) { return; }
+
+    const FlatCluster flat(cluster_probs, num_paths);
+    rpvg_b200_clusters clusters = flat.view();
+
+    auto * ctx = threadContext();
+
+    // rpvg:src/path_abundance_estimator.cpp:229-252
+    vector<uint8_t> in_cover(num_paths, 0);
+    if (rpvg_b200_path_cover(ctx, &clusters, in_cover.data()) != RPVG_B200_OK) { fatal(ctx, "rpvg_b200_path_cover"); }
+
+    vector<uint32_t> min_path_cover;
+    for (uint32_t j = 0; j < num_paths; ++j) {
+        if (in_cover[j]) { min_path_cover.push_back(j); }
+    }
+
+    if (min_path_cover.empty()) { return; }
+
+    // :254-269 partial matrix on the cover, normalise, collapse, EM
+    const uint32_t subset_cluster = 0;
+    const uint64_t subset_offset[2] = {0, min_path_cover.size()};
+    rpvg_b200_subsets subsets = {1, &subset_cluster, subset_offset, min_path_cover.data()};
+
+    rpvg_b200_em_params params;
+    rpvg_b200_em_params_default(&params);
+    params.max_em_its = max_em_its;
+    params.max_rel_em_conv = max_rel_em_conv;
+
+    vector<double> cover_abundances(min_path_cover.size(), 0);
+    double noise_count = 0, total_count = 0;
+
+    if (rpvg_b200_subset_em(ctx, &clusters, &subsets, &params, prob_precision, cover_abundances.data(), &noise_count, &total_count, nullptr, nullptr) != RPVG_B200_OK) {
+        fatal(ctx, "rpvg_b200_subset_em");
+    }
+
+    if (num_gibbs_samples > 0) { notBuiltYet("the Gibbs read-count sampler (--num-gibbs-samples)"); }
+
+    // :286-292
+    for (size_t i = 0; i < min_path_cover.size(); ++i) { path_cluster_estimates->abundances.at(min_path_cover.at(i)) += cover_abundances.at(i); }
+
+    path_cluster_estimates->noise_count = noise_count;
+    path_cluster_estimates->total_count = total_count;
 }
 
 NestedPathAbundanceEstimator::NestedPathAbundanceEstimator(const uint32_t group_size_in, const double min_hap_prob_in, const bool infer_collapsed_in, const bool use_group_post_gibbs_in, const uint32_t max_em_its, const double max_rel_em_conv, const uint32_t num_gibbs_samples, const uint32_t gibbs_thin_its, const double prob_precision) : PathAbundanceEstimator(max_em_its, max_rel_em_conv, num_gibbs_samples, gibbs_thin_its, prob_precision), group_size(group_size_in), min_hap_prob(min_hap_prob_in), infer_collapsed(infer_collapsed_in), use_group_post_gibbs(use_group_post_gibbs_in) {}
