@@ -164,6 +164,24 @@ typedef struct {
 int rpvg_b200_subset_em(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * clusters, const rpvg_b200_subsets * subsets, const rpvg_b200_em_params * params,
                         double prob_precision, double * abundances, double * noise_count, double * total_count, uint32_t * iterations, uint32_t * n_classes);
 
+/* ---- haplotype-transcripts model: the grouped, normalised, collapsed matrix the haplotype posteriors are computed on ----
+ * Per cluster: constructGroupedProbabilityMatrix (rpvg:src/path_estimator.cpp:115-154: column g = sum over the paths of
+ * group g), addNoiseAndNormalizeProbabilityMatrix (:156-166), readCollapseProbabilityMatrix (:219-259), noise column
+ * split off again (rpvg:src/path_abundance_estimator.cpp:440-446). With one group per path of a transcript it is the
+ * partial-matrix variant of inferAbundancesIndependentGroups (:377-383).
+ *   n_classes [n_clusters]   read classes left per cluster
+ *   matrix    capacity sum_c M_c x G_c; cluster c's block starts at sum_{c' < c} M_c' x G_c' and holds
+ *             n_classes[c] x G_c doubles, column-major (leading dimension n_classes[c])
+ *   noise, counts capacity n_reads; cluster c's values start at read_offset[c] (first n_classes[c] entries) */
+typedef struct {
+    const uint64_t * group_offset;   /* [n_clusters + 1] groups of cluster c */
+    const uint64_t * group_path_ptr; /* [n_groups + 1] */
+    const uint32_t * group_paths;    /* cluster-local path indices */
+} rpvg_b200_path_groups;
+
+int rpvg_b200_grouped_collapse(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * clusters, const rpvg_b200_path_groups * groups, double prob_precision,
+                               uint32_t * n_classes, double * matrix, double * noise, double * counts);
+
 /* ---- strains model: greedy weighted minimum path cover ----
  * The cover construction of MinimumPathAbundanceEstimator::estimate (rpvg:src/path_abundance_estimator.cpp:229-251:
  * cover = the non-zero pattern, read counts zeroed for noise-only read classes, weight_j = -sum_i log(p_ij) count_i) and

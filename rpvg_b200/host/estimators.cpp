@@ -405,13 +405,6 @@ void MinimumPathAbundanceEstimator::estimate(PathClusterEstimates * path_cluster
     path_cluster_estimates->total_count = total_count;
 }
 
-NestedPathAbundanceEstimator::NestedPathAbundanceEstimator(const uint32_t group_size_in, const double min_hap_prob_in, const bool infer_collapsed_in, const bool use_group_post_gibbs_in, const uint32_t max_em_its, const double max_rel_em_conv, const uint32_t num_gibbs_samples, const uint32_t gibbs_thin_its, const double prob_precision) : PathAbundanceEstimator(max_em_its, max_rel_em_conv, num_gibbs_samples, gibbs_thin_its, prob_precision), group_size(group_size_in), min_hap_prob(min_hap_prob_in), infer_collapsed(infer_collapsed_in), use_group_post_gibbs(use_group_post_gibbs_in) {}
-
-void NestedPathAbundanceEstimator::estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng) {
-
-    notBuiltYet("the haplotype-transcripts model (NestedPathAbundanceEstimator)");
-}
-
 // ---- haplotypes ------------------------------------------------------------------------------------------------------
 
 static const double min_rel_likelihood = 1e-8;   // rpvg:src/path_posterior_estimator.cpp:5

@@ -16,8 +16,15 @@
 
 #ifdef RPVG_B200_WITH_RPVG_HEADERS
 
+#include "sparsepp/spp.h"
 #include "path_cluster_estimates.hpp"
 #include "read_path_probabilities.hpp"
+#include "path_estimator.hpp"   // std::hash<vector<uint32_t>>
+
+namespace rpvg_b200_host {
+template <class K> using hash_set = spp::sparse_hash_set<K>;
+template <class K, class V> using hash_map = spp::sparse_hash_map<K, V>;
+}
 
 #else
 
@@ -107,6 +114,26 @@ class ReadPathProbabilities {
         double prob_precision;
 };
 
+// rpvg:src/path_estimator.hpp:51-68 — the hash the nested model's maps of path lists are keyed with; it decides their
+// iteration order, which is observable in the output.
+namespace std {
+
+    template<>
+    struct hash<vector<uint32_t> > {
+
+        size_t operator()(vector<uint32_t> const & vec) const {
+
+            size_t seed = 0;
+#ifdef RPVG_B200_HAVE_SPARSEPP
+            for (auto & val: vec) { spp::hash_combine(seed, val); }
+#else
+            for (auto & val: vec) { seed ^= std::hash<uint32_t>()(val) + 0x9e3779b9 + (seed << 6) + (seed >> 2); }
+#endif
+            return seed;
+        }
+    };
+}
+
 #endif
 
 struct rpvg_b200_ctx;
@@ -179,6 +206,19 @@ class NestedPathAbundanceEstimator : public PathAbundanceEstimator {
 
         const bool infer_collapsed;
         const bool use_group_post_gibbs;
+
+        typedef rpvg_b200_host::hash_map<vector<uint32_t>, double> SubsetSamples;
+
+        void inferAbundancesIndependentGroups(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng) const;
+        void inferAbundancesCollapsedGroups(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng) const;
+
+        // group posteriors on the grouped + normalised + collapsed matrix of the given path groups
+        void groupPosteriors(PathClusterEstimates * group_estimates, const vector<ReadPathProbabilities> & cluster_probs, const uint32_t num_paths, const vector<vector<uint32_t> > & path_groups, const vector<uint32_t> & group_counts) const;
+
+        vector<vector<uint32_t> > findPathGroups(const vector<PathInfo> & paths) const;
+        pair<vector<vector<uint32_t> >, vector<uint32_t> > findPathSourceGroups(const vector<PathInfo> & paths) const;
+
+        void inferPathSubsetAbundance(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng, const SubsetSamples & path_subset_samples) const;
 };
 
 class PathPosteriorEstimator : public PathEstimator {
