@@ -327,6 +327,108 @@ void PathEstimator::calculatePathGroupPosteriorsBounded(PathClusterEstimates * p
     for (auto & ll: log_likelihoods) { path_cluster_estimates->posteriors.emplace_back(exp(ll - sum_log_posterior)); }
 }
 
+void PathEstimator::estimatePathGroupPosteriorsGibbs(PathClusterEstimates * path_cluster_estimates, const vector<double> & matrix, const vector<double> & noise, const vector<double> & counts, const uint32_t num_paths, const vector<uint32_t> & path_counts, const uint32_t group_size, mt19937 * mt_rng) const {
+
+    assert(group_size > 0);
+    assert(group_size <= 8);
+
+    auto path_log_freqs = calcPathLogFrequences(path_counts);
+
+    path_cluster_estimates->resetEstimates(0, 0);
+
+    uniform_int_distribution<uint32_t> init_path_sampler(0, num_paths - 1);
+
+    // Neither map's iteration order is observable (one is a cache, the other a first-seen index).
+    rpvg_b200_host::hash_map<vector<uint32_t>, discrete_distribution<uint32_t> > group_path_sampler_cache;
+    rpvg_b200_host::hash_map<vector<uint32_t>, uint32_t> path_group_sets_indices;
+
+    vector<uint32_t> path_group_sample_counts;
+
+    const uint32_t num_gibbs_chains = 10 + round(0.01 * group_size * num_paths);
+    const uint32_t num_burn_its = 50 + round(0.025 * group_size * num_paths);
+    const uint32_t num_gibbs_its = 100 + round(0.05 * group_size * num_paths);
+
+    auto * ctx = threadContext();
+
+    // Conditional of one slot given the others: log-likelihood of {others} + {k} for every path k. The device adds
+    // noise + col / group_size over the set in the order given: the other slots first, the candidate last, like the
+    // reference does.
+    auto conditional = [&](const vector<uint32_t> & others) {
+
+        vector<uint32_t> flat_sets;
+        flat_sets.reserve(static_cast<size_t>(num_paths) * group_size);
+
+        for (uint32_t k = 0; k < num_paths; ++k) {
+            flat_sets.insert(flat_sets.end(), others.begin(), others.end());
+            flat_sets.push_back(k);
+        }
+
+        auto group_probs = deviceLogLikelihoods(ctx, matrix, noise, counts, num_paths, group_size, flat_sets);
+
+        double sum_log_group_probs = numeric_limits<double>::lowest();
+
+        for (uint32_t k = 0; k < num_paths; ++k) {
+            group_probs.at(k) += path_log_freqs.at(k);
+            sum_log_group_probs = add_log(sum_log_group_probs, group_probs.at(k));
+        }
+
+        for (auto & prob: group_probs) { prob = exp(prob - sum_log_group_probs); }
+
+        return discrete_distribution<uint32_t>(group_probs.begin(), group_probs.end());
+    };
+
+    vector<uint32_t> cur_sampled_group_paths;
+    cur_sampled_group_paths.reserve(group_size);
+
+    for (uint32_t c = 0; c < num_gibbs_chains; ++c) {
+
+        cur_sampled_group_paths.clear();
+        for (uint32_t i = 0; i < group_size; ++i) { cur_sampled_group_paths.emplace_back(init_path_sampler(*mt_rng)); }
+
+        for (uint32_t i = 0; i < num_burn_its + num_gibbs_its; ++i) {
+
+            for (uint32_t j = 0; j < group_size; ++j) {
+
+                vector<uint32_t> key = cur_sampled_group_paths;
+                key.at(j) = num_paths;
+                sort(key.begin(), key.end());
+
+                auto cache_it = group_path_sampler_cache.emplace(key, discrete_distribution<uint32_t>());
+
+                if (cache_it.second) {
+
+                    vector<uint32_t> others;
+                    for (uint32_t k = 0; k < group_size; ++k) {
+                        if (j != k) { others.emplace_back(cur_sampled_group_paths.at(k)); }
+                    }
+                    cache_it.first->second = conditional(others);
+                }
+
+                cur_sampled_group_paths.at(j) = cache_it.first->second(*mt_rng);
+            }
+
+            if (i >= num_burn_its) {
+
+                vector<uint32_t> sorted_paths = cur_sampled_group_paths;
+                sort(sorted_paths.begin(), sorted_paths.end());
+
+                auto index_it = path_group_sets_indices.emplace(sorted_paths, path_cluster_estimates->path_group_sets.size());
+
+                if (index_it.second) {
+                    path_cluster_estimates->path_group_sets.emplace_back(sorted_paths);
+                    path_group_sample_counts.emplace_back(1);
+                } else {
+                    path_group_sample_counts.at(index_it.first->second)++;
+                }
+            }
+        }
+    }
+
+    for (auto & sample_count: path_group_sample_counts) {
+        path_cluster_estimates->posteriors.emplace_back(sample_count / static_cast<double>(num_gibbs_chains * num_gibbs_its));
+    }
+}
+
 // ---- transcripts -----------------------------------------------------------------------------------------------------
 
 PathAbundanceEstimator::PathAbundanceEstimator(const uint32_t max_em_its_in, const double max_rel_em_conv_in, const uint32_t num_gibbs_samples_in, const uint32_t gibbs_thin_its_in, const double prob_precision) : PathEstimator(prob_precision), max_em_its(max_em_its_in), max_rel_em_conv(max_rel_em_conv_in), num_gibbs_samples(num_gibbs_samples_in), gibbs_thin_its(gibbs_thin_its_in) {}
@@ -444,7 +546,7 @@ void PathGroupPosteriorEstimator::estimate(PathClusterEstimates * path_cluster_e
 
     if (use_group_post_gibbs) {
 
-        notBuiltYet("the haplotype Gibbs sampler (--use-hap-gibbs)");
+        estimatePathGroupPosteriorsGibbs(path_cluster_estimates, matrix, noise, counts, num_paths, path_counts, group_size, mt_rng);
 
     } else if (group_size == 2) {
 

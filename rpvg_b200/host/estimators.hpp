@@ -160,6 +160,11 @@ class PathEstimator {
         // rpvg:src/path_estimator.cpp:332-377 / 379-473 with the log-likelihoods computed on the device.
         void calculatePathGroupPosteriorsFull(PathClusterEstimates * path_cluster_estimates, const vector<double> & matrix, const vector<double> & noise, const vector<double> & counts, const uint32_t num_paths, const vector<uint32_t> & path_counts, const uint32_t group_size) const;
         void calculatePathGroupPosteriorsBounded(PathClusterEstimates * path_cluster_estimates, const vector<double> & matrix, const vector<double> & noise, const vector<double> & counts, const uint32_t num_paths, const vector<uint32_t> & path_counts, const uint32_t group_size, const double min_rel_likelihood) const;
+
+        // rpvg:src/path_estimator.cpp:475-589. The chain runs on the host with the caller's mt19937 and libstdc++'s
+        // discrete_distribution, in the reference's consumption order (the RNG contract of rpvg:src/main.cpp:976); each
+        // conditional distribution it needs (N log-likelihoods over all read classes) is computed on the device.
+        void estimatePathGroupPosteriorsGibbs(PathClusterEstimates * path_cluster_estimates, const vector<double> & matrix, const vector<double> & noise, const vector<double> & counts, const uint32_t num_paths, const vector<uint32_t> & path_counts, const uint32_t group_size, mt19937 * mt_rng) const;
 };
 
 class PathAbundanceEstimator : public PathEstimator {
@@ -213,7 +218,7 @@ class NestedPathAbundanceEstimator : public PathAbundanceEstimator {
         void inferAbundancesCollapsedGroups(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng) const;
 
         // group posteriors on the grouped + normalised + collapsed matrix of the given path groups
-        void groupPosteriors(PathClusterEstimates * group_estimates, const vector<ReadPathProbabilities> & cluster_probs, const uint32_t num_paths, const vector<vector<uint32_t> > & path_groups, const vector<uint32_t> & group_counts) const;
+        void groupPosteriors(PathClusterEstimates * group_estimates, const vector<ReadPathProbabilities> & cluster_probs, const uint32_t num_paths, const vector<vector<uint32_t> > & path_groups, const vector<uint32_t> & group_counts, mt19937 * mt_rng) const;
 
         vector<vector<uint32_t> > findPathGroups(const vector<PathInfo> & paths) const;
         pair<vector<vector<uint32_t> >, vector<uint32_t> > findPathSourceGroups(const vector<PathInfo> & paths) const;

@@ -85,7 +85,7 @@ void NestedPathAbundanceEstimator::estimate(PathClusterEstimates * path_cluster_
 }
 
 // Posteriors of the size-k multisets of `path_groups` (rpvg:src/path_abundance_estimator.cpp:377-409 and 440-464).
-void NestedPathAbundanceEstimator::groupPosteriors(PathClusterEstimates * group_estimates, const vector<ReadPathProbabilities> & cluster_probs, const uint32_t num_paths, const vector<vector<uint32_t> > & path_groups, const vector<uint32_t> & group_counts) const {
+void NestedPathAbundanceEstimator::groupPosteriors(PathClusterEstimates * group_estimates, const vector<ReadPathProbabilities> & cluster_probs, const uint32_t num_paths, const vector<vector<uint32_t> > & path_groups, const vector<uint32_t> & group_counts, mt19937 * mt_rng) const {
 
     const FlatCluster flat(cluster_probs, num_paths);
     rpvg_b200_clusters clusters = flat.view();
@@ -119,7 +119,7 @@ void NestedPathAbundanceEstimator::groupPosteriors(PathClusterEstimates * group_
 
     if (use_group_post_gibbs) {
 
-        notBuiltYetNested("the haplotype Gibbs sampler (--use-hap-gibbs)");
+        estimatePathGroupPosteriorsGibbs(group_estimates, matrix, noise, counts, num_groups, group_counts, group_size, mt_rng);
 
     } else if (group_size == 2) {
 
@@ -195,7 +195,7 @@ void NestedPathAbundanceEstimator::inferAbundancesCollapsedGroups(PathClusterEst
     auto path_source_groups = findPathSourceGroups(path_cluster_estimates->paths);
 
     PathClusterEstimates group_estimates;
-    groupPosteriors(&group_estimates, cluster_probs, path_cluster_estimates->paths.size(), path_source_groups.first, path_source_groups.second);
+    groupPosteriors(&group_estimates, cluster_probs, path_cluster_estimates->paths.size(), path_source_groups.first, path_source_groups.second, mt_rng);
 
     // selectPathSubsetIndices (:569-606): combinations at or above min_hap_prob, expanded to sorted path lists
     SubsetSamples path_subset_samples;
@@ -247,7 +247,7 @@ void NestedPathAbundanceEstimator::inferAbundancesIndependentGroups(PathClusterE
         }
 
         PathClusterEstimates group_estimates;
-        groupPosteriors(&group_estimates, cluster_probs, path_cluster_estimates->paths.size(), singletons, group_path_counts);
+        groupPosteriors(&group_estimates, cluster_probs, path_cluster_estimates->paths.size(), singletons, group_path_counts, mt_rng);
 
         // sampleGroupPathIndices (:548-567): one draw per joint sample, host RNG
         discrete_distribution<uint32_t> path_group_set_sampler(group_estimates.posteriors.begin(), group_estimates.posteriors.end());
