@@ -189,6 +189,31 @@ int rpvg_b200_grouped_collapse(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * c
  * (A cluster with one path gets {0}; a cluster whose read classes are all noise-only gets the empty cover.) */
 int rpvg_b200_path_cover(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * clusters, uint8_t * in_cover);
 
+/* ---- Gibbs read-count sampler ----
+ * gibbsReadCountSampler (rpvg:src/path_abundance_estimator.cpp:116-212), started from the EM result of each cluster
+ * (or path subset): num_samples[c] samples, one every thin_its iterations. Random numbers are counter-based
+ * (Philox4x32-10 keyed by seeds[c]); the reference's sequential mt19937 stream is not reproduced, results agree in
+ * distribution and are bit-reproducible for equal seeds.
+ *   abundance_samples: cluster c's block starts at sum_{c' < c} num_samples[c'] * N_c' and is sample-major
+ *                      (CountSamples::abundance_samples); noise_samples: block at sum_{c' < c} num_samples[c']. */
+typedef struct {
+    const uint32_t * num_samples; /* [n_clusters] or [n_subsets]; 0 = none for that cluster */
+    uint32_t thin_its;            /* --gibbs-thin-its, default 25 (rpvg:src/main.cpp:418) */
+    const uint64_t * seeds;       /* [n_clusters] or [n_subsets] */
+    double * abundance_samples;   /* out */
+    double * noise_samples;       /* out */
+} rpvg_b200_gibbs;
+
+/* rpvg_b200_em_abundances / rpvg_b200_subset_em followed by the sampler (gibbs may be NULL: then they are the same calls). */
+int rpvg_b200_em_abundances_gibbs(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * clusters, const rpvg_b200_em_params * params, const rpvg_b200_gibbs * gibbs,
+                                  double * abundances, double * noise_count, double * total_count, uint32_t * iterations);
+int rpvg_b200_subset_em_gibbs(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * clusters, const rpvg_b200_subsets * subsets, const rpvg_b200_em_params * params,
+                              double prob_precision, const rpvg_b200_gibbs * gibbs, double * abundances, double * noise_count, double * total_count,
+                              uint32_t * iterations, uint32_t * n_classes);
+/* The sampler alone, on a resident batch whose EM has run. */
+int rpvg_b200_batch_gibbs(rpvg_b200_ctx * ctx, rpvg_b200_batch * batch, const uint32_t * num_samples, uint32_t thin_its, const uint64_t * seeds,
+                          double * abundance_samples, double * noise_samples);
+
 /* ---- EM of one cluster for callers that must not allocate ----
  * No counterpart in the reference (rpvg runs on the host and allocates freely); it exists for callers of this library
  * that cannot call cudaMalloc while they run: code under a fixed device-memory budget sized at start-up, real-time

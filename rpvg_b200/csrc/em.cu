@@ -864,6 +864,12 @@ void rpvg_b200_batch_free(rpvg_b200_ctx * ctx, rpvg_b200_batch * b) {
 int rpvg_b200_em_abundances(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * clusters, const rpvg_b200_em_params * params,
                             double * abundances, double * noise_count, double * total_count, uint32_t * iterations) {
 
+    return rpvg_b200_em_abundances_gibbs(ctx, clusters, params, nullptr, abundances, noise_count, total_count, iterations);
+}
+
+int rpvg_b200_em_abundances_gibbs(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * clusters, const rpvg_b200_em_params * params, const rpvg_b200_gibbs * gibbs,
+                                  double * abundances, double * noise_count, double * total_count, uint32_t * iterations) {
+
     rpvg_b200_batch * batch = nullptr;
 
     int status = rpvg_b200_batch_upload(ctx, clusters, &batch);
@@ -871,6 +877,10 @@ int rpvg_b200_em_abundances(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * clus
 
     status = rpvg_b200_batch_em(ctx, batch, params);
     if (status == RPVG_B200_OK) { status = rpvg_b200_batch_download(ctx, batch, abundances, noise_count, total_count, iterations); }
+
+    if (status == RPVG_B200_OK && gibbs) {
+        status = rpvg_b200_batch_gibbs(ctx, batch, gibbs->num_samples, gibbs->thin_its, gibbs->seeds, gibbs->abundance_samples, gibbs->noise_samples);
+    }
 
     rpvg_b200_batch_free(ctx, batch);
     return status;

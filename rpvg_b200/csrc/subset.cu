@@ -162,9 +162,12 @@ __global__ void compactClassesKernel(uint64_t n_classes, const uint32_t * __rest
 
 }
 
-extern "C" int rpvg_b200_subset_em(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, const rpvg_b200_subsets * ss, const rpvg_b200_em_params * params,
-                                   double prob_precision, double * abundances, double * noise_count, double * total_count, uint32_t * iterations,
-                                   uint32_t * n_classes) {
+int rpvgBatchGibbs(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const uint32_t * num_samples, uint32_t thin_its, const uint64_t * seeds, double * abundance_samples,
+                   double * noise_samples);
+
+extern "C" int rpvg_b200_subset_em_gibbs(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, const rpvg_b200_subsets * ss, const rpvg_b200_em_params * params,
+                                         double prob_precision, const rpvg_b200_gibbs * gibbs, double * abundances, double * noise_count, double * total_count,
+                                         uint32_t * iterations, uint32_t * n_classes) {
 
     if (!ctx || !cl || !ss || !params) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "NULL argument"); }
     if (ss->n_subsets == 0 || cl->n_clusters == 0) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "no subsets / no clusters"); }
@@ -394,6 +397,15 @@ extern "C" int rpvg_b200_subset_em(rpvg_b200_ctx * ctx, const rpvg_b200_clusters
     if (status == RPVG_B200_OK) { status = rpvg_b200_batch_em(ctx, batch, params); }
     if (status == RPVG_B200_OK) { status = rpvg_b200_batch_download(ctx, batch, abundances, noise_count, total_count, iterations); }
 
+    // rpvg:src/path_abundance_estimator.cpp:675-697: the sampler runs on the collapsed matrix of the subset
+    if (status == RPVG_B200_OK && gibbs) {
+        if (!gibbs->num_samples || !gibbs->seeds || !gibbs->abundance_samples || !gibbs->noise_samples) {
+            status = rpvgFail(ctx, RPVG_B200_ERR_INVALID, "gibbs: NULL array");
+        } else {
+            status = rpvgBatchGibbs(ctx, batch, gibbs->num_samples, gibbs->thin_its, gibbs->seeds, gibbs->abundance_samples, gibbs->noise_samples);
+        }
+    }
+
     if (status == RPVG_B200_OK && n_classes) {
         for (uint32_t s = 0; s < S; ++s) { n_classes[s] = h_n_classes[s]; }
     }
@@ -402,4 +414,11 @@ extern "C" int rpvg_b200_subset_em(rpvg_b200_ctx * ctx, const rpvg_b200_clusters
     cudaFreeAsync(base, st);
 
     return status;
+}
+
+extern "C" int rpvg_b200_subset_em(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, const rpvg_b200_subsets * ss, const rpvg_b200_em_params * params,
+                                   double prob_precision, double * abundances, double * noise_count, double * total_count, uint32_t * iterations,
+                                   uint32_t * n_classes) {
+
+    return rpvg_b200_subset_em_gibbs(ctx, cl, ss, params, prob_precision, nullptr, abundances, noise_count, total_count, iterations, n_classes);
 }

@@ -80,12 +80,6 @@ void generateGroupsRecursive(vector<vector<uint32_t> > * sets, const uint32_t nu
     abort();
 }
 
-[[noreturn]] void notBuiltYet(const char * what) {
-
-    cerr << "ERROR: rpvg_b200 does not provide " << what << " on the GPU yet, and it has no CPU fallback" << endl;
-    abort();
-}
-
 // One cluster as a one-cluster arena: every pair<double, vector<uint32_t>> expanded, entries of a read class sorted by path.
 struct FlatCluster {
 
@@ -449,11 +443,32 @@ void PathAbundanceEstimator::estimate(PathClusterEstimates * path_cluster_estima
 
     auto * ctx = threadContext();
 
-    if (rpvg_b200_em_abundances(ctx, &clusters, &params, path_cluster_estimates->abundances.data(), &path_cluster_estimates->noise_count, &path_cluster_estimates->total_count, nullptr) != RPVG_B200_OK) {
+    // Gibbs samples (rpvg:src/path_abundance_estimator.cpp:34-43): the device sampler is counter-based; its key is drawn
+    // from the caller's generator, which keeps the cluster's result a function of (rng_seed + cluster rank)
+    const uint32_t num_paths = path_cluster_estimates->paths.size();
+    uint64_t gibbs_seed = 0;
+    if (num_gibbs_samples > 0) { gibbs_seed = (static_cast<uint64_t>((*mt_rng)()) << 32) | (*mt_rng)(); }
+
+    CountSamples samples;
+    rpvg_b200_gibbs gibbs = {&num_gibbs_samples, gibbs_thin_its, &gibbs_seed, nullptr, nullptr};
+
+    if (num_gibbs_samples > 0) {
+
+        samples.path_ids.resize(num_paths);
+        iota(samples.path_ids.begin(), samples.path_ids.end(), 0);
+        samples.noise_samples.resize(num_gibbs_samples);
+        samples.abundance_samples.resize(static_cast<size_t>(num_gibbs_samples) * num_paths);
+
+        gibbs.abundance_samples = samples.abundance_samples.data();
+        gibbs.noise_samples = samples.noise_samples.data();
+    }
+
+    if (rpvg_b200_em_abundances_gibbs(ctx, &clusters, &params, num_gibbs_samples > 0 ? &gibbs : nullptr, path_cluster_estimates->abundances.data(),
+                                      &path_cluster_estimates->noise_count, &path_cluster_estimates->total_count, nullptr) != RPVG_B200_OK) {
         fatal(ctx, "rpvg_b200_em_abundances");
     }
 
-    if (num_gibbs_samples > 0) { notBuiltYet("the Gibbs read-count sampler (--num-gibbs-samples)"); }
+    if (num_gibbs_samples > 0) { path_cluster_estimates->gibbs_read_count_samples.emplace_back(std::move(samples)); }
 }
 
 MinimumPathAbundanceEstimator::MinimumPathAbundanceEstimator(const uint32_t max_em_its, const double max_rel_em_conv, const uint32_t num_gibbs_samples, const uint32_t gibbs_thin_its, const double prob_precision) : PathAbundanceEstimator(max_em_its, max_rel_em_conv, num_gibbs_samples, gibbs_thin_its, prob_precision) {}
@@ -494,11 +509,29 @@ void MinimumPathAbundanceEstimator::estimate(PathClusterEstimates * path_cluster
     vector<double> cover_abundances(min_path_cover.size(), 0);
     double noise_count = 0, total_count = 0;
 
-    if (rpvg_b200_subset_em(ctx, &clusters, &subsets, &params, prob_precision, cover_abundances.data(), &noise_count, &total_count, nullptr, nullptr) != RPVG_B200_OK) {
+    // :271-282 Gibbs samples on the cover's collapsed matrix
+    uint64_t gibbs_seed = 0;
+    if (num_gibbs_samples > 0) { gibbs_seed = (static_cast<uint64_t>((*mt_rng)()) << 32) | (*mt_rng)(); }
+
+    CountSamples samples;
+    rpvg_b200_gibbs gibbs = {&num_gibbs_samples, gibbs_thin_its, &gibbs_seed, nullptr, nullptr};
+
+    if (num_gibbs_samples > 0) {
+
+        samples.path_ids = min_path_cover;
+        samples.noise_samples.resize(num_gibbs_samples);
+        samples.abundance_samples.resize(static_cast<size_t>(num_gibbs_samples) * min_path_cover.size());
+
+        gibbs.abundance_samples = samples.abundance_samples.data();
+        gibbs.noise_samples = samples.noise_samples.data();
+    }
+
+    if (rpvg_b200_subset_em_gibbs(ctx, &clusters, &subsets, &params, prob_precision, num_gibbs_samples > 0 ? &gibbs : nullptr, cover_abundances.data(), &noise_count,
+                                  &total_count, nullptr, nullptr) != RPVG_B200_OK) {
         fatal(ctx, "rpvg_b200_subset_em");
     }
 
-    if (num_gibbs_samples > 0) { notBuiltYet("the Gibbs read-count sampler (--num-gibbs-samples)"); }
+    if (num_gibbs_samples > 0) { path_cluster_estimates->gibbs_read_count_samples.emplace_back(std::move(samples)); }
 
     // :286-292
     for (size_t i = 0; i < min_path_cover.size(); ++i) { path_cluster_estimates->abundances.at(min_path_cover.at(i)) += cover_abundances.at(i); }

@@ -26,12 +26,6 @@ namespace {
     abort();
 }
 
-[[noreturn]] void notBuiltYetNested(const char * what) {
-
-    cerr << "ERROR: rpvg_b200 does not provide " << what << " on the GPU yet, and it has no CPU fallback" << endl;
-    abort();
-}
-
 // same flattening as in estimators.cpp (one cluster as a one-cluster arena)
 struct FlatCluster {
 
@@ -277,8 +271,6 @@ void NestedPathAbundanceEstimator::inferAbundancesIndependentGroups(PathClusterE
 // rpvg:src/path_abundance_estimator.cpp:608-750, with the sub-EMs of all subsets batched into one device call.
 void NestedPathAbundanceEstimator::inferPathSubsetAbundance(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng, const SubsetSamples & path_subset_samples) const {
 
-    if (num_gibbs_samples > 0) { notBuiltYetNested("the Gibbs read-count sampler (--num-gibbs-samples)"); }
-
     for (auto & cluster_prob: cluster_probs) { path_cluster_estimates->total_count += cluster_prob.readCount(); }
 
     // pass 1, in the map's iteration order: the subsets that take part, duplicates (homozygous paths) removed
@@ -287,7 +279,12 @@ void NestedPathAbundanceEstimator::inferPathSubsetAbundance(PathClusterEstimates
         double prob;
         vector<uint32_t> collapsed;            // duplicates removed
         vector<uint32_t> multiplicity;         // per collapsed path
+        uint32_t gibbs_samples;                // this subset's share of --num-gibbs-samples
     };
+
+    // :675-683 the sample budget is split over the subsets by conditional binomials, host generator, subset order
+    uint32_t subset_gibbs_samples = num_gibbs_samples;
+    double subset_gibbs_prob = 1;
 
     vector<SubsetJob> jobs;
 
@@ -306,6 +303,17 @@ void NestedPathAbundanceEstimator::inferPathSubsetAbundance(PathClusterEstimates
             } else {
                 job.multiplicity.back()++;
             }
+        }
+
+        job.gibbs_samples = 0;
+
+        if (subset_gibbs_samples > 0) {
+
+            binomial_distribution<uint32_t> sample_count_sampler(subset_gibbs_samples, min(1.0, path_subset.second / subset_gibbs_prob));
+            job.gibbs_samples = sample_count_sampler(*mt_rng);
+
+            subset_gibbs_samples -= job.gibbs_samples;
+            subset_gibbs_prob -= path_subset.second;
         }
 
         jobs.emplace_back(std::move(job));
@@ -339,8 +347,43 @@ void NestedPathAbundanceEstimator::inferPathSubsetAbundance(PathClusterEstimates
         abundances.resize(subset_paths.size());
         auto * ctx = threadContext();
 
-        if (rpvg_b200_subset_em(ctx, &clusters, &subsets, &params, prob_precision, abundances.data(), noise_counts.data(), total_counts.data(), nullptr, nullptr) != RPVG_B200_OK) {
+        // Gibbs samples of every subset that got a share, in the same call
+        vector<uint32_t> gibbs_counts;
+        vector<uint64_t> gibbs_seeds;
+        size_t total_samples = 0, total_values = 0;
+
+        for (auto & job: jobs) {
+            gibbs_counts.push_back(job.gibbs_samples);
+            gibbs_seeds.push_back(job.gibbs_samples > 0 ? ((static_cast<uint64_t>((*mt_rng)()) << 32) | (*mt_rng)()) : 0);
+            total_samples += job.gibbs_samples;
+            total_values += static_cast<size_t>(job.gibbs_samples) * job.collapsed.size();
+        }
+
+        vector<double> gibbs_abundances(total_values), gibbs_noise(total_samples);
+        rpvg_b200_gibbs gibbs = {gibbs_counts.data(), gibbs_thin_its, gibbs_seeds.data(), gibbs_abundances.data(), gibbs_noise.data()};
+
+        if (rpvg_b200_subset_em_gibbs(ctx, &clusters, &subsets, &params, prob_precision, total_samples > 0 ? &gibbs : nullptr, abundances.data(), noise_counts.data(),
+                                      total_counts.data(), nullptr, nullptr) != RPVG_B200_OK) {
             fatalNested(ctx, "rpvg_b200_subset_em");
+        }
+
+        // :685-696 one CountSamples per subset with samples, in subset order
+        size_t value_pos = 0, sample_pos = 0;
+
+        for (auto & job: jobs) {
+
+            if (job.gibbs_samples > 0) {
+
+                CountSamples samples;
+                samples.path_ids = job.collapsed;
+                samples.noise_samples.assign(gibbs_noise.begin() + sample_pos, gibbs_noise.begin() + sample_pos + job.gibbs_samples);
+                samples.abundance_samples.assign(gibbs_abundances.begin() + value_pos, gibbs_abundances.begin() + value_pos + static_cast<size_t>(job.gibbs_samples) * job.collapsed.size());
+
+                path_cluster_estimates->gibbs_read_count_samples.emplace_back(std::move(samples));
+            }
+
+            sample_pos += job.gibbs_samples;
+            value_pos += static_cast<size_t>(job.gibbs_samples) * job.collapsed.size();
         }
     }
 
