@@ -37,7 +37,7 @@ if ROOT not in sys.path:
 
 METRIC = "em_nnz_iterations_per_second"
 UNIT = "nnz*it/s"
-WORKLOAD = "config2: transcripts-model EM, 1M read classes, 200k paths, power-law cluster sizes 1-5000 (synthetic, seed 20240603+rank)"
+WORKLOAD = "config2: transcripts-model EM, 1M read classes, 200k paths, power-law cluster sizes 1-5000 (synthetic, seeds 20240603..)"
 
 
 def measured_peak_hbm():
@@ -155,7 +155,7 @@ def main():
     n_max = max(20, int(5000 * min(1.0, args.scale * 4))) if args.scale < 1 else 5000
     config = {"workload": WORKLOAD if args.scale == 1.0 else f"DEBUG scale={args.scale} of config2",
               "read_classes_per_gpu": n_reads, "paths_per_gpu": n_paths, "max_em_its": 10000, "max_rel_em_conv": 0.001,
-              "sharding": f"clusters sharded over {world} rank(s), no collective", "l2": "flushed between timed steps (256 MiB write)"}
+              "sharding": f"{world} arena(s) of this shape; clusters dealt to {world} rank(s) by LPT on nnz x E[iterations], no collective", "l2": "flushed between timed steps (256 MiB write)"}
 
     # ------------------------------------------------------------------------------------------------ reference arm
     if args.impl == "reference":
@@ -193,7 +193,16 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    arena = synth.transcripts_arena(seed=synth.BASE_SEED + 2 + rank, n_paths=n_paths, n_reads=n_reads, n_max=n_max)
+    if world == 1:
+        arena = synth.transcripts_arena(seed=synth.BASE_SEED + 2, n_paths=n_paths, n_reads=n_reads, n_max=n_max)
+    else:
+        # weak scaling: the job is `world` arenas of the config-2 shape; its clusters are dealt to the ranks by LPT on the
+        # nnz x E[iterations] cost model (rpvg_b200/multi_gpu.py). No data-path collective: clusters are independent.
+        from rpvg_b200 import multi_gpu
+        from rpvg_b200.arena import concat
+        job = concat([synth.transcripts_arena(seed=synth.BASE_SEED + 2 + r, n_paths=n_paths, n_reads=n_reads, n_max=n_max) for r in range(world)])
+        arena = job.select(multi_gpu.lpt_partition(multi_gpu.cluster_costs(job), world)[rank])
+        del job
 
     # pinned host copies of the arena: the e2e leg uploads from these every step
     class Pinned:
