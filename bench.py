@@ -115,12 +115,21 @@ def reference_sample(arena, max_dense_entries=1.5e6, max_clusters=400, max_total
     return sorted(keep)
 
 
+def host_threads() -> int:
+    """All host cores this process may use (torchrun exports OMP_NUM_THREADS=1: the CPU arm must not inherit that)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
 def run_reference_sample(arena, sample_ids, threads=0):
     """Times the reference's own PathAbundanceEstimator (oracle/_ref) — or, if that library is absent, the CPU port — on
     the sample. Returns (nnz*it/s, seconds, kind, cores)."""
     from oracle import loader
+    threads = threads or host_threads()
     sub = arena.select(sample_ids)
-    _, _, _, its, _ = loader.port_em_abundances(sub)     # iteration counts (the reference does not report them)
+    _, _, _, its, _ = loader.port_em_abundances(sub, num_threads=threads)     # iteration counts (the reference does not report them)
     work = 0.0
     for k in range(sub.n_clusters):
         m, _, nnz_path = sub.cluster_shape(k)
@@ -129,9 +138,9 @@ def run_reference_sample(arena, sample_ids, threads=0):
         lib = loader.reference()
         cfg = loader.make_config(loader.MODEL_TRANSCRIPTS)
         seconds, _ = loader.harness_estimate_batch(lib, cfg, sub, rng_seed=1, num_threads=threads)
-        return work / seconds, seconds, "reference", int(lib.harness_max_threads())
+        return work / seconds, seconds, "reference", threads
     _, _, _, _, seconds = loader.port_em_abundances(sub, num_threads=threads)
-    return work / seconds, seconds, "port", int(loader.port().oracle_max_threads())
+    return work / seconds, seconds, "port", threads
 
 
 def main():
