@@ -23,6 +23,8 @@ struct rpvg_b200_ctx {
     // EM launch machinery (em.cu): side streams for concurrent bins, largest thread-block cluster this device accepts
     std::vector<cudaStream_t> side_streams;
     std::vector<cudaEvent_t> join_events;
+    std::vector<cudaStream_t> lane_streams;   // highest priority; the largest groups run here one cluster per launch
+    std::vector<cudaEvent_t> lane_events;
     cudaEvent_t fork_event = nullptr;
     uint32_t max_group_size = 1;
 };

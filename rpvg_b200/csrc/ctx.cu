@@ -1,5 +1,9 @@
 // Context management of librpvg_b200.so.
 
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+
 #include "common.cuh"
 
 extern "C" {
@@ -22,6 +26,10 @@ int rpvg_b200_create(int device, void * stream, rpvg_b200_ctx ** out_ctx) {
     if (device < 0 || device >= count) { return RPVG_B200_ERR_INVALID; }
 
     if (cudaSetDevice(device) != cudaSuccess) { return RPVG_B200_ERR_CUDA; }
+
+#ifdef RPVG_B200_EM_TIMELINE
+    cudaDeviceSetLimit(cudaLimitPrintfFifoSize, 64u << 20);   // one line per CTA
+#endif
 
     auto * ctx = new rpvg_b200_ctx();
     ctx->device = device;
@@ -56,16 +64,19 @@ int rpvg_b200_create(int device, void * stream, rpvg_b200_ctx ** out_ctx) {
         cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold);
     }
 
-    // side streams: the first few have high priority (large thread-block clusters are launched there)
+    // side streams, one priority level each as far as the device has them (numerically lower = higher priority): the work
+    // distributor hands out the CTAs of one kernel per priority level at a time, so launches that are to overlap with a
+    // kernel that still has undispatched thread-block clusters must sit on another level (see rpvg_b200_batch_em)
     int prio_low = 0, prio_high = 0;
     cudaDeviceGetStreamPriorityRange(&prio_low, &prio_high);
+    if (std::getenv("RPVG_B200_DEBUG")) { fprintf(stderr, "[rpvg_b200] stream priorities %d (lowest) .. %d (highest)\n", prio_low, prio_high); }
 
     for (int k = 0; k < 8; ++k) {
 
         cudaStream_t side = nullptr;
         cudaEvent_t join = nullptr;
 
-        if (cudaStreamCreateWithPriority(&side, cudaStreamNonBlocking, k < 3 ? prio_high : prio_low) != cudaSuccess ||
+        if (cudaStreamCreateWithPriority(&side, cudaStreamNonBlocking, std::min(prio_low, prio_high + 1 + static_cast<int>(k))) != cudaSuccess ||
             cudaEventCreateWithFlags(&join, cudaEventDisableTiming) != cudaSuccess) {
             rpvg_b200_destroy(ctx);
             return RPVG_B200_ERR_CUDA;
@@ -73,6 +84,21 @@ int rpvg_b200_create(int device, void * stream, rpvg_b200_ctx ** out_ctx) {
 
         ctx->side_streams.push_back(side);
         ctx->join_events.push_back(join);
+    }
+
+    for (int k = 0; k < 8; ++k) {
+
+        cudaStream_t lane = nullptr;
+        cudaEvent_t done = nullptr;
+
+        if (cudaStreamCreateWithPriority(&lane, cudaStreamNonBlocking, prio_high) != cudaSuccess ||
+            cudaEventCreateWithFlags(&done, cudaEventDisableTiming) != cudaSuccess) {
+            rpvg_b200_destroy(ctx);
+            return RPVG_B200_ERR_CUDA;
+        }
+
+        ctx->lane_streams.push_back(lane);
+        ctx->lane_events.push_back(done);
     }
 
     if (cudaEventCreateWithFlags(&ctx->fork_event, cudaEventDisableTiming) != cudaSuccess || rpvgEmInit(ctx) != RPVG_B200_OK) {
@@ -95,6 +121,11 @@ void rpvg_b200_destroy(rpvg_b200_ctx * ctx) {
         cudaStreamDestroy(side);
     }
     for (auto ev: ctx->join_events) { cudaEventDestroy(ev); }
+    for (auto lane: ctx->lane_streams) {
+        cudaStreamSynchronize(lane);
+        cudaStreamDestroy(lane);
+    }
+    for (auto ev: ctx->lane_events) { cudaEventDestroy(ev); }
     if (ctx->fork_event) { cudaEventDestroy(ctx->fork_event); }
     if (ctx->own_stream) { cudaStreamDestroy(ctx->stream); }
 

@@ -17,6 +17,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <numeric>
@@ -158,15 +159,46 @@ __global__ void gatherColumnsKernel(uint64_t nnz, const uint32_t * __restrict__ 
     csc_val[k] = val[e];
 }
 
+// Holds a stream back for a fixed time (one thread, no memory traffic): see the launch loop of rpvg_b200_batch_em.
+__global__ void spacerKernel(unsigned long long ns) {
+
+    unsigned long long t0, t1;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t0));
+    do {
+        __nanosleep(1000);
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+    } while (t1 - t0 < ns);
+}
+
 uint32_t envKnob(const char * name, uint32_t fallback) {
 
     const char * v = std::getenv(name);
     return (v && *v) ? static_cast<uint32_t>(std::strtoul(v, nullptr, 10)) : fallback;
 }
 
-constexpr uint32_t kSmemTiers[] = {8 * 1024, 24 * 1024, 56 * 1024, 108 * 1024, 216 * 1024};
-constexpr uint32_t kTierThreads[] = {64, 128, 256, 512, 512};
 constexpr int kNumTiers = 5;
+
+// Shared-memory tiers of the EM launches and the CTA size that goes with each; RPVG_B200_EM_TIERS="kb:threads,..." (five
+// pairs, ascending) overrides them for tuning runs.
+struct SellTiers {
+
+    uint32_t smem[kNumTiers] = {8 * 1024, 24 * 1024, 56 * 1024, 108 * 1024, 216 * 1024};
+    uint32_t threads[kNumTiers] = {64, 128, 256, 512, 512};
+
+    SellTiers() {
+        const char * v = std::getenv("RPVG_B200_EM_TIERS");
+        if (!v || !*v) { return; }
+        unsigned kb[kNumTiers], th[kNumTiers];
+        if (std::sscanf(v, "%u:%u,%u:%u,%u:%u,%u:%u,%u:%u", &kb[0], &th[0], &kb[1], &th[1], &kb[2], &th[2], &kb[3], &th[3], &kb[4], &th[4]) == 2 * kNumTiers) {
+            for (int t = 0; t < kNumTiers; ++t) { smem[t] = kb[t] * 1024; threads[t] = th[t]; }
+        }
+    }
+};
+
+const SellTiers & sellTiers() {
+    static const SellTiers tiers;
+    return tiers;
+}
 constexpr uint32_t kStaticSmemReserve = 12 * 1024;   // static shared memory of emSellKernel<512> + slack
 
 struct GroupPlan {
@@ -186,7 +218,7 @@ void planEmLaunches(const rpvg_b200_ctx * ctx, rpvg_b200_batch * b, std::vector<
     const uint32_t slice_weight = std::max(64u, envKnob("RPVG_B200_EM_SLICE_WEIGHT", 8000));
     const uint32_t big_threads = envKnob("RPVG_B200_EM_BIG_THREADS", 512);
     const uint32_t max_group = std::min(ctx->max_group_size, std::max(1u, envKnob("RPVG_B200_EM_MAX_GROUP", kMaxGroupSize)));
-    const uint32_t smem_cap = std::min<uint32_t>(kSmemTiers[kNumTiers - 1], static_cast<uint32_t>(ctx->max_smem_optin) - kStaticSmemReserve);
+    const uint32_t smem_cap = std::min<uint32_t>(sellTiers().smem[kNumTiers - 1], static_cast<uint32_t>(ctx->max_smem_optin) - kStaticSmemReserve);
 
     std::vector<GroupPlan> items(b->n_clusters);
 
@@ -224,12 +256,12 @@ void planEmLaunches(const rpvg_b200_ctx * ctx, rpvg_b200_batch * b, std::vector<
 
             int tier_typical = kNumTiers - 1;
             for (int t = 0; t < kNumTiers; ++t) {
-                if (need_typical <= std::min(kSmemTiers[t], smem_cap)) { tier_typical = t; break; }
+                if (need_typical <= std::min(sellTiers().smem[t], smem_cap)) { tier_typical = t; break; }
             }
 
             int tier_worst = kNumTiers;
             for (int t = 0; t < kNumTiers; ++t) {
-                if (need_worst <= std::min(kSmemTiers[t], smem_cap)) { tier_worst = t; break; }
+                if (need_worst <= std::min(sellTiers().smem[t], smem_cap)) { tier_worst = t; break; }
             }
 
             // one tier up buys the guarantee that nothing spills; beyond that the slice is given scratch for its entries
@@ -285,11 +317,11 @@ void planEmLaunches(const rpvg_b200_ctx * ctx, rpvg_b200_batch * b, std::vector<
 
                 bin.group_size = 1u << (4 - code / kNumTiers);
                 bin.index_bytes = (items[k].bin & 1) ? 4 : 2;
-                bin.smem = std::min(kSmemTiers[tier], smem_cap);
-                bin.threads = kTierThreads[tier];
+                bin.smem = std::min(sellTiers().smem[tier], smem_cap);
+                bin.threads = sellTiers().threads[tier];
 
                 // instantiations that exist: one CTA {64,128,256,512,1024} x u16; groups {256,512,1024} x u16; 512 x u32
-                if (tier == kNumTiers - 1) { bin.threads = (big_threads == 1024) ? 1024 : 512; }
+                if (tier == kNumTiers - 1 && big_threads == 1024) { bin.threads = 1024; }
                 if (bin.index_bytes == 4) { bin.threads = 512; }
                 if (bin.group_size > 1) { bin.threads = std::max(bin.threads, 256u); }
             }
@@ -353,7 +385,7 @@ cudaError_t launchSellBin(const SellArgs & sa, const rpvg_b200_batch::EmBin & bi
 template <int THREADS, bool MULTI, typename IndexT>
 cudaError_t configureSell(const rpvg_b200_ctx * ctx, uint32_t * max_group) {
 
-    const int smem_cap = std::min<int>(kSmemTiers[kNumTiers - 1], ctx->max_smem_optin - static_cast<int>(kStaticSmemReserve));
+    const int smem_cap = std::min<int>(sellTiers().smem[kNumTiers - 1], ctx->max_smem_optin - static_cast<int>(kStaticSmemReserve));
 
     cudaError_t err = cudaFuncSetAttribute(emSellKernel<THREADS, MULTI, IndexT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap);
     if (err != cudaSuccess || !MULTI) { return err; }
@@ -466,6 +498,7 @@ int rpvgBatchCreate(rpvg_b200_ctx * ctx, uint32_t n_clusters, const uint64_t * r
     std::vector<uint64_t> group_scratch;
     std::vector<uint64_t> group_cta_bytes;
     planEmLaunches(ctx, b, &order, &group_scratch, &group_cta_bytes);
+    b->h_order = order;
 
     const uint64_t C = b->n_clusters, R = b->n_reads, P = b->n_paths, Z = b->nnz;
 
@@ -721,11 +754,20 @@ int rpvg_b200_batch_em(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const rpvg_b200
 
     RPVG_CUDA(ctx, cudaEventRecord(b->ev_built, s));
 
-    // Bins run concurrently on the ctx's side streams (fork after the build, join before ev_done); the bins of large
-    // groups go first and on high-priority streams so that they get whole GPCs before the small ones fill the rest.
+    // Bins run concurrently on the ctx's side streams (fork after the build, join before ev_done), one stream priority
+    // level per bin, larger groups higher: a thread-block cluster of 16 needs 16 idle SMs of one GPC at the same moment,
+    // which it only gets if it is placed before anything smaller. Measured on B200 (tools/em_timeline.py): 7 of the 8
+    // GPCs can host a cluster of 16; what they leave over (2-4 SMs each, 10 in the small GPC) is filled by the bins
+    // of groups of 2 and 8 while the big ones run.
     RPVG_CUDA(ctx, cudaEventRecord(ctx->fork_event, s));
 
     const bool debug = std::getenv("RPVG_B200_DEBUG") != nullptr;
+    const uint32_t spacer_us = envKnob("RPVG_B200_EM_SPACER_US", 20);
+    const uint32_t lane_min_group = envKnob("RPVG_B200_EM_LANE_MIN_GROUP", 16);
+    const size_t n_lanes = std::min<size_t>(envKnob("RPVG_B200_EM_LANES", 7), ctx->lane_streams.size());
+    std::vector<double> lane_load(n_lanes, 0.0);
+    std::vector<bool> lane_forked(n_lanes, false);
+    bool lanes_used = false;
 
     for (size_t k = 0; k < b->bins.size(); ++k) {
 
@@ -737,6 +779,13 @@ int rpvg_b200_batch_em(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const rpvg_b200
 
         cudaStream_t bs = ctx->side_streams[k % ctx->side_streams.size()];
         RPVG_CUDA(ctx, cudaStreamWaitEvent(bs, ctx->fork_event, 0));
+
+        // The launch of the largest groups goes first and alone: its thread-block clusters need whole GPCs, which they
+        // only find while the GPU is empty. Everything else starts a few microseconds later.
+        if (spacer_us > 0 && k > 0 && b->bins[0].group_size >= 8) {
+            spacerKernel<<<1, 1, 0, bs>>>(1000ull * spacer_us);
+            RPVG_LAUNCHED(ctx);
+        }
 
         if (bin.group_size == 0) {
 
@@ -755,7 +804,47 @@ int rpvg_b200_batch_em(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const rpvg_b200
             sa.scratch = b->d_scratch;
             sa.smem_bytes = bin.smem;
 
-            const cudaError_t launch_err = launchSellBin(sa, bin, bs);
+            cudaError_t launch_err = cudaSuccess;
+
+            if (bin.group_size >= lane_min_group && n_lanes > 0) {
+
+                // One launch per cluster, dealt over the lane streams: a launch with more thread-block clusters than fit
+                // at once would keep the SMs it cannot use idle until its last cluster is placed (the work distributor
+                // holds freed SMs back for the pending clusters of the kernel it is dispatching).
+                // (within a bin the clusters come heaviest first: each goes to the lane with the least expected work,
+                // cost ~ weight^1.5, i.e. entries x iterations)
+                for (uint32_t i = 0; i < bin.count && launch_err == cudaSuccess; ++i) {
+
+                    size_t lane = 0;
+                    for (size_t l = 1; l < n_lanes; ++l) {
+                        if (lane_load[l] < lane_load[lane]) { lane = l; }
+                    }
+
+                    const uint32_t c = b->h_order[bin.first + i];
+                    const double weight = static_cast<double>(b->h_cluster_nnz[c] + (b->h_read_offset[c + 1] - b->h_read_offset[c]));
+                    lane_load[lane] += weight * std::sqrt(weight);
+
+                    if (!lane_forked[lane]) {
+                        RPVG_CUDA(ctx, cudaStreamWaitEvent(ctx->lane_streams[lane], ctx->fork_event, 0));
+                        lane_forked[lane] = true;
+                    }
+
+                    SellArgs one = sa;
+                    one.group_cluster += i;
+                    one.group_scratch += i;
+                    one.group_cta_bytes += i;
+
+                    rpvg_b200_batch::EmBin single = bin;
+                    single.count = 1;
+                    launch_err = launchSellBin(one, single, ctx->lane_streams[lane]);
+                    if (i > 0) { RPVG_LAUNCHED(ctx); }
+                }
+
+                lanes_used = true;
+
+            } else {
+                launch_err = launchSellBin(sa, bin, bs);
+            }
 
             if (launch_err != cudaSuccess) {
                 return rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("emSellKernel launch (group ") + std::to_string(bin.group_size) + ", threads " +
@@ -763,11 +852,18 @@ int rpvg_b200_batch_em(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const rpvg_b200
             }
             RPVG_LAUNCHED(ctx);
         }
+
     }
 
     for (size_t k = 0; k < std::min(b->bins.size(), ctx->side_streams.size()); ++k) {
         RPVG_CUDA(ctx, cudaEventRecord(ctx->join_events[k], ctx->side_streams[k]));
         RPVG_CUDA(ctx, cudaStreamWaitEvent(s, ctx->join_events[k], 0));
+    }
+
+    for (size_t k = 0; lanes_used && k < n_lanes; ++k) {
+        if (!lane_forked[k]) { continue; }
+        RPVG_CUDA(ctx, cudaEventRecord(ctx->lane_events[k], ctx->lane_streams[k]));
+        RPVG_CUDA(ctx, cudaStreamWaitEvent(s, ctx->lane_events[k], 0));
     }
 
     RPVG_CUDA(ctx, cudaEventRecord(b->ev_done, s));
@@ -887,3 +983,20 @@ int rpvg_b200_em_abundances_gibbs(rpvg_b200_ctx * ctx, const rpvg_b200_clusters 
 }
 
 }
+
+#ifdef RPVG_B200_EM_TIMELINE
+// tuning builds only: copies the per-CTA records out (12 values each) and resets the counter
+extern "C" int rpvg_b200_timeline_read(unsigned long long * records, unsigned int capacity, unsigned int * count) {
+
+    unsigned int n = 0;
+    if (cudaDeviceSynchronize() != cudaSuccess) { return -1; }
+    if (cudaMemcpyFromSymbol(&n, rpvg_timeline_count, sizeof(n)) != cudaSuccess) { return -1; }
+    n = n < 65536 ? n : 65536;
+    n = n < capacity ? n : capacity;
+    if (n > 0 && cudaMemcpyFromSymbol(records, rpvg_timeline_records, 12ull * 8 * n) != cudaSuccess) { return -1; }
+    const unsigned int zero = 0;
+    if (cudaMemcpyToSymbol(rpvg_timeline_count, &zero, sizeof(zero)) != cudaSuccess) { return -1; }
+    *count = n;
+    return 0;
+}
+#endif

@@ -36,6 +36,7 @@ struct rpvg_b200_batch {
     std::vector<uint64_t> h_path_offset;
     std::vector<uint64_t> h_cluster_nnz;   // path non-zeros per cluster
     std::vector<uint32_t> h_iterations;
+    std::vector<uint32_t> h_order;         // clusters in launch order (bins are ranges of it)
 
     // launch plan of the EM: clusters binned by thread-block-cluster size, shared-memory tier and index width
     struct EmBin {

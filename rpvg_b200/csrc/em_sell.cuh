@@ -4,8 +4,10 @@
 // slices of equal weight. In its prologue every CTA re-lays its slice out as two sliced-ELL structures, one per
 // orientation, built so that the inner loops of both EM steps are the same branch-free, bank-conflict-free loop:
 //
-//   chunk = 32 lane slots; a row (column) of the chunk owns L = 1..32 adjacent lanes (L chosen from its length so a
-//   chunk is ~5-8 steps deep); entry t of that row sits at [chunk_off + (t / L) * 32 + first_lane + (t % L)].
+//   chunk = kSellSlots = 32 * kSellWays slots per step; a lane works on slots lane, lane + 32, ... (kSellWays
+//   independent dependency chains per lane, which is what hides the shared-memory latency). A row (column) of the
+//   chunk owns L = 1..32 adjacent slots (L chosen from its length so a chunk is ~8 steps deep); entry t of that row
+//   sits at [chunk_off + (t / L) * kSellSlots + first_slot + (t % L)].
 //   Rows (columns) are ordered by length (stable bucket sort) so rows sharing a chunk have near-equal length; padding
 //   entries are (value 0, index 0) and need no predicate.
 //
@@ -41,13 +43,24 @@ struct SellChunk {
 
     uint32_t off;     // first entry slot (multiple of 32)
     uint32_t first;   // first row (column) of the chunk, in sorted order
-    uint16_t count;   // rows (columns) in the chunk, <= 32 >> l2
+    uint16_t count;   // rows (columns) in the chunk, <= kSellSlots >> l2
     uint8_t l2;       // log2(lanes per row)
     uint8_t pad;
     uint32_t width;   // steps
 };
 
 constexpr uint32_t kSellBuckets = 64;
+
+#ifndef RPVG_B200_SELL_WAYS
+#define RPVG_B200_SELL_WAYS 1
+#endif
+
+#ifndef RPVG_B200_SELL_ROUNDS
+#define RPVG_B200_SELL_ROUNDS 1   // depth divisor (see sellDepth): 1 = about two chunks per warp and phase
+#endif
+
+constexpr uint32_t kSellWays = RPVG_B200_SELL_WAYS;   // slots per lane and step
+constexpr uint32_t kSellSlots = 32 * kSellWays;
 
 // Length bucket: exact up to 32, then one bucket per power of two.
 __host__ __device__ __forceinline__ uint32_t sellBucket(uint32_t len) {
@@ -74,8 +87,8 @@ __host__ __device__ __forceinline__ uint32_t sellLanesLog2(uint32_t len_upper, u
 }
 
 // Entry slots one orientation of a slice occupies (z entries in n rows): worst case and what is typical after sorting.
-__host__ __device__ inline uint64_t sellSlotsWorst(uint64_t z, uint64_t n) { return 4 * z + 32 * n + 320; }
-__host__ __device__ inline uint64_t sellSlotsTypical(uint64_t z, uint64_t n) { return z + z / 4 + 2 * n + 128; }
+__host__ __device__ inline uint64_t sellSlotsWorst(uint64_t z, uint64_t n) { return 4 * z + 32 * n + 10 * kSellSlots * kSellWays + 3 * kSellSlots; }
+__host__ __device__ inline uint64_t sellSlotsTypical(uint64_t z, uint64_t n) { return z + z / 4 + 2 * n + 4 * kSellSlots * kSellWays + 3 * kSellSlots; }
 
 __host__ __device__ inline uint64_t sellRound16(uint64_t bytes) { return (bytes + 15) & ~uint64_t(15); }
 
@@ -97,7 +110,7 @@ __host__ __device__ inline uint64_t sellScratchBytes(uint64_t m, uint64_t z, uin
 
     const uint64_t temps = 2 * sellRound16(4 * (m + 1)) + 4 * sellRound16(4 * (N + 1));
     const uint64_t vectors = 3 * sellRound16(8 * (m + 1));
-    const uint64_t chunks = 16 * (m + N + 130);
+    const uint64_t chunks = 2 * 16 * (m + N + 130) + 2 * 4 * (m + N + 260);   // final and unassigned descriptors, assignment
     const uint64_t col_id = sellRound16(index_bytes * (N + 1));
     const uint64_t entries = with_entries ? (8 + index_bytes) * (sellSlotsWorst(z, m) + sellSlotsWorst(z, N)) + 128 : 64;
     const uint64_t masks = sellRound16(2 * (N + 2));
@@ -190,7 +203,7 @@ __device__ void sellStableSort(SellSort<THREADS> & st, const uint32_t n, LenFn l
 // be as deep as the warp count allows (about two rounds of chunks per warp), but at least 8 and at most 64 steps.
 __host__ __device__ __forceinline__ uint32_t sellDepth(uint32_t z, uint32_t num_warps) {
 
-    const uint32_t d = (2 * z) / (32 * num_warps);
+    const uint32_t d = (2 * z) / (RPVG_B200_SELL_ROUNDS * kSellSlots * num_warps);
     return d < 8 ? 8 : (d > 64 ? 64 : d);
 }
 
@@ -205,7 +218,7 @@ __device__ uint32_t sellCountChunks(SellSort<THREADS> & st, const uint32_t n, co
 
         while (p < n) {
             while (st.bucket_start[b] + st.bucket_total[b] <= p) { --b; }
-            p += min(32u >> sellLanesLog2(sellBucketUpper(b), depth), n - p);
+            p += min(kSellSlots >> sellLanesLog2(sellBucketUpper(b), depth), n - p);
             ++k;
         }
 
@@ -216,7 +229,7 @@ __device__ uint32_t sellCountChunks(SellSort<THREADS> & st, const uint32_t n, co
     return st.chunk_base[1];
 }
 
-// Chunk descriptors for items already sorted by descending bucket: a chunk takes the next 32 >> l2 items, l2 from the
+// Chunk descriptors for items already sorted by descending bucket: a chunk takes the next kSellSlots >> l2 items, l2 from the
 // bucket of its first (longest) item. Returns the number of chunks; total_slots receives the number of entry slots.
 template <int THREADS, typename LenFn>
 __device__ uint32_t sellMakeChunks(SellSort<THREADS> & st, const uint32_t n, const uint32_t depth, LenFn len, const uint32_t * src, SellChunk * chunks, uint32_t * scan_tmp, uint32_t * total_slots) {
@@ -236,7 +249,7 @@ __device__ uint32_t sellMakeChunks(SellSort<THREADS> & st, const uint32_t n, con
             while (st.bucket_start[b] + st.bucket_total[b] <= p) { --b; }
 
             const uint32_t l2 = sellLanesLog2(sellBucketUpper(b), depth);
-            const uint32_t count = min(32u >> l2, n - p);
+            const uint32_t count = min(kSellSlots >> l2, n - p);
 
             SellChunk ch;
             ch.off = 0;
@@ -272,13 +285,13 @@ __device__ uint32_t sellMakeChunks(SellSort<THREADS> & st, const uint32_t n, con
 
     __syncthreads();
 
-    // exclusive scan of width * 32 over the chunks (block-wide, chunked per thread)
+    // exclusive scan of width * kSellSlots over the chunks (block-wide, chunked per thread)
     const uint32_t per_thread = (n_chunks + THREADS - 1) / THREADS;
     const uint32_t k_begin = min(n_chunks, tid * per_thread);
     const uint32_t k_end = min(n_chunks, k_begin + per_thread);
 
     uint32_t local = 0;
-    for (uint32_t k = k_begin; k < k_end; ++k) { local += chunks[k].width * 32; }
+    for (uint32_t k = k_begin; k < k_end; ++k) { local += chunks[k].width * kSellSlots; }
 
     uint32_t incl = local;
     #pragma unroll
@@ -295,13 +308,59 @@ __device__ uint32_t sellMakeChunks(SellSort<THREADS> & st, const uint32_t n, con
     uint32_t offset = warp_base + incl - local;
     for (uint32_t k = k_begin; k < k_end; ++k) {
         chunks[k].off = offset;
-        offset += chunks[k].width * 32;
+        offset += chunks[k].width * kSellSlots;
     }
 
     if (tid == THREADS - 1) { *total_slots = offset; }
     __syncthreads();
 
     return n_chunks;
+}
+
+// Deals the chunks to the warps: longest-processing-time-first on (width + a fixed per-chunk cost), so that every warp of
+// the CTA has about the same number of steps in each EM phase. `in` holds the descriptors in the order they were made
+// (widest first, roughly); `out` receives them grouped by warp, warp_begin[w] .. warp_begin[w + 1] being warp w's.
+constexpr uint32_t kSellChunkCost = 5;   // steps a chunk costs on top of its width (descriptor, reduction, division)
+
+template <int THREADS>
+__device__ void sellAssignChunks(const SellChunk * in, const uint32_t n_chunks, SellChunk * out, uint32_t * warp_begin, uint32_t * dest) {
+
+    constexpr uint32_t W = THREADS / 32;
+
+    if (threadIdx.x == 0) {
+
+        uint32_t load[W];
+        uint32_t count[W];
+        for (uint32_t w = 0; w < W; ++w) { load[w] = 0; count[w] = 0; }
+
+        for (uint32_t k = 0; k < n_chunks; ++k) {
+
+            uint32_t best = 0;
+            for (uint32_t w = 1; w < W; ++w) {
+                if (load[w] < load[best]) { best = w; }
+            }
+
+            load[best] += in[k].width + kSellChunkCost;
+            count[best]++;
+            dest[k] = best;
+        }
+
+        uint32_t run = 0;
+        for (uint32_t w = 0; w < W; ++w) {
+            warp_begin[w] = run;
+            run += count[w];
+            count[w] = warp_begin[w];
+        }
+        warp_begin[W] = run;
+
+        for (uint32_t k = 0; k < n_chunks; ++k) { dest[k] = count[dest[k]]++; }
+    }
+
+    __syncthreads();
+
+    for (uint32_t k = threadIdx.x; k < n_chunks; k += THREADS) { out[dest[k]] = in[k]; }
+
+    __syncthreads();
 }
 
 // Bump allocator over the CTA's dynamic shared memory with overflow into its global scratch area.
@@ -341,9 +400,10 @@ struct SellArena {
 template <typename IndexT>
 struct SellSide {
 
-    const SellChunk * chunks;
+    const SellChunk * chunks;    // grouped by the warp that works on them (warp_begin)
+    const uint32_t * warp_begin; // [num_warps + 1]
     uint32_t n_chunks;
-    uint32_t n_resident;         // chunks [0, n_resident) have their entries in shared memory
+    uint32_t n_resident;         // number of chunks whose entries are in shared memory: those with off < resident_slots
     uint32_t resident_slots;     // entry slots of the resident chunks
     const double * val_s;        // resident entries
     const IndexT * idx_s;
@@ -389,10 +449,32 @@ __device__ __forceinline__ double sellLaneSum(double acc, uint32_t l2) {
     return acc;
 }
 
-// chunk handled by `warp` in round q: rounds alternate direction so that the chunk widths (descending) even out
-__device__ __forceinline__ uint32_t sellChunkOfRound(uint32_t q, uint32_t warp, uint32_t num_warps) {
+// the same for the kSellWays partial sums of a lane at once (independent shuffle chains)
+__device__ __forceinline__ void sellLaneSumWays(double (&acc)[kSellWays], uint32_t l2) {
 
-    return q * num_warps + ((q & 1) ? (num_warps - 1 - warp) : warp);
+    #pragma unroll
+    for (uint32_t step = 0; step < 5; ++step) {
+        if (l2 > step) {
+            #pragma unroll
+            for (uint32_t u = 0; u < kSellWays; ++u) { acc[u] += __shfl_xor_sync(0xffffffffu, acc[u], 1u << step); }
+        }
+    }
+}
+
+// sum_t val[t] * x[idx[t]] over the steps of a chunk for each of the lane's slots. (Measured on B200: the plain loop,
+// one running sum per slot and four steps unrolled, beats grouped/predicated loads and split sums — the phase is bound by
+// the shared-memory pipe, not by the dependent adds.)
+template <typename IndexT>
+__device__ __forceinline__ void sellChunkDot(const double * __restrict__ val, const IndexT * __restrict__ idx, const double * x, const uint32_t width, double (&acc)[kSellWays]) {
+
+    #pragma unroll
+    for (uint32_t u = 0; u < kSellWays; ++u) { acc[u] = 0; }
+
+    #pragma unroll 4
+    for (uint32_t t = 0; t < width; ++t) {
+        #pragma unroll
+        for (uint32_t u = 0; u < kSellWays; ++u) { acc[u] = fma(val[t * kSellSlots + u * 32], x[idx[t * kSellSlots + u * 32]], acc[u]); }
+    }
 }
 
 #ifdef RPVG_B200_EM_TRACE
@@ -423,8 +505,8 @@ __device__ __forceinline__ uint32_t emSellIterate(const SellLoop<IndexT> & lp, c
     const double min_abundance = params.min_em_abundance;
     const double inv_total = 1.0 / total;
 
-    const uint32_t row_rounds = (lp.rows.n_chunks + num_warps - 1) / num_warps;
-    const uint32_t col_rounds = (lp.cols.n_chunks + num_warps - 1) / num_warps;
+    const uint32_t row_k0 = lp.rows.warp_begin[warp], row_k1 = lp.rows.warp_begin[warp + 1];
+    const uint32_t col_k0 = lp.cols.warp_begin[warp], col_k1 = lp.cols.warp_begin[warp + 1];
 
     uint32_t conv_its = 0;
     uint32_t it = 0;
@@ -438,36 +520,43 @@ __device__ __forceinline__ uint32_t emSellIterate(const SellLoop<IndexT> & lp, c
         double noise_acc = 0;
 
         #pragma unroll 1
-        for (uint32_t q = 0; q < row_rounds; ++q) {
-
-            const uint32_t k = sellChunkOfRound(q, warp, num_warps);
-            if (k >= lp.rows.n_chunks) { continue; }
+        for (uint32_t k = row_k0; k < row_k1; ++k) {
 
             const SellChunk ch = lp.rows.chunks[k];
-            const uint32_t r = lane >> ch.l2;
-            const bool head = (lane & ((1u << ch.l2) - 1)) == 0 && r < ch.count;
-            const uint32_t p = ch.first + r;
+            const bool lead = (lane & ((1u << ch.l2) - 1)) == 0;
 
-            double nz = 0, ct = 0;
-            if (head) {
-                nz = lp.noise[p];
-                ct = lp.cnt[p];
+            uint32_t p[kSellWays];
+            bool head[kSellWays];
+            double nz[kSellWays], ct[kSellWays];
+
+            #pragma unroll
+            for (uint32_t u = 0; u < kSellWays; ++u) {
+                const uint32_t r = (u * 32 + lane) >> ch.l2;
+                head[u] = lead && r < ch.count;
+                p[u] = ch.first + r;
+                nz[u] = 0;
+                ct[u] = 0;
+                if (head[u]) {
+                    nz[u] = lp.noise[p[u]];
+                    ct[u] = lp.cnt[p[u]];
+                }
             }
 
-            const bool res = ALL_SHARED || k < lp.rows.n_resident;
+            const bool res = ALL_SHARED || ch.off < lp.rows.resident_slots;
             const double * val = (res ? lp.rows.val_s + ch.off : lp.rows.val_g + (ch.off - lp.rows.resident_slots)) + lane;
             const IndexT * idx = (res ? lp.rows.idx_s + ch.off : lp.rows.idx_g + (ch.off - lp.rows.resident_slots)) + lane;
 
-            double acc = 0;
-            #pragma unroll 4
-            for (uint32_t t = 0; t < ch.width; ++t) { acc = fma(val[t * 32], a[idx[t * 32]], acc); }
+            double acc[kSellWays];
+            sellChunkDot<IndexT>(val, idx, a, ch.width, acc);
+            sellLaneSumWays(acc, ch.l2);
 
-            acc = sellLaneSum(acc, ch.l2);
-
-            if (head) {
-                const double wv = ct * sellReciprocal(fma(nz, a_noise, acc));
-                w[p] = wv;
-                noise_acc = fma(nz, wv, noise_acc);
+            #pragma unroll
+            for (uint32_t u = 0; u < kSellWays; ++u) {
+                if (head[u]) {
+                    const double wv = ct[u] * sellReciprocal(fma(nz[u], a_noise, acc[u]));
+                    w[p[u]] = wv;
+                    noise_acc = fma(nz[u], wv, noise_acc);
+                }
             }
         }
 
@@ -486,39 +575,45 @@ __device__ __forceinline__ uint32_t emSellIterate(const SellLoop<IndexT> & lp, c
         bool ok = true;
 
         #pragma unroll 1
-        for (uint32_t q = 0; q < col_rounds; ++q) {
-
-            const uint32_t k = sellChunkOfRound(q, warp, num_warps);
-            if (k >= lp.cols.n_chunks) { continue; }
+        for (uint32_t k = col_k0; k < col_k1; ++k) {
 
             const SellChunk ch = lp.cols.chunks[k];
-            const uint32_t r = lane >> ch.l2;
-            const bool head = (lane & ((1u << ch.l2) - 1)) == 0 && r < ch.count;
+            const bool lead = (lane & ((1u << ch.l2) - 1)) == 0;
 
-            uint32_t j = 0;
-            double a_old = 0;
-            if (head) {
-                j = lp.col_id[ch.first + r];
-                if (!MULTI) { a_old = a[j]; }
+            uint32_t j[kSellWays];
+            bool head[kSellWays];
+            double a_old[kSellWays];
+
+            #pragma unroll
+            for (uint32_t u = 0; u < kSellWays; ++u) {
+                const uint32_t r = (u * 32 + lane) >> ch.l2;
+                head[u] = lead && r < ch.count;
+                j[u] = 0;
+                a_old[u] = 0;
+                if (head[u]) {
+                    j[u] = lp.col_id[ch.first + r];
+                    if (!MULTI) { a_old[u] = a[j[u]]; }
+                }
             }
 
-            const bool res = ALL_SHARED || k < lp.cols.n_resident;
+            const bool res = ALL_SHARED || ch.off < lp.cols.resident_slots;
             const double * val = (res ? lp.cols.val_s + ch.off : lp.cols.val_g + (ch.off - lp.cols.resident_slots)) + lane;
             const IndexT * idx = (res ? lp.cols.idx_s + ch.off : lp.cols.idx_g + (ch.off - lp.cols.resident_slots)) + lane;
 
-            double acc = 0;
-            #pragma unroll 4
-            for (uint32_t t = 0; t < ch.width; ++t) { acc = fma(val[t * 32], w[idx[t * 32]], acc); }
+            double acc[kSellWays];
+            sellChunkDot<IndexT>(val, idx, w, ch.width, acc);
+            sellLaneSumWays(acc, ch.l2);
 
-            acc = sellLaneSum(acc, ch.l2);
-
-            if (head) {
-                if (MULTI) {
-                    g[j] = acc;
-                } else {
-                    const double a_new = (a_old * acc) * inv_total;
-                    a[j] = a_new;
-                    if (a_new >= min_abundance && fabs(a_new - a_old) > conv * a_new) { ok = false; }
+            #pragma unroll
+            for (uint32_t u = 0; u < kSellWays; ++u) {
+                if (head[u]) {
+                    if (MULTI) {
+                        g[j[u]] = acc[u];
+                    } else {
+                        const double a_new = (a_old[u] * acc[u]) * inv_total;
+                        a[j[u]] = a_new;
+                        if (a_new >= min_abundance && fabs(a_new - a_old[u]) > conv * a_new) { ok = false; }
+                    }
                 }
             }
         }
@@ -633,8 +728,18 @@ __device__ __forceinline__ uint32_t emSellIterate(const SellLoop<IndexT> & lp, c
     return it;
 }
 
+#ifdef RPVG_B200_EM_TIMELINE
+// tuning builds only: one record per CTA (tools/em_timeline.py)
+__device__ unsigned long long rpvg_timeline_records[12 * 65536];
+__device__ unsigned int rpvg_timeline_count;
+#endif
+
+#ifndef RPVG_B200_EM_MIN_CTAS_512
+#define RPVG_B200_EM_MIN_CTAS_512 1
+#endif
+
 template <int THREADS, bool MULTI, typename IndexT>
-__global__ void __launch_bounds__(THREADS) emSellKernel(const SellArgs sa) {
+__global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CTAS_512 : (THREADS == 128 ? 6 : (THREADS == 64 ? 12 : 1)))) emSellKernel(const SellArgs sa) {
 
     extern __shared__ __align__(16) unsigned char smem_raw[];
 
@@ -643,6 +748,8 @@ __global__ void __launch_bounds__(THREADS) emSellKernel(const SellArgs sa) {
     __shared__ double final_part[kMaxGroupSize];
     __shared__ uint32_t scan_tmp[THREADS / 32];
     __shared__ uint32_t shared_u32[4];
+    __shared__ uint32_t row_warp_begin[THREADS / 32 + 1];
+    __shared__ uint32_t col_warp_begin[THREADS / 32 + 1];
     __shared__ SellSort<THREADS> sort_state;
 
     const EmArgs & args = sa.em;
@@ -657,6 +764,11 @@ __global__ void __launch_bounds__(THREADS) emSellKernel(const SellArgs sa) {
     constexpr uint32_t num_warps = THREADS / 32;
 
     if (*args.error) { return; }   // malformed arena: indices cannot be trusted (uniform over the whole grid)
+
+#ifdef RPVG_B200_EM_TIMELINE
+    unsigned long long timeline_t0, timeline_t1;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(timeline_t0));
+#endif
 
     const uint32_t group = blockIdx.x / S;
     const uint32_t c = sa.group_cluster[group];
@@ -749,7 +861,9 @@ __global__ void __launch_bounds__(THREADS) emSellKernel(const SellArgs sa) {
     const uint32_t row_chunk_bound = sellCountChunks<THREADS>(sort_state, m, depth);
 
     SellChunk * row_chunks = static_cast<SellChunk *>(arena.take(sizeof(SellChunk) * (row_chunk_bound + 1), true, nullptr));
-    const uint32_t n_row_chunks = sellMakeChunks<THREADS>(sort_state, m, depth, row_len, row_src, row_chunks, scan_tmp, &shared_u32[0]);
+    SellChunk * row_chunks_made = static_cast<SellChunk *>(arena.take(sizeof(SellChunk) * (row_chunk_bound + 1), false, nullptr));
+    uint32_t * row_chunk_dest = static_cast<uint32_t *>(arena.take(4ull * (row_chunk_bound + 1), false, nullptr));
+    const uint32_t n_row_chunks = sellMakeChunks<THREADS>(sort_state, m, depth, row_len, row_src, row_chunks_made, scan_tmp, &shared_u32[0]);
     const uint32_t row_slots = shared_u32[0];
 
     for (uint32_t p = tid; p < m; p += THREADS) {
@@ -827,7 +941,9 @@ __global__ void __launch_bounds__(THREADS) emSellKernel(const SellArgs sa) {
     const uint32_t col_chunk_bound = sellCountChunks<THREADS>(sort_state, n_cols_present, depth);
 
     SellChunk * col_chunks = static_cast<SellChunk *>(arena.take(sizeof(SellChunk) * (col_chunk_bound + 1), true, nullptr));
-    const uint32_t n_col_chunks = sellMakeChunks<THREADS>(sort_state, n_cols_present, depth, col_len, col_src, col_chunks, scan_tmp, &shared_u32[1]);
+    SellChunk * col_chunks_made = static_cast<SellChunk *>(arena.take(sizeof(SellChunk) * (col_chunk_bound + 1), false, nullptr));
+    uint32_t * col_chunk_dest = static_cast<uint32_t *>(arena.take(4ull * (col_chunk_bound + 1), false, nullptr));
+    const uint32_t n_col_chunks = sellMakeChunks<THREADS>(sort_state, n_cols_present, depth, col_len, col_src, col_chunks_made, scan_tmp, &shared_u32[1]);
     const uint32_t col_slots = shared_u32[1];
 
     // column ids in sorted order (kept for the whole kernel)
@@ -848,13 +964,13 @@ __global__ void __launch_bounds__(THREADS) emSellKernel(const SellArgs sa) {
             uint32_t lo = 0, hi = n_chunks;   // first chunk whose end exceeds the budget
             while (lo < hi) {
                 const uint32_t mid = (lo + hi) >> 1;
-                if (static_cast<uint64_t>(chunks[mid].off) + chunks[mid].width * 32 > budget_slots) { hi = mid; } else { lo = mid + 1; }
+                if (static_cast<uint64_t>(chunks[mid].off) + chunks[mid].width * kSellSlots > budget_slots) { hi = mid; } else { lo = mid + 1; }
             }
             n_res = lo;
             res_slots = (n_res < n_chunks) ? chunks[n_res].off : slots;
         }
 
-        side->chunks = chunks;
+        side->chunks = nullptr;   // set once the chunks are dealt to the warps
         side->n_chunks = n_chunks;
         side->n_resident = n_res;
         side->resident_slots = res_slots;
@@ -865,8 +981,8 @@ __global__ void __launch_bounds__(THREADS) emSellKernel(const SellArgs sa) {
     };
 
     SellSide<IndexT> cols, rows;
-    place(col_chunks, n_col_chunks, col_slots, &cols);
-    place(row_chunks, n_row_chunks, row_slots, &rows);
+    place(col_chunks_made, n_col_chunks, col_slots, &cols);
+    place(row_chunks_made, n_row_chunks, row_slots, &rows);
 
     // capacity check, uniform over the group: every CTA publishes its flag before anyone proceeds
     if (MULTI) {
@@ -891,6 +1007,15 @@ __global__ void __launch_bounds__(THREADS) emSellKernel(const SellArgs sa) {
         return;
     }
 
+    // ---- deal the chunks to the warps (after the capacity check: the scratch arrays are known to be in bounds)
+    sellAssignChunks<THREADS>(row_chunks_made, n_row_chunks, row_chunks, row_warp_begin, row_chunk_dest);
+    sellAssignChunks<THREADS>(col_chunks_made, n_col_chunks, col_chunks, col_warp_begin, col_chunk_dest);
+
+    rows.chunks = row_chunks;
+    rows.warp_begin = row_warp_begin;
+    cols.chunks = col_chunks;
+    cols.warp_begin = col_warp_begin;
+
     // ---- fill: one warp per chunk
     auto fill = [&](const SellSide<IndexT> & side, auto entry_range, auto entry_value, auto entry_index, const uint32_t * src) {
 
@@ -898,28 +1023,34 @@ __global__ void __launch_bounds__(THREADS) emSellKernel(const SellArgs sa) {
 
             const SellChunk ch = side.chunks[k];
             const uint32_t lanes = 1u << ch.l2;
-            const uint32_t r = lane >> ch.l2;
             const uint32_t sub = lane & (lanes - 1);
 
-            const bool res = k < side.n_resident;
+            const bool res = ch.off < side.resident_slots;
             double * val = const_cast<double *>(res ? side.val_s + ch.off : side.val_g + (ch.off - side.resident_slots));
             IndexT * idx = const_cast<IndexT *>(res ? side.idx_s + ch.off : side.idx_g + (ch.off - side.resident_slots));
 
-            uint64_t base = 0;
-            uint32_t len = 0;
-            if (r < ch.count) { entry_range(src[ch.first + r], &base, &len); }
+            #pragma unroll
+            for (uint32_t u = 0; u < kSellWays; ++u) {
 
-            for (uint32_t t = 0; t < ch.width; ++t) {
+                const uint32_t slot = u * 32 + lane;
+                const uint32_t r = slot >> ch.l2;
 
-                const uint32_t e = t * lanes + sub;
-                double v = 0;
-                IndexT x = 0;
-                if (e < len) {
-                    v = entry_value(base + e);
-                    x = static_cast<IndexT>(entry_index(base + e));
+                uint64_t base = 0;
+                uint32_t len = 0;
+                if (r < ch.count) { entry_range(src[ch.first + r], &base, &len); }
+
+                for (uint32_t t = 0; t < ch.width; ++t) {
+
+                    const uint32_t e = t * lanes + sub;
+                    double v = 0;
+                    IndexT x = 0;
+                    if (e < len) {
+                        v = entry_value(base + e);
+                        x = static_cast<IndexT>(entry_index(base + e));
+                    }
+                    val[t * kSellSlots + slot] = v;
+                    idx[t * kSellSlots + slot] = x;
                 }
-                val[t * 32 + lane] = v;
-                idx[t * 32 + lane] = x;
             }
         }
     };
@@ -966,6 +1097,20 @@ __global__ void __launch_bounds__(THREADS) emSellKernel(const SellArgs sa) {
 
     const double total_count = total;
     uint32_t it;
+
+#ifdef RPVG_B200_EM_TRACE
+    if (tid == 0 && (rank == 0 || rank == S - 1)) {
+        uint32_t widest_row = 0, widest_col = 0;
+        for (uint32_t k = 0; k < n_row_chunks; ++k) { widest_row = max(widest_row, row_chunks[k].width); }
+        for (uint32_t k = 0; k < n_col_chunks; ++k) { widest_col = max(widest_col, col_chunks[k].width); }
+        printf("[layout] rank %u/%u m %u z %u cols present %u | rows: chunks %u slots %u widest %u resident %u | cols: chunks %u slots %u widest %u resident %u | depth %u\n", rank, S, m, z_slice,
+               n_cols_present, n_row_chunks, row_slots, widest_row, rows.n_resident, n_col_chunks, col_slots, widest_col, cols.n_resident, depth);
+    }
+#endif
+
+#ifdef RPVG_B200_EM_TIMELINE
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(timeline_t1));
+#endif
 
     if (all_shared) {
 
@@ -1033,6 +1178,21 @@ __global__ void __launch_bounds__(THREADS) emSellKernel(const SellArgs sa) {
         args.total_count[c] = total;
         args.iterations[c] = it;
     }
+
+#ifdef RPVG_B200_EM_TIMELINE
+    if (tid == 0) {
+        unsigned long long timeline_t2;
+        uint32_t smid;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(timeline_t2));
+        asm volatile("mov.u32 %0, %smid;" : "=r"(smid));
+        const unsigned int slot = atomicAdd(&rpvg_timeline_count, 1u);
+        if (slot < 65536) {
+            unsigned long long * rec = rpvg_timeline_records + 12ull * slot;
+            rec[0] = THREADS; rec[1] = S; rec[2] = rank; rec[3] = c; rec[4] = smid; rec[5] = M; rec[6] = N;
+            rec[7] = timeline_t0; rec[8] = timeline_t1; rec[9] = timeline_t2; rec[10] = it; rec[11] = all_shared ? 1u : 0u;
+        }
+    }
+#endif
 
     // no CTA may exit while a peer can still touch its shared memory
     if (MULTI) { cluster.sync(); }
