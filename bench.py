@@ -309,6 +309,16 @@ def main():
         peak, peak_src = measured_peak_hbm()
         em_ms_mean = float(np.mean(em_ms))
         achieved = alg_bytes / (em_ms_mean * 1e-3) / 1e9
+        # DRAM bytes the EM launches of one step really move (ncu, same workload): the slices live in shared memory, so
+        # this is a small fraction of the algorithmic bytes the HBM roofline is quoted on (profiles/r01b_*).
+        traffic, traffic_src = None, None
+        try:
+            with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01b_em_traffic.json")) as fh:
+                measured = json.load(fh)
+            if world == 1:
+                traffic, traffic_src = measured["em_dram_bytes_per_step"], measured["source"]
+        except OSError:
+            pass
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": max_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f64", "data": "synthetic", "config": config, "clocks": clocks,
@@ -316,7 +326,8 @@ def main():
                         "ms_per_step": max_e2e_ms / args.steps},
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "hbm", "kernel": "emSellKernel (all bins, concurrent streams)", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                             "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                             "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                             "limiter": "shared-memory pipe and cluster barriers (69% of the shared pipe on one SM, profiles/r01b_ncu_launches_summary.md)",
                              "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": em_ms_mean, "build_ms": float(np.mean(build_ms)),
                              "kernel_share_of_step": em_ms_mean / (max_ms / args.steps)},
                 "inference_stage_wall_ms": max_e2e_ms / args.steps,

@@ -241,7 +241,15 @@ void planEmLaunches(const rpvg_b200_ctx * ctx, rpvg_b200_batch * b, std::vector<
         const uint64_t index_bytes = (N + 1 < 65536 && m_b < 65536) ? 2 : 4;
 
         const bool multi = group > 1;
-        const uint64_t fixed = sellRound16(8 * (N + 1)) * (multi ? 2 : 1);
+
+        // columns a slice has entries in: all of them at worst; with the read classes ordered by first path a slice
+        // of a group touches a band of about N / group columns
+        const uint64_t cols_worst = std::min(N, z_b);
+        const uint64_t cols_typical = multi ? std::min(cols_worst, 2 * N / group + 64) : cols_worst;
+
+        // what must be in shared memory whatever the layout: the abundances (one CTA) or the two generations of column
+        // sums the peers read (group); a group also needs N bytes of exchange area while it is being set up
+        const uint64_t fixed = multi ? std::max<uint64_t>(2 * sellRound16(8 * (cols_worst + 2)), N) : sellRound16(8 * (N + 1));
 
         GroupPlan plan;
         plan.cluster = c;
@@ -251,8 +259,8 @@ void planEmLaunches(const rpvg_b200_ctx * ctx, rpvg_b200_batch * b, std::vector<
 
         if (fixed + 4096 <= smem_cap) {
 
-            const uint64_t need_typical = sellSmemBytes(m_b, z_b, N, index_bytes, multi, false);
-            const uint64_t need_worst = sellSmemBytes(m_b, z_b, N, index_bytes, multi, true);
+            const uint64_t need_typical = std::max(fixed + 4096, sellSmemBytes(m_b, z_b, N, cols_typical, index_bytes, multi, false));
+            const uint64_t need_worst = std::max(fixed + 4096, sellSmemBytes(m_b, z_b, N, cols_worst, index_bytes, multi, true));
 
             int tier_typical = kNumTiers - 1;
             for (int t = 0; t < kNumTiers; ++t) {

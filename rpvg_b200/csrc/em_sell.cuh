@@ -14,8 +14,12 @@
 // E-step: warp per row chunk  : acc = sum val * a[col]; reduce over L lanes; w_row = count / (acc + noise * a_noise)
 // M-step: warp per column chunk: acc = sum val * w[row]; reduce over L lanes; partial column sum g[col] (S > 1) or the
 //         abundance update itself (S = 1).
-// S > 1: reduce-scatter + all-gather of the N + 1 column sums over distributed shared memory, two cluster barriers per
-//        iteration; S = 1: two block barriers per iteration (the second one carries the convergence vote).
+// S > 1: every CTA works on local ids of the columns its slice touches. After the M-step and ONE cluster barrier each
+//        CTA pulls, for each of its columns, the partial sums of the other CTAs that hold the column (distributed shared
+//        memory; the read classes are ordered by first path, so most columns live in one or two slices) and updates its
+//        own copy of the abundance — all holders add in the same order and get the same bits. The convergence vote
+//        travels one iteration behind (previous abundances are kept), so it costs no barrier either.
+//        S = 1: two block barriers per iteration (the second one carries the convergence vote).
 //
 // The slice lives in shared memory as far as it fits (vectors first, then column chunks, then row chunks); chunks
 // that do not fit are streamed from a global scratch area with coalesced 128-byte warp loads ("hybrid residency").
@@ -92,29 +96,32 @@ __host__ __device__ inline uint64_t sellSlotsTypical(uint64_t z, uint64_t n) { r
 
 __host__ __device__ inline uint64_t sellRound16(uint64_t bytes) { return (bytes + 15) & ~uint64_t(15); }
 
-// Shared-memory need of one CTA: m rows, z entries, N columns (worst: upper bound; otherwise the expected need).
-__host__ __device__ inline uint64_t sellSmemBytes(uint64_t m, uint64_t z, uint64_t N, uint64_t index_bytes, bool multi, bool worst) {
+// Shared-memory need of one CTA: m rows, z entries, N columns of which n_cols have entries in the slice (worst: upper
+// bound; otherwise the expected need). One CTA keeps the abundances of all N + 1 columns; a CTA of a group keeps
+// vectors over its own columns only (two generations of column sums, abundances, previous abundances) and the tables of
+// the exchange with its peers.
+__host__ __device__ inline uint64_t sellSmemBytes(uint64_t m, uint64_t z, uint64_t N, uint64_t n_cols, uint64_t index_bytes, bool multi, bool worst) {
 
-    const uint64_t fixed = sellRound16(8 * (N + 1)) * (multi ? 2 : 1);
+    const uint64_t fixed = multi ? 4 * sellRound16(8 * (n_cols + 2)) : sellRound16(8 * (N + 1));
     const uint64_t vectors = 3 * sellRound16(8 * (m + 1));
-    const uint64_t chunks = worst ? 16 * (m + N + 130) : 16 * ((m + N) / 8 + 140);
-    const uint64_t col_id = sellRound16(index_bytes * (N + 1));
-    const uint64_t slots = worst ? sellSlotsWorst(z, m) + sellSlotsWorst(z, N) : sellSlotsTypical(z, m) + sellSlotsTypical(z, N);
-    const uint64_t masks = multi ? sellRound16(2 * (N + 2)) : 0;
-    return fixed + vectors + chunks + col_id + masks + (8 + index_bytes) * slots + 256;
+    const uint64_t chunks = worst ? 16 * (m + n_cols + 130) : 16 * ((m + n_cols) / 8 + 140);
+    const uint64_t col_id = multi ? 0 : sellRound16(index_bytes * (N + 1));
+    const uint64_t slots = worst ? sellSlotsWorst(z, m) + sellSlotsWorst(z, n_cols) : sellSlotsTypical(z, m) + sellSlotsTypical(z, n_cols);
+    const uint64_t tables = multi ? (6 * (n_cols + 2) + (worst ? 2 * 15 * n_cols : n_cols) + 64) : 0;
+    return fixed + vectors + chunks + col_id + tables + (8 + index_bytes) * slots + 256;
 }
 
 // Global scratch one CTA owns: prologue temporaries, everything that may spill out of shared memory and, when
 // with_entries, the worst-case entry arrays.
 __host__ __device__ inline uint64_t sellScratchBytes(uint64_t m, uint64_t z, uint64_t N, uint64_t index_bytes, bool with_entries) {
 
-    const uint64_t temps = 2 * sellRound16(4 * (m + 1)) + 4 * sellRound16(4 * (N + 1));
-    const uint64_t vectors = 3 * sellRound16(8 * (m + 1));
+    const uint64_t temps = 2 * sellRound16(4 * (m + 1)) + 5 * sellRound16(4 * (N + 1));
+    const uint64_t vectors = 3 * sellRound16(8 * (m + 1)) + 2 * sellRound16(8 * (N + 2));
     const uint64_t chunks = 2 * 16 * (m + N + 130) + 2 * 4 * (m + N + 260);   // final and unassigned descriptors, assignment
     const uint64_t col_id = sellRound16(index_bytes * (N + 1));
     const uint64_t entries = with_entries ? (8 + index_bytes) * (sellSlotsWorst(z, m) + sellSlotsWorst(z, N)) + 128 : 64;
-    const uint64_t masks = sellRound16(2 * (N + 2));
-    return ((temps + vectors + chunks + col_id + masks + entries + 1023) / 1024) * 1024;
+    const uint64_t tables = 6 * (N + 2) + 2 * 15 * (N + 1) + 64;
+    return ((temps + vectors + chunks + col_id + tables + entries + 1023) / 1024) * 1024;
 }
 
 template <int THREADS>
@@ -196,6 +203,51 @@ __device__ void sellStableSort(SellSort<THREADS> & st, const uint32_t n, LenFn l
     }
 
     __syncthreads();
+}
+
+// Exclusive prefix sum over n values held in (global or shared) memory, in place; returns the total. Block-wide; tmp has
+// one slot per warp.
+template <int THREADS>
+__device__ uint32_t sellExclusiveScan(uint32_t * values, const uint32_t n, uint32_t * tmp) {
+
+    const uint32_t tid = threadIdx.x;
+    const uint32_t lane = tid & 31;
+    const uint32_t warp = tid >> 5;
+
+    const uint32_t per_thread = (n + THREADS - 1) / THREADS;
+    const uint32_t begin = min(n, tid * per_thread);
+    const uint32_t end = min(n, begin + per_thread);
+
+    uint32_t local = 0;
+    for (uint32_t k = begin; k < end; ++k) { local += values[k]; }
+
+    uint32_t incl = local;
+    #pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const uint32_t up = __shfl_up_sync(0xffffffffu, incl, off);
+        if (lane >= off) { incl += up; }
+    }
+
+    __syncthreads();   // tmp may still be read from an earlier call
+    if (lane == 31) { tmp[warp] = incl; }
+    __syncthreads();
+
+    uint32_t warp_base = 0;
+    uint32_t total = 0;
+    for (uint32_t w = 0; w < THREADS / 32; ++w) {
+        if (w < warp) { warp_base += tmp[w]; }
+        total += tmp[w];
+    }
+
+    uint32_t run = warp_base + incl - local;
+    for (uint32_t k = begin; k < end; ++k) {
+        const uint32_t v = values[k];
+        values[k] = run;
+        run += v;
+    }
+
+    __syncthreads();
+    return total;
 }
 
 // Number of chunks sellMakeChunks will form for the items just sorted (same walk, nothing written).
@@ -397,6 +449,7 @@ struct SellArena {
     }
 };
 
+
 template <typename IndexT>
 struct SellSide {
 
@@ -411,16 +464,31 @@ struct SellSide {
     const IndexT * idx_g;
 };
 
+// Exchange state of a CTA that is part of a group (static shared memory, same offsets in every CTA of the group).
+struct SellPeers {
+
+    uint32_t present[kMaxGroupSize];   // columns (with entries) of every CTA's slice: its noise column has that local id
+    uint32_t flag[2];                  // "all my columns converged in the previous update", one per barrier generation
+    uint32_t vote[32];                 // per warp, from the update just done
+    uint32_t stop;
+};
+
 template <typename IndexT>
 struct SellLoop {
 
-    double * a;
-    double * g;
+    double * a;                  // abundances: all N + 1 columns (one CTA) or this slice's columns + noise (group)
+    double * a_prev;             // group: abundances before the latest update
+    double * g;                  // group: two generations of partial column sums, g + gen * g_stride
+    uint32_t g_stride;
+    uint32_t n_local;            // group: columns of this slice; the noise column has local id n_local
     double * w;
     const double * noise;
     const double * cnt;
-    const IndexT * col_id;
-    const uint16_t * owned_mask;
+    const IndexT * col_id;       // one CTA: column of each sorted position
+    const uint16_t * holders;    // group: bit s set = CTA s holds the column
+    const uint32_t * pull_begin; // group: first entry of the column in peer_id
+    const IndexT * peer_id;      // group: local id of the column in each other holder, ascending CTA rank
+    SellPeers * peers;
     SellSide<IndexT> rows;
     SellSide<IndexT> cols;
 };
@@ -438,18 +506,7 @@ __device__ __forceinline__ double sellReciprocal(double x) {
     return r;
 }
 
-// sum over the 1 << l2 adjacent lanes that share a row (column)
-__device__ __forceinline__ double sellLaneSum(double acc, uint32_t l2) {
-
-    if (l2 > 0) { acc += __shfl_xor_sync(0xffffffffu, acc, 1); }
-    if (l2 > 1) { acc += __shfl_xor_sync(0xffffffffu, acc, 2); }
-    if (l2 > 2) { acc += __shfl_xor_sync(0xffffffffu, acc, 4); }
-    if (l2 > 3) { acc += __shfl_xor_sync(0xffffffffu, acc, 8); }
-    if (l2 > 4) { acc += __shfl_xor_sync(0xffffffffu, acc, 16); }
-    return acc;
-}
-
-// the same for the kSellWays partial sums of a lane at once (independent shuffle chains)
+// sum over the 1 << l2 adjacent lanes that share a row (column), for the kSellWays partial sums of a lane at once
 __device__ __forceinline__ void sellLaneSumWays(double (&acc)[kSellWays], uint32_t l2) {
 
     #pragma unroll
@@ -485,12 +542,61 @@ __device__ __forceinline__ void sellChunkDot(const double * __restrict__ val, co
 #define SELL_TRACE(k)
 #endif
 
-// The EM iterations of one CTA (see the header comment of this file). Returns the number of iterations executed.
-template <int THREADS, bool MULTI, bool ALL_SHARED, typename IndexT>
-__device__ __forceinline__ uint32_t emSellIterate(const SellLoop<IndexT> & lp, const rpvg_b200_em_params & params, const uint32_t N, const uint32_t S, const uint32_t rank,
-                                                  const uint32_t jc0, const uint32_t jc1, const double total, double * red, uint32_t * conv_flags) {
+// E-step over the slice: w_i = count_i / (sum_j p_ij a_j + noise_i a_noise); returns this warp's share of
+// sum_i noise_i w_i (summed over the warp).
+template <bool ALL_SHARED, typename IndexT>
+__device__ __forceinline__ double sellExpectation(const SellLoop<IndexT> & lp, const double * a, const double a_noise, const uint32_t k0, const uint32_t k1, const uint32_t lane) {
 
-    cg::cluster_group cluster = cg::this_cluster();
+    double noise_acc = 0;
+
+    #pragma unroll 1
+    for (uint32_t k = k0; k < k1; ++k) {
+
+        const SellChunk ch = lp.rows.chunks[k];
+        const bool lead = (lane & ((1u << ch.l2) - 1)) == 0;
+
+        uint32_t p[kSellWays];
+        bool head[kSellWays];
+        double nz[kSellWays], ct[kSellWays];
+
+        #pragma unroll
+        for (uint32_t u = 0; u < kSellWays; ++u) {
+            const uint32_t r = (u * 32 + lane) >> ch.l2;
+            head[u] = lead && r < ch.count;
+            p[u] = ch.first + r;
+            nz[u] = 0;
+            ct[u] = 0;
+            if (head[u]) {
+                nz[u] = lp.noise[p[u]];
+                ct[u] = lp.cnt[p[u]];
+            }
+        }
+
+        const bool res = ALL_SHARED || ch.off < lp.rows.resident_slots;
+        const double * val = (res ? lp.rows.val_s + ch.off : lp.rows.val_g + (ch.off - lp.rows.resident_slots)) + lane;
+        const IndexT * idx = (res ? lp.rows.idx_s + ch.off : lp.rows.idx_g + (ch.off - lp.rows.resident_slots)) + lane;
+
+        double acc[kSellWays];
+        sellChunkDot<IndexT>(val, idx, a, ch.width, acc);
+        sellLaneSumWays(acc, ch.l2);
+
+        #pragma unroll
+        for (uint32_t u = 0; u < kSellWays; ++u) {
+            if (head[u]) {
+                const double wv = ct[u] * sellReciprocal(fma(nz[u], a_noise, acc[u]));
+                lp.w[p[u]] = wv;
+                noise_acc = fma(nz[u], wv, noise_acc);
+            }
+        }
+    }
+
+    return warpSum(noise_acc);
+}
+
+// The EM iterations of a CTA that has the whole path cluster (see the header comment of this file). Returns the number of
+// iterations executed.
+template <int THREADS, bool ALL_SHARED, typename IndexT>
+__device__ __forceinline__ uint32_t emSellIterateSingle(const SellLoop<IndexT> & lp, const rpvg_b200_em_params & params, const uint32_t N, const double total, double * red) {
 
     const uint32_t tid = threadIdx.x;
     const uint32_t lane = tid & 31;
@@ -498,8 +604,7 @@ __device__ __forceinline__ uint32_t emSellIterate(const SellLoop<IndexT> & lp, c
     constexpr uint32_t num_warps = THREADS / 32;
 
     double * a = lp.a;
-    double * g = lp.g;
-    double * w = lp.w;
+    const double * w = lp.w;
 
     const double conv = params.max_rel_em_conv;
     const double min_abundance = params.min_em_abundance;
@@ -515,63 +620,19 @@ __device__ __forceinline__ uint32_t emSellIterate(const SellLoop<IndexT> & lp, c
 
     while (it < params.max_em_its) {
 
-        // ---- E-step over the slice: w_i = count_i / sum_j p_ij a_j
         const double a_noise = a[N];
-        double noise_acc = 0;
-
-        #pragma unroll 1
-        for (uint32_t k = row_k0; k < row_k1; ++k) {
-
-            const SellChunk ch = lp.rows.chunks[k];
-            const bool lead = (lane & ((1u << ch.l2) - 1)) == 0;
-
-            uint32_t p[kSellWays];
-            bool head[kSellWays];
-            double nz[kSellWays], ct[kSellWays];
-
-            #pragma unroll
-            for (uint32_t u = 0; u < kSellWays; ++u) {
-                const uint32_t r = (u * 32 + lane) >> ch.l2;
-                head[u] = lead && r < ch.count;
-                p[u] = ch.first + r;
-                nz[u] = 0;
-                ct[u] = 0;
-                if (head[u]) {
-                    nz[u] = lp.noise[p[u]];
-                    ct[u] = lp.cnt[p[u]];
-                }
-            }
-
-            const bool res = ALL_SHARED || ch.off < lp.rows.resident_slots;
-            const double * val = (res ? lp.rows.val_s + ch.off : lp.rows.val_g + (ch.off - lp.rows.resident_slots)) + lane;
-            const IndexT * idx = (res ? lp.rows.idx_s + ch.off : lp.rows.idx_g + (ch.off - lp.rows.resident_slots)) + lane;
-
-            double acc[kSellWays];
-            sellChunkDot<IndexT>(val, idx, a, ch.width, acc);
-            sellLaneSumWays(acc, ch.l2);
-
-            #pragma unroll
-            for (uint32_t u = 0; u < kSellWays; ++u) {
-                if (head[u]) {
-                    const double wv = ct[u] * sellReciprocal(fma(nz[u], a_noise, acc[u]));
-                    w[p[u]] = wv;
-                    noise_acc = fma(nz[u], wv, noise_acc);
-                }
-            }
-        }
+        const double noise_acc = sellExpectation<ALL_SHARED, IndexT>(lp, a, a_noise, row_k0, row_k1, lane);
 
         SELL_TRACE(0)
 
         // noise column: per-warp partials now, combined in a fixed order after the barrier
-        noise_acc = warpSum(noise_acc);
         if (lane == 0) { red[warp] = noise_acc; }
-        if (MULTI && tid < S) { conv_flags[tid] = 1; }
 
         __syncthreads();
 
         SELL_TRACE(1)
 
-        // ---- M-step over the slice: column sums (and, with one CTA, the abundance update itself)
+        // ---- M-step: column sums and the abundance update itself
         bool ok = true;
 
         #pragma unroll 1
@@ -592,7 +653,7 @@ __device__ __forceinline__ uint32_t emSellIterate(const SellLoop<IndexT> & lp, c
                 a_old[u] = 0;
                 if (head[u]) {
                     j[u] = lp.col_id[ch.first + r];
-                    if (!MULTI) { a_old[u] = a[j[u]]; }
+                    a_old[u] = a[j[u]];
                 }
             }
 
@@ -607,13 +668,9 @@ __device__ __forceinline__ uint32_t emSellIterate(const SellLoop<IndexT> & lp, c
             #pragma unroll
             for (uint32_t u = 0; u < kSellWays; ++u) {
                 if (head[u]) {
-                    if (MULTI) {
-                        g[j[u]] = acc[u];
-                    } else {
-                        const double a_new = (a_old[u] * acc[u]) * inv_total;
-                        a[j[u]] = a_new;
-                        if (a_new >= min_abundance && fabs(a_new - a_old[u]) > conv * a_new) { ok = false; }
-                    }
+                    const double a_new = (a_old[u] * acc[u]) * inv_total;
+                    a[j[u]] = a_new;
+                    if (a_new >= min_abundance && fabs(a_new - a_old[u]) > conv * a_new) { ok = false; }
                 }
             }
         }
@@ -624,107 +681,228 @@ __device__ __forceinline__ uint32_t emSellIterate(const SellLoop<IndexT> & lp, c
             #pragma unroll
             for (uint32_t wi = 0; wi < num_warps; ++wi) { noise_g += red[wi]; }
 
-            if (MULTI) {
-                g[N] = noise_g;
-            } else {
-                const double a_new = (a_noise * noise_g) * inv_total;
-                a[N] = a_new;
-                if (a_new >= min_abundance && fabs(a_new - a_noise) > conv * a_new) { ok = false; }
-            }
+            const double a_new = (a_noise * noise_g) * inv_total;
+            a[N] = a_new;
+            if (a_new >= min_abundance && fabs(a_new - a_noise) > conv * a_new) { ok = false; }
         }
 
         ++it;
 
         SELL_TRACE(2)
 
-        if constexpr (!MULTI) {
+        const int block_ok = __syncthreads_and(ok);
 
-            const int block_ok = __syncthreads_and(ok);
-            SELL_TRACE(3)
+        SELL_TRACE(3)
 
-            if (block_ok) {
-                if (++conv_its == params.min_em_conv_its) { break; }
-            } else {
-                conv_its = 0;
-            }
-
+        if (block_ok) {
+            if (++conv_its == params.min_em_conv_its) { break; }
         } else {
-
-            cluster.sync();
-
-            SELL_TRACE(3)
-
-            // reduce-scatter + all-gather over the group, restricted to the CTAs that hold the column: this CTA owns
-            // columns [jc0, jc1); partial sums are added in ascending CTA order. The noise column (owned by the last
-            // CTA, held by everyone) is reduced by one warp, a lane per CTA, so that its S remote loads overlap.
-            const uint32_t jc1_paths = min(jc1, N);
-
-            for (uint32_t j = jc0 + tid; j < jc1_paths; j += THREADS) {
-
-                const uint32_t mask = lp.owned_mask[j - jc0];
-                double sum = 0;
-
-                if (__popc(mask) <= 2) {
-
-                    for (uint32_t mm = mask; mm; mm &= mm - 1) { sum += *(cluster.map_shared_rank(g, __ffs(mm) - 1) + j); }
-
-                } else {
-
-                    double part[kMaxGroupSize];
-                    #pragma unroll
-                    for (uint32_t s = 0; s < kMaxGroupSize; ++s) { part[s] = ((mask >> s) & 1u) ? *(cluster.map_shared_rank(g, s) + j) : 0.0; }
-                    #pragma unroll
-                    for (uint32_t s = 0; s < kMaxGroupSize; ++s) { sum += part[s]; }
-                }
-
-                const double a_old = a[j];
-                const double a_new = (a_old * sum) * inv_total;
-                if (a_new >= min_abundance && fabs(a_new - a_old) > conv * a_new) { ok = false; }
-
-                a[j] = a_new;
-                for (uint32_t mm = mask & ~(1u << rank); mm; mm &= mm - 1) { *(cluster.map_shared_rank(a, __ffs(mm) - 1) + j) = a_new; }
-            }
-
-            if (jc1 == N + 1 && warp == num_warps - 1) {
-
-                double part = (lane < S) ? *(cluster.map_shared_rank(g, lane) + N) : 0.0;
-                part = warpSum(part);
-
-                const double a_new = (a_noise * part) * inv_total;
-                if (a_new >= min_abundance && fabs(a_new - a_noise) > conv * a_new) { ok = false; }
-
-                if (lane < S) { *(cluster.map_shared_rank(a, lane) + N) = a_new; }
-            }
-
-            // convergence vote: flags were set to 1 before the block barrier above; a CTA in which any column failed
-            // clears its flag in every CTA of the group
-            SELL_TRACE(4)
-
-            const int cta_failed = __syncthreads_or(!ok);
-            if (cta_failed && tid < S) { *(cluster.map_shared_rank(conv_flags, tid) + rank) = 0; }
-
-            cluster.sync();
-
-            SELL_TRACE(5)
-
-            bool all_ok = true;
-            for (uint32_t s = 0; s < S; ++s) { all_ok = all_ok && (conv_flags[s] != 0); }
-
-            if (all_ok) {
-                if (++conv_its == params.min_em_conv_its) { break; }
-            } else {
-                conv_its = 0;
-            }
+            conv_its = 0;
         }
     }
 
 #ifdef RPVG_B200_EM_TRACE
+    if (lane == 0 && (warp == 0 || warp == num_warps - 1) && it > 50) {
+        printf("[trace] one CTA warp %u its %u N %u chunks %u/%u cycles/it: E %lld | bar %lld | M %lld | vote %lld\n", warp, it, N, lp.rows.n_chunks, lp.cols.n_chunks,
+               trace_acc[0] / it, trace_acc[1] / it, trace_acc[2] / it, trace_acc[3] / it);
+    }
+#endif
+
+    return it;
+}
+
+// The EM iterations of one CTA of a group (thread-block cluster of S CTAs). Returns the number of iterations the
+// estimate went through; *final_a receives the vector that holds it (a, or a_prev when the stop came one iteration late).
+template <int THREADS, bool ALL_SHARED, typename IndexT>
+__device__ __forceinline__ uint32_t emSellIterateGroup(const SellLoop<IndexT> & lp, const rpvg_b200_em_params & params, const uint32_t S, const uint32_t rank, const double total,
+                                                       double * red, const double ** final_a) {
+
+    cg::cluster_group cluster = cg::this_cluster();
+
+    const uint32_t tid = threadIdx.x;
+    const uint32_t lane = tid & 31;
+    const uint32_t warp = tid >> 5;
+    constexpr uint32_t num_warps = THREADS / 32;
+
+    double * a = lp.a;
+    double * a_prev = lp.a_prev;
+    const double * w = lp.w;
+    SellPeers * peers = lp.peers;
+
+    const uint32_t n_local = lp.n_local;
+
+    const double conv = params.max_rel_em_conv;
+    const double min_abundance = params.min_em_abundance;
+    const double inv_total = 1.0 / total;
+
+    const uint32_t row_k0 = lp.rows.warp_begin[warp], row_k1 = lp.rows.warp_begin[warp + 1];
+    const uint32_t col_k0 = lp.cols.warp_begin[warp], col_k1 = lp.cols.warp_begin[warp + 1];
+
+    // where each peer keeps its noise partial (lane = peer)
+    const uint32_t peer_noise_id = lane < S ? peers->present[lane] : 0;
+
+    uint32_t conv_its = 0;   // kept by the last warp (uniform over the group: everyone sees the same flags)
+    uint32_t it = 0;
+    uint32_t gen = 0;
+    bool stopped_late = false;
+
+    SELL_TRACE_DECL
+
+    while (it < params.max_em_its) {
+
+        const double a_noise = a[n_local];
+        const double noise_acc = sellExpectation<ALL_SHARED, IndexT>(lp, a, a_noise, row_k0, row_k1, lane);
+
+        SELL_TRACE(0)
+
+        if (lane == 0) { red[warp] = noise_acc; }
+
+        __syncthreads();
+
+        SELL_TRACE(1)
+
+        // ---- M-step: this slice's share of the column sums, generation `gen`
+        double * g = lp.g + gen * lp.g_stride;
+
+        #pragma unroll 1
+        for (uint32_t k = col_k0; k < col_k1; ++k) {
+
+            const SellChunk ch = lp.cols.chunks[k];
+            const bool lead = (lane & ((1u << ch.l2) - 1)) == 0;
+
+            const bool res = ALL_SHARED || ch.off < lp.cols.resident_slots;
+            const double * val = (res ? lp.cols.val_s + ch.off : lp.cols.val_g + (ch.off - lp.cols.resident_slots)) + lane;
+            const IndexT * idx = (res ? lp.cols.idx_s + ch.off : lp.cols.idx_g + (ch.off - lp.cols.resident_slots)) + lane;
+
+            double acc[kSellWays];
+            sellChunkDot<IndexT>(val, idx, w, ch.width, acc);
+            sellLaneSumWays(acc, ch.l2);
+
+            #pragma unroll
+            for (uint32_t u = 0; u < kSellWays; ++u) {
+                const uint32_t r = (u * 32 + lane) >> ch.l2;
+                if (lead && r < ch.count) { g[ch.first + r] = acc[u]; }   // local id = sorted position
+            }
+        }
+
+        if (tid == THREADS - 1) {
+
+            double noise_g = 0;
+            #pragma unroll
+            for (uint32_t wi = 0; wi < num_warps; ++wi) { noise_g += red[wi]; }
+            g[n_local] = noise_g;
+
+            // this CTA's vote on the update before this one
+            uint32_t all = 1;
+            #pragma unroll
+            for (uint32_t wi = 0; wi < num_warps; ++wi) { all &= peers->vote[wi]; }
+            peers->flag[gen] = all;
+        }
+
+        ++it;
+
+        SELL_TRACE(2)
+
+        cluster.sync();   // the only group-wide barrier of the iteration
+
+        SELL_TRACE(3)
+
+        // ---- update: every holder of a column adds the partial sums of all its holders, in ascending CTA order
+        bool ok = true;
+
+        for (uint32_t l = tid; l < n_local; l += THREADS) {
+
+            const uint32_t mask = lp.holders[l];
+            double sum;
+
+            if (mask == (1u << rank)) {
+
+                sum = g[l];
+
+            } else {
+
+                uint32_t k = lp.pull_begin[l];
+                sum = 0;
+                for (uint32_t mm = mask; mm; mm &= mm - 1) {
+                    const uint32_t s = __ffs(mm) - 1;
+                    sum += (s == rank) ? g[l] : *(cluster.map_shared_rank(g, s) + lp.peer_id[k++]);
+                }
+            }
+
+            const double a_old = a[l];
+            const double a_new = (a_old * sum) * inv_total;
+            if (a_new >= min_abundance && fabs(a_new - a_old) > conv * a_new) { ok = false; }
+
+            a_prev[l] = a_old;
+            a[l] = a_new;
+        }
+
+        if (warp == num_warps - 1) {
+
+            // noise column: a lane per CTA, so that the remote loads overlap; same summation tree everywhere
+            double part = 0;
+            uint32_t peer_flag = 1;
+
+            if (lane < S) {
+                part = (lane == rank) ? g[n_local] : *(cluster.map_shared_rank(g, lane) + peer_noise_id);
+                if (it > 1) { peer_flag = (lane == rank) ? peers->flag[gen] : *(cluster.map_shared_rank(&peers->flag[gen], lane)); }
+            }
+
+            part = warpSum(part);
+
+            const double a_new = (a_noise * part) * inv_total;
+            if (a_new >= min_abundance && fabs(a_new - a_noise) > conv * a_new) { ok = false; }
+
+            if (lane == 0) {
+                a_prev[n_local] = a_noise;
+                a[n_local] = a_new;
+            }
+
+            // the group's verdict on the previous update (iteration it - 1)
+            if (it > 1) {
+
+                const bool all_ok = __all_sync(0xffffffffu, peer_flag != 0);
+                uint32_t stop = 0;
+
+                if (all_ok) {
+                    if (++conv_its == params.min_em_conv_its) { stop = 1; }
+                } else {
+                    conv_its = 0;
+                }
+                if (lane == 0) { peers->stop = stop; }
+
+            } else if (lane == 0) {
+                peers->stop = 0;
+            }
+        }
+
+        const bool warp_ok = __all_sync(0xffffffffu, ok);
+        if (lane == 0) { peers->vote[warp] = warp_ok ? 1u : 0u; }
+
+        SELL_TRACE(4)
+
+        __syncthreads();   // abundances, votes and the stop flag are in place
+
+        SELL_TRACE(5)
+
+        if (peers->stop) {
+            // iteration it - 1 was the one that completed the run of converged iterations: its result is a_prev
+            stopped_late = true;
+            --it;
+            break;
+        }
+
+        gen ^= 1;
+    }
+
+#ifdef RPVG_B200_EM_TRACE
     if (lane == 0 && (warp == 0 || warp == num_warps - 1) && (rank == 0 || rank == S - 1) && it > 50) {
-        printf("[trace] rank %u/%u warp %u its %u N %u chunks %u/%u cycles/it: E %lld | bar %lld | M %lld | sync1 %lld | reduce %lld | sync2 %lld\n", rank, S, warp, it, N,
+        printf("[trace] rank %u/%u warp %u its %u local cols %u chunks %u/%u cycles/it: E %lld | bar %lld | M %lld | cluster %lld | update %lld | bar2 %lld\n", rank, S, warp, it, n_local,
                lp.rows.n_chunks, lp.cols.n_chunks, trace_acc[0] / it, trace_acc[1] / it, trace_acc[2] / it, trace_acc[3] / it, trace_acc[4] / it, trace_acc[5] / it);
     }
 #endif
 
+    *final_a = stopped_late ? a_prev : a;
     return it;
 }
 
@@ -744,8 +922,9 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
     extern __shared__ __align__(16) unsigned char smem_raw[];
 
     __shared__ double red[32];
-    __shared__ uint32_t conv_flags[kMaxGroupSize];
     __shared__ double final_part[kMaxGroupSize];
+    __shared__ SellPeers peers;
+    __shared__ uint32_t capacity_flag;
     __shared__ uint32_t scan_tmp[THREADS / 32];
     __shared__ uint32_t shared_u32[4];
     __shared__ uint32_t row_warp_begin[THREADS / 32 + 1];
@@ -816,10 +995,6 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
     const uint32_t m = bounds[1] - i0;
     const uint64_t e_slice = row_ptr[i0];
 
-    // columns (noise included as column N) this CTA reduces and owns in the finalisation
-    const uint32_t jc0 = static_cast<uint32_t>((static_cast<uint64_t>(N + 1) * rank) / S);
-    const uint32_t jc1 = static_cast<uint32_t>((static_cast<uint64_t>(N + 1) * (rank + 1)) / S);
-
     // ---- memory: shared first, scratch for what does not fit
     SellArena arena;
     arena.smem = smem_raw;
@@ -828,30 +1003,25 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
     arena.gmem_left = sa.group_cta_bytes[group];
     arena.overflow = false;
 
-    // a and g come first so that they sit at the same offsets in every CTA of the group (remote access); the host only
-    // sends a cluster here when they fit
-    double * a = static_cast<double *>(arena.take(8ull * (N + 1), true, nullptr));
-    double * g = MULTI ? static_cast<double *>(arena.take(8ull * (N + 1), true, nullptr)) : nullptr;
+    const unsigned char * scratch_base = arena.gmem;
 
-    // prologue temporaries (global scratch only)
-    uint32_t * row_pos = static_cast<uint32_t *>(arena.take(4ull * (m + 1), false, nullptr));
-    uint32_t * row_src = static_cast<uint32_t *>(arena.take(4ull * (m + 1), false, nullptr));
+    // prologue temporaries (global scratch only); those sized by N come first, so that they sit at the same offsets in
+    // the scratch areas of all CTAs of the group (col_pos is read by the peers)
     uint32_t * cstart = static_cast<uint32_t *>(arena.take(4ull * (N + 1), false, nullptr));
     uint32_t * clen = static_cast<uint32_t *>(arena.take(4ull * (N + 1), false, nullptr));
     uint32_t * col_pos = static_cast<uint32_t *>(arena.take(4ull * (N + 1), false, nullptr));
     uint32_t * col_src = static_cast<uint32_t *>(arena.take(4ull * (N + 1), false, nullptr));
-
-    // per-row vectors in sorted order
-    double * w = static_cast<double *>(arena.take(8ull * (m + 1), true, nullptr));
-    double * noise = static_cast<double *>(arena.take(8ull * (m + 1), true, nullptr));
-    double * cnt = static_cast<double *>(arena.take(8ull * (m + 1), true, nullptr));
+    uint32_t * col_holders = static_cast<uint32_t *>(arena.take(4ull * (N + 1), false, nullptr));
+    uint32_t * col_pulls = static_cast<uint32_t *>(arena.take(4ull * (N + 1), false, nullptr));
+    uint32_t * row_pos = static_cast<uint32_t *>(arena.take(4ull * (m + 1), false, nullptr));
+    uint32_t * row_src = static_cast<uint32_t *>(arena.take(4ull * (m + 1), false, nullptr));
 
     // ---- total read count: every CTA sums all rows in the same order, so all agree bit for bit
     double count_sum = 0;
     for (uint32_t i = tid; i < M; i += THREADS) { count_sum += args.cnt[r0 + i]; }
     const double total = blockSum(count_sum, red);
 
-    // ---- rows: sort by length, chunk, fill
+    // ---- rows: sort by length, chunk (descriptors in scratch until they are dealt to the warps)
     auto row_len = [&](uint32_t i) { return static_cast<uint32_t>(row_ptr[i0 + i + 1] - row_ptr[i0 + i]); };
     sellStableSort<THREADS>(sort_state, m, row_len, row_pos, row_src);
 
@@ -860,17 +1030,10 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
 
     const uint32_t row_chunk_bound = sellCountChunks<THREADS>(sort_state, m, depth);
 
-    SellChunk * row_chunks = static_cast<SellChunk *>(arena.take(sizeof(SellChunk) * (row_chunk_bound + 1), true, nullptr));
     SellChunk * row_chunks_made = static_cast<SellChunk *>(arena.take(sizeof(SellChunk) * (row_chunk_bound + 1), false, nullptr));
     uint32_t * row_chunk_dest = static_cast<uint32_t *>(arena.take(4ull * (row_chunk_bound + 1), false, nullptr));
     const uint32_t n_row_chunks = sellMakeChunks<THREADS>(sort_state, m, depth, row_len, row_src, row_chunks_made, scan_tmp, &shared_u32[0]);
     const uint32_t row_slots = shared_u32[0];
-
-    for (uint32_t p = tid; p < m; p += THREADS) {
-        const uint32_t i = row_src[p];
-        noise[p] = args.noise[r0 + i0 + i];
-        cnt[p] = args.cnt[r0 + i0 + i];
-    }
 
     // ---- columns: range of this slice inside each column of the column-major arrays (rows ascend within a column)
     {
@@ -902,55 +1065,96 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
 
     __syncthreads();
 
-    // ---- which CTAs of the group hold entries of each column this CTA owns: only those take part in the column's
-    // reduction and need its abundance. With read classes ordered by their first path (em.cu) a slice touches a band of
-    // columns, so most masks have one or two bits.
-    uint16_t * owned_mask = nullptr;
-
-    if (MULTI) {
-
-        owned_mask = static_cast<uint16_t *>(arena.take(2ull * (jc1 - jc0 + 1), true, nullptr));
-
-        unsigned char * present = reinterpret_cast<unsigned char *>(g);   // g is not in use yet
-        for (uint32_t j = tid; j < N; j += THREADS) { present[j] = clen[j] > 0; }
-
-        cluster.sync();
-
-        for (uint32_t j = jc0 + tid; j < jc1; j += THREADS) {
-
-            uint32_t mask = 0;
-            if (j == N) {
-                mask = (1u << S) - 1;   // the noise column concerns everyone
-            } else {
-                for (uint32_t s = 0; s < S; ++s) { mask |= static_cast<uint32_t>(*(reinterpret_cast<unsigned char *>(cluster.map_shared_rank(g, s)) + j)) << s; }
-            }
-            owned_mask[j - jc0] = static_cast<uint16_t>(mask);
-        }
-
-        cluster.sync();   // g may be overwritten from here on
-    }
-
+    // Columns sorted by their length in this slice; only those with entries get chunks (empty ones sort last). A column
+    // that is empty in every slice has no read class behind it: its abundance is 0 from the first update on
+    // (a_j * 0 / total).
     auto col_len = [&](uint32_t j) { return clen[j]; };
     sellStableSort<THREADS>(sort_state, N, col_len, col_pos, col_src);
 
-    // Only the columns with entries in this slice get chunks (empty ones sort last). A column that is empty in every
-    // slice has no read class behind it: its abundance is 0 from the first update on (a_j * 0 / total), which is what it
-    // is set to — with one CTA right away (nothing ever reads it), with several by the reduction (mask 0, sum 0).
     const uint32_t n_cols_present = N - sort_state.bucket_total[0];
 
     const uint32_t col_chunk_bound = sellCountChunks<THREADS>(sort_state, n_cols_present, depth);
 
-    SellChunk * col_chunks = static_cast<SellChunk *>(arena.take(sizeof(SellChunk) * (col_chunk_bound + 1), true, nullptr));
     SellChunk * col_chunks_made = static_cast<SellChunk *>(arena.take(sizeof(SellChunk) * (col_chunk_bound + 1), false, nullptr));
     uint32_t * col_chunk_dest = static_cast<uint32_t *>(arena.take(4ull * (col_chunk_bound + 1), false, nullptr));
     const uint32_t n_col_chunks = sellMakeChunks<THREADS>(sort_state, n_cols_present, depth, col_len, col_src, col_chunks_made, scan_tmp, &shared_u32[1]);
     const uint32_t col_slots = shared_u32[1];
 
-    // column ids in sorted order (kept for the whole kernel)
-    IndexT * col_id = static_cast<IndexT *>(arena.take(sizeof(IndexT) * (n_cols_present + 1), true, nullptr));
-    for (uint32_t p = tid; p < n_cols_present; p += THREADS) { col_id[p] = static_cast<IndexT>(col_src[p]); }
+    // ---- group: local column ids (= sorted position), and for each of this slice's columns the other CTAs that hold it.
+    // Nothing has been placed in shared memory yet: its start serves as exchange area.
+    double * a = nullptr;
+    double * a_prev = nullptr;
+    double * g = nullptr;
+    uint32_t g_stride = 0;
+    uint32_t total_pulls = 0;
 
-    // ---- entry arrays: column side first (it also carries the update), then row side; whole chunks only
+    if (MULTI) {
+
+        // columns nobody holds: abundance 0, written by the CTA whose share of the path range they fall in
+        const uint32_t jc0 = static_cast<uint32_t>((static_cast<uint64_t>(N) * rank) / S);
+        const uint32_t jc1 = static_cast<uint32_t>((static_cast<uint64_t>(N) * (rank + 1)) / S);
+        for (uint32_t j = jc0 + tid; j < jc1; j += THREADS) { args.abundances[p0 + j] = 0; }
+
+        unsigned char * present = smem_raw;   // N flags, needed until the masks are made (N <= smem: see sellSmemBytes)
+        for (uint32_t j = tid; j < N; j += THREADS) { present[j] = clen[j] > 0; }
+
+        if (tid < S) { *(cluster.map_shared_rank(&peers.present[rank], tid)) = n_cols_present; }
+        if (tid < 32) { peers.vote[tid] = 0; }
+        if (tid == 0) {
+            peers.flag[0] = 0;
+            peers.flag[1] = 0;
+            peers.stop = 0;
+        }
+
+        __threadfence();   // col_pos travels through L2
+        cluster.sync();
+
+        uint32_t most = 0;
+        for (uint32_t s = 0; s < S; ++s) { most = max(most, peers.present[s]); }
+        g_stride = (most + 2) & ~1u;   // columns + noise, even
+
+        for (uint32_t l = tid; l < n_cols_present; l += THREADS) {
+
+            const uint32_t j = col_src[l];
+            uint32_t mask = 0;
+            for (uint32_t s = 0; s < S; ++s) { mask |= static_cast<uint32_t>(*(cluster.map_shared_rank(present, s) + j)) << s; }
+
+            col_holders[l] = mask;
+            col_pulls[l] = __popc(mask) - 1;
+        }
+
+        cluster.sync();   // the flags may be overwritten from here on
+
+        total_pulls = sellExclusiveScan<THREADS>(col_pulls, n_cols_present, scan_tmp);
+
+        // the column sums are read by the peers: shared memory, same offset everywhere, or the group cannot run
+        bool g_in_smem = false;
+        g = static_cast<double *>(arena.take(16ull * g_stride, true, &g_in_smem));
+        if (!g_in_smem) { arena.overflow = true; }
+
+        a = static_cast<double *>(arena.take(8ull * g_stride, true, nullptr));
+        a_prev = static_cast<double *>(arena.take(8ull * g_stride, true, nullptr));
+
+    } else {
+
+        a = static_cast<double *>(arena.take(8ull * (N + 1), true, nullptr));
+    }
+
+    uint16_t * holders = MULTI ? static_cast<uint16_t *>(arena.take(2ull * (n_cols_present + 1), true, nullptr)) : nullptr;
+    uint32_t * pull_begin = MULTI ? static_cast<uint32_t *>(arena.take(4ull * (n_cols_present + 2), true, nullptr)) : nullptr;
+    IndexT * peer_id = MULTI ? static_cast<IndexT *>(arena.take(sizeof(IndexT) * (static_cast<uint64_t>(total_pulls) + 1), true, nullptr)) : nullptr;
+
+    // per-row vectors in sorted order
+    double * w = static_cast<double *>(arena.take(8ull * (m + 1), true, nullptr));
+    double * noise = static_cast<double *>(arena.take(8ull * (m + 1), true, nullptr));
+    double * cnt = static_cast<double *>(arena.take(8ull * (m + 1), true, nullptr));
+
+    // chunk descriptors as the loops will read them, and (one CTA) the column of each sorted position
+    SellChunk * row_chunks = static_cast<SellChunk *>(arena.take(sizeof(SellChunk) * (n_row_chunks + 1), true, nullptr));
+    SellChunk * col_chunks = static_cast<SellChunk *>(arena.take(sizeof(SellChunk) * (n_col_chunks + 1), true, nullptr));
+    IndexT * col_id = MULTI ? nullptr : static_cast<IndexT *>(arena.take(sizeof(IndexT) * (n_cols_present + 1), true, nullptr));
+
+    // ---- entry arrays: column side first, then row side; whole chunks only
     auto place = [&](const SellChunk * chunks, uint32_t n_chunks, uint32_t slots, SellSide<IndexT> * side) {
 
         // largest prefix of chunks whose entries fit in what is left of shared memory
@@ -971,6 +1175,7 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
         }
 
         side->chunks = nullptr;   // set once the chunks are dealt to the warps
+        side->warp_begin = nullptr;
         side->n_chunks = n_chunks;
         side->n_resident = n_res;
         side->resident_slots = res_slots;
@@ -986,15 +1191,15 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
 
     // capacity check, uniform over the group: every CTA publishes its flag before anyone proceeds
     if (MULTI) {
-        if (tid == 0) { conv_flags[0] = 0; }
+        if (tid == 0) { capacity_flag = 0; }
         cluster.sync();
         if (arena.overflow && tid == 0) {
-            for (uint32_t s = 0; s < S; ++s) { *(cluster.map_shared_rank(conv_flags, s)) = 1; }
-            printf("[rpvg_b200] capacity: cluster %u rank %u/%u M %u N %u m %u row_slots %u col_slots %u chunks %u/%u cta_bytes %llu smem %u\n", c, rank, S, M, N, m,
-                   row_slots, col_slots, n_row_chunks, n_col_chunks, static_cast<unsigned long long>(sa.group_cta_bytes[group]), sa.smem_bytes);
+            for (uint32_t s = 0; s < S; ++s) { *(cluster.map_shared_rank(&capacity_flag, s)) = 1; }
+            printf("[rpvg_b200] capacity: cluster %u rank %u/%u M %u N %u m %u columns %u (stride %u) row_slots %u col_slots %u chunks %u/%u pulls %u cta_bytes %llu smem %u\n", c, rank, S, M,
+                   N, m, n_cols_present, g_stride, row_slots, col_slots, n_row_chunks, n_col_chunks, total_pulls, static_cast<unsigned long long>(sa.group_cta_bytes[group]), sa.smem_bytes);
         }
         cluster.sync();
-        if (conv_flags[0]) {
+        if (capacity_flag) {
             if (rank == 0 && tid == 0) { atomicOr(const_cast<uint32_t *>(args.error), RPVG_DEV_ERR_CAPACITY); }
             return;
         }
@@ -1015,6 +1220,43 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
     rows.warp_begin = row_warp_begin;
     cols.chunks = col_chunks;
     cols.warp_begin = col_warp_begin;
+
+    // ---- per-row vectors, in sorted order
+    for (uint32_t p = tid; p < m; p += THREADS) {
+        const uint32_t i = row_src[p];
+        noise[p] = args.noise[r0 + i0 + i];
+        cnt[p] = args.cnt[r0 + i0 + i];
+    }
+
+    // ---- group: exchange tables. The local id a column has in a peer is its sorted position there (the peer's col_pos).
+    if (MULTI) {
+
+        const uint64_t col_pos_offset = reinterpret_cast<const unsigned char *>(col_pos) - scratch_base;
+        const unsigned char * group_base = sa.scratch + sa.group_scratch[group];
+        const uint64_t cta_bytes = sa.group_cta_bytes[group];
+
+        for (uint32_t l = tid; l < n_cols_present; l += THREADS) {
+
+            const uint32_t mask = col_holders[l];
+            const uint32_t j = col_src[l];
+            uint32_t k = col_pulls[l];
+
+            holders[l] = static_cast<uint16_t>(mask);
+            pull_begin[l] = k;
+
+            for (uint32_t mm = mask & ~(1u << rank); mm; mm &= mm - 1) {
+                const uint32_t s = __ffs(mm) - 1;
+                const uint32_t * peer_col_pos = reinterpret_cast<const uint32_t *>(group_base + s * cta_bytes + col_pos_offset);
+                peer_id[k++] = static_cast<IndexT>(__ldcg(peer_col_pos + j));
+            }
+        }
+
+        if (tid == 0) { pull_begin[n_cols_present] = total_pulls; }
+
+    } else {
+
+        for (uint32_t p = tid; p < n_cols_present; p += THREADS) { col_id[p] = static_cast<IndexT>(col_src[p]); }
+    }
 
     // ---- fill: one warp per chunk
     auto fill = [&](const SellSide<IndexT> & side, auto entry_range, auto entry_value, auto entry_index, const uint32_t * src) {
@@ -1055,10 +1297,11 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
         }
     };
 
+    // row side: the index is the column's local id in a group, the path's index in the cluster otherwise
     fill(rows,
          [&](uint32_t i, uint64_t * base, uint32_t * len) { *base = row_ptr[i0 + i]; *len = static_cast<uint32_t>(row_ptr[i0 + i + 1] - *base); },
          [&](uint64_t e) { return args.val[e]; },
-         [&](uint64_t e) { return args.col[e]; },
+         [&](uint64_t e) { return MULTI ? col_pos[args.col[e]] : args.col[e]; },
          row_src);
 
     fill(cols,
@@ -1069,20 +1312,34 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
 
     // rpvg:src/path_abundance_estimator.cpp:54 — single-precision quotient widened to double
     const double a_init = static_cast<double>(1 / static_cast<float>(N + 1));
-    for (uint32_t j = tid; j <= N; j += THREADS) { a[j] = (MULTI || j == N || clen[j] > 0) ? a_init : 0.0; }
 
-    if (MULTI) { cluster.sync(); } else { __syncthreads(); }
+    if (MULTI) {
+        for (uint32_t l = tid; l <= n_cols_present; l += THREADS) {
+            a[l] = a_init;
+            a_prev[l] = a_init;
+        }
+        cluster.sync();
+    } else {
+        for (uint32_t j = tid; j <= N; j += THREADS) { a[j] = (j == N || clen[j] > 0) ? a_init : 0.0; }
+        __syncthreads();
+    }
 
     // ---- EM iterations. When everything this CTA touches sits in shared memory the loop runs on pointers the compiler
     // can prove to be shared (plain LDS/STS); otherwise on generic pointers (hybrid residency).
     SellLoop<IndexT> loop;
     loop.a = a;
+    loop.a_prev = a_prev;
     loop.g = g;
+    loop.g_stride = g_stride;
+    loop.n_local = n_cols_present;
     loop.w = w;
     loop.noise = noise;
     loop.cnt = cnt;
     loop.col_id = col_id;
-    loop.owned_mask = owned_mask;
+    loop.holders = holders;
+    loop.pull_begin = pull_begin;
+    loop.peer_id = peer_id;
+    loop.peers = &peers;
     loop.rows = rows;
     loop.cols = cols;
 
@@ -1092,25 +1349,26 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
         return ptr == nullptr || (q >= smem_raw && q < smem_end);
     };
 
-    const bool all_shared = in_shared(a) && in_shared(g) && in_shared(w) && in_shared(noise) && in_shared(cnt) && in_shared(col_id) && in_shared(owned_mask) &&
-                            in_shared(rows.chunks) && in_shared(cols.chunks) && rows.n_resident == rows.n_chunks && cols.n_resident == cols.n_chunks;
-
-    const double total_count = total;
-    uint32_t it;
+    const bool all_shared = in_shared(a) && in_shared(a_prev) && in_shared(g) && in_shared(w) && in_shared(noise) && in_shared(cnt) && in_shared(col_id) && in_shared(holders) &&
+                            in_shared(pull_begin) && in_shared(peer_id) && in_shared(rows.chunks) && in_shared(cols.chunks) && rows.n_resident == rows.n_chunks &&
+                            cols.n_resident == cols.n_chunks;
 
 #ifdef RPVG_B200_EM_TRACE
     if (tid == 0 && (rank == 0 || rank == S - 1)) {
         uint32_t widest_row = 0, widest_col = 0;
         for (uint32_t k = 0; k < n_row_chunks; ++k) { widest_row = max(widest_row, row_chunks[k].width); }
         for (uint32_t k = 0; k < n_col_chunks; ++k) { widest_col = max(widest_col, col_chunks[k].width); }
-        printf("[layout] rank %u/%u m %u z %u cols present %u | rows: chunks %u slots %u widest %u resident %u | cols: chunks %u slots %u widest %u resident %u | depth %u\n", rank, S, m, z_slice,
-               n_cols_present, n_row_chunks, row_slots, widest_row, rows.n_resident, n_col_chunks, col_slots, widest_col, cols.n_resident, depth);
+        printf("[layout] rank %u/%u m %u z %u cols present %u pulls %u | rows: chunks %u slots %u widest %u resident %u | cols: chunks %u slots %u widest %u resident %u | depth %u all shared %d\n", rank,
+               S, m, z_slice, n_cols_present, total_pulls, n_row_chunks, row_slots, widest_row, rows.n_resident, n_col_chunks, col_slots, widest_col, cols.n_resident, depth, all_shared ? 1 : 0);
     }
 #endif
 
 #ifdef RPVG_B200_EM_TIMELINE
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(timeline_t1));
 #endif
+
+    uint32_t it;
+    const double * final_a = a;
 
     if (all_shared) {
 
@@ -1123,12 +1381,15 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
 
         SellLoop<IndexT> fast = loop;
         fast.a = rebase(loop.a);
+        fast.a_prev = rebase(loop.a_prev);
         fast.g = rebase(loop.g);
         fast.w = rebase(loop.w);
         fast.noise = rebase(loop.noise);
         fast.cnt = rebase(loop.cnt);
         fast.col_id = rebase(loop.col_id);
-        fast.owned_mask = rebase(loop.owned_mask);
+        fast.holders = rebase(loop.holders);
+        fast.pull_begin = rebase(loop.pull_begin);
+        fast.peer_id = rebase(loop.peer_id);
         fast.rows.chunks = rebase(loop.rows.chunks);
         fast.rows.val_s = rebase(loop.rows.val_s);
         fast.rows.idx_s = rebase(loop.rows.idx_s);
@@ -1136,25 +1397,53 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
         fast.cols.val_s = rebase(loop.cols.val_s);
         fast.cols.idx_s = rebase(loop.cols.idx_s);
 
-        it = emSellIterate<THREADS, MULTI, true, IndexT>(fast, args.params, N, S, rank, jc0, jc1, total_count, red, conv_flags);
+        if constexpr (MULTI) {
+            it = emSellIterateGroup<THREADS, true, IndexT>(fast, args.params, S, rank, total, red, &final_a);
+        } else {
+            it = emSellIterateSingle<THREADS, true, IndexT>(fast, args.params, N, total, red);
+        }
 
     } else {
 
-        it = emSellIterate<THREADS, MULTI, false, IndexT>(loop, args.params, N, S, rank, jc0, jc1, total_count, red, conv_flags);
+        if constexpr (MULTI) {
+            it = emSellIterateGroup<THREADS, false, IndexT>(loop, args.params, S, rank, total, red, &final_a);
+        } else {
+            it = emSellIterateSingle<THREADS, false, IndexT>(loop, args.params, N, total, red);
+        }
     }
 
     const double min_abundance = args.params.min_em_abundance;
 
-
-    // rpvg:src/path_abundance_estimator.cpp:100-113; every CTA finalises the columns it owns
+    // rpvg:src/path_abundance_estimator.cpp:100-113. In a group every column is written by the first CTA that holds it
+    // (all holders have the same value).
     double noise_part = 0;
-    for (uint32_t j = jc0 + tid; j < min(jc1, N); j += THREADS) {
-        const double aj = a[j];
-        if (aj < min_abundance) {
-            noise_part += aj * total;
-            args.abundances[p0 + j] = 0;
-        } else {
-            args.abundances[p0 + j] = aj * total;
+
+    if (MULTI) {
+
+        for (uint32_t l = tid; l < n_cols_present; l += THREADS) {
+
+            if ((__ffs(holders[l]) - 1) != static_cast<int>(rank)) { continue; }
+
+            const uint32_t j = col_src[l];
+            const double aj = final_a[l];
+            if (aj < min_abundance) {
+                noise_part += aj * total;
+                args.abundances[p0 + j] = 0;
+            } else {
+                args.abundances[p0 + j] = aj * total;
+            }
+        }
+
+    } else {
+
+        for (uint32_t j = tid; j < N; j += THREADS) {
+            const double aj = final_a[j];
+            if (aj < min_abundance) {
+                noise_part += aj * total;
+                args.abundances[p0 + j] = 0;
+            } else {
+                args.abundances[p0 + j] = aj * total;
+            }
         }
     }
 
@@ -1173,8 +1462,8 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
             for (uint32_t s = 0; s < S; ++s) { low_total += final_part[s]; }
         }
 
-        // the noise column is owned by the last CTA of the group; every CTA holds its value
-        args.noise_count[c] = low_total + a[N] * total;
+        // every CTA holds the noise column
+        args.noise_count[c] = low_total + final_a[MULTI ? n_cols_present : N] * total;
         args.total_count[c] = total;
         args.iterations[c] = it;
     }
