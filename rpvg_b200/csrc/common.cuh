@@ -10,6 +10,8 @@
 
 #include "rpvg_b200.h"
 
+constexpr int kNumSideStreams = 12;
+
 struct rpvg_b200_ctx {
 
     int device = 0;
@@ -21,7 +23,7 @@ struct rpvg_b200_ctx {
     std::string error;
 
     // EM launch machinery (em.cu): side streams for concurrent bins, largest thread-block cluster this device accepts
-    std::vector<cudaStream_t> side_streams;
+    std::vector<cudaStream_t> side_streams;   // kNumSideStreams: pairs of equal priority, the last four lowest
     std::vector<cudaEvent_t> join_events;
     std::vector<cudaStream_t> lane_streams;   // highest priority; the largest groups run here one cluster per launch
     std::vector<cudaEvent_t> lane_events;

@@ -64,19 +64,20 @@ int rpvg_b200_create(int device, void * stream, rpvg_b200_ctx ** out_ctx) {
         cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold);
     }
 
-    // side streams, one priority level each as far as the device has them (numerically lower = higher priority): the work
-    // distributor hands out the CTAs of one kernel per priority level at a time, so launches that are to overlap with a
-    // kernel that still has undispatched thread-block clusters must sit on another level (see rpvg_b200_batch_em)
+    // Side streams for the concurrent launches of rpvg_b200_batch_em, two per priority level below the lanes' and four at
+    // the lowest (numerically lower = higher priority). The work distributor hands out the CTAs of one kernel per
+    // priority level at a time: launches that are to overlap with a kernel that still has undispatched thread-block
+    // clusters must sit on another level.
     int prio_low = 0, prio_high = 0;
     cudaDeviceGetStreamPriorityRange(&prio_low, &prio_high);
     if (std::getenv("RPVG_B200_DEBUG")) { fprintf(stderr, "[rpvg_b200] stream priorities %d (lowest) .. %d (highest)\n", prio_low, prio_high); }
 
-    for (int k = 0; k < 8; ++k) {
+    for (int k = 0; k < kNumSideStreams; ++k) {
 
         cudaStream_t side = nullptr;
         cudaEvent_t join = nullptr;
 
-        if (cudaStreamCreateWithPriority(&side, cudaStreamNonBlocking, std::min(prio_low, prio_high + 1 + static_cast<int>(k))) != cudaSuccess ||
+        if (cudaStreamCreateWithPriority(&side, cudaStreamNonBlocking, std::min(prio_low, prio_high + 1 + std::min(k / 2, 4))) != cudaSuccess ||
             cudaEventCreateWithFlags(&join, cudaEventDisableTiming) != cudaSuccess) {
             rpvg_b200_destroy(ctx);
             return RPVG_B200_ERR_CUDA;

@@ -215,7 +215,7 @@ void planEmLaunches(const rpvg_b200_ctx * ctx, rpvg_b200_batch * b, std::vector<
                     std::vector<uint64_t> * group_cta_bytes) {
 
     // weight (entries + rows) one CTA should own; above it a cluster is split over 2, 4, 8, 16 CTAs
-    const uint32_t slice_weight = std::max(64u, envKnob("RPVG_B200_EM_SLICE_WEIGHT", 8000));
+    const uint32_t slice_weight = std::max(64u, envKnob("RPVG_B200_EM_SLICE_WEIGHT", 12000));
     const uint32_t big_threads = envKnob("RPVG_B200_EM_BIG_THREADS", 512);
     const uint32_t max_group = std::min(ctx->max_group_size, std::max(1u, envKnob("RPVG_B200_EM_MAX_GROUP", kMaxGroupSize)));
     const uint32_t smem_cap = std::min<uint32_t>(sellTiers().smem[kNumTiers - 1], static_cast<uint32_t>(ctx->max_smem_optin) - kStaticSmemReserve);
@@ -773,6 +773,36 @@ int rpvg_b200_batch_em(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const rpvg_b200
     const uint32_t spacer_us = envKnob("RPVG_B200_EM_SPACER_US", 20);
     const uint32_t lane_min_group = envKnob("RPVG_B200_EM_LANE_MIN_GROUP", 16);
     const size_t n_lanes = std::min<size_t>(envKnob("RPVG_B200_EM_LANES", 7), ctx->lane_streams.size());
+    // Bin -> side stream. Priority classes, highest first (the groups of 16 run on the lane streams, above all):
+    // groups of 2, groups of 4, single CTAs with a full shared-memory tier, groups of 8, everything small. Small
+    // footprints first: they fit the SMs the big clusters leave over in each GPC (measured with tools/em_timeline.py: a
+    // group of 8 pending at a higher level keeps those SMs idle instead); the small single-CTA launches are the filler
+    // at the end. RPVG_B200_EM_STREAMS="i j k ..." overrides the choice for tuning runs.
+    std::vector<size_t> stream_map;
+    if (const char * v = std::getenv("RPVG_B200_EM_STREAMS")) {
+        for (const char * q = v; *q;) {
+            char * end = nullptr;
+            const unsigned long x = std::strtoul(q, &end, 10);
+            if (end == q) { break; }
+            stream_map.push_back(x % ctx->side_streams.size());
+            q = end;
+        }
+    }
+
+    size_t class_cursor[5] = {0, 0, 0, 0, 0};
+    auto stream_of_bin = [&](size_t k) -> size_t {
+        if (k < stream_map.size()) { return stream_map[k]; }
+        const auto & bin = b->bins[k];
+        const uint32_t top_smem = std::min<uint32_t>(sellTiers().smem[kNumTiers - 1], static_cast<uint32_t>(ctx->max_smem_optin) - kStaticSmemReserve);
+        size_t cls = 4;
+        if (bin.group_size == 2) { cls = 0; }
+        else if (bin.group_size == 4) { cls = 1; }
+        else if (bin.group_size == 1 && bin.smem >= top_smem) { cls = 2; }
+        else if (bin.group_size >= 8) { cls = 3; }
+        const size_t width = cls == 4 ? 4 : 2;
+        return 2 * cls + (class_cursor[cls]++ % width);
+    };
+
     std::vector<double> lane_load(n_lanes, 0.0);
     std::vector<bool> lane_forked(n_lanes, false);
     bool lanes_used = false;
@@ -785,7 +815,7 @@ int rpvg_b200_batch_em(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const rpvg_b200
                     bin.threads, bin.smem, bin.index_bytes, bin.count, ctx->max_group_size, b->scratch_bytes / 1e6);
         }
 
-        cudaStream_t bs = ctx->side_streams[k % ctx->side_streams.size()];
+        cudaStream_t bs = ctx->side_streams[stream_of_bin(k)];
         RPVG_CUDA(ctx, cudaStreamWaitEvent(bs, ctx->fork_event, 0));
 
         // The launch of the largest groups goes first and alone: its thread-block clusters need whole GPCs, which they
@@ -863,7 +893,7 @@ int rpvg_b200_batch_em(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const rpvg_b200
 
     }
 
-    for (size_t k = 0; k < std::min(b->bins.size(), ctx->side_streams.size()); ++k) {
+    for (size_t k = 0; k < ctx->side_streams.size(); ++k) {   // (streams no bin went to join at once)
         RPVG_CUDA(ctx, cudaEventRecord(ctx->join_events[k], ctx->side_streams[k]));
         RPVG_CUDA(ctx, cudaStreamWaitEvent(s, ctx->join_events[k], 0));
     }

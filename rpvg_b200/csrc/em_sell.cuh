@@ -43,7 +43,7 @@ struct SellArgs {
     uint32_t smem_bytes;               // dynamic shared memory per CTA of this launch
 };
 
-struct SellChunk {
+struct alignas(16) SellChunk {   // one 16-byte load
 
     uint32_t off;     // first entry slot (multiple of 32)
     uint32_t first;   // first row (column) of the chunk, in sorted order
@@ -468,7 +468,8 @@ struct SellSide {
 struct SellPeers {
 
     uint32_t present[kMaxGroupSize];   // columns (with entries) of every CTA's slice: its noise column has that local id
-    uint32_t flag[2];                  // "all my columns converged in the previous update", one per barrier generation
+    double noise_in[2][kMaxGroupSize]; // noise partial of every CTA, pushed before the barrier; one set per generation
+    uint32_t flag_in[2][kMaxGroupSize];// "all my columns converged in the update before", likewise
     uint32_t vote[32];                 // per warp, from the update just done
     uint32_t stop;
 };
@@ -520,7 +521,7 @@ __device__ __forceinline__ void sellLaneSumWays(double (&acc)[kSellWays], uint32
 
 // sum_t val[t] * x[idx[t]] over the steps of a chunk for each of the lane's slots. (Measured on B200: the plain loop,
 // one running sum per slot and four steps unrolled, beats grouped/predicated loads and split sums — the phase is bound by
-// the shared-memory pipe, not by the dependent adds.)
+// the shared-memory pipe, not by the dependent adds; eight steps in flight for chunks that stream from L2 lose as well.)
 template <typename IndexT>
 __device__ __forceinline__ void sellChunkDot(const double * __restrict__ val, const IndexT * __restrict__ idx, const double * x, const uint32_t width, double (&acc)[kSellWays]) {
 
@@ -738,9 +739,6 @@ __device__ __forceinline__ uint32_t emSellIterateGroup(const SellLoop<IndexT> & 
     const uint32_t row_k0 = lp.rows.warp_begin[warp], row_k1 = lp.rows.warp_begin[warp + 1];
     const uint32_t col_k0 = lp.cols.warp_begin[warp], col_k1 = lp.cols.warp_begin[warp + 1];
 
-    // where each peer keeps its noise partial (lane = peer)
-    const uint32_t peer_noise_id = lane < S ? peers->present[lane] : 0;
-
     uint32_t conv_its = 0;   // kept by the last warp (uniform over the group: everyone sees the same flags)
     uint32_t it = 0;
     uint32_t gen = 0;
@@ -764,6 +762,19 @@ __device__ __forceinline__ uint32_t emSellIterateGroup(const SellLoop<IndexT> & 
         // ---- M-step: this slice's share of the column sums, generation `gen`
         double * g = lp.g + gen * lp.g_stride;
 
+        // The noise partial and this CTA's vote on the update before this one go to every CTA of the group right away:
+        // plain remote stores, complete by the time the barrier lets anyone read them.
+        if (warp == num_warps - 1) {
+
+            const double noise_g = warpSum(lane < num_warps ? red[lane] : 0.0);
+            const bool all = __all_sync(0xffffffffu, lane < num_warps ? peers->vote[lane] != 0 : true);
+
+            if (lane < S) {
+                *(cluster.map_shared_rank(&peers->noise_in[gen][rank], lane)) = noise_g;
+                *(cluster.map_shared_rank(&peers->flag_in[gen][rank], lane)) = all ? 1u : 0u;
+            }
+        }
+
         #pragma unroll 1
         for (uint32_t k = col_k0; k < col_k1; ++k) {
 
@@ -783,20 +794,6 @@ __device__ __forceinline__ uint32_t emSellIterateGroup(const SellLoop<IndexT> & 
                 const uint32_t r = (u * 32 + lane) >> ch.l2;
                 if (lead && r < ch.count) { g[ch.first + r] = acc[u]; }   // local id = sorted position
             }
-        }
-
-        if (tid == THREADS - 1) {
-
-            double noise_g = 0;
-            #pragma unroll
-            for (uint32_t wi = 0; wi < num_warps; ++wi) { noise_g += red[wi]; }
-            g[n_local] = noise_g;
-
-            // this CTA's vote on the update before this one
-            uint32_t all = 1;
-            #pragma unroll
-            for (uint32_t wi = 0; wi < num_warps; ++wi) { all &= peers->vote[wi]; }
-            peers->flag[gen] = all;
         }
 
         ++it;
@@ -839,16 +836,9 @@ __device__ __forceinline__ uint32_t emSellIterateGroup(const SellLoop<IndexT> & 
 
         if (warp == num_warps - 1) {
 
-            // noise column: a lane per CTA, so that the remote loads overlap; same summation tree everywhere
-            double part = 0;
-            uint32_t peer_flag = 1;
-
-            if (lane < S) {
-                part = (lane == rank) ? g[n_local] : *(cluster.map_shared_rank(g, lane) + peer_noise_id);
-                if (it > 1) { peer_flag = (lane == rank) ? peers->flag[gen] : *(cluster.map_shared_rank(&peers->flag[gen], lane)); }
-            }
-
-            part = warpSum(part);
+            // noise column: a lane per CTA, the same summation tree everywhere
+            const double part = warpSum(lane < S ? peers->noise_in[gen][lane] : 0.0);
+            const uint32_t peer_flag = (it > 1 && lane < S) ? peers->flag_in[gen][lane] : 1u;
 
             const double a_new = (a_noise * part) * inv_total;
             if (a_new >= min_abundance && fabs(a_new - a_noise) > conv * a_new) { ok = false; }
@@ -1073,11 +1063,16 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
 
     const uint32_t n_cols_present = N - sort_state.bucket_total[0];
 
-    const uint32_t col_chunk_bound = sellCountChunks<THREADS>(sort_state, n_cols_present, depth);
+#ifndef RPVG_B200_SELL_COL_DEPTH_DIV
+#define RPVG_B200_SELL_COL_DEPTH_DIV 1
+#endif
+    const uint32_t col_depth = max(8u, depth / RPVG_B200_SELL_COL_DEPTH_DIV);
+
+    const uint32_t col_chunk_bound = sellCountChunks<THREADS>(sort_state, n_cols_present, col_depth);
 
     SellChunk * col_chunks_made = static_cast<SellChunk *>(arena.take(sizeof(SellChunk) * (col_chunk_bound + 1), false, nullptr));
     uint32_t * col_chunk_dest = static_cast<uint32_t *>(arena.take(4ull * (col_chunk_bound + 1), false, nullptr));
-    const uint32_t n_col_chunks = sellMakeChunks<THREADS>(sort_state, n_cols_present, depth, col_len, col_src, col_chunks_made, scan_tmp, &shared_u32[1]);
+    const uint32_t n_col_chunks = sellMakeChunks<THREADS>(sort_state, n_cols_present, col_depth, col_len, col_src, col_chunks_made, scan_tmp, &shared_u32[1]);
     const uint32_t col_slots = shared_u32[1];
 
     // ---- group: local column ids (= sorted position), and for each of this slice's columns the other CTAs that hold it.
@@ -1100,11 +1095,7 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
 
         if (tid < S) { *(cluster.map_shared_rank(&peers.present[rank], tid)) = n_cols_present; }
         if (tid < 32) { peers.vote[tid] = 0; }
-        if (tid == 0) {
-            peers.flag[0] = 0;
-            peers.flag[1] = 0;
-            peers.stop = 0;
-        }
+        if (tid == 0) { peers.stop = 0; }
 
         __threadfence();   // col_pos travels through L2
         cluster.sync();
