@@ -121,3 +121,36 @@ def test_full_size_properties(ctx):
         q0, q1 = int(rev.path_offset[k]), int(rev.path_offset[k + 1])
         assert np.array_equal(r_ab[q0:q1], abundances[p0:p1])
         assert r_its[k] == iterations[c]
+
+
+def _random_cluster(rng, m, n, per_row, dense=False):
+    """One cluster as arena pieces: m read classes over n paths, per_row paths each (all n when dense)."""
+    if dense:
+        cols = np.tile(np.arange(n, dtype=np.uint32), m)
+        lens = np.full(m, n, dtype=np.int64)
+    else:
+        lens = rng.integers(1, 2 * per_row, size=m)
+        lens = np.minimum(lens, n)
+        cols = np.concatenate([np.sort(rng.choice(n, size=k, replace=False)).astype(np.uint32) for k in lens])
+    row_ptr = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    prob = rng.uniform(1e-6, 1.0, size=cols.size)
+    noise = rng.uniform(1e-4, 0.05, size=m)
+    count = rng.integers(1, 50, size=m).astype(np.uint32)
+    return ClusterArena(np.array([0, m], dtype=np.uint64), np.array([0, n], dtype=np.uint64), row_ptr, cols, prob, noise, count)
+
+
+def test_em_groups_without_band_structure(ctx):
+    """Clusters that are split over several CTAs and in which every slice touches (nearly) every path: the exchange of
+    partial column sums between the CTAs is all-to-all then (the band structure config 2 has is what makes it cheap,
+    not what makes it correct). Dense small-N, dense mid-N and scattered large-N clusters, next to a tiny one."""
+    rng = np.random.default_rng(77)
+    parts = [
+        _random_cluster(rng, 1500, 24, 0, dense=True),       # weight 37.5k -> group of 4
+        _random_cluster(rng, 4000, 40, 0, dense=True),       # weight 164k -> group of 16, every column in every slice
+        _random_cluster(rng, 20000, 3000, 5),                # scattered: ~100k entries over 3000 paths, group of 8-16
+        _random_cluster(rng, 30, 4, 2),
+        _random_cluster(rng, 9000, 700, 3),                  # group of 2-4
+    ]
+    arena = concat(parts)
+    _, _, _, its = check_against_port(ctx, arena)
+    assert its.min() >= 10
