@@ -214,6 +214,15 @@ int rpvg_b200_subset_em_gibbs(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl
 int rpvg_b200_batch_gibbs(rpvg_b200_ctx * ctx, rpvg_b200_batch * batch, const uint32_t * num_samples, uint32_t thin_its, const uint64_t * seeds,
                           double * abundance_samples, double * noise_samples);
 
+/* ---- transcripts per million (the reducer behind the abundance table) ----
+ * total_transcript_count = sum over all paths with effective_length > 0 of abundance / effective_length
+ * (rpvg:src/main.cpp:1029-1057); tpm[i] = abundance[i] / effective_length[i] / total_transcript_count * 10^6, 0 for a
+ * path without effective length (AbundanceEstimatesWriter::addEstimates, rpvg:src/threaded_output_writer.cpp:305-320).
+ * Arrays are over all paths of all clusters of a run (host memory); total_transcript_count may be NULL. As in the
+ * reference, a run without any transcript count divides by zero (NaN). */
+int rpvg_b200_tpm(rpvg_b200_ctx * ctx, uint64_t n_paths, const double * abundances, const double * effective_lengths, double * tpm,
+                  double * total_transcript_count);
+
 /* ---- EM of one cluster for callers that must not allocate ----
  * No counterpart in the reference (rpvg runs on the host and allocates freely); it exists for callers of this library
  * that cannot call cudaMalloc while they run: code under a fixed device-memory budget sized at start-up, real-time

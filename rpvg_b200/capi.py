@@ -78,6 +78,7 @@ def lib():
         l.rpvg_b200_batch_em_work.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         l.rpvg_b200_batch_em_timings.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]
         l.rpvg_b200_batch_free.argtypes = [C.c_void_p, C.c_void_p]
+        l.rpvg_b200_tpm.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_double)]
         l.rpvg_b200_collapse.argtypes = [C.c_void_p, C.POINTER(CollapseProblems), C.c_double] + [C.c_void_p] * 4
         l.rpvg_b200_subset_em.argtypes = [C.c_void_p, C.POINTER(Clusters), C.POINTER(Subsets), C.POINTER(EmParams), C.c_double] + [C.c_void_p] * 5
         l.rpvg_b200_path_cover.argtypes = [C.c_void_p, C.POINTER(Clusters), C.c_void_p]
@@ -205,6 +206,16 @@ class Context:
         cl = clusters_struct(arena)
         self._check(lib().rpvg_b200_path_cover(self._h, C.byref(cl), in_cover.ctypes.data))
         return in_cover.astype(bool)
+
+    def tpm(self, abundances, effective_lengths):
+        """rpvg_b200_tpm: (tpm[n_paths], total_transcript_count)."""
+        abundances = np.ascontiguousarray(abundances, dtype=np.float64)
+        effective_lengths = np.ascontiguousarray(effective_lengths, dtype=np.float64)
+        assert abundances.shape == effective_lengths.shape
+        out = np.zeros(abundances.size, dtype=np.float64)
+        total = C.c_double(0)
+        self._check(lib().rpvg_b200_tpm(self._h, abundances.size, _ptr(abundances), _ptr(effective_lengths), _ptr(out), C.byref(total)))
+        return out, total.value
 
     def upload(self, arena) -> "Batch":
         cl = clusters_struct(arena)

@@ -182,8 +182,9 @@ constexpr int kNumTiers = 5;
 // pairs, ascending) overrides them for tuning runs.
 struct SellTiers {
 
-    uint32_t smem[kNumTiers] = {8 * 1024, 24 * 1024, 56 * 1024, 108 * 1024, 216 * 1024};
-    uint32_t threads[kNumTiers] = {64, 128, 256, 512, 512};
+    // (two CTAs of the 104 KB tier, four of the 52 KB tier per SM; with ~125 registers per thread an SM holds 512 threads)
+    uint32_t smem[kNumTiers] = {8 * 1024, 24 * 1024, 52 * 1024, 104 * 1024, 216 * 1024};
+    uint32_t threads[kNumTiers] = {64, 128, 128, 256, 512};
 
     SellTiers() {
         const char * v = std::getenv("RPVG_B200_EM_TIERS");

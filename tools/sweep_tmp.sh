@@ -1,6 +1,6 @@
 run() {
-  echo "== lib $1"
-  RPVG_B200_LIB=$PWD/$1 timeout 300 python bench.py --steps 3 --warmup 2 --no-cpu-baseline 2>&1 | python -c "
+  echo "== tiers '$1' slice $2"
+  RPVG_B200_EM_TIERS="$1" RPVG_B200_EM_SLICE_WEIGHT=$2 timeout 300 python bench.py --steps 3 --warmup 2 --no-cpu-baseline 2>&1 | python -c "
 import sys,json
 for l in sys.stdin:
     if l.startswith('{'):
@@ -8,8 +8,9 @@ for l in sys.stdin:
     elif 'rror' in l or 'capacity' in l: print(l.strip()[:300])
 " | head -20
 }
-timeout 300 python -m pytest tests/test_em_gpu.py -x -q 2>&1 | tail -3
-run tools/bin/librpvg_b200_prev.so
-run rpvg_b200/librpvg_b200.so
-run tools/bin/librpvg_b200_prev.so
-run rpvg_b200/librpvg_b200.so
+run "" 12000
+run "8:64,24:128,52:128,104:256,216:512" 12000
+run "8:64,24:128,52:128,104:256,216:512" 4500
+run "8:64,24:128,52:128,104:256,216:512" 5500
+run "8:64,24:64,52:128,104:256,216:512" 12000
+run "8:64,24:128,56:256,108:256,216:512" 12000
