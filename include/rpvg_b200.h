@@ -214,6 +214,31 @@ int rpvg_b200_subset_em_gibbs(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl
 int rpvg_b200_batch_gibbs(rpvg_b200_ctx * ctx, rpvg_b200_batch * batch, const uint32_t * num_samples, uint32_t thin_its, const uint64_t * seeds,
                           double * abundance_samples, double * noise_samples);
 
+/* ---- sort + merge of the read records of every cluster, before they reach the estimators ----
+ * What rpvg:src/main.cpp:953-973 does per cluster with std::sort (operator< of ReadPathProbabilities,
+ * rpvg:src/read_path_probabilities.cpp:283-322) and quickMergeIdentical (:223-250), for all clusters of a batch.
+ * A record = noise probability, read count and its probability groups (probability + ascending path ids), as
+ * ReadPathProbabilities::pathProbs() holds them.
+ *   n_merged[c]                                : records cluster c keeps
+ *   merged_rep[read_offset[c] + k], k < n_merged: cluster-local index of the k-th kept record, in the reference's order
+ *   merged_count[...same...]                   : its read count after the merges (uint32 arithmetic like the reference)
+ *   record_class[r]                            : k of the kept record that input record r went into
+ * Exact: the partition, the order and the counts. Records the comparator calls equal (all values within 100 eps, same
+ * count) are in arbitrary order in the reference (unstable std::sort) and in input order here. */
+typedef struct rpvg_b200_read_records {
+    uint32_t n_clusters;
+    const uint64_t * read_offset;   /* [n_clusters + 1] first record of each cluster */
+    const uint64_t * group_ptr;     /* [n_records + 1] first probability group of each record */
+    const double * group_prob;      /* [n_groups] */
+    const uint64_t * id_ptr;        /* [n_groups + 1] first path id of each group */
+    const uint32_t * ids;           /* path ids */
+    const double * noise;           /* [n_records] */
+    const uint32_t * count;         /* [n_records] */
+} rpvg_b200_read_records;
+
+int rpvg_b200_merge_read_records(rpvg_b200_ctx * ctx, const rpvg_b200_read_records * records, double prob_precision, uint32_t * n_merged, uint32_t * record_class,
+                                 uint32_t * merged_rep, uint32_t * merged_count);
+
 /* ---- transcripts per million (the reducer behind the abundance table) ----
  * total_transcript_count = sum over all paths with effective_length > 0 of abundance / effective_length
  * (rpvg:src/main.cpp:1029-1057); tpm[i] = abundance[i] / effective_length[i] / total_transcript_count * 10^6, 0 for a

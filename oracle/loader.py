@@ -141,6 +141,8 @@ def reference():
             raise RuntimeError("oracle/_ref/libharness_ref.so is missing: run `make -C oracle ref` where /root/reference exists")
         l = load_harness(path)
         l.ref_build_matrix.argtypes = [C.c_double, C.POINTER(HarnessCluster), C.c_int32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_int32] + [C.c_void_p] * 3
+        l.ref_merge_read_records.restype = C.c_uint32
+        l.ref_merge_read_records.argtypes = [C.c_double, C.POINTER(HarnessCluster)] + [C.c_void_p] * 6
         l.ref_collapse.restype = C.c_uint32
         l.ref_collapse.argtypes = [C.c_double, C.c_uint32, C.c_uint32] + [C.c_void_p] * 4
         l.ref_em.argtypes = [C.c_uint32, C.c_double, C.c_uint32, C.c_uint32] + [C.c_void_p] * 5
@@ -283,3 +285,27 @@ def port_em_abundances(arena, max_em_its=10000, max_rel_em_conv=0.001, min_em_co
     seconds = port().oracle_em_abundances(C.byref(cl), max_em_its, max_rel_em_conv, min_em_conv_its, min_em_abundance, num_threads,
                                           abundances.ctypes.data, noise_count.ctypes.data, total_count.ctypes.data, iterations.ctypes.data)
     return abundances, noise_count, total_count, iterations, seconds
+
+
+def ref_merge_read_records(ref, num_paths, count, noise, entry_ptr, entry_prob, entry_path_ptr, entry_path_ids, prob_precision=1e-8):
+    """The reference's own sort + quickMergeIdentical scan (rpvg:src/main.cpp:953-973) over one cluster's records.
+    -> (noise, count, entry_ptr, entry_prob, entry_path_ptr, entry_path_ids) of the kept records."""
+    count = np.ascontiguousarray(count, dtype=np.uint32)
+    noise = np.ascontiguousarray(noise, dtype=np.float64)
+    entry_ptr = np.ascontiguousarray(entry_ptr, dtype=np.uint64)
+    entry_prob = np.ascontiguousarray(entry_prob, dtype=np.float64)
+    entry_path_ptr = np.ascontiguousarray(entry_path_ptr, dtype=np.uint64)
+    entry_path_ids = np.ascontiguousarray(entry_path_ids, dtype=np.uint32)
+    R = len(count)
+    cluster = HarnessCluster(num_paths, R, count.ctypes.data, noise.ctypes.data, entry_ptr.ctypes.data, entry_prob.ctypes.data, entry_path_ptr.ctypes.data,
+                             entry_path_ids.ctypes.data, None, None, None, None)
+    o_noise = np.zeros(R, dtype=np.float64)
+    o_count = np.zeros(R, dtype=np.uint32)
+    o_entry_ptr = np.zeros(R + 1, dtype=np.uint64)
+    o_entry_prob = np.zeros(len(entry_prob) + 1, dtype=np.float64)
+    o_path_ptr = np.zeros(len(entry_prob) + 1, dtype=np.uint64)
+    o_ids = np.zeros(len(entry_path_ids) + 1, dtype=np.uint32)
+    n = ref.ref_merge_read_records(prob_precision, C.byref(cluster), o_noise.ctypes.data, o_count.ctypes.data, o_entry_ptr.ctypes.data, o_entry_prob.ctypes.data,
+                                   o_path_ptr.ctypes.data, o_ids.ctypes.data)
+    ne = int(o_entry_ptr[n])
+    return o_noise[:n], o_count[:n], o_entry_ptr[:n + 1], o_entry_prob[:ne], o_path_ptr[:ne + 1], o_ids[:int(o_path_ptr[ne])]

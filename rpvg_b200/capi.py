@@ -47,6 +47,10 @@ class CollapseProblems(C.Structure):
     _fields_ = [("n_problems", C.c_uint32)] + [(n, C.c_void_p) for n in ("row_offset", "row_ptr", "col", "val", "noise", "count")]
 
 
+class ReadRecords(C.Structure):
+    _fields_ = [("n_clusters", C.c_uint32)] + [(n, C.c_void_p) for n in ("read_offset", "group_ptr", "group_prob", "id_ptr", "ids", "noise", "count")]
+
+
 class Subsets(C.Structure):
     _fields_ = [("n_subsets", C.c_uint32), ("subset_cluster", C.c_void_p), ("subset_offset", C.c_void_p), ("subset_paths", C.c_void_p)]
 
@@ -78,6 +82,7 @@ def lib():
         l.rpvg_b200_batch_em_work.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]
         l.rpvg_b200_batch_em_timings.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]
         l.rpvg_b200_batch_free.argtypes = [C.c_void_p, C.c_void_p]
+        l.rpvg_b200_merge_read_records.argtypes = [C.c_void_p, C.POINTER(ReadRecords), C.c_double] + [C.c_void_p] * 4
         l.rpvg_b200_tpm.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_double)]
         l.rpvg_b200_collapse.argtypes = [C.c_void_p, C.POINTER(CollapseProblems), C.c_double] + [C.c_void_p] * 4
         l.rpvg_b200_subset_em.argtypes = [C.c_void_p, C.POINTER(Clusters), C.POINTER(Subsets), C.POINTER(EmParams), C.c_double] + [C.c_void_p] * 5
@@ -206,6 +211,19 @@ class Context:
         cl = clusters_struct(arena)
         self._check(lib().rpvg_b200_path_cover(self._h, C.byref(cl), in_cover.ctypes.data))
         return in_cover.astype(bool)
+
+    def merge_read_records(self, read_offset, group_ptr, group_prob, id_ptr, ids, noise, count, prob_precision=1e-8):
+        """rpvg_b200_merge_read_records: (n_merged[C], record_class[R], merged_rep[R], merged_count[R])."""
+        arrays = [np.ascontiguousarray(a, dtype=t) for a, t in ((read_offset, np.uint64), (group_ptr, np.uint64), (group_prob, np.float64), (id_ptr, np.uint64),
+                                                                   (ids, np.uint32), (noise, np.float64), (count, np.uint32))]
+        rec = ReadRecords(len(arrays[0]) - 1, *[_ptr(a) for a in arrays])
+        R = int(arrays[0][-1])
+        n_merged = np.zeros(rec.n_clusters, dtype=np.uint32)
+        record_class = np.zeros(R, dtype=np.uint32)
+        merged_rep = np.zeros(R, dtype=np.uint32)
+        merged_count = np.zeros(R, dtype=np.uint32)
+        self._check(lib().rpvg_b200_merge_read_records(self._h, C.byref(rec), prob_precision, _ptr(n_merged), _ptr(record_class), _ptr(merged_rep), _ptr(merged_count)))
+        return n_merged, record_class, merged_rep, merged_count
 
     def tpm(self, abundances, effective_lengths):
         """rpvg_b200_tpm: (tpm[n_paths], total_transcript_count)."""

@@ -76,19 +76,13 @@ struct CollapseRowLess {
 
 constexpr int kCollapseSortThreads = 512;
 
-// One CTA per problem: bitonic network (all compare-exchanges ascending, so the virtual +inf padding above n stays put)
-// over sorted[s0, s1), which holds the problem's row ids on entry.
-static __global__ void __launch_bounds__(kCollapseSortThreads) collapseSortKernel(const CollapseRows rows, uint32_t * __restrict__ sorted) {
+// Bitonic network over keys[0, n) run by one CTA of kCollapseSortThreads threads (all compare-exchanges ascending, so the
+// virtual +inf padding above n stays put). `less` is the reference's comparator on two keys; keys the comparator calls
+// equal are ordered by key value.
+template <typename Less>
+__device__ __forceinline__ void collapseBitonicNetwork(uint32_t * keys, const uint32_t n, const Less & less) {
 
-    const uint32_t p = blockIdx.x;
-    const uint64_t s0 = rows.problem_row_offset[p];
-    const uint32_t n = static_cast<uint32_t>(rows.problem_row_offset[p + 1] - s0);
     if (n < 2) { return; }
-
-    uint32_t * keys = sorted + s0;
-
-    CollapseRowLess less;
-    less.rows = rows;
 
     uint32_t padded = 2;
     while (padded < n) { padded <<= 1; }
@@ -98,7 +92,7 @@ static __global__ void __launch_bounds__(kCollapseSortThreads) collapseSortKerne
         if (hi < n) {
             const uint32_t a = keys[lo];
             const uint32_t b = keys[hi];
-            // b before a: strictly less, or tied under the comparator with the smaller row id
+            // b before a: strictly less, or tied under the comparator with the smaller key
             if (less(b, a) || (!less(a, b) && b < a)) {
                 keys[lo] = b;
                 keys[hi] = a;
@@ -123,6 +117,19 @@ static __global__ void __launch_bounds__(kCollapseSortThreads) collapseSortKerne
             __syncthreads();
         }
     }
+}
+
+// One CTA per problem: sorted[s0, s1) holds the problem's row ids on entry, in the reference's order on exit.
+static __global__ void __launch_bounds__(kCollapseSortThreads) collapseSortKernel(const CollapseRows rows, uint32_t * __restrict__ sorted) {
+
+    const uint32_t p = blockIdx.x;
+    const uint64_t s0 = rows.problem_row_offset[p];
+    const uint32_t n = static_cast<uint32_t>(rows.problem_row_offset[p + 1] - s0);
+
+    CollapseRowLess less;
+    less.rows = rows;
+
+    collapseBitonicNetwork(sorted + s0, n, less);
 }
 
 // true iff every column (absent = 0) and the noise value of rows a and b differ by less than prob_precision

@@ -395,6 +395,53 @@ void * ref_group_posteriors(int32_t kind, uint32_t group_size, double min_rel_li
     return flattenEstimates(est);
 }
 
+// The cluster driver's sort + merge of the read records (main.cpp:953-973), with the reference's own operator< and
+// quickMergeIdentical. Outputs the kept records, flattened: returns their number.
+uint32_t ref_merge_read_records(double prob_precision, const HarnessCluster * cluster, double * out_noise, uint32_t * out_count, uint64_t * out_entry_ptr, double * out_entry_prob,
+                                uint64_t * out_entry_path_ptr, uint32_t * out_entry_path_ids) {
+
+    PathClusterEstimates unused;
+    vector<ReadPathProbabilities> records;
+    unflattenCluster(*cluster, prob_precision, &unused, &records);
+
+    sort(records.begin(), records.end());
+
+    if (!records.empty()) {
+
+        uint32_t prev_unique = 0;
+
+        for (size_t i = 1; i < records.size(); ++i) {
+
+            if (!records.at(prev_unique).quickMergeIdentical(records.at(i))) {
+
+                if (prev_unique + 1 < i) { records.at(prev_unique + 1) = records.at(i); }
+                prev_unique++;
+            }
+        }
+
+        records.resize(prev_unique + 1);
+    }
+
+    uint64_t n_entries = 0, n_ids = 0;
+    out_entry_ptr[0] = 0;
+    out_entry_path_ptr[0] = 0;
+
+    for (size_t r = 0; r < records.size(); ++r) {
+
+        out_noise[r] = records[r].noiseProb();
+        out_count[r] = records[r].readCount();
+
+        for (auto & group: records[r].pathProbs()) {
+            out_entry_prob[n_entries] = group.first;
+            for (auto id: group.second) { out_entry_path_ids[n_ids++] = id; }
+            out_entry_path_ptr[++n_entries] = n_ids;
+        }
+        out_entry_ptr[r + 1] = n_entries;
+    }
+
+    return static_cast<uint32_t>(records.size());
+}
+
 uint32_t ref_path_cover(uint32_t rows, uint32_t n_paths, const uint8_t * cover, const double * counts, const double * weights, uint32_t * out_cover) {
 
     MinimumPathAbundanceEstimator estimator(1, 1, 0, 1, 1e-8);

@@ -101,6 +101,10 @@ int32_t harness_max_threads(void);
  * out_matrix: col-major [num_reads x (ncols + (add_noise?1:0))]; out_noise/out_counts: [num_reads]. */
 void ref_build_matrix(double prob_precision, const HarnessCluster * cluster, int32_t mode, uint32_t n_ids, const uint64_t * id_ptr, const uint32_t * ids, int32_t add_noise, double * out_matrix, double * out_noise, double * out_counts);
 
+/* sort + quickMergeIdentical scan of the cluster driver (main.cpp:953-973); outputs sized like the inputs. */
+uint32_t ref_merge_read_records(double prob_precision, const HarnessCluster * cluster, double * out_noise, uint32_t * out_count, uint64_t * out_entry_ptr, double * out_entry_prob,
+                                uint64_t * out_entry_path_ptr, uint32_t * out_entry_path_ids);
+
 /* readCollapseProbabilityMatrix (path_estimator.cpp:219-259). Matrices col-major; returns new row count. */
 uint32_t ref_collapse(double prob_precision, uint32_t rows, uint32_t cols, const double * matrix, const double * counts, double * out_matrix, double * out_counts);
 
