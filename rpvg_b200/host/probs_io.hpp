@@ -1,5 +1,5 @@
 // Reader and writer of rpvg's `--write-probs` text dump (`<prefix>_probs.txt.gz`): the boundary input of the estimators,
-// one block per path cluster. With it a dump made by a real rpvg run drives the GPU path (and the oracle) without GBWT,
+// one block per path cluster. With it a dump made by a real rpvg run drives the GPU path (and any CPU checker) without GBWT,
 // protobuf or htslib.
 //
 // Format restated from ProbabilityClusterWriter::addCluster (rpvg:src/threaded_output_writer.cpp:42-95), never its code:
