@@ -200,7 +200,7 @@ const SellTiers & sellTiers() {
     static const SellTiers tiers;
     return tiers;
 }
-constexpr uint32_t kStaticSmemReserve = 12 * 1024;   // static shared memory of emSellKernel<512> + slack
+constexpr uint32_t kStaticSmemReserve = 12 * 1024;   // static shared memory of emSellBuildKernel<512> + slack
 
 struct GroupPlan {
 
@@ -217,7 +217,7 @@ void planEmLaunches(const rpvg_b200_ctx * ctx, rpvg_b200_batch * b, std::vector<
 
     // weight (entries + rows) one CTA should own; above it a cluster is split over 2, 4, 8, 16 CTAs
     const uint32_t slice_weight = std::max(64u, envKnob("RPVG_B200_EM_SLICE_WEIGHT", 12000));
-    const uint32_t big_threads = envKnob("RPVG_B200_EM_BIG_THREADS", 512);
+    const uint32_t big_threads = envKnob("RPVG_B200_EM_BIG_THREADS", 1024);
     const uint32_t max_group = std::min(ctx->max_group_size, std::max(1u, envKnob("RPVG_B200_EM_MAX_GROUP", kMaxGroupSize)));
     const uint32_t smem_cap = std::min<uint32_t>(sellTiers().smem[kNumTiers - 1], static_cast<uint32_t>(ctx->max_smem_optin) - kStaticSmemReserve);
 
@@ -285,7 +285,7 @@ void planEmLaunches(const rpvg_b200_ctx * ctx, rpvg_b200_batch * b, std::vector<
             while ((1u << group_log2) < group) { group_log2++; }
 
             plan.bin = ((4 - group_log2) * kNumTiers + (kNumTiers - 1 - tier)) * 2 + (index_bytes == 4 ? 1 : 0);
-            plan.cta_bytes = sellScratchBytes(m_b, z_b, N, index_bytes, with_entries);
+            plan.cta_bytes = sellScratchBytes(m_b, z_b, N, index_bytes, with_entries) + sellHandoverBytes(std::min(sellTiers().smem[tier], smem_cap));
         }
 
         items[c] = plan;
@@ -347,12 +347,14 @@ void planEmLaunches(const rpvg_b200_ctx * ctx, rpvg_b200_batch * b, std::vector<
     }
 }
 
-template <int THREADS, bool MULTI, typename IndexT>
+// One bin = two launches on the same stream with the same grid and thread-block clusters: the build kernel lays the
+// slices out, the run kernel iterates on them (em_sell.cuh).
+template <int BUILD_THREADS, int RUN_THREADS, bool MULTI, typename IndexT>
 cudaError_t launchSell(const SellArgs & sa, uint32_t group_size, uint32_t n_groups, cudaStream_t stream) {
 
     cudaLaunchConfig_t config = {};
     config.gridDim = dim3(n_groups * group_size, 1, 1);
-    config.blockDim = dim3(THREADS, 1, 1);
+    config.blockDim = dim3(BUILD_THREADS, 1, 1);
     config.dynamicSmemBytes = sa.smem_bytes;
     config.stream = stream;
 
@@ -364,7 +366,14 @@ cudaError_t launchSell(const SellArgs & sa, uint32_t group_size, uint32_t n_grou
     config.attrs = attr;
     config.numAttrs = MULTI ? 1 : 0;
 
-    return cudaLaunchKernelEx(&config, emSellKernel<THREADS, MULTI, IndexT>, sa);
+    SellArgs args = sa;
+    args.run_warps = RUN_THREADS / 32;
+
+    cudaError_t err = cudaLaunchKernelEx(&config, emSellBuildKernel<BUILD_THREADS, MULTI, IndexT>, args);
+    if (err != cudaSuccess) { return err; }
+
+    config.blockDim = dim3(RUN_THREADS, 1, 1);
+    return cudaLaunchKernelEx(&config, emSellRunKernel<RUN_THREADS, MULTI, IndexT>, args);
 }
 
 cudaError_t launchSellBin(const SellArgs & sa, const rpvg_b200_batch::EmBin & bin, cudaStream_t stream) {
@@ -372,34 +381,34 @@ cudaError_t launchSellBin(const SellArgs & sa, const rpvg_b200_batch::EmBin & bi
     const bool multi = bin.group_size > 1;
 
     if (bin.index_bytes == 4) {
-        return multi ? launchSell<512, true, uint32_t>(sa, bin.group_size, bin.count, stream)
-                     : launchSell<512, false, uint32_t>(sa, 1, bin.count, stream);
+        if (bin.threads == 1024) {
+            return multi ? launchSell<512, 1024, true, uint32_t>(sa, bin.group_size, bin.count, stream) : launchSell<512, 1024, false, uint32_t>(sa, 1, bin.count, stream);
+        }
+        return multi ? launchSell<512, 512, true, uint32_t>(sa, bin.group_size, bin.count, stream) : launchSell<512, 512, false, uint32_t>(sa, 1, bin.count, stream);
     }
 
     if (multi) {
-        if (bin.threads == 256) { return launchSell<256, true, uint16_t>(sa, bin.group_size, bin.count, stream); }
-        if (bin.threads == 1024) { return launchSell<1024, true, uint16_t>(sa, bin.group_size, bin.count, stream); }
-        return launchSell<512, true, uint16_t>(sa, bin.group_size, bin.count, stream);
+        if (bin.threads == 256) { return launchSell<256, 256, true, uint16_t>(sa, bin.group_size, bin.count, stream); }
+        if (bin.threads == 1024) { return launchSell<512, 1024, true, uint16_t>(sa, bin.group_size, bin.count, stream); }
+        return launchSell<512, 512, true, uint16_t>(sa, bin.group_size, bin.count, stream);
     }
 
     switch (bin.threads) {
-        case 64: return launchSell<64, false, uint16_t>(sa, 1, bin.count, stream);
-        case 128: return launchSell<128, false, uint16_t>(sa, 1, bin.count, stream);
-        case 256: return launchSell<256, false, uint16_t>(sa, 1, bin.count, stream);
-        case 1024: return launchSell<1024, false, uint16_t>(sa, 1, bin.count, stream);
-        default: return launchSell<512, false, uint16_t>(sa, 1, bin.count, stream);
+        case 64: return launchSell<64, 64, false, uint16_t>(sa, 1, bin.count, stream);
+        case 128: return launchSell<128, 128, false, uint16_t>(sa, 1, bin.count, stream);
+        case 256: return launchSell<256, 256, false, uint16_t>(sa, 1, bin.count, stream);
+        case 1024: return launchSell<512, 1024, false, uint16_t>(sa, 1, bin.count, stream);
+        default: return launchSell<512, 512, false, uint16_t>(sa, 1, bin.count, stream);
     }
 }
 
-template <int THREADS, bool MULTI, typename IndexT>
-cudaError_t configureSell(const rpvg_b200_ctx * ctx, uint32_t * max_group) {
+template <typename Kernel>
+cudaError_t configureSellKernel(Kernel kernel, int threads, bool multi, int smem_cap, uint32_t * max_group) {
 
-    const int smem_cap = std::min<int>(sellTiers().smem[kNumTiers - 1], ctx->max_smem_optin - static_cast<int>(kStaticSmemReserve));
+    cudaError_t err = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap);
+    if (err != cudaSuccess || !multi) { return err; }
 
-    cudaError_t err = cudaFuncSetAttribute(emSellKernel<THREADS, MULTI, IndexT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cap);
-    if (err != cudaSuccess || !MULTI) { return err; }
-
-    err = cudaFuncSetAttribute(emSellKernel<THREADS, MULTI, IndexT>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    err = cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
     if (err != cudaSuccess) { return err; }
 
     // largest thread-block cluster that can be co-scheduled with the biggest shared-memory tier
@@ -409,7 +418,7 @@ cudaError_t configureSell(const rpvg_b200_ctx * ctx, uint32_t * max_group) {
 
         cudaLaunchConfig_t config = {};
         config.gridDim = dim3(group, 1, 1);
-        config.blockDim = dim3(THREADS, 1, 1);
+        config.blockDim = dim3(threads, 1, 1);
         config.dynamicSmemBytes = smem_cap;
 
         cudaLaunchAttribute attr[1];
@@ -421,7 +430,7 @@ cudaError_t configureSell(const rpvg_b200_ctx * ctx, uint32_t * max_group) {
         config.numAttrs = 1;
 
         int num_clusters = 0;
-        err = cudaOccupancyMaxActiveClusters(&num_clusters, emSellKernel<THREADS, MULTI, IndexT>, &config);
+        err = cudaOccupancyMaxActiveClusters(&num_clusters, kernel, &config);
         if (err == cudaSuccess && num_clusters > 0) { break; }
 
         cudaGetLastError();
@@ -430,6 +439,16 @@ cudaError_t configureSell(const rpvg_b200_ctx * ctx, uint32_t * max_group) {
 
     *max_group = std::min(*max_group, group);
     return cudaSuccess;
+}
+
+template <int BUILD_THREADS, int RUN_THREADS, bool MULTI, typename IndexT>
+cudaError_t configureSell(const rpvg_b200_ctx * ctx, uint32_t * max_group) {
+
+    const int smem_cap = std::min<int>(sellTiers().smem[kNumTiers - 1], ctx->max_smem_optin - static_cast<int>(kStaticSmemReserve));
+
+    cudaError_t err = configureSellKernel(emSellBuildKernel<BUILD_THREADS, MULTI, IndexT>, BUILD_THREADS, MULTI, smem_cap, max_group);
+    if (err != cudaSuccess) { return err; }
+    return configureSellKernel(emSellRunKernel<RUN_THREADS, MULTI, IndexT>, RUN_THREADS, MULTI, smem_cap, max_group);
 }
 
 int checkClusters(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl) {
@@ -468,16 +487,18 @@ int rpvgEmInit(rpvg_b200_ctx * ctx) {
     uint32_t max_group = kMaxGroupSize;
     uint32_t unused = kMaxGroupSize;
 
-    RPVG_CUDA(ctx, (configureSell<64, false, uint16_t>(ctx, &unused)));
-    RPVG_CUDA(ctx, (configureSell<128, false, uint16_t>(ctx, &unused)));
-    RPVG_CUDA(ctx, (configureSell<256, false, uint16_t>(ctx, &unused)));
-    RPVG_CUDA(ctx, (configureSell<512, false, uint16_t>(ctx, &unused)));
-    RPVG_CUDA(ctx, (configureSell<512, false, uint32_t>(ctx, &unused)));
-    RPVG_CUDA(ctx, (configureSell<256, true, uint16_t>(ctx, &max_group)));
-    RPVG_CUDA(ctx, (configureSell<512, true, uint16_t>(ctx, &max_group)));
-    RPVG_CUDA(ctx, (configureSell<512, true, uint32_t>(ctx, &max_group)));
-    RPVG_CUDA(ctx, (configureSell<1024, false, uint16_t>(ctx, &unused)));
-    RPVG_CUDA(ctx, (configureSell<1024, true, uint16_t>(ctx, &max_group)));
+    RPVG_CUDA(ctx, (configureSell<64, 64, false, uint16_t>(ctx, &unused)));
+    RPVG_CUDA(ctx, (configureSell<128, 128, false, uint16_t>(ctx, &unused)));
+    RPVG_CUDA(ctx, (configureSell<256, 256, false, uint16_t>(ctx, &unused)));
+    RPVG_CUDA(ctx, (configureSell<512, 512, false, uint16_t>(ctx, &unused)));
+    RPVG_CUDA(ctx, (configureSell<512, 1024, false, uint16_t>(ctx, &unused)));
+    RPVG_CUDA(ctx, (configureSell<512, 512, false, uint32_t>(ctx, &unused)));
+    RPVG_CUDA(ctx, (configureSell<512, 1024, false, uint32_t>(ctx, &unused)));
+    RPVG_CUDA(ctx, (configureSell<256, 256, true, uint16_t>(ctx, &max_group)));
+    RPVG_CUDA(ctx, (configureSell<512, 512, true, uint16_t>(ctx, &max_group)));
+    RPVG_CUDA(ctx, (configureSell<512, 1024, true, uint16_t>(ctx, &max_group)));
+    RPVG_CUDA(ctx, (configureSell<512, 512, true, uint32_t>(ctx, &max_group)));
+    RPVG_CUDA(ctx, (configureSell<512, 1024, true, uint32_t>(ctx, &max_group)));
 
     ctx->max_group_size = max_group;
     return RPVG_B200_OK;
@@ -876,7 +897,7 @@ int rpvg_b200_batch_em(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const rpvg_b200
                     rpvg_b200_batch::EmBin single = bin;
                     single.count = 1;
                     launch_err = launchSellBin(one, single, ctx->lane_streams[lane]);
-                    if (i > 0) { RPVG_LAUNCHED(ctx); }
+                    if (i > 0) { RPVG_LAUNCHED(ctx); RPVG_LAUNCHED(ctx); }
                 }
 
                 lanes_used = true;
@@ -886,10 +907,11 @@ int rpvg_b200_batch_em(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const rpvg_b200
             }
 
             if (launch_err != cudaSuccess) {
-                return rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("emSellKernel launch (group ") + std::to_string(bin.group_size) + ", threads " +
+                return rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("emSell kernels launch (group ") + std::to_string(bin.group_size) + ", threads " +
                                 std::to_string(bin.threads) + ", smem " + std::to_string(bin.smem) + "): " + cudaGetErrorString(launch_err));
             }
             RPVG_LAUNCHED(ctx);
+            RPVG_LAUNCHED(ctx);   // build + run
         }
 
     }

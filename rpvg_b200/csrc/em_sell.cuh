@@ -41,7 +41,13 @@ struct SellArgs {
     const uint64_t * group_cta_bytes;  // [n_groups] scratch bytes each CTA of the group owns
     unsigned char * scratch;
     uint32_t smem_bytes;               // dynamic shared memory per CTA of this launch
+    uint32_t run_warps;                // warps of the CTAs that will iterate (the layout is made for them)
 };
+
+// Bytes at the end of a CTA's scratch area that hand the slice from the build kernel to the run kernel: a header and
+// the image of the build kernel's dynamic shared memory.
+constexpr uint64_t kSellHeaderBytes = 1024;
+__host__ __device__ inline uint64_t sellHandoverBytes(uint64_t smem_bytes) { return kSellHeaderBytes + ((smem_bytes + 255) & ~uint64_t(255)); }
 
 struct alignas(16) SellChunk {   // one 16-byte load
 
@@ -375,14 +381,12 @@ __device__ uint32_t sellMakeChunks(SellSort<THREADS> & st, const uint32_t n, con
 constexpr uint32_t kSellChunkCost = 5;   // steps a chunk costs on top of its width (descriptor, reduction, division)
 
 template <int THREADS>
-__device__ void sellAssignChunks(const SellChunk * in, const uint32_t n_chunks, SellChunk * out, uint32_t * warp_begin, uint32_t * dest) {
-
-    constexpr uint32_t W = THREADS / 32;
+__device__ void sellAssignChunks(const SellChunk * in, const uint32_t n_chunks, SellChunk * out, uint32_t * warp_begin, uint32_t * dest, const uint32_t W) {
 
     if (threadIdx.x == 0) {
 
-        uint32_t load[W];
-        uint32_t count[W];
+        uint32_t load[32];
+        uint32_t count[32];
         for (uint32_t w = 0; w < W; ++w) { load[w] = 0; count[w] = 0; }
 
         for (uint32_t k = 0; k < n_chunks; ++k) {
@@ -493,6 +497,26 @@ struct SellLoop {
     SellSide<IndexT> rows;
     SellSide<IndexT> cols;
 };
+
+// What the build kernel leaves for the run kernel at the end of the CTA's scratch area (sellHandoverBytes).
+template <typename IndexT>
+struct SellHeader {
+
+    uint32_t state;            // 0: nothing to iterate (cluster without read classes, or capacity error); 1: slice ready
+    uint32_t all_shared;       // everything the loop touches is in the shared-memory image
+    uint32_t image_bytes;      // used part of the build kernel's dynamic shared memory, copied behind this header
+    uint32_t n_cols_present;
+    uint64_t smem_base;        // generic address of the build kernel's dynamic shared memory: pointers into
+                               // [smem_base, smem_base + image_bytes) are relative to it
+    double total;
+    const uint32_t * col_src;  // column of each sorted position (global scratch)
+    uint32_t row_warp_begin[33];
+    uint32_t col_warp_begin[33];
+    uint32_t present[kMaxGroupSize];
+    SellLoop<IndexT> loop;
+};
+
+static_assert(sizeof(SellHeader<uint32_t>) <= kSellHeaderBytes, "SellHeader outgrew its slot");
 
 // 1 / x to within an ulp or two: hardware seed (20 bits) and two Newton steps. The E-step divides once per read class;
 // an IEEE division would be a dependent chain four times as long on the critical path of every iteration.
@@ -902,12 +926,11 @@ __device__ unsigned long long rpvg_timeline_records[12 * 65536];
 __device__ unsigned int rpvg_timeline_count;
 #endif
 
-#ifndef RPVG_B200_EM_MIN_CTAS_512
-#define RPVG_B200_EM_MIN_CTAS_512 1
-#endif
-
+// Build kernel: re-lays the slice out (see the header comment of this file) in its own shared memory and scratch area and
+// hands the result to emSellRunKernel. Separate kernels because the layout code needs twice the registers of the EM loop:
+// the loop alone fits 64 registers, which doubles the warps an SM holds while it iterates.
 template <int THREADS, bool MULTI, typename IndexT>
-__global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CTAS_512 : (THREADS == 128 ? 6 : (THREADS == 64 ? 12 : 1)))) emSellKernel(const SellArgs sa) {
+__global__ void __launch_bounds__(THREADS, (THREADS == 128 ? 6 : (THREADS == 64 ? 12 : 1))) emSellBuildKernel(const SellArgs sa) {
 
     extern __shared__ __align__(16) unsigned char smem_raw[];
 
@@ -917,8 +940,8 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
     __shared__ uint32_t capacity_flag;
     __shared__ uint32_t scan_tmp[THREADS / 32];
     __shared__ uint32_t shared_u32[4];
-    __shared__ uint32_t row_warp_begin[THREADS / 32 + 1];
-    __shared__ uint32_t col_warp_begin[THREADS / 32 + 1];
+    __shared__ uint32_t row_warp_begin[33];
+    __shared__ uint32_t col_warp_begin[33];
     __shared__ SellSort<THREADS> sort_state;
 
     const EmArgs & args = sa.em;
@@ -934,13 +957,12 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
 
     if (*args.error) { return; }   // malformed arena: indices cannot be trusted (uniform over the whole grid)
 
-#ifdef RPVG_B200_EM_TIMELINE
-    unsigned long long timeline_t0, timeline_t1;
-    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(timeline_t0));
-#endif
-
     const uint32_t group = blockIdx.x / S;
     const uint32_t c = sa.group_cluster[group];
+
+    unsigned char * cta_scratch = sa.scratch + sa.group_scratch[group] + static_cast<uint64_t>(rank) * sa.group_cta_bytes[group];
+    const uint64_t cta_scratch_bytes = sa.group_cta_bytes[group] - sellHandoverBytes(sa.smem_bytes);
+    SellHeader<IndexT> * header = reinterpret_cast<SellHeader<IndexT> *>(cta_scratch + cta_scratch_bytes);
 
     const uint64_t r0 = args.read_offset[c];
     const uint32_t M = static_cast<uint32_t>(args.read_offset[c + 1] - r0);
@@ -956,6 +978,7 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
             args.total_count[c] = 0;
             args.iterations[c] = 0;
         }
+        if (tid == 0) { header->state = 0; }
         return;
     }
 
@@ -989,8 +1012,8 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
     SellArena arena;
     arena.smem = smem_raw;
     arena.smem_left = sa.smem_bytes;
-    arena.gmem = sa.scratch + sa.group_scratch[group] + static_cast<uint64_t>(rank) * sa.group_cta_bytes[group];
-    arena.gmem_left = sa.group_cta_bytes[group];
+    arena.gmem = cta_scratch;
+    arena.gmem_left = cta_scratch_bytes;
     arena.overflow = false;
 
     const unsigned char * scratch_base = arena.gmem;
@@ -1016,7 +1039,7 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
     sellStableSort<THREADS>(sort_state, m, row_len, row_pos, row_src);
 
     const uint32_t z_slice = static_cast<uint32_t>(row_ptr[i0 + m] - e_slice);
-    const uint32_t depth = sellDepth(z_slice, num_warps);
+    const uint32_t depth = sellDepth(z_slice, sa.run_warps);
 
     const uint32_t row_chunk_bound = sellCountChunks<THREADS>(sort_state, m, depth);
 
@@ -1192,6 +1215,7 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
         cluster.sync();
         if (capacity_flag) {
             if (rank == 0 && tid == 0) { atomicOr(const_cast<uint32_t *>(args.error), RPVG_DEV_ERR_CAPACITY); }
+            if (tid == 0) { header->state = 0; }
             return;
         }
     } else if (arena.overflow) {
@@ -1199,13 +1223,14 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
             atomicOr(const_cast<uint32_t *>(args.error), RPVG_DEV_ERR_CAPACITY);
             printf("[rpvg_b200] capacity: cluster %u M %u N %u m %u row_slots %u col_slots %u chunks %u/%u cta_bytes %llu smem %u\n", c, M, N, m, row_slots, col_slots,
                    n_row_chunks, n_col_chunks, static_cast<unsigned long long>(sa.group_cta_bytes[group]), sa.smem_bytes);
+            header->state = 0;
         }
         return;
     }
 
     // ---- deal the chunks to the warps (after the capacity check: the scratch arrays are known to be in bounds)
-    sellAssignChunks<THREADS>(row_chunks_made, n_row_chunks, row_chunks, row_warp_begin, row_chunk_dest);
-    sellAssignChunks<THREADS>(col_chunks_made, n_col_chunks, col_chunks, col_warp_begin, col_chunk_dest);
+    sellAssignChunks<THREADS>(row_chunks_made, n_row_chunks, row_chunks, row_warp_begin, row_chunk_dest, sa.run_warps);
+    sellAssignChunks<THREADS>(col_chunks_made, n_col_chunks, col_chunks, col_warp_begin, col_chunk_dest, sa.run_warps);
 
     rows.chunks = row_chunks;
     rows.warp_begin = row_warp_begin;
@@ -1315,8 +1340,7 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
         __syncthreads();
     }
 
-    // ---- EM iterations. When everything this CTA touches sits in shared memory the loop runs on pointers the compiler
-    // can prove to be shared (plain LDS/STS); otherwise on generic pointers (hybrid residency).
+    // ---- hand the slice over: loop arguments, and the image of this CTA's shared memory
     SellLoop<IndexT> loop;
     loop.a = a;
     loop.a_prev = a_prev;
@@ -1330,9 +1354,11 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
     loop.holders = holders;
     loop.pull_begin = pull_begin;
     loop.peer_id = peer_id;
-    loop.peers = &peers;
+    loop.peers = nullptr;
     loop.rows = rows;
     loop.cols = cols;
+    loop.rows.warp_begin = nullptr;
+    loop.cols.warp_begin = nullptr;
 
     const unsigned char * smem_end = smem_raw + sa.smem_bytes;
     auto in_shared = [&](const void * ptr) {
@@ -1344,22 +1370,149 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
                             in_shared(pull_begin) && in_shared(peer_id) && in_shared(rows.chunks) && in_shared(cols.chunks) && rows.n_resident == rows.n_chunks &&
                             cols.n_resident == cols.n_chunks;
 
+    const uint32_t image_bytes = static_cast<uint32_t>(arena.smem - smem_raw);
+
 #ifdef RPVG_B200_EM_TRACE
     if (tid == 0 && (rank == 0 || rank == S - 1)) {
         uint32_t widest_row = 0, widest_col = 0;
         for (uint32_t k = 0; k < n_row_chunks; ++k) { widest_row = max(widest_row, row_chunks[k].width); }
         for (uint32_t k = 0; k < n_col_chunks; ++k) { widest_col = max(widest_col, col_chunks[k].width); }
-        printf("[layout] rank %u/%u m %u z %u cols present %u pulls %u | rows: chunks %u slots %u widest %u resident %u | cols: chunks %u slots %u widest %u resident %u | depth %u all shared %d\n", rank,
-               S, m, z_slice, n_cols_present, total_pulls, n_row_chunks, row_slots, widest_row, rows.n_resident, n_col_chunks, col_slots, widest_col, cols.n_resident, depth, all_shared ? 1 : 0);
+        printf("[layout] rank %u/%u m %u z %u cols present %u pulls %u | rows: chunks %u slots %u widest %u resident %u | cols: chunks %u slots %u widest %u resident %u | depth %u all shared %d image %u\n",
+               rank, S, m, z_slice, n_cols_present, total_pulls, n_row_chunks, row_slots, widest_row, rows.n_resident, n_col_chunks, col_slots, widest_col, cols.n_resident, depth, all_shared ? 1 : 0,
+               image_bytes);
     }
 #endif
+
+    {
+        const uint4 * src = reinterpret_cast<const uint4 *>(smem_raw);
+        uint4 * dst = reinterpret_cast<uint4 *>(reinterpret_cast<unsigned char *>(header) + kSellHeaderBytes);
+        for (uint32_t i = tid; i < (image_bytes + 15) / 16; i += THREADS) { dst[i] = src[i]; }
+    }
+
+    if (tid < 33) {
+        header->row_warp_begin[tid] = tid <= sa.run_warps ? row_warp_begin[tid] : 0;
+        header->col_warp_begin[tid] = tid <= sa.run_warps ? col_warp_begin[tid] : 0;
+    }
+    if (MULTI && tid < kMaxGroupSize) { header->present[tid] = tid < S ? peers.present[tid] : 0; }
+
+    if (tid == 0) {
+        header->all_shared = all_shared ? 1 : 0;
+        header->image_bytes = image_bytes;
+        header->n_cols_present = n_cols_present;
+        header->smem_base = reinterpret_cast<uint64_t>(smem_raw);
+        header->total = total;
+        header->col_src = col_src;
+        header->loop = loop;
+        header->state = 1;
+    }
+}
+
+template <int THREADS>
+constexpr int sellRunMinBlocks() { return THREADS >= 1024 ? 1 : 1024 / THREADS; }   // 64 registers per thread
+
+// Run kernel: takes the slice the build kernel left (same grid, same thread-block clusters), loads it into shared memory
+// and iterates. Its register budget is half the build kernel's, so an SM holds 32 warps of it.
+template <int THREADS, bool MULTI, typename IndexT>
+__global__ void __launch_bounds__(THREADS, sellRunMinBlocks<THREADS>()) emSellRunKernel(const SellArgs sa) {
+
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+
+    __shared__ double red[32];
+    __shared__ double final_part[kMaxGroupSize];
+    __shared__ SellPeers peers;
+    __shared__ uint32_t row_warp_begin[33];
+    __shared__ uint32_t col_warp_begin[33];
+
+    const EmArgs & args = sa.em;
+
+    cg::cluster_group cluster = cg::this_cluster();
+    const uint32_t S = MULTI ? cluster.num_blocks() : 1;
+    const uint32_t rank = MULTI ? cluster.block_rank() : 0;
+
+    const uint32_t tid = threadIdx.x;
+
+    if (*args.error) { return; }   // malformed arena or a slice without room (uniform over the whole grid)
+
+#ifdef RPVG_B200_EM_TIMELINE
+    unsigned long long timeline_t0, timeline_t1;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(timeline_t0));
+#endif
+
+    const uint32_t group = blockIdx.x / S;
+    const uint32_t c = sa.group_cluster[group];
+
+    const uint64_t p0 = args.path_offset[c];
+    const uint32_t N = static_cast<uint32_t>(args.path_offset[c + 1] - p0);
+
+    unsigned char * cta_scratch = sa.scratch + sa.group_scratch[group] + static_cast<uint64_t>(rank) * sa.group_cta_bytes[group];
+    const SellHeader<IndexT> * header = reinterpret_cast<const SellHeader<IndexT> *>(cta_scratch + sa.group_cta_bytes[group] - sellHandoverBytes(sa.smem_bytes));
+
+    if (header->state == 0) { return; }   // uniform over the group
+
+    // ---- the slice: image into shared memory, loop arguments with their pointers moved along
+    {
+        const uint4 * src = reinterpret_cast<const uint4 *>(reinterpret_cast<const unsigned char *>(header) + kSellHeaderBytes);
+        uint4 * dst = reinterpret_cast<uint4 *>(smem_raw);
+        const uint32_t n16 = (header->image_bytes + 15) / 16;
+        for (uint32_t i = tid; i < n16; i += THREADS) { dst[i] = src[i]; }
+    }
+
+    if (tid < 33) {
+        row_warp_begin[tid] = header->row_warp_begin[tid];
+        col_warp_begin[tid] = header->col_warp_begin[tid];
+    }
+    if (tid < kMaxGroupSize) { peers.present[tid] = header->present[tid]; }
+    if (tid < 32) { peers.vote[tid] = 0; }
+    if (tid == 0) { peers.stop = 0; }
+
+    SellLoop<IndexT> loop = header->loop;
+
+    const uint64_t old_base = header->smem_base;
+    const uint64_t image_bytes = header->image_bytes;
+
+    auto moved = [&](auto * ptr) {
+        using T = std::remove_pointer_t<decltype(ptr)>;
+        const uint64_t address = reinterpret_cast<uint64_t>(ptr);
+        if (ptr != nullptr && address >= old_base && address < old_base + image_bytes) { return reinterpret_cast<T *>(smem_raw + (address - old_base)); }
+        return ptr;
+    };
+
+    loop.a = moved(loop.a);
+    loop.a_prev = moved(loop.a_prev);
+    loop.g = moved(loop.g);
+    loop.w = moved(loop.w);
+    loop.noise = moved(loop.noise);
+    loop.cnt = moved(loop.cnt);
+    loop.col_id = moved(loop.col_id);
+    loop.holders = moved(loop.holders);
+    loop.pull_begin = moved(loop.pull_begin);
+    loop.peer_id = moved(loop.peer_id);
+    loop.peers = &peers;
+    loop.rows.chunks = moved(loop.rows.chunks);
+    loop.rows.val_s = moved(loop.rows.val_s);
+    loop.rows.idx_s = moved(loop.rows.idx_s);
+    loop.rows.warp_begin = row_warp_begin;
+    loop.cols.chunks = moved(loop.cols.chunks);
+    loop.cols.val_s = moved(loop.cols.val_s);
+    loop.cols.idx_s = moved(loop.cols.idx_s);
+    loop.cols.warp_begin = col_warp_begin;
+
+    const double total = header->total;
+    const uint32_t n_cols_present = header->n_cols_present;
+    const uint32_t * col_src = header->col_src;
+    const bool all_shared = header->all_shared != 0;
+
+    // every CTA of the group is running and has its slice before anyone touches a peer's shared memory
+    if (MULTI) { cluster.sync(); } else { __syncthreads(); }
 
 #ifdef RPVG_B200_EM_TIMELINE
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(timeline_t1));
 #endif
 
+    // ---- EM iterations. When everything this CTA touches sits in shared memory the loop runs on pointers the compiler
+    // can prove to be shared (plain LDS/STS); otherwise on generic pointers (hybrid residency).
     uint32_t it;
-    const double * final_a = a;
+    const double * final_a = loop.a;
 
     if (all_shared) {
 
@@ -1404,6 +1557,7 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
     }
 
     const double min_abundance = args.params.min_em_abundance;
+    const uint16_t * holders = loop.holders;
 
     // rpvg:src/path_abundance_estimator.cpp:100-113. In a group every column is written by the first CTA that holds it
     // (all holders have the same value).
@@ -1468,7 +1622,7 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 512 ? RPVG_B200_EM_MIN_CT
         const unsigned int slot = atomicAdd(&rpvg_timeline_count, 1u);
         if (slot < 65536) {
             unsigned long long * rec = rpvg_timeline_records + 12ull * slot;
-            rec[0] = THREADS; rec[1] = S; rec[2] = rank; rec[3] = c; rec[4] = smid; rec[5] = M; rec[6] = N;
+            rec[0] = THREADS; rec[1] = S; rec[2] = rank; rec[3] = c; rec[4] = smid; rec[5] = n_cols_present; rec[6] = N;
             rec[7] = timeline_t0; rec[8] = timeline_t1; rec[9] = timeline_t2; rec[10] = it; rec[11] = all_shared ? 1u : 0u;
         }
     }
