@@ -327,7 +327,8 @@ def main():
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "hbm", "kernel": "emSellKernel (all bins, concurrent streams)", "achieved": achieved, "peak": peak, "unit": "GB/s",
                              "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
-                             "limiter": "shared-memory pipe and cluster barriers (69% of the shared pipe on one SM, profiles/r01b_ncu_launches_summary.md)",
+                             "limiter": "shared-memory data pipe: 76% busy over a whole single-cluster launch (ncu, profiles/r01c_ncu_single_cluster_metrics.txt); the rest is barriers",
+                             "shared_pipe_busy_frac": 0.76,
                              "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": em_ms_mean, "build_ms": float(np.mean(build_ms)),
                              "kernel_share_of_step": em_ms_mean / (max_ms / args.steps)},
                 "inference_stage_wall_ms": max_e2e_ms / args.steps,

@@ -65,6 +65,10 @@ constexpr uint32_t kSellBuckets = 64;
 #define RPVG_B200_SELL_WAYS 1
 #endif
 
+#ifndef RPVG_B200_SELL_SPREAD_MIN_THREADS
+#define RPVG_B200_SELL_SPREAD_MIN_THREADS 256   // CTAs from this size on reorder their entries against bank conflicts
+#endif
+
 #ifndef RPVG_B200_SELL_ROUNDS
 #define RPVG_B200_SELL_ROUNDS 1   // depth divisor (see sellDepth): 1 = about two chunks per warp and phase
 #endif
@@ -1325,6 +1329,70 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 128 ? 6 : (THREADS == 64 
          [&](uint64_t k) { return args.csc_val[k]; },
          [&](uint64_t k) { return row_pos[args.csc_row[k] - i0]; },
          col_src);
+
+    // ---- spread the gathers over the banks. The EM phases are bound by the shared-memory pipe and nearly half of its
+    // wavefronts are the fp64 gathers a[col] / w[row]: the 16 lanes of a half-warp read 16 eight-byte words, and words
+    // whose index agrees mod 16 collide (4.2 wavefronts per gather in the E-step, 5.5 in the M-step as laid out; 2 is the
+    // floor). The order of a lane's entries is free, so each lane permutes its own: step by step the lanes of a half-warp
+    // pick, one after the other, an entry of theirs whose bank is still free (tools/bank_sim2.py: ~3.6 both ways).
+    // Only for the larger CTAs: it costs a few thousand instructions per chunk.
+    if (THREADS >= RPVG_B200_SELL_SPREAD_MIN_THREADS) {
+
+        __syncwarp();
+
+        auto spread = [&](const SellSide<IndexT> & side) {
+
+            for (uint32_t k = warp; k < side.n_chunks; k += num_warps) {
+
+                const SellChunk ch = side.chunks[k];
+                if (ch.width < 2) { continue; }
+
+                const bool res = ch.off < side.resident_slots;
+                double * val = const_cast<double *>(res ? side.val_s + ch.off : side.val_g + (ch.off - side.resident_slots)) + lane;
+                IndexT * idx = const_cast<IndexT *>(res ? side.idx_s + ch.off : side.idx_g + (ch.off - side.resident_slots)) + lane;
+
+                const uint32_t half_base = lane & 16;
+
+                for (uint32_t t = 0; t + 1 < ch.width; ++t) {
+
+                    uint32_t taken = 0;
+                    uint32_t pick = t;
+
+                    for (uint32_t i = 0; i < 16; ++i) {
+
+                        uint32_t bank_bit = 0;
+
+                        if ((lane & 15) == i) {
+
+                            uint32_t s_found = t;
+                            for (uint32_t q = t; q < ch.width; ++q) {
+                                if (((taken >> (static_cast<uint32_t>(idx[q * kSellSlots]) & 15)) & 1u) == 0) {
+                                    s_found = q;
+                                    break;
+                                }
+                            }
+                            pick = s_found;
+                            bank_bit = 1u << (static_cast<uint32_t>(idx[pick * kSellSlots]) & 15);
+                        }
+
+                        taken |= __shfl_sync(0xffffffffu, bank_bit, half_base + i);
+                    }
+
+                    if (pick != t) {
+                        const double v = val[t * kSellSlots];
+                        const IndexT x = idx[t * kSellSlots];
+                        val[t * kSellSlots] = val[pick * kSellSlots];
+                        idx[t * kSellSlots] = idx[pick * kSellSlots];
+                        val[pick * kSellSlots] = v;
+                        idx[pick * kSellSlots] = x;
+                    }
+                }
+            }
+        };
+
+        spread(rows);
+        spread(cols);
+    }
 
     // rpvg:src/path_abundance_estimator.cpp:54 — single-precision quotient widened to double
     const double a_init = static_cast<double>(1 / static_cast<float>(N + 1));

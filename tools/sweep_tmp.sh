@@ -1,6 +1,6 @@
 run() {
-  echo "== lanes $1 streams '$2' lane_min_group $3"
-  RPVG_B200_EM_LANES=$1 RPVG_B200_EM_STREAMS="$2" RPVG_B200_EM_LANE_MIN_GROUP=$3 timeout 300 python bench.py --steps 3 --warmup 2 --no-cpu-baseline 2>&1 | python -c "
+  echo "== lib $1"
+  RPVG_B200_LIB=$PWD/$1 timeout 300 python bench.py --steps 3 --warmup 2 --no-cpu-baseline 2>&1 | python -c "
 import sys,json
 for l in sys.stdin:
     if l.startswith('{'):
@@ -8,10 +8,8 @@ for l in sys.stdin:
     elif 'rror' in l or 'capacity' in l: print(l.strip()[:300])
 " | head -20
 }
-RPVG_B200_DEBUG=1 python bench.py --steps 1 --warmup 1 --no-cpu-baseline 2>&1 | grep "em bin" | head -8
-run 7 "" 16
-run 5 "" 16
-run 4 "" 16
-run 7 "0 0 2 4 6 8 9 10" 16
-run 7 "" 8
-run 8 "" 8
+timeout 600 python -m pytest tests/test_em_gpu.py -x -q 2>&1 | tail -5
+run tools/bin/librpvg_b200_prev.so
+run rpvg_b200/librpvg_b200.so
+run tools/bin/librpvg_b200_prev.so
+run rpvg_b200/librpvg_b200.so
