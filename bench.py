@@ -310,10 +310,10 @@ def main():
         em_ms_mean = float(np.mean(em_ms))
         achieved = alg_bytes / (em_ms_mean * 1e-3) / 1e9
         # DRAM bytes the EM launches of one step really move (ncu, same workload): the slices live in shared memory, so
-        # this is a small fraction of the algorithmic bytes the HBM roofline is quoted on (profiles/r01b_*).
+        # this is a small fraction of the algorithmic bytes the HBM roofline is quoted on (profiles/r01d_*).
         traffic, traffic_src = None, None
         try:
-            with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01b_em_traffic.json")) as fh:
+            with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01d_em_traffic.json")) as fh:
                 measured = json.load(fh)
             if world == 1:
                 traffic, traffic_src = measured["em_dram_bytes_per_step"], measured["source"]

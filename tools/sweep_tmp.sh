@@ -1,6 +1,6 @@
 run() {
-  echo "== lib $1"
-  RPVG_B200_LIB=$PWD/$1 timeout 300 python bench.py --steps 3 --warmup 2 --no-cpu-baseline 2>&1 | python -c "
+  echo "== big_group $1 big_slice $2 slice $3"
+  RPVG_B200_EM_BIG_GROUP=$1 RPVG_B200_EM_BIG_SLICE_WEIGHT=$2 RPVG_B200_EM_SLICE_WEIGHT=$3 timeout 300 python bench.py --steps 3 --warmup 2 --no-cpu-baseline 2>&1 | python -c "
 import sys,json
 for l in sys.stdin:
     if l.startswith('{'):
@@ -8,8 +8,9 @@ for l in sys.stdin:
     elif 'rror' in l or 'capacity' in l: print(l.strip()[:300])
 " | head -20
 }
-timeout 600 python -m pytest tests/test_em_gpu.py -x -q 2>&1 | tail -5
-run tools/bin/librpvg_b200_prev.so
-run rpvg_b200/librpvg_b200.so
-run tools/bin/librpvg_b200_prev.so
-run rpvg_b200/librpvg_b200.so
+run 32 12000 12000
+run 8 6000 12000
+run 8 7000 12000
+run 4 6000 12000
+run 8 6000 14000
+run 8 5000 12000
