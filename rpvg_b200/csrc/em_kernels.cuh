@@ -1,6 +1,6 @@
 // EM kernels (sm_100a). See em.cu for the data layout and the reference semantics they restate.
 //
-// emSellKernel (em_sell.cuh): the EM kernel proper.
+// emSellBuildKernel / emSellRunKernel (em_sell.cuh): the EM kernels proper.
 // emClusterKernel (here): fallback, one CTA per path cluster with every array in global memory (any N).
 #pragma once
 

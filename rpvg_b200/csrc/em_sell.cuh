@@ -1,11 +1,12 @@
-// emSellKernel — the EM kernel proper (sm_100a).
+// emSellBuildKernel + emSellRunKernel — the EM kernels proper (sm_100a).
 //
 // One thread-block cluster of S CTAs (S = 1, 2, 4, 8, 16) per path cluster; read classes (rows) are split into S
-// slices of equal weight. In its prologue every CTA re-lays its slice out as two sliced-ELL structures, one per
-// orientation, built so that the inner loops of both EM steps are the same branch-free, bank-conflict-free loop:
+// slices of equal weight. The build kernel re-lays every CTA's slice out as two sliced-ELL structures, one per
+// orientation, built so that the inner loops of both EM steps are the same branch-free loop; the run kernel (same
+// grid, same clusters, half the registers) iterates on them:
 //
-//   chunk = kSellSlots = 32 * kSellWays slots per step; a lane works on slots lane, lane + 32, ... (kSellWays
-//   independent dependency chains per lane, which is what hides the shared-memory latency). A row (column) of the
+//   chunk = kSellSlots = 32 * kSellWays slots per step; a lane works on slots lane, lane + 32, ... (kSellWays = 1:
+//   wider chunks were measured slower, the phases are bound by the shared-memory pipe). A row (column) of the
 //   chunk owns L = 1..32 adjacent slots (L chosen from its length so a chunk is ~8 steps deep); entry t of that row
 //   sits at [chunk_off + (t / L) * kSellSlots + first_slot + (t % L)].
 //   Rows (columns) are ordered by length (stable bucket sort) so rows sharing a chunk have near-equal length; padding
