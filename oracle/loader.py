@@ -273,6 +273,22 @@ def harness_estimate_batch(lib_, config: HarnessConfig, arena, cluster_ids=None,
         lib_.harness_estimator_destroy(est)
 
 
+def harness_estimate_batched(lib_, config: HarnessConfig, arena, cluster_ids=None, rng_seed: int = 1):
+    """rpvg_b200 harness only: the same clusters, order and generators through the classes' estimateBatch (one call)."""
+    ids = list(range(arena.n_clusters)) if cluster_ids is None else list(cluster_ids)
+    datas = [HarnessClusterData(arena, c) for c in ids]
+    structs = (HarnessCluster * len(ids))(*[d.struct for d in datas])
+    handles = (C.c_void_p * len(ids))()
+    lib_.harness_estimate_batched.restype = C.c_double
+    lib_.harness_estimate_batched.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(HarnessCluster), C.c_uint32, C.POINTER(C.c_void_p)]
+    est = lib_.harness_estimator_create(C.byref(config))
+    try:
+        seconds = lib_.harness_estimate_batched(est, len(ids), structs, rng_seed, handles)
+        return seconds, [result_to_dict(lib_, handles[i]) for i in range(len(ids))]
+    finally:
+        lib_.harness_estimator_destroy(est)
+
+
 # ---- convenience wrappers over the port ---------------------------------------------------------------------------------
 
 def port_em_abundances(arena, max_em_its=10000, max_rel_em_conv=0.001, min_em_conv_its=10, min_em_abundance=1e-8, num_threads=0):

@@ -1,0 +1,483 @@
+// Batched drivers: the cluster loop of rpvg:src/main.cpp:829-977 re-stated as "flatten all clusters, a few device calls
+// for the whole batch, scatter the results" (SURVEY.md §8(f) rank 1). Per cluster the device calls of estimate() cost a
+// few hundred microseconds of launches, copies and synchronisation whatever the cluster's size; clusters of a real run
+// are mostly small, so the per-cluster drop-in is launch-bound (tools/nested_bench.py). The batch entry points give the
+// same results cluster by cluster: they run the same staged host code around the same C ABI calls, which take many
+// clusters as easily as one.
+
+#include "estimators.hpp"
+
+#include <algorithm>
+#include <cassert>
+#include <chrono>
+#include <cstdlib>
+#include <iostream>
+#include <numeric>
+
+#include "rpvg_b200.h"
+
+namespace {
+
+[[noreturn]] void fatalBatch(rpvg_b200_ctx * ctx, const char * what) {
+
+    cerr << "ERROR: rpvg_b200 " << what << ": " << rpvg_b200_last_error(ctx) << endl;
+    abort();
+}
+
+// Many clusters as one arena (include/rpvg_b200.h): every pair<double, vector<uint32_t>> expanded, entries of a read
+// class sorted by path — the flattening estimate() does for one cluster.
+struct BatchArena {
+
+    vector<uint64_t> read_offset = {0}, path_offset = {0}, row_ptr = {0};
+    vector<uint32_t> col, count;
+    vector<double> prob, noise;
+
+    void add(const vector<ReadPathProbabilities> & cluster_probs, const uint32_t num_paths) {
+
+        vector<pair<uint32_t, double> > row;
+
+        for (auto & read_probs: cluster_probs) {
+
+            row.clear();
+            for (auto & path_probs: read_probs.pathProbs()) {
+                for (auto & path: path_probs.second) { row.emplace_back(path, path_probs.first); }
+            }
+            sort(row.begin(), row.end());
+
+            for (auto & entry: row) {
+                col.push_back(entry.first);
+                prob.push_back(entry.second);
+            }
+
+            row_ptr.push_back(col.size());
+            noise.push_back(read_probs.noiseProb());
+            count.push_back(read_probs.readCount());
+        }
+
+        read_offset.push_back(noise.size());
+        path_offset.push_back(path_offset.back() + num_paths);
+    }
+
+    // all clusters at once, the clusters filled in parallel
+    void build(const vector<const vector<ReadPathProbabilities> *> & members, const vector<uint32_t> & num_paths) {
+
+        const size_t n = members.size();
+        vector<uint64_t> entries(n, 0);
+
+        #pragma omp parallel for schedule(dynamic, 8)
+        for (size_t k = 0; k < n; ++k) {
+            uint64_t e = 0;
+            for (auto & read_probs: *members[k]) {
+                for (auto & path_probs: read_probs.pathProbs()) { e += path_probs.second.size(); }
+            }
+            entries[k] = e;
+        }
+
+        read_offset.assign(1, 0);
+        path_offset.assign(1, 0);
+        vector<uint64_t> entry_offset = {0};
+
+        for (size_t k = 0; k < n; ++k) {
+            read_offset.push_back(read_offset.back() + members[k]->size());
+            path_offset.push_back(path_offset.back() + num_paths[k]);
+            entry_offset.push_back(entry_offset.back() + entries[k]);
+        }
+
+        row_ptr.assign(read_offset.back() + 1, 0);
+        col.resize(entry_offset.back());
+        prob.resize(entry_offset.back());
+        noise.resize(read_offset.back());
+        count.resize(read_offset.back());
+
+        #pragma omp parallel for schedule(dynamic, 8)
+        for (size_t k = 0; k < n; ++k) {
+
+            vector<pair<uint32_t, double> > row;
+            uint64_t e = entry_offset[k];
+            uint64_t r = read_offset[k];
+
+            for (auto & read_probs: *members[k]) {
+
+                row.clear();
+                for (auto & path_probs: read_probs.pathProbs()) {
+                    for (auto & path: path_probs.second) { row.emplace_back(path, path_probs.first); }
+                }
+                sort(row.begin(), row.end());
+
+                for (auto & entry: row) {
+                    col[e] = entry.first;
+                    prob[e] = entry.second;
+                    ++e;
+                }
+
+                row_ptr[r + 1] = e;
+                noise[r] = read_probs.noiseProb();
+                count[r] = read_probs.readCount();
+                ++r;
+            }
+        }
+    }
+
+    uint32_t size() const { return static_cast<uint32_t>(read_offset.size() - 1); }
+
+    rpvg_b200_clusters view() const {
+        return rpvg_b200_clusters{size(), read_offset.data(), path_offset.data(), row_ptr.data(), col.data(), prob.data(), noise.data(), count.data()};
+    }
+};
+
+}
+
+void PathEstimator::estimateBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const vector<mt19937 *> & rngs) {
+
+    assert(estimates.size() == cluster_probs.size());
+    assert(estimates.size() == rngs.size());
+
+    for (size_t i = 0; i < estimates.size(); ++i) { estimate(estimates[i], *cluster_probs[i], rngs[i]); }
+}
+
+// transcripts model: EM (and Gibbs read counts) of all clusters in one device batch
+void PathAbundanceEstimator::estimateBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const vector<mt19937 *> & rngs) {
+
+    assert(estimates.size() == cluster_probs.size());
+    assert(estimates.size() == rngs.size());
+
+    BatchArena arena;
+    vector<size_t> members;   // clusters with read classes, in order
+
+    for (size_t i = 0; i < estimates.size(); ++i) {
+
+        estimates[i]->resetEstimates(estimates[i]->paths.size(), 1);
+
+        if (!cluster_probs[i]->empty()) { members.push_back(i); }
+    }
+
+    if (members.empty()) { return; }
+
+    {
+        vector<const vector<ReadPathProbabilities> *> member_probs;
+        vector<uint32_t> member_paths;
+        for (auto i: members) {
+            member_probs.push_back(cluster_probs[i]);
+            member_paths.push_back(estimates[i]->paths.size());
+        }
+        arena.build(member_probs, member_paths);
+    }
+
+    rpvg_b200_em_params params;
+    rpvg_b200_em_params_default(&params);
+    params.max_em_its = max_em_its;
+    params.max_rel_em_conv = max_rel_em_conv;
+
+    // the sampler's keys come from each cluster's own generator, as in estimate()
+    vector<uint32_t> gibbs_counts(members.size(), num_gibbs_samples);
+    vector<uint64_t> gibbs_seeds(members.size(), 0);
+    size_t total_values = 0;
+
+    if (num_gibbs_samples > 0) {
+        for (size_t k = 0; k < members.size(); ++k) {
+            mt19937 * mt_rng = rngs[members[k]];
+            gibbs_seeds[k] = (static_cast<uint64_t>((*mt_rng)()) << 32) | (*mt_rng)();
+            total_values += static_cast<size_t>(num_gibbs_samples) * estimates[members[k]]->paths.size();
+        }
+    }
+
+    vector<double> abundances(arena.path_offset.back());
+    vector<double> noise_counts(members.size()), total_counts(members.size());
+    vector<double> gibbs_abundances(total_values), gibbs_noise(static_cast<size_t>(num_gibbs_samples) * members.size());
+
+    rpvg_b200_gibbs gibbs = {gibbs_counts.data(), gibbs_thin_its, gibbs_seeds.data(), gibbs_abundances.data(), gibbs_noise.data()};
+    rpvg_b200_clusters clusters = arena.view();
+
+    auto * ctx = threadContext();
+
+    if (rpvg_b200_em_abundances_gibbs(ctx, &clusters, &params, num_gibbs_samples > 0 ? &gibbs : nullptr, abundances.data(), noise_counts.data(), total_counts.data(),
+                                      nullptr) != RPVG_B200_OK) {
+        fatalBatch(ctx, "rpvg_b200_em_abundances");
+    }
+
+    size_t value_pos = 0;
+
+    for (size_t k = 0; k < members.size(); ++k) {
+
+        PathClusterEstimates * est = estimates[members[k]];
+        const size_t num_paths = est->paths.size();
+        const size_t p0 = arena.path_offset[k];
+
+        copy(abundances.begin() + p0, abundances.begin() + p0 + num_paths, est->abundances.begin());
+        est->noise_count = noise_counts[k];
+        est->total_count = total_counts[k];
+
+        if (num_gibbs_samples > 0) {
+
+            CountSamples samples;
+            samples.path_ids.resize(num_paths);
+            iota(samples.path_ids.begin(), samples.path_ids.end(), 0);
+            samples.noise_samples.assign(gibbs_noise.begin() + k * num_gibbs_samples, gibbs_noise.begin() + (k + 1) * num_gibbs_samples);
+            samples.abundance_samples.assign(gibbs_abundances.begin() + value_pos, gibbs_abundances.begin() + value_pos + static_cast<size_t>(num_gibbs_samples) * num_paths);
+            value_pos += static_cast<size_t>(num_gibbs_samples) * num_paths;
+
+            est->gibbs_read_count_samples.emplace_back(std::move(samples));
+        }
+    }
+}
+
+// haplotype-transcripts model, collapsed mode: the stages of inferAbundancesCollapsedGroups (nested.cpp) for all clusters
+// at once, each device request of a stage put into one call
+void NestedPathAbundanceEstimator::estimateBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const vector<mt19937 *> & rngs) {
+
+    assert(estimates.size() == cluster_probs.size());
+    assert(estimates.size() == rngs.size());
+
+    if (!infer_collapsed || use_group_post_gibbs) {   // host-side sampling between the device calls of a cluster: looped
+        PathEstimator::estimateBatch(estimates, cluster_probs, rngs);
+        return;
+    }
+
+    struct Item {
+        size_t index;
+        pair<vector<vector<uint32_t> >, vector<uint32_t> > source_groups;
+        PathClusterEstimates group_estimates;
+        GroupPosteriorPlan plan;
+        vector<SubsetJob> jobs;
+    };
+
+    const bool trace = getenv("RPVG_B200_BATCH_TRACE") != nullptr;
+    auto clock_now = chrono::steady_clock::now();
+    auto lap = [&](const char * what) {
+        if (!trace) { return; }
+        const auto now = chrono::steady_clock::now();
+        cerr << "[rpvg_b200 batch] " << what << ": " << chrono::duration<double, milli>(now - clock_now).count() << " ms" << endl;
+        clock_now = now;
+    };
+
+    // ---- stage A: flatten, haplotype groups
+    BatchArena arena;
+    vector<Item> items;
+
+    for (size_t i = 0; i < estimates.size(); ++i) {
+
+        estimates[i]->resetEstimates(0, 0);
+        if (cluster_probs[i]->empty()) { continue; }
+
+        items.emplace_back();
+        items.back().index = i;
+    }
+
+    if (items.empty()) { return; }
+
+    {
+        vector<const vector<ReadPathProbabilities> *> members;
+        vector<uint32_t> member_paths;
+        for (auto & item: items) {
+            members.push_back(cluster_probs[item.index]);
+            member_paths.push_back(estimates[item.index]->paths.size());
+        }
+        arena.build(members, member_paths);
+    }
+
+    // (the host stages are independent per cluster: all cores, like the reference's loop; the device calls are made by
+    // this thread)
+    #pragma omp parallel for schedule(dynamic, 8)
+    for (size_t k = 0; k < items.size(); ++k) { items[k].source_groups = findPathSourceGroups(estimates[items[k].index]->paths); }
+
+    auto * ctx = threadContext();
+    rpvg_b200_clusters clusters = arena.view();
+
+    lap("A flatten + haplotype groups");
+
+    // ---- stage B: grouped + normalised + collapsed matrix of every cluster, then packed: cluster k's matrix
+    // (rows_k x groups_k, column-major) at c_matrix_offset[k], its noise and counts at c_row_offset[k]
+    vector<uint64_t> c_row_offset = {0}, c_path_offset = {0}, c_matrix_offset = {0};
+    vector<double> c_matrix, c_noise, c_counts;
+    {
+        vector<uint64_t> group_offset = {0}, group_path_ptr = {0};
+        vector<uint32_t> group_paths;
+        vector<uint64_t> block_start = {0};
+
+        for (size_t k = 0; k < items.size(); ++k) {
+
+            for (auto & group: items[k].source_groups.first) {
+                group_paths.insert(group_paths.end(), group.begin(), group.end());
+                group_path_ptr.push_back(group_paths.size());
+            }
+
+            group_offset.push_back(group_path_ptr.size() - 1);
+            block_start.push_back(block_start.back() + (arena.read_offset[k + 1] - arena.read_offset[k]) * items[k].source_groups.first.size());
+        }
+
+        rpvg_b200_path_groups groups = {group_offset.data(), group_path_ptr.data(), group_paths.data()};
+
+        vector<uint32_t> n_classes(items.size(), 0);
+        vector<double> matrix(block_start.back()), noise(arena.noise.size()), counts(arena.noise.size());
+
+        if (rpvg_b200_grouped_collapse(ctx, &clusters, &groups, prob_precision, n_classes.data(), matrix.data(), noise.data(), counts.data()) != RPVG_B200_OK) {
+            fatalBatch(ctx, "rpvg_b200_grouped_collapse");
+        }
+
+        for (size_t k = 0; k < items.size(); ++k) {
+            const size_t num_groups = items[k].source_groups.first.size();
+            assert(n_classes[k] > 0);
+            c_row_offset.push_back(c_row_offset.back() + n_classes[k]);
+            c_path_offset.push_back(c_path_offset.back() + num_groups);
+            c_matrix_offset.push_back(c_matrix_offset.back() + static_cast<uint64_t>(n_classes[k]) * num_groups);
+        }
+
+        c_matrix.resize(c_matrix_offset.back());
+        c_noise.resize(c_row_offset.back());
+        c_counts.resize(c_row_offset.back());
+
+        #pragma omp parallel for schedule(dynamic, 8)
+        for (size_t k = 0; k < items.size(); ++k) {
+
+            const size_t rows = n_classes[k];
+            const size_t num_groups = items[k].source_groups.first.size();
+            const size_t r0 = arena.read_offset[k];
+
+            copy(matrix.begin() + block_start[k], matrix.begin() + block_start[k] + rows * num_groups, c_matrix.begin() + c_matrix_offset[k]);
+            copy(noise.begin() + r0, noise.begin() + r0 + rows, c_noise.begin() + c_row_offset[k]);
+            copy(counts.begin() + r0, counts.begin() + r0 + rows, c_counts.begin() + c_row_offset[k]);
+
+            planPathGroupPosteriors(&items[k].plan, &items[k].group_estimates, num_groups, items[k].source_groups.second, group_size, group_size == 2, min_hap_prob);
+        }
+    }
+
+    lap("B grouped collapse");
+
+    // ---- stage C: posteriors of the haplotype combinations; every round is one log-likelihood call for all clusters
+    // that still have a request (Full: one round; Bounded: marginals, then the pairs)
+    {
+        vector<size_t> active(items.size());
+        iota(active.begin(), active.end(), 0);
+
+        while (!active.empty()) {
+
+            const uint32_t set_size = items[active.front()].plan.set_size;
+
+            // all clusters run the same kind of plan, so they have a request in the same rounds: the packed matrices serve
+            // every round as they are; a cluster without a request would just bring no sets
+            assert(active.size() == items.size());
+
+            vector<uint64_t> set_offset = {0};
+            vector<uint32_t> sets;
+
+            for (auto k: active) {
+
+                auto & item = items[k];
+                assert(item.plan.set_size == set_size);
+
+                sets.insert(sets.end(), item.plan.flat_sets.begin(), item.plan.flat_sets.end());
+                set_offset.push_back(sets.size() / set_size);
+            }
+
+            rpvg_b200_loglik_problems problems;
+            problems.n_problems = static_cast<uint32_t>(items.size());
+            problems.row_offset = c_row_offset.data();
+            problems.path_offset = c_path_offset.data();
+            problems.matrix_offset = c_matrix_offset.data();
+            problems.set_offset = set_offset.data();
+            problems.matrix = c_matrix.data();
+            problems.noise = c_noise.data();
+            problems.counts = c_counts.data();
+            problems.group_size = set_size;
+            problems.sets = sets.data();
+
+            lap("C   concatenate");
+
+            vector<double> loglik(set_offset.back(), 0);
+            if (!loglik.empty() && rpvg_b200_group_loglik(ctx, &problems, loglik.data()) != RPVG_B200_OK) { fatalBatch(ctx, "rpvg_b200_group_loglik"); }
+
+            if (trace) { cerr << "[rpvg_b200 batch]     " << set_offset.back() << " sets of " << set_size << ", " << c_noise.size() << " rows, " << c_matrix.size() << " matrix entries" << endl; }
+            lap("C   device log-likelihoods");
+
+            vector<char> more(active.size(), 0);
+
+            #pragma omp parallel for schedule(dynamic, 8)
+            for (size_t a = 0; a < active.size(); ++a) {
+                auto & item = items[active[a]];
+                more[a] = advancePathGroupPosteriors(&item.plan, &item.group_estimates, loglik.data() + set_offset[a]) ? 1 : 0;
+            }
+
+            lap("C   advance");
+
+            vector<size_t> next;
+            for (size_t a = 0; a < active.size(); ++a) {
+                if (more[a]) { next.push_back(active[a]); }
+            }
+
+            active.swap(next);
+        }
+    }
+
+    lap("C posteriors");
+
+    // ---- stage D: the path subsets of every cluster (host; each cluster draws from its own generator, in the order
+    // estimate() would)
+    vector<uint32_t> subset_cluster, subset_paths, gibbs_counts;
+    vector<uint64_t> subset_offset = {0}, gibbs_seeds;
+    vector<size_t> first_subset = {0}, first_path = {0}, first_sample = {0}, first_value = {0};
+
+    #pragma omp parallel for schedule(dynamic, 8)
+    for (size_t k = 0; k < items.size(); ++k) {
+
+        auto & item = items[k];
+
+        const SubsetSamples path_subset_samples = collapsedSubsetSamples(item.group_estimates, item.source_groups.first);
+        item.jobs = planPathSubsets(estimates[item.index], *cluster_probs[item.index], rngs[item.index], path_subset_samples);
+    }
+
+    for (size_t k = 0; k < items.size(); ++k) {
+
+        auto & item = items[k];
+
+        size_t samples = first_sample.back(), values = first_value.back();
+
+        for (auto & job: item.jobs) {
+            subset_cluster.push_back(static_cast<uint32_t>(k));
+            subset_paths.insert(subset_paths.end(), job.collapsed.begin(), job.collapsed.end());
+            subset_offset.push_back(subset_paths.size());
+            gibbs_counts.push_back(job.gibbs_samples);
+            gibbs_seeds.push_back(job.gibbs_seed);
+            samples += job.gibbs_samples;
+            values += static_cast<size_t>(job.gibbs_samples) * job.collapsed.size();
+        }
+
+        first_subset.push_back(subset_cluster.size());
+        first_path.push_back(subset_paths.size());
+        first_sample.push_back(samples);
+        first_value.push_back(values);
+    }
+
+    lap("D subsets");
+
+    // ---- stage E: all sub-EMs (and their Gibbs samples) of all clusters in one call
+    vector<double> abundances(subset_paths.size()), noise_counts(subset_cluster.size(), 0), total_counts(subset_cluster.size(), 0);
+    vector<double> gibbs_abundances(first_value.back()), gibbs_noise(first_sample.back());
+
+    if (!subset_cluster.empty()) {
+
+        rpvg_b200_subsets subsets = {static_cast<uint32_t>(subset_cluster.size()), subset_cluster.data(), subset_offset.data(), subset_paths.data()};
+
+        rpvg_b200_em_params params;
+        rpvg_b200_em_params_default(&params);
+        params.max_em_its = max_em_its;
+        params.max_rel_em_conv = max_rel_em_conv;
+
+        rpvg_b200_gibbs gibbs = {gibbs_counts.data(), gibbs_thin_its, gibbs_seeds.data(), gibbs_abundances.data(), gibbs_noise.data()};
+
+        if (rpvg_b200_subset_em_gibbs(ctx, &clusters, &subsets, &params, prob_precision, first_sample.back() > 0 ? &gibbs : nullptr, abundances.data(), noise_counts.data(),
+                                      total_counts.data(), nullptr, nullptr) != RPVG_B200_OK) {
+            fatalBatch(ctx, "rpvg_b200_subset_em");
+        }
+    }
+
+    lap("E sub-EMs");
+
+    // ---- stage F: weight, file under the transcripts' path tuples (host)
+    #pragma omp parallel for schedule(dynamic, 8)
+    for (size_t k = 0; k < items.size(); ++k) {
+        finishPathSubsets(estimates[items[k].index], items[k].jobs, abundances.data() + first_path[k], noise_counts.data() + first_subset[k],
+                          gibbs_abundances.data() + first_value[k], gibbs_noise.data() + first_sample[k]);
+    }
+
+    lap("F accumulate");
+}

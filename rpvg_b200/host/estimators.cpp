@@ -218,91 +218,106 @@ void PathEstimator::denseMatrix(vector<double> * matrix, vector<double> * noise,
     }
 }
 
-void PathEstimator::calculatePathGroupPosteriorsFull(PathClusterEstimates * path_cluster_estimates, const vector<double> & matrix, const vector<double> & noise, const vector<double> & counts, const uint32_t num_paths, const vector<uint32_t> & path_counts, const uint32_t group_size) const {
+void PathEstimator::planPathGroupPosteriors(GroupPosteriorPlan * plan, PathClusterEstimates * path_cluster_estimates, const uint32_t num_paths, const vector<uint32_t> & path_counts, const uint32_t group_size, const bool bounded, const double min_rel_likelihood) const {
 
-    assert(!noise.empty());
     assert(group_size > 0);
+    assert(!bounded || group_size == 2);
 
-    auto path_log_freqs = calcPathLogFrequences(path_counts);
+    plan->num_paths = num_paths;
+    plan->group_size = group_size;
+    plan->bounded = bounded;
+    plan->min_log_likelihood_diff = bounded ? log(min_rel_likelihood) : 0;
+    plan->path_log_freqs = calcPathLogFrequences(path_counts);
+    plan->stage = 0;
+    plan->marginal_posteriors.clear();
 
-    path_cluster_estimates->resetEstimates(num_paths, group_size);
+    // Full: every size-k multiset. Bounded (rpvg:src/path_estimator.cpp:398): the marginals first, i.e. Full with k = 1.
+    PathClusterEstimates * first = bounded ? &plan->marginal_estimates : path_cluster_estimates;
 
-    vector<uint32_t> flat_sets;
-    flat_sets.reserve(path_cluster_estimates->path_group_sets.size() * group_size);
-    for (auto & group_set: path_cluster_estimates->path_group_sets) { flat_sets.insert(flat_sets.end(), group_set.begin(), group_set.end()); }
+    if (bounded) { path_cluster_estimates->resetEstimates(0, 0); }
+    first->resetEstimates(num_paths, bounded ? 1 : group_size);
 
-    auto loglik = deviceLogLikelihoods(threadContext(), matrix, noise, counts, num_paths, group_size, flat_sets);
-
-    double sum_log_posterior = numeric_limits<double>::lowest();
-
-    for (uint32_t i = 0; i < path_cluster_estimates->path_group_sets.size(); ++i) {
-
-        path_cluster_estimates->posteriors.at(i) = loglik.at(i);
-
-        for (auto & path_idx: path_cluster_estimates->path_group_sets.at(i)) { path_cluster_estimates->posteriors.at(i) += path_log_freqs.at(path_idx); }
-
-        path_cluster_estimates->posteriors.at(i) += log(numPermutations(path_cluster_estimates->path_group_sets.at(i)));
-        sum_log_posterior = add_log(sum_log_posterior, path_cluster_estimates->posteriors.at(i));
-    }
-
-    for (size_t i = 0; i < path_cluster_estimates->posteriors.size(); ++i) {
-        path_cluster_estimates->posteriors.at(i) = exp(path_cluster_estimates->posteriors.at(i) - sum_log_posterior);
-    }
+    plan->set_size = bounded ? 1 : group_size;
+    plan->flat_sets.clear();
+    plan->flat_sets.reserve(first->path_group_sets.size() * plan->set_size);
+    for (auto & group_set: first->path_group_sets) { plan->flat_sets.insert(plan->flat_sets.end(), group_set.begin(), group_set.end()); }
 }
 
-void PathEstimator::calculatePathGroupPosteriorsBounded(PathClusterEstimates * path_cluster_estimates, const vector<double> & matrix, const vector<double> & noise, const vector<double> & counts, const uint32_t num_paths, const vector<uint32_t> & path_counts, const uint32_t group_size, const double min_rel_likelihood) const {
+bool PathEstimator::advancePathGroupPosteriors(GroupPosteriorPlan * plan, PathClusterEstimates * path_cluster_estimates, const double * loglik) const {
 
-    assert(group_size == 2);
+    if (plan->stage == 0) {
 
-    const double min_log_likelihood_diff = log(min_rel_likelihood);
-    auto path_log_freqs = calcPathLogFrequences(path_counts);
+        // rpvg:src/path_estimator.cpp:332-377 from the log-likelihoods on
+        PathClusterEstimates * estimates = plan->bounded ? &plan->marginal_estimates : path_cluster_estimates;
 
-    path_cluster_estimates->resetEstimates(0, 0);
+        double sum_log_posterior = numeric_limits<double>::lowest();
 
-    PathClusterEstimates marginal_path_cluster_estimates;
-    calculatePathGroupPosteriorsFull(&marginal_path_cluster_estimates, matrix, noise, counts, num_paths, path_counts, 1);
+        for (uint32_t i = 0; i < estimates->path_group_sets.size(); ++i) {
 
-    vector<pair<double, uint32_t> > marginal_posteriors;
-    marginal_posteriors.reserve(marginal_path_cluster_estimates.posteriors.size());
+            estimates->posteriors.at(i) = loglik[i];
 
-    for (size_t i = 0; i < marginal_path_cluster_estimates.posteriors.size(); ++i) {
-        marginal_posteriors.emplace_back(marginal_path_cluster_estimates.posteriors.at(i), marginal_path_cluster_estimates.path_group_sets.at(i).front());
-    }
+            for (auto & path_idx: estimates->path_group_sets.at(i)) { estimates->posteriors.at(i) += plan->path_log_freqs.at(path_idx); }
 
-    sort(marginal_posteriors.rbegin(), marginal_posteriors.rend());
-
-    // Every pair (i, j >= i) in the reference's enumeration order is evaluated on the device; the reference's pruning
-    // (per-first-path upper bound, running maximum) is then replayed over the finished values. A pair the bound would
-    // have skipped has a log-likelihood below the bound, so the replay drops it as well: the list comes out the same.
-    vector<uint32_t> flat_sets;
-    flat_sets.reserve(static_cast<size_t>(num_paths) * (num_paths + 1));
-
-    for (uint32_t i = 0; i < marginal_posteriors.size(); ++i) {
-        for (uint32_t j = i; j < marginal_posteriors.size(); ++j) {
-            flat_sets.push_back(marginal_posteriors.at(i).second);
-            flat_sets.push_back(marginal_posteriors.at(j).second);
+            estimates->posteriors.at(i) += log(numPermutations(estimates->path_group_sets.at(i)));
+            sum_log_posterior = add_log(sum_log_posterior, estimates->posteriors.at(i));
         }
+
+        for (size_t i = 0; i < estimates->posteriors.size(); ++i) {
+            estimates->posteriors.at(i) = exp(estimates->posteriors.at(i) - sum_log_posterior);
+        }
+
+        if (!plan->bounded) {
+            plan->stage = 2;
+            return false;
+        }
+
+        // rpvg:src/path_estimator.cpp:400-412: paths by marginal posterior, descending (ties: index descending)
+        plan->marginal_posteriors.clear();
+        plan->marginal_posteriors.reserve(estimates->posteriors.size());
+
+        for (size_t i = 0; i < estimates->posteriors.size(); ++i) {
+            plan->marginal_posteriors.emplace_back(estimates->posteriors.at(i), estimates->path_group_sets.at(i).front());
+        }
+
+        sort(plan->marginal_posteriors.rbegin(), plan->marginal_posteriors.rend());
+
+        // Every pair (i, j >= i) in the reference's enumeration order is evaluated on the device; the reference's pruning
+        // (per-first-path upper bound, running maximum) is then replayed over the finished values. A pair the bound would
+        // have skipped has a log-likelihood below the bound, so the replay drops it as well: the list comes out the same.
+        plan->set_size = 2;
+        plan->flat_sets.clear();
+        plan->flat_sets.reserve(static_cast<size_t>(plan->num_paths) * (plan->num_paths + 1));
+
+        for (uint32_t i = 0; i < plan->marginal_posteriors.size(); ++i) {
+            for (uint32_t j = i; j < plan->marginal_posteriors.size(); ++j) {
+                plan->flat_sets.push_back(plan->marginal_posteriors.at(i).second);
+                plan->flat_sets.push_back(plan->marginal_posteriors.at(j).second);
+            }
+        }
+
+        plan->stage = 1;
+        return true;
     }
 
-    auto loglik = deviceLogLikelihoods(threadContext(), matrix, noise, counts, num_paths, group_size, flat_sets);
+    assert(plan->stage == 1);
 
     vector<double> log_likelihoods;
     double max_log_likelihood = numeric_limits<double>::lowest();
 
     size_t pair_idx = 0;
 
-    for (uint32_t i = 0; i < marginal_posteriors.size(); ++i) {
+    for (uint32_t i = 0; i < plan->marginal_posteriors.size(); ++i) {
 
-        const uint32_t first_path_idx = marginal_posteriors.at(i).second;
+        const uint32_t first_path_idx = plan->marginal_posteriors.at(i).second;
 
-        for (uint32_t j = i; j < marginal_posteriors.size(); ++j, ++pair_idx) {
+        for (uint32_t j = i; j < plan->marginal_posteriors.size(); ++j, ++pair_idx) {
 
-            const uint32_t second_path_idx = marginal_posteriors.at(j).second;
+            const uint32_t second_path_idx = plan->marginal_posteriors.at(j).second;
 
-            double log_likelihood = loglik.at(pair_idx);
-            log_likelihood += path_log_freqs.at(first_path_idx) + path_log_freqs.at(second_path_idx) + log(numPermutations(vector<uint32_t>({first_path_idx, second_path_idx})));
+            double log_likelihood = loglik[pair_idx];
+            log_likelihood += plan->path_log_freqs.at(first_path_idx) + plan->path_log_freqs.at(second_path_idx) + log(numPermutations(vector<uint32_t>({first_path_idx, second_path_idx})));
 
-            if (log_likelihood - max_log_likelihood < min_log_likelihood_diff) { continue; }
+            if (log_likelihood - max_log_likelihood < plan->min_log_likelihood_diff) { continue; }
 
             log_likelihoods.emplace_back(log_likelihood);
             max_log_likelihood = max(max_log_likelihood, log_likelihood);
@@ -314,11 +329,39 @@ void PathEstimator::calculatePathGroupPosteriorsBounded(PathClusterEstimates * p
 
     for (size_t i = 0; i < log_likelihoods.size(); ++i) {
 
-        if (log_likelihoods.at(i) - max_log_likelihood < min_log_likelihood_diff) { log_likelihoods.at(i) = numeric_limits<double>::lowest(); }
+        if (log_likelihoods.at(i) - max_log_likelihood < plan->min_log_likelihood_diff) { log_likelihoods.at(i) = numeric_limits<double>::lowest(); }
         sum_log_posterior = add_log(sum_log_posterior, log_likelihoods.at(i));
     }
 
     for (auto & ll: log_likelihoods) { path_cluster_estimates->posteriors.emplace_back(exp(ll - sum_log_posterior)); }
+
+    plan->stage = 2;
+    return false;
+}
+
+void PathEstimator::calculatePathGroupPosteriorsFull(PathClusterEstimates * path_cluster_estimates, const vector<double> & matrix, const vector<double> & noise, const vector<double> & counts, const uint32_t num_paths, const vector<uint32_t> & path_counts, const uint32_t group_size) const {
+
+    assert(!noise.empty());
+
+    GroupPosteriorPlan plan;
+    planPathGroupPosteriors(&plan, path_cluster_estimates, num_paths, path_counts, group_size, false, 1);
+
+    auto loglik = deviceLogLikelihoods(threadContext(), matrix, noise, counts, num_paths, plan.set_size, plan.flat_sets);
+    advancePathGroupPosteriors(&plan, path_cluster_estimates, loglik.data());
+}
+
+void PathEstimator::calculatePathGroupPosteriorsBounded(PathClusterEstimates * path_cluster_estimates, const vector<double> & matrix, const vector<double> & noise, const vector<double> & counts, const uint32_t num_paths, const vector<uint32_t> & path_counts, const uint32_t group_size, const double min_rel_likelihood) const {
+
+    assert(group_size == 2);
+
+    GroupPosteriorPlan plan;
+    planPathGroupPosteriors(&plan, path_cluster_estimates, num_paths, path_counts, group_size, true, min_rel_likelihood);
+
+    bool more = true;
+    while (more) {
+        auto loglik = deviceLogLikelihoods(threadContext(), matrix, noise, counts, num_paths, plan.set_size, plan.flat_sets);
+        more = advancePathGroupPosteriors(&plan, path_cluster_estimates, loglik.data());
+    }
 }
 
 void PathEstimator::estimatePathGroupPosteriorsGibbs(PathClusterEstimates * path_cluster_estimates, const vector<double> & matrix, const vector<double> & noise, const vector<double> & counts, const uint32_t num_paths, const vector<uint32_t> & path_counts, const uint32_t group_size, mt19937 * mt_rng) const {

@@ -147,9 +147,38 @@ class PathEstimator {
 
         virtual void estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng) = 0;
 
+        // Not in rpvg: the cluster driver loop (rpvg:src/main.cpp:829-977) re-stated as one call for many clusters, so that
+        // the device sees a few large launches instead of several small ones per cluster. Same
+        // results, cluster by cluster, as estimate(estimates[i], *cluster_probs[i], rngs[i]); the default does just that.
+        virtual void estimateBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const vector<mt19937 *> & rngs);
+
     protected:
 
         const double prob_precision;
+
+        // The posterior calculations below in stages, so that the device requests of many clusters can be put into one
+        // call: a plan holds the path sets whose log-likelihoods are wanted next (flat_sets, set_size paths each).
+        struct GroupPosteriorPlan {
+
+            uint32_t num_paths = 0;
+            uint32_t group_size = 0;
+            bool bounded = false;
+            double min_log_likelihood_diff = 0;
+            vector<double> path_log_freqs;
+
+            int stage = 0;
+            uint32_t set_size = 0;
+            vector<uint32_t> flat_sets;
+
+            vector<pair<double, uint32_t> > marginal_posteriors;
+            PathClusterEstimates marginal_estimates;
+        };
+
+        void planPathGroupPosteriors(GroupPosteriorPlan * plan, PathClusterEstimates * path_cluster_estimates, const uint32_t num_paths, const vector<uint32_t> & path_counts, const uint32_t group_size, const bool bounded, const double min_rel_likelihood) const;
+
+        // Consumes the log-likelihoods of plan->flat_sets; true = the plan holds another request, false = the posteriors
+        // are in path_cluster_estimates.
+        bool advancePathGroupPosteriors(GroupPosteriorPlan * plan, PathClusterEstimates * path_cluster_estimates, const double * loglik) const;
 
         // One context per calling thread: estimate() is re-entrant on a shared object (rpvg:src/main.cpp:829-830).
         static rpvg_b200_ctx * threadContext();
@@ -176,6 +205,9 @@ class PathAbundanceEstimator : public PathEstimator {
 
         void estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng);
 
+        // all clusters in one device batch (EM and, if asked for, the Gibbs read-count samples)
+        void estimateBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const vector<mt19937 *> & rngs);
+
     protected:
 
         const uint32_t max_em_its;
@@ -193,6 +225,11 @@ class MinimumPathAbundanceEstimator : public PathAbundanceEstimator {
         ~MinimumPathAbundanceEstimator() {};
 
         void estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng);
+
+        // (the greedy cover couples the phases of a cluster; clusters are looped over)
+        void estimateBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const vector<mt19937 *> & rngs) {
+            PathEstimator::estimateBatch(estimates, cluster_probs, rngs);
+        }
 };
 
 class NestedPathAbundanceEstimator : public PathAbundanceEstimator {
@@ -203,6 +240,10 @@ class NestedPathAbundanceEstimator : public PathAbundanceEstimator {
         ~NestedPathAbundanceEstimator() {};
 
         void estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng);
+
+        // Collapsed mode without --use-hap-gibbs: four device calls for the whole batch (grouped + collapsed matrices,
+        // one or two rounds of log-likelihoods, all sub-EMs of all clusters) instead of four per cluster.
+        void estimateBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const vector<mt19937 *> & rngs);
 
     private:
 
@@ -224,6 +265,22 @@ class NestedPathAbundanceEstimator : public PathAbundanceEstimator {
         pair<vector<vector<uint32_t> >, vector<uint32_t> > findPathSourceGroups(const vector<PathInfo> & paths) const;
 
         void inferPathSubsetAbundance(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng, const SubsetSamples & path_subset_samples) const;
+
+        // inferPathSubsetAbundance in two halves around its device call (the sub-EMs of the subsets)
+        struct SubsetJob {
+            vector<uint32_t> paths;                // sorted, duplicates kept
+            double prob;
+            vector<uint32_t> collapsed;            // duplicates removed
+            vector<uint32_t> multiplicity;         // per collapsed path
+            uint32_t gibbs_samples;                // this subset's share of --num-gibbs-samples
+            uint64_t gibbs_seed;
+        };
+
+        vector<SubsetJob> planPathSubsets(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng, const SubsetSamples & path_subset_samples) const;
+        void finishPathSubsets(PathClusterEstimates * path_cluster_estimates, const vector<SubsetJob> & jobs, const double * abundances, const double * noise_counts, const double * gibbs_abundances, const double * gibbs_noise) const;
+
+        // selectPathSubsetIndices of the collapsed mode (rpvg:src/path_abundance_estimator.cpp:569-606)
+        SubsetSamples collapsedSubsetSamples(const PathClusterEstimates & group_estimates, const vector<vector<uint32_t> > & path_groups) const;
 };
 
 class PathPosteriorEstimator : public PathEstimator {

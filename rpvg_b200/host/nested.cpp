@@ -179,19 +179,10 @@ pair<vector<vector<uint32_t> >, vector<uint32_t> > NestedPathAbundanceEstimator:
     return path_source_groups;
 }
 
-// rpvg:src/path_abundance_estimator.cpp:428-471
-void NestedPathAbundanceEstimator::inferAbundancesCollapsedGroups(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng) const {
+// selectPathSubsetIndices (rpvg:src/path_abundance_estimator.cpp:569-606): combinations at or above min_hap_prob, expanded
+// to sorted path lists, their posteriors renormalised
+NestedPathAbundanceEstimator::SubsetSamples NestedPathAbundanceEstimator::collapsedSubsetSamples(const PathClusterEstimates & group_estimates, const vector<vector<uint32_t> > & path_groups) const {
 
-    path_cluster_estimates->resetEstimates(0, 0);
-
-    if (cluster_probs.empty()) { return; }
-
-    auto path_source_groups = findPathSourceGroups(path_cluster_estimates->paths);
-
-    PathClusterEstimates group_estimates;
-    groupPosteriors(&group_estimates, cluster_probs, path_cluster_estimates->paths.size(), path_source_groups.first, path_source_groups.second, mt_rng);
-
-    // selectPathSubsetIndices (:569-606): combinations at or above min_hap_prob, expanded to sorted path lists
     SubsetSamples path_subset_samples;
     double sum_posterior = 0;
 
@@ -201,7 +192,7 @@ void NestedPathAbundanceEstimator::inferAbundancesCollapsedGroups(PathClusterEst
 
             vector<uint32_t> path_subset;
             for (auto & group: group_estimates.path_group_sets.at(i)) {
-                for (auto & path: path_source_groups.first.at(group)) { path_subset.emplace_back(path); }
+                for (auto & path: path_groups.at(group)) { path_subset.emplace_back(path); }
             }
 
             sort(path_subset.begin(), path_subset.end());
@@ -214,6 +205,23 @@ void NestedPathAbundanceEstimator::inferAbundancesCollapsedGroups(PathClusterEst
     }
 
     for (auto & subset_sample: path_subset_samples) { subset_sample.second /= sum_posterior; }
+
+    return path_subset_samples;
+}
+
+// rpvg:src/path_abundance_estimator.cpp:428-471
+void NestedPathAbundanceEstimator::inferAbundancesCollapsedGroups(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng) const {
+
+    path_cluster_estimates->resetEstimates(0, 0);
+
+    if (cluster_probs.empty()) { return; }
+
+    auto path_source_groups = findPathSourceGroups(path_cluster_estimates->paths);
+
+    PathClusterEstimates group_estimates;
+    groupPosteriors(&group_estimates, cluster_probs, path_cluster_estimates->paths.size(), path_source_groups.first, path_source_groups.second, mt_rng);
+
+    const SubsetSamples path_subset_samples = collapsedSubsetSamples(group_estimates, path_source_groups.first);
 
     inferPathSubsetAbundance(path_cluster_estimates, cluster_probs, mt_rng, path_subset_samples);
 }
@@ -269,19 +277,11 @@ void NestedPathAbundanceEstimator::inferAbundancesIndependentGroups(PathClusterE
 }
 
 // rpvg:src/path_abundance_estimator.cpp:608-750, with the sub-EMs of all subsets batched into one device call.
-void NestedPathAbundanceEstimator::inferPathSubsetAbundance(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng, const SubsetSamples & path_subset_samples) const {
+vector<NestedPathAbundanceEstimator::SubsetJob> NestedPathAbundanceEstimator::planPathSubsets(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng, const SubsetSamples & path_subset_samples) const {
 
     for (auto & cluster_prob: cluster_probs) { path_cluster_estimates->total_count += cluster_prob.readCount(); }
 
-    // pass 1, in the map's iteration order: the subsets that take part, duplicates (homozygous paths) removed
-    struct SubsetJob {
-        const vector<uint32_t> * paths;       // sorted, duplicates kept
-        double prob;
-        vector<uint32_t> collapsed;            // duplicates removed
-        vector<uint32_t> multiplicity;         // per collapsed path
-        uint32_t gibbs_samples;                // this subset's share of --num-gibbs-samples
-    };
-
+    // pass 1, in the map's iteration order: the subsets that take part, duplicates (homozygous paths) removed.
     // :675-683 the sample budget is split over the subsets by conditional binomials, host generator, subset order
     uint32_t subset_gibbs_samples = num_gibbs_samples;
     double subset_gibbs_prob = 1;
@@ -293,7 +293,7 @@ void NestedPathAbundanceEstimator::inferPathSubsetAbundance(PathClusterEstimates
         if (path_subset.second < min_hap_prob) { continue; }
 
         SubsetJob job;
-        job.paths = &path_subset.first;
+        job.paths = path_subset.first;
         job.prob = path_subset.second;
 
         for (auto & path: path_subset.first) {
@@ -306,6 +306,7 @@ void NestedPathAbundanceEstimator::inferPathSubsetAbundance(PathClusterEstimates
         }
 
         job.gibbs_samples = 0;
+        job.gibbs_seed = 0;
 
         if (subset_gibbs_samples > 0) {
 
@@ -319,89 +320,52 @@ void NestedPathAbundanceEstimator::inferPathSubsetAbundance(PathClusterEstimates
         jobs.emplace_back(std::move(job));
     }
 
-    // all sub-EMs of the cluster in one call
-    vector<double> abundances;
-    vector<double> noise_counts(jobs.size(), 0), total_counts(jobs.size(), 0);
-    vector<uint64_t> subset_offset = {0};
+    // keys of the device sampler: after the allotment, in subset order
+    for (auto & job: jobs) {
+        if (job.gibbs_samples > 0) { job.gibbs_seed = (static_cast<uint64_t>((*mt_rng)()) << 32) | (*mt_rng)(); }
+    }
 
-    if (!jobs.empty()) {
+    return jobs;
+}
 
-        const FlatCluster flat(cluster_probs, path_cluster_estimates->paths.size());
-        rpvg_b200_clusters clusters = flat.view();
+void NestedPathAbundanceEstimator::finishPathSubsets(PathClusterEstimates * path_cluster_estimates, const vector<SubsetJob> & jobs, const double * abundances, const double * noise_counts, const double * gibbs_abundances, const double * gibbs_noise) const {
 
-        vector<uint32_t> subset_cluster(jobs.size(), 0);
-        vector<uint32_t> subset_paths;
+    // :685-696 one CountSamples per subset with samples, in subset order
+    size_t value_pos = 0, sample_pos = 0;
 
-        for (auto & job: jobs) {
-            subset_paths.insert(subset_paths.end(), job.collapsed.begin(), job.collapsed.end());
-            subset_offset.push_back(subset_paths.size());
+    for (auto & job: jobs) {
+
+        if (job.gibbs_samples > 0) {
+
+            CountSamples samples;
+            samples.path_ids = job.collapsed;
+            samples.noise_samples.assign(gibbs_noise + sample_pos, gibbs_noise + sample_pos + job.gibbs_samples);
+            samples.abundance_samples.assign(gibbs_abundances + value_pos, gibbs_abundances + value_pos + static_cast<size_t>(job.gibbs_samples) * job.collapsed.size());
+
+            path_cluster_estimates->gibbs_read_count_samples.emplace_back(std::move(samples));
         }
 
-        rpvg_b200_subsets subsets = {static_cast<uint32_t>(jobs.size()), subset_cluster.data(), subset_offset.data(), subset_paths.data()};
-
-        rpvg_b200_em_params params;
-        rpvg_b200_em_params_default(&params);
-        params.max_em_its = max_em_its;
-        params.max_rel_em_conv = max_rel_em_conv;
-
-        abundances.resize(subset_paths.size());
-        auto * ctx = threadContext();
-
-        // Gibbs samples of every subset that got a share, in the same call
-        vector<uint32_t> gibbs_counts;
-        vector<uint64_t> gibbs_seeds;
-        size_t total_samples = 0, total_values = 0;
-
-        for (auto & job: jobs) {
-            gibbs_counts.push_back(job.gibbs_samples);
-            gibbs_seeds.push_back(job.gibbs_samples > 0 ? ((static_cast<uint64_t>((*mt_rng)()) << 32) | (*mt_rng)()) : 0);
-            total_samples += job.gibbs_samples;
-            total_values += static_cast<size_t>(job.gibbs_samples) * job.collapsed.size();
-        }
-
-        vector<double> gibbs_abundances(total_values), gibbs_noise(total_samples);
-        rpvg_b200_gibbs gibbs = {gibbs_counts.data(), gibbs_thin_its, gibbs_seeds.data(), gibbs_abundances.data(), gibbs_noise.data()};
-
-        if (rpvg_b200_subset_em_gibbs(ctx, &clusters, &subsets, &params, prob_precision, total_samples > 0 ? &gibbs : nullptr, abundances.data(), noise_counts.data(),
-                                      total_counts.data(), nullptr, nullptr) != RPVG_B200_OK) {
-            fatalNested(ctx, "rpvg_b200_subset_em");
-        }
-
-        // :685-696 one CountSamples per subset with samples, in subset order
-        size_t value_pos = 0, sample_pos = 0;
-
-        for (auto & job: jobs) {
-
-            if (job.gibbs_samples > 0) {
-
-                CountSamples samples;
-                samples.path_ids = job.collapsed;
-                samples.noise_samples.assign(gibbs_noise.begin() + sample_pos, gibbs_noise.begin() + sample_pos + job.gibbs_samples);
-                samples.abundance_samples.assign(gibbs_abundances.begin() + value_pos, gibbs_abundances.begin() + value_pos + static_cast<size_t>(job.gibbs_samples) * job.collapsed.size());
-
-                path_cluster_estimates->gibbs_read_count_samples.emplace_back(std::move(samples));
-            }
-
-            sample_pos += job.gibbs_samples;
-            value_pos += static_cast<size_t>(job.gibbs_samples) * job.collapsed.size();
-        }
+        sample_pos += job.gibbs_samples;
+        value_pos += static_cast<size_t>(job.gibbs_samples) * job.collapsed.size();
     }
 
     // pass 2, same order: weight by the subset's probability and file under the transcript's path tuple
     rpvg_b200_host::hash_map<vector<uint32_t>, pair<double, vector<double> > > path_group_estimates;
     double sum_hap_prob = 0;
+    size_t subset_pos = 0;
 
     for (size_t s = 0; s < jobs.size(); ++s) {
 
         const auto & job = jobs.at(s);
-        const double * subset_abundances = abundances.data() + subset_offset.at(s);
+        const double * subset_abundances = abundances + subset_pos;
+        subset_pos += job.collapsed.size();
 
         sum_hap_prob += job.prob;
-        path_cluster_estimates->noise_count += noise_counts.at(s) * job.prob;
+        path_cluster_estimates->noise_count += noise_counts[s] * job.prob;
 
         rpvg_b200_host::hash_map<uint32_t, vector<uint32_t> > subset_path_group_index;
 
-        for (auto & path: *job.paths) {
+        for (auto & path: job.paths) {
             auto inserted = subset_path_group_index.emplace(path_cluster_estimates->paths.at(path).group_id, vector<uint32_t>());
             inserted.first->second.emplace_back(path);
         }
@@ -433,4 +397,57 @@ void NestedPathAbundanceEstimator::inferPathSubsetAbundance(PathClusterEstimates
     }
 
     path_cluster_estimates->noise_count += (1 - sum_hap_prob) * path_cluster_estimates->total_count;
+}
+
+void NestedPathAbundanceEstimator::inferPathSubsetAbundance(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng, const SubsetSamples & path_subset_samples) const {
+
+    const vector<SubsetJob> jobs = planPathSubsets(path_cluster_estimates, cluster_probs, mt_rng, path_subset_samples);
+
+    // all sub-EMs of the cluster in one call
+    vector<double> abundances, gibbs_abundances, gibbs_noise;
+    vector<double> noise_counts(jobs.size(), 0), total_counts(jobs.size(), 0);
+
+    if (!jobs.empty()) {
+
+        const FlatCluster flat(cluster_probs, path_cluster_estimates->paths.size());
+        rpvg_b200_clusters clusters = flat.view();
+
+        vector<uint32_t> subset_cluster(jobs.size(), 0);
+        vector<uint64_t> subset_offset = {0};
+        vector<uint32_t> subset_paths;
+        vector<uint32_t> gibbs_counts;
+        vector<uint64_t> gibbs_seeds;
+        size_t total_samples = 0, total_values = 0;
+
+        for (auto & job: jobs) {
+            subset_paths.insert(subset_paths.end(), job.collapsed.begin(), job.collapsed.end());
+            subset_offset.push_back(subset_paths.size());
+            gibbs_counts.push_back(job.gibbs_samples);
+            gibbs_seeds.push_back(job.gibbs_seed);
+            total_samples += job.gibbs_samples;
+            total_values += static_cast<size_t>(job.gibbs_samples) * job.collapsed.size();
+        }
+
+        rpvg_b200_subsets subsets = {static_cast<uint32_t>(jobs.size()), subset_cluster.data(), subset_offset.data(), subset_paths.data()};
+
+        rpvg_b200_em_params params;
+        rpvg_b200_em_params_default(&params);
+        params.max_em_its = max_em_its;
+        params.max_rel_em_conv = max_rel_em_conv;
+
+        abundances.resize(subset_paths.size());
+        gibbs_abundances.resize(total_values);
+        gibbs_noise.resize(total_samples);
+
+        rpvg_b200_gibbs gibbs = {gibbs_counts.data(), gibbs_thin_its, gibbs_seeds.data(), gibbs_abundances.data(), gibbs_noise.data()};
+
+        auto * ctx = threadContext();
+
+        if (rpvg_b200_subset_em_gibbs(ctx, &clusters, &subsets, &params, prob_precision, total_samples > 0 ? &gibbs : nullptr, abundances.data(), noise_counts.data(),
+                                      total_counts.data(), nullptr, nullptr) != RPVG_B200_OK) {
+            fatalNested(ctx, "rpvg_b200_subset_em");
+        }
+    }
+
+    finishPathSubsets(path_cluster_estimates, jobs, abundances.data(), noise_counts.data(), gibbs_abundances.data(), gibbs_noise.data());
 }

@@ -254,6 +254,50 @@ double harness_estimate_batch(void * estimator, uint32_t n, const HarnessCluster
     return chrono::duration<double>(time_end - time_start).count();
 }
 
+#ifndef HARNESS_REFERENCE
+// The same loop through the batched driver entry of this repository's classes (estimateBatch): same order of clusters,
+// same generator per cluster as harness_estimate_batch, one call. Returns wall seconds of the call.
+double harness_estimate_batched(void * estimator, uint32_t n, const HarnessCluster * clusters, uint32_t rng_seed, void ** handles) {
+
+    auto * holder = static_cast<EstimatorHolder *>(estimator);
+
+    vector<PathClusterEstimates> ests(n);
+    vector<vector<ReadPathProbabilities> > probs(n);
+
+    for (uint32_t i = 0; i < n; ++i) {
+        unflattenCluster(clusters[i], holder->cfg.prob_precision, &ests[i], &probs[i]);
+    }
+
+    vector<pair<uint32_t, uint32_t> > indices;
+    indices.reserve(n);
+    for (uint32_t i = 0; i < n; ++i) { indices.emplace_back(clusters[i].num_reads, i); }
+    sort(indices.rbegin(), indices.rend());
+
+    vector<mt19937> generators;
+    generators.reserve(n);
+
+    vector<PathClusterEstimates *> est_ptrs;
+    vector<const vector<ReadPathProbabilities> *> prob_ptrs;
+    vector<mt19937 *> rng_ptrs;
+
+    for (size_t i = 0; i < indices.size(); ++i) {
+        auto idx = indices.at(i).second;
+        generators.emplace_back(rng_seed + i);
+        est_ptrs.push_back(&ests[idx]);
+        prob_ptrs.push_back(&probs[idx]);
+        rng_ptrs.push_back(&generators.back());
+    }
+
+    auto time_start = chrono::steady_clock::now();
+    holder->estimator->estimateBatch(est_ptrs, prob_ptrs, rng_ptrs);
+    auto time_end = chrono::steady_clock::now();
+
+    for (uint32_t i = 0; i < n; ++i) { handles[i] = flattenEstimates(ests[i]); }
+
+    return chrono::duration<double>(time_end - time_start).count();
+}
+#endif
+
 const HarnessResult * harness_result_view(void * handle) {
 
     return &(static_cast<ResultHolder *>(handle)->view);

@@ -88,6 +88,11 @@ void * harness_estimate(void * estimator, const HarnessCluster * cluster, uint32
  * Returns wall seconds of the loop. num_threads <= 0 -> omp default. */
 double harness_estimate_batch(void * estimator, uint32_t n, const HarnessCluster * clusters, uint32_t rng_seed, int32_t num_threads, void ** handles);
 
+#ifndef HARNESS_REFERENCE
+/* rpvg_b200 classes only: the same clusters, order and generators through estimateBatch (one call). */
+double harness_estimate_batched(void * estimator, uint32_t n, const HarnessCluster * clusters, uint32_t rng_seed, void ** handles);
+#endif
+
 const HarnessResult * harness_result_view(void * handle);
 void harness_result_free(void * handle);
 

@@ -1,0 +1,37 @@
+"""Inference-stage wall time of the haplotype-transcripts model (config-1-like synthetic clusters) through the SAME harness
+source compiled against the reference's classes (CPU, oracle/_ref) and against this repository's drop-in classes (GPU).
+python tools/nested_bench.py [n_clusters] [threads]"""
+import os, sys, time
+import numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from oracle import loader
+from rpvg_b200 import synth
+from rpvg_b200.arena import concat
+
+n_clusters = int(sys.argv[1]) if len(sys.argv) > 1 else 400
+threads = int(sys.argv[2]) if len(sys.argv) > 2 else 16
+rng = np.random.default_rng(20240601)
+t0 = time.time()
+arena = concat([synth.haplotype_cluster(rng, n_transcripts=int(rng.integers(1, 5)), paths_per_transcript=(2, 24), n_haplotypes=60,
+                                        n_reads=int(rng.integers(200, 3000))) for _ in range(n_clusters)])
+print(f"{n_clusters} clusters, {arena.n_paths} paths, {arena.n_reads} read classes, generated in {time.time() - t0:.1f} s", flush=True)
+cfg = loader.make_config(loader.MODEL_HAPLOTYPE_TRANSCRIPTS, group_size=2)
+
+b200 = loader.load_harness(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "_build", "libharness_b200.so"))
+for name, lib_ in (("reference classes (CPU)", loader.reference()), ("rpvg_b200 classes (GPU)", b200)):
+    if lib_ is None:
+        continue
+    best = None
+    for rep in range(2):
+        secs, results = loader.harness_estimate_batch(lib_, cfg, arena, rng_seed=1, num_threads=threads)
+        best = secs if best is None else min(best, secs)
+    n_sets = sum(len(r["sets"]) for r in results)
+    print(f"{name}: {best * 1e3:.1f} ms for {n_clusters} clusters with {threads} threads = {n_clusters / best:.0f} clusters/s ({n_sets} output tuples)", flush=True)
+
+best = None
+for rep in range(3):
+    secs, batched = loader.harness_estimate_batched(b200, cfg, arena, rng_seed=1)
+    best = secs if best is None else min(best, secs)
+print(f"rpvg_b200 classes, estimateBatch (GPU, one host thread): {best * 1e3:.1f} ms = {n_clusters / best:.0f} clusters/s", flush=True)
+same = all(a["sets"] == b["sets"] and np.array_equal(a["abundances"], b["abundances"]) for a, b in zip(batched, results))
+print("batched results identical to the per-cluster ones:", same)
