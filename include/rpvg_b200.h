@@ -182,6 +182,18 @@ typedef struct {
 int rpvg_b200_grouped_collapse(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * clusters, const rpvg_b200_path_groups * groups, double prob_precision,
                                uint32_t * n_classes, double * matrix, double * noise, double * counts);
 
+/* The same matrices kept on the device, for callers that go on to rpvg_b200_group_loglik with them (the batched driver
+ * of the haplotype-transcripts class): rpvg_b200_grouped_create = rpvg_b200_grouped_collapse without the copy back,
+ * rpvg_b200_grouped_loglik = rpvg_b200_group_loglik on those matrices (problem c = cluster c, paths = its groups;
+ * set_offset [n_clusters + 1], sets problem-local group indices). Free with rpvg_b200_grouped_free. */
+typedef struct rpvg_b200_grouped rpvg_b200_grouped;
+
+int rpvg_b200_grouped_create(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * clusters, const rpvg_b200_path_groups * groups, double prob_precision,
+                             uint32_t * n_classes, rpvg_b200_grouped ** grouped);
+int rpvg_b200_grouped_loglik(rpvg_b200_ctx * ctx, const rpvg_b200_grouped * grouped, uint32_t group_size, const uint64_t * set_offset, const uint32_t * sets,
+                             double * loglik);
+void rpvg_b200_grouped_free(rpvg_b200_ctx * ctx, rpvg_b200_grouped * grouped);
+
 /* ---- strains model: greedy weighted minimum path cover ----
  * The cover construction of MinimumPathAbundanceEstimator::estimate (rpvg:src/path_abundance_estimator.cpp:229-251:
  * cover = the non-zero pattern, read counts zeroed for noise-only read classes, weight_j = -sum_i log(p_ij) count_i) and

@@ -19,6 +19,7 @@
 #include <cub/device/device_scan.cuh>
 
 #include "collapse.cuh"
+#include "grouped.cuh"
 
 int rpvgCollapseDevice(rpvg_b200_ctx * ctx, CollapseRows rows, uint32_t * d_row_problem, double prob_precision, uint32_t * d_sorted, uint32_t * d_sorted_class,
                        uint32_t * d_n_classes);
@@ -137,10 +138,11 @@ __global__ void groupedGatherKernel(const GroupedArgs a, uint64_t n_classes_tota
 
 }
 
-extern "C" int rpvg_b200_grouped_collapse(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, const rpvg_b200_path_groups * gr, double prob_precision,
-                                          uint32_t * n_classes, double * matrix, double * noise, double * counts) {
+// keep == nullptr: results to the host arrays; otherwise they stay on the device under *keep (matrix/noise/counts unused)
+static int groupedCollapse(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, const rpvg_b200_path_groups * gr, double prob_precision, uint32_t * n_classes, double * matrix,
+                           double * noise, double * counts, rpvg_b200_grouped ** keep) {
 
-    if (!ctx || !cl || !gr || !n_classes || !matrix || !noise || !counts) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "NULL argument"); }
+    if (!ctx || !cl || !gr || !n_classes || (!keep && (!matrix || !noise || !counts))) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "NULL argument"); }
     if (cl->n_clusters == 0) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "no clusters"); }
 
     const uint32_t C = cl->n_clusters;
@@ -191,6 +193,7 @@ extern "C" int rpvg_b200_grouped_collapse(rpvg_b200_ctx * ctx, const rpvg_b200_c
 
     if (R == 0) {
         for (uint32_t c = 0; c < C; ++c) { n_classes[c] = 0; }
+        if (keep) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "rpvg_b200_grouped_create: no read classes"); }
         return RPVG_B200_OK;
     }
 
@@ -322,9 +325,11 @@ extern "C" int rpvg_b200_grouped_collapse(rpvg_b200_ctx * ctx, const rpvg_b200_c
             err = cudaGetLastError();
         }
 
-        RPVG_STEP(cudaMemcpyAsync(matrix, d_out_matrix, 8 * MX, cudaMemcpyDeviceToHost, s))
-        RPVG_STEP(cudaMemcpyAsync(noise, d_res_noise, 8 * R, cudaMemcpyDeviceToHost, s))
-        RPVG_STEP(cudaMemcpyAsync(counts, d_res_counts, 8 * R, cudaMemcpyDeviceToHost, s))
+        if (!keep) {
+            RPVG_STEP(cudaMemcpyAsync(matrix, d_out_matrix, 8 * MX, cudaMemcpyDeviceToHost, s))
+            RPVG_STEP(cudaMemcpyAsync(noise, d_res_noise, 8 * R, cudaMemcpyDeviceToHost, s))
+            RPVG_STEP(cudaMemcpyAsync(counts, d_res_counts, 8 * R, cudaMemcpyDeviceToHost, s))
+        }
         RPVG_STEP(cudaStreamSynchronize(s))
     }
 
@@ -333,6 +338,46 @@ extern "C" int rpvg_b200_grouped_collapse(rpvg_b200_ctx * ctx, const rpvg_b200_c
 
     if (status == RPVG_B200_OK && err != cudaSuccess) { status = rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("rpvg_b200_grouped_collapse: ") + cudaGetErrorString(err)); }
 
+    if (keep && status == RPVG_B200_OK) {
+
+        auto * grouped = new rpvg_b200_grouped();
+        grouped->n_clusters = C;
+        grouped->base = base;
+        grouped->d_matrix = d_out_matrix;
+        grouped->d_noise = d_res_noise;
+        grouped->d_counts = d_res_counts;
+        grouped->d_row_offset = d_read_offset;
+        grouped->d_group_offset = d_group_offset;
+        grouped->d_matrix_offset = d_matrix_offset;
+        grouped->d_n_classes = d_n_classes;
+        *keep = grouped;
+        return status;
+    }
+
     cudaFreeAsync(base, s);
     return status;
+}
+
+extern "C" int rpvg_b200_grouped_collapse(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, const rpvg_b200_path_groups * gr, double prob_precision,
+                                          uint32_t * n_classes, double * matrix, double * noise, double * counts) {
+
+    return groupedCollapse(ctx, cl, gr, prob_precision, n_classes, matrix, noise, counts, nullptr);
+}
+
+extern "C" int rpvg_b200_grouped_create(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, const rpvg_b200_path_groups * gr, double prob_precision,
+                                        uint32_t * n_classes, rpvg_b200_grouped ** grouped) {
+
+    if (!grouped) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "NULL argument"); }
+    *grouped = nullptr;
+    return groupedCollapse(ctx, cl, gr, prob_precision, n_classes, nullptr, nullptr, nullptr, grouped);
+}
+
+extern "C" void rpvg_b200_grouped_free(rpvg_b200_ctx * ctx, rpvg_b200_grouped * grouped) {
+
+    if (!grouped) { return; }
+    if (ctx) {
+        cudaSetDevice(ctx->device);
+        cudaFreeAsync(grouped->base, ctx->stream);
+    }
+    delete grouped;
 }

@@ -14,6 +14,7 @@
 #include <cmath>
 
 #include "common.cuh"
+#include "grouped.cuh"
 
 namespace {
 
@@ -26,6 +27,7 @@ struct LoglikArgs {
     uint32_t group_size;
     uint64_t n_sets;
     const uint64_t * row_offset;
+    const uint32_t * rows;          // rows of each problem when they do not fill [row_offset[p], row_offset[p + 1]); else NULL
     const uint64_t * path_offset;
     const uint64_t * matrix_offset;
     const uint64_t * set_offset;
@@ -44,7 +46,7 @@ __global__ void __launch_bounds__(kLoglikThreads) groupLoglikKernel(const Loglik
 
     const uint32_t p = clusterOf(args.set_offset, args.n_problems, set);
     const uint64_t r0 = args.row_offset[p];
-    const uint32_t rows = static_cast<uint32_t>(args.row_offset[p + 1] - r0);
+    const uint32_t rows = args.rows ? args.rows[p] : static_cast<uint32_t>(args.row_offset[p + 1] - r0);
     const double * matrix = args.matrix + args.matrix_offset[p];
     const double * noise = args.noise + r0;
     const double * counts = args.counts + r0;
@@ -142,6 +144,7 @@ extern "C" int rpvg_b200_group_loglik(rpvg_b200_ctx * ctx, const rpvg_b200_logli
         args.group_size = pr->group_size;
         args.n_sets = S;
         args.row_offset = d_row_offset;
+        args.rows = nullptr;
         args.path_offset = d_path_offset;
         args.matrix_offset = d_matrix_offset;
         args.set_offset = d_set_offset;
@@ -161,6 +164,69 @@ extern "C" int rpvg_b200_group_loglik(rpvg_b200_ctx * ctx, const rpvg_b200_logli
     if (err == cudaSuccess) { err = cudaStreamSynchronize(s); }
 
     if (err != cudaSuccess) { status = rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("rpvg_b200_group_loglik: ") + cudaGetErrorString(err)); }
+
+    cudaFreeAsync(base, s);
+    return status;
+}
+
+// The same sums on matrices that are already on the device (rpvg_b200_grouped_create): only the sets go up and the
+// log-likelihoods come down.
+extern "C" int rpvg_b200_grouped_loglik(rpvg_b200_ctx * ctx, const rpvg_b200_grouped * grouped, uint32_t group_size, const uint64_t * set_offset, const uint32_t * sets,
+                                        double * loglik) {
+
+    if (!ctx || !grouped || !set_offset || !loglik) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "NULL argument"); }
+    if (group_size == 0 || group_size > kMaxGroupSizeLoglik) { return rpvgFail(ctx, RPVG_B200_ERR_LIMIT, "group_size must be 1..8"); }
+
+    const uint32_t P = grouped->n_clusters;
+    const uint64_t S = set_offset[P];
+
+    if (S == 0) { return RPVG_B200_OK; }
+    if (!sets) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "NULL argument"); }
+
+    RPVG_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+
+    auto pad = [](size_t b) { return (b + 255) & ~size_t(255); };
+    const size_t bytes = pad(8 * (P + 1)) + pad(4 * S * group_size) + pad(8 * S) + 1024;
+
+    char * base = nullptr;
+    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&base), bytes, s));
+
+    uint64_t * d_set_offset = reinterpret_cast<uint64_t *>(base);
+    uint32_t * d_sets = reinterpret_cast<uint32_t *>(base + pad(8 * (P + 1)));
+    double * d_loglik = reinterpret_cast<double *>(base + pad(8 * (P + 1)) + pad(4 * S * group_size));
+
+    cudaError_t err = cudaMemcpyAsync(d_set_offset, set_offset, 8 * (P + 1), cudaMemcpyHostToDevice, s);
+    if (err == cudaSuccess) { err = cudaMemcpyAsync(d_sets, sets, 4 * S * group_size, cudaMemcpyHostToDevice, s); }
+
+    if (err == cudaSuccess) {
+
+        LoglikArgs args;
+        args.n_problems = P;
+        args.group_size = group_size;
+        args.n_sets = S;
+        args.row_offset = grouped->d_row_offset;
+        args.rows = grouped->d_n_classes;
+        args.path_offset = grouped->d_group_offset;
+        args.matrix_offset = grouped->d_matrix_offset;
+        args.set_offset = d_set_offset;
+        args.matrix = grouped->d_matrix;
+        args.noise = grouped->d_noise;
+        args.counts = grouped->d_counts;
+        args.sets = d_sets;
+        args.loglik = d_loglik;
+
+        const uint64_t blocks = (S * 32 + kLoglikThreads - 1) / kLoglikThreads;
+        groupLoglikKernel<<<static_cast<unsigned>(blocks), kLoglikThreads, 0, s>>>(args);
+        ctx->launches++;
+        err = cudaGetLastError();
+    }
+
+    if (err == cudaSuccess) { err = cudaMemcpyAsync(loglik, d_loglik, 8 * S, cudaMemcpyDeviceToHost, s); }
+    if (err == cudaSuccess) { err = cudaStreamSynchronize(s); }
+
+    int status = RPVG_B200_OK;
+    if (err != cudaSuccess) { status = rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("rpvg_b200_grouped_loglik: ") + cudaGetErrorString(err)); }
 
     cudaFreeAsync(base, s);
     return status;

@@ -285,14 +285,11 @@ void NestedPathAbundanceEstimator::estimateBatch(const vector<PathClusterEstimat
 
     lap("A flatten + haplotype groups");
 
-    // ---- stage B: grouped + normalised + collapsed matrix of every cluster, then packed: cluster k's matrix
-    // (rows_k x groups_k, column-major) at c_matrix_offset[k], its noise and counts at c_row_offset[k]
-    vector<uint64_t> c_row_offset = {0}, c_path_offset = {0}, c_matrix_offset = {0};
-    vector<double> c_matrix, c_noise, c_counts;
+    // ---- stage B: grouped + normalised + collapsed matrix of every cluster; they stay on the device for stage C
+    rpvg_b200_grouped * grouped = nullptr;
     {
         vector<uint64_t> group_offset = {0}, group_path_ptr = {0};
         vector<uint32_t> group_paths;
-        vector<uint64_t> block_start = {0};
 
         for (size_t k = 0; k < items.size(); ++k) {
 
@@ -302,110 +299,64 @@ void NestedPathAbundanceEstimator::estimateBatch(const vector<PathClusterEstimat
             }
 
             group_offset.push_back(group_path_ptr.size() - 1);
-            block_start.push_back(block_start.back() + (arena.read_offset[k + 1] - arena.read_offset[k]) * items[k].source_groups.first.size());
         }
 
         rpvg_b200_path_groups groups = {group_offset.data(), group_path_ptr.data(), group_paths.data()};
-
         vector<uint32_t> n_classes(items.size(), 0);
-        vector<double> matrix(block_start.back()), noise(arena.noise.size()), counts(arena.noise.size());
 
-        if (rpvg_b200_grouped_collapse(ctx, &clusters, &groups, prob_precision, n_classes.data(), matrix.data(), noise.data(), counts.data()) != RPVG_B200_OK) {
-            fatalBatch(ctx, "rpvg_b200_grouped_collapse");
-        }
-
-        for (size_t k = 0; k < items.size(); ++k) {
-            const size_t num_groups = items[k].source_groups.first.size();
-            assert(n_classes[k] > 0);
-            c_row_offset.push_back(c_row_offset.back() + n_classes[k]);
-            c_path_offset.push_back(c_path_offset.back() + num_groups);
-            c_matrix_offset.push_back(c_matrix_offset.back() + static_cast<uint64_t>(n_classes[k]) * num_groups);
-        }
-
-        c_matrix.resize(c_matrix_offset.back());
-        c_noise.resize(c_row_offset.back());
-        c_counts.resize(c_row_offset.back());
+        if (rpvg_b200_grouped_create(ctx, &clusters, &groups, prob_precision, n_classes.data(), &grouped) != RPVG_B200_OK) { fatalBatch(ctx, "rpvg_b200_grouped_create"); }
 
         #pragma omp parallel for schedule(dynamic, 8)
         for (size_t k = 0; k < items.size(); ++k) {
-
-            const size_t rows = n_classes[k];
-            const size_t num_groups = items[k].source_groups.first.size();
-            const size_t r0 = arena.read_offset[k];
-
-            copy(matrix.begin() + block_start[k], matrix.begin() + block_start[k] + rows * num_groups, c_matrix.begin() + c_matrix_offset[k]);
-            copy(noise.begin() + r0, noise.begin() + r0 + rows, c_noise.begin() + c_row_offset[k]);
-            copy(counts.begin() + r0, counts.begin() + r0 + rows, c_counts.begin() + c_row_offset[k]);
-
-            planPathGroupPosteriors(&items[k].plan, &items[k].group_estimates, num_groups, items[k].source_groups.second, group_size, group_size == 2, min_hap_prob);
+            assert(n_classes[k] > 0);
+            planPathGroupPosteriors(&items[k].plan, &items[k].group_estimates, items[k].source_groups.first.size(), items[k].source_groups.second, group_size, group_size == 2,
+                                    min_hap_prob);
         }
     }
 
     lap("B grouped collapse");
 
     // ---- stage C: posteriors of the haplotype combinations; every round is one log-likelihood call for all clusters
-    // that still have a request (Full: one round; Bounded: marginals, then the pairs)
+    // (Full: one round; Bounded: marginals, then the pairs). All clusters run the same kind of plan, so they have a
+    // request in the same rounds.
     {
-        vector<size_t> active(items.size());
-        iota(active.begin(), active.end(), 0);
+        bool more_rounds = true;
 
-        while (!active.empty()) {
+        while (more_rounds) {
 
-            const uint32_t set_size = items[active.front()].plan.set_size;
-
-            // all clusters run the same kind of plan, so they have a request in the same rounds: the packed matrices serve
-            // every round as they are; a cluster without a request would just bring no sets
-            assert(active.size() == items.size());
+            const uint32_t set_size = items.front().plan.set_size;
 
             vector<uint64_t> set_offset = {0};
             vector<uint32_t> sets;
 
-            for (auto k: active) {
-
-                auto & item = items[k];
+            for (auto & item: items) {
                 assert(item.plan.set_size == set_size);
-
                 sets.insert(sets.end(), item.plan.flat_sets.begin(), item.plan.flat_sets.end());
                 set_offset.push_back(sets.size() / set_size);
             }
 
-            rpvg_b200_loglik_problems problems;
-            problems.n_problems = static_cast<uint32_t>(items.size());
-            problems.row_offset = c_row_offset.data();
-            problems.path_offset = c_path_offset.data();
-            problems.matrix_offset = c_matrix_offset.data();
-            problems.set_offset = set_offset.data();
-            problems.matrix = c_matrix.data();
-            problems.noise = c_noise.data();
-            problems.counts = c_counts.data();
-            problems.group_size = set_size;
-            problems.sets = sets.data();
-
             lap("C   concatenate");
 
             vector<double> loglik(set_offset.back(), 0);
-            if (!loglik.empty() && rpvg_b200_group_loglik(ctx, &problems, loglik.data()) != RPVG_B200_OK) { fatalBatch(ctx, "rpvg_b200_group_loglik"); }
+            if (rpvg_b200_grouped_loglik(ctx, grouped, set_size, set_offset.data(), sets.data(), loglik.data()) != RPVG_B200_OK) { fatalBatch(ctx, "rpvg_b200_grouped_loglik"); }
 
-            if (trace) { cerr << "[rpvg_b200 batch]     " << set_offset.back() << " sets of " << set_size << ", " << c_noise.size() << " rows, " << c_matrix.size() << " matrix entries" << endl; }
+            if (trace) { cerr << "[rpvg_b200 batch]     " << set_offset.back() << " sets of " << set_size << endl; }
             lap("C   device log-likelihoods");
 
-            vector<char> more(active.size(), 0);
+            vector<char> more(items.size(), 0);
 
             #pragma omp parallel for schedule(dynamic, 8)
-            for (size_t a = 0; a < active.size(); ++a) {
-                auto & item = items[active[a]];
-                more[a] = advancePathGroupPosteriors(&item.plan, &item.group_estimates, loglik.data() + set_offset[a]) ? 1 : 0;
+            for (size_t k = 0; k < items.size(); ++k) {
+                more[k] = advancePathGroupPosteriors(&items[k].plan, &items[k].group_estimates, loglik.data() + set_offset[k]) ? 1 : 0;
             }
 
             lap("C   advance");
 
-            vector<size_t> next;
-            for (size_t a = 0; a < active.size(); ++a) {
-                if (more[a]) { next.push_back(active[a]); }
-            }
-
-            active.swap(next);
+            more_rounds = more.front() != 0;
+            for (auto m: more) { assert((m != 0) == more_rounds); }
         }
+
+        rpvg_b200_grouped_free(ctx, grouped);
     }
 
     lap("C posteriors");

@@ -18,8 +18,10 @@ print(f"{n_clusters} clusters, {arena.n_paths} paths, {arena.n_reads} read class
 cfg = loader.make_config(loader.MODEL_HAPLOTYPE_TRANSCRIPTS, group_size=2)
 
 b200 = loader.load_harness(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "_build", "libharness_b200.so"))
+batch_only = len(sys.argv) > 3 and sys.argv[3] == "batch-only"
+results = None
 for name, lib_ in (("reference classes (CPU)", loader.reference()), ("rpvg_b200 classes (GPU)", b200)):
-    if lib_ is None:
+    if lib_ is None or batch_only:
         continue
     best = None
     for rep in range(2):
@@ -33,5 +35,6 @@ for rep in range(3):
     secs, batched = loader.harness_estimate_batched(b200, cfg, arena, rng_seed=1)
     best = secs if best is None else min(best, secs)
 print(f"rpvg_b200 classes, estimateBatch (GPU, one host thread): {best * 1e3:.1f} ms = {n_clusters / best:.0f} clusters/s", flush=True)
-same = all(a["sets"] == b["sets"] and np.array_equal(a["abundances"], b["abundances"]) for a, b in zip(batched, results))
-print("batched results identical to the per-cluster ones:", same)
+if results is not None:
+    same = all(a["sets"] == b["sets"] and np.array_equal(a["abundances"], b["abundances"]) for a, b in zip(batched, results))
+    print("batched results identical to the per-cluster ones:", same)
