@@ -34,7 +34,7 @@ best = None
 for rep in range(3):
     secs, batched = loader.harness_estimate_batched(b200, cfg, arena, rng_seed=1)
     best = secs if best is None else min(best, secs)
-print(f"rpvg_b200 classes, estimateBatch (GPU, one host thread): {best * 1e3:.1f} ms = {n_clusters / best:.0f} clusters/s", flush=True)
+print(f"rpvg_b200 classes, estimateBatch (GPU, one call): {best * 1e3:.1f} ms = {n_clusters / best:.0f} clusters/s", flush=True)
 if results is not None:
     same = all(a["sets"] == b["sets"] and np.array_equal(a["abundances"], b["abundances"]) for a, b in zip(batched, results))
     print("batched results identical to the per-cluster ones:", same)
