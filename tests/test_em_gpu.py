@@ -154,3 +154,16 @@ def test_em_groups_without_band_structure(ctx):
     arena = concat(parts)
     _, _, _, its = check_against_port(ctx, arena)
     assert its.min() >= 10
+
+
+def test_em_wide_clusters(ctx):
+    """Clusters with more than 65535 paths (32-bit indices in the kernels): one split over a group of CTAs, one small
+    enough for a single CTA but with an abundance vector that does not fit shared memory (global-memory fallback)."""
+    rng = np.random.default_rng(91)
+    parts = [
+        _random_cluster(rng, 30000, 70000, 3),    # weight ~120k -> group, each slice touches a few thousand paths
+        _random_cluster(rng, 800, 90000, 4),      # one CTA, N + 1 doubles do not fit shared memory
+        _random_cluster(rng, 50, 6, 2),
+    ]
+    arena = concat(parts)
+    check_against_port(ctx, arena)

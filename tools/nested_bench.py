@@ -10,11 +10,24 @@ from rpvg_b200.arena import concat
 
 n_clusters = int(sys.argv[1]) if len(sys.argv) > 1 else 400
 threads = int(sys.argv[2]) if len(sys.argv) > 2 else 16
-rng = np.random.default_rng(20240601)
+# the generator is slow Python: the arena is cached under tools/cache (git-ignored, travels to the GPU box)
+cache = os.path.join(os.path.dirname(os.path.abspath(__file__)), "cache", f"nested_{n_clusters}.npz")
 t0 = time.time()
-arena = concat([synth.haplotype_cluster(rng, n_transcripts=int(rng.integers(1, 5)), paths_per_transcript=(2, 24), n_haplotypes=60,
-                                        n_reads=int(rng.integers(200, 3000))) for _ in range(n_clusters)])
-print(f"{n_clusters} clusters, {arena.n_paths} paths, {arena.n_reads} read classes, generated in {time.time() - t0:.1f} s", flush=True)
+if os.path.exists(cache):
+    z = np.load(cache)
+    from rpvg_b200.arena import ClusterArena
+    arena = ClusterArena(z["read_offset"], z["path_offset"], z["row_ptr"], z["col"], z["prob"], z["noise"], z["count"], group_id=z["group_id"],
+                         source_count=z["source_count"], source_ptr=z["source_ptr"], source_ids=z["source_ids"])
+else:
+    rng = np.random.default_rng(20240601)
+    arena = concat([synth.haplotype_cluster(rng, n_transcripts=int(rng.integers(1, 5)), paths_per_transcript=(2, 24), n_haplotypes=60,
+                                            n_reads=int(rng.integers(200, 3000))) for _ in range(n_clusters)])
+    os.makedirs(os.path.dirname(cache), exist_ok=True)
+    np.savez_compressed(cache, read_offset=arena.read_offset, path_offset=arena.path_offset, row_ptr=arena.row_ptr, col=arena.col, prob=arena.prob, noise=arena.noise,
+                        count=arena.count, group_id=arena.group_id, source_count=arena.source_count, source_ptr=arena.source_ptr, source_ids=arena.source_ids)
+print(f"{n_clusters} clusters, {arena.n_paths} paths, {arena.n_reads} read classes, ready in {time.time() - t0:.1f} s", flush=True)
+if len(sys.argv) > 3 and sys.argv[3] == "generate-only":
+    raise SystemExit(0)
 cfg = loader.make_config(loader.MODEL_HAPLOTYPE_TRANSCRIPTS, group_size=2)
 
 b200 = loader.load_harness(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "_build", "libharness_b200.so"))
