@@ -12,6 +12,8 @@
 // Bound: fp64 ALU / log throughput, not HBM.
 
 #include <cmath>
+#include <string>
+#include <vector>
 
 #include "common.cuh"
 #include "grouped.cuh"
@@ -230,4 +232,80 @@ extern "C" int rpvg_b200_grouped_loglik(rpvg_b200_ctx * ctx, const rpvg_b200_gro
 
     cudaFreeAsync(base, s);
     return status;
+}
+
+// Host matrices put on the device once, for several rounds of rpvg_b200_grouped_loglik (problems->sets is not used).
+extern "C" int rpvg_b200_grouped_upload(rpvg_b200_ctx * ctx, const rpvg_b200_loglik_problems * pr, rpvg_b200_grouped ** out) {
+
+    if (!ctx || !pr || !out) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "NULL argument"); }
+    *out = nullptr;
+    if (pr->n_problems == 0) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "no problems"); }
+
+    const uint32_t P = pr->n_problems;
+    const uint64_t R = pr->row_offset[P];
+    const uint64_t Mx = pr->matrix_offset[P];
+
+    std::vector<uint32_t> rows(P);
+
+    for (uint32_t p = 0; p < P; ++p) {
+        const uint64_t r = pr->row_offset[p + 1] - pr->row_offset[p];
+        const uint64_t paths = pr->path_offset[p + 1] - pr->path_offset[p];
+        if (pr->matrix_offset[p + 1] - pr->matrix_offset[p] != r * paths) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "matrix_offset does not match rows x paths"); }
+        if (r >= 0xffffffffull) { return rpvgFail(ctx, RPVG_B200_ERR_LIMIT, "too many rows in one problem"); }
+        rows[p] = static_cast<uint32_t>(r);
+    }
+
+    RPVG_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+
+    auto pad = [](size_t b) { return (b + 255) & ~size_t(255); };
+    const size_t bytes = 3 * pad(8 * (P + 1)) + pad(4 * P) + pad(8 * Mx) + 2 * pad(8 * R) + 1024;
+
+    char * base = nullptr;
+    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&base), bytes, s));
+
+    size_t used = 0;
+    auto take = [&](size_t b) { char * q = base + used; used += pad(b); return q; };
+
+    uint64_t * d_row_offset = reinterpret_cast<uint64_t *>(take(8 * (P + 1)));
+    uint64_t * d_path_offset = reinterpret_cast<uint64_t *>(take(8 * (P + 1)));
+    uint64_t * d_matrix_offset = reinterpret_cast<uint64_t *>(take(8 * (P + 1)));
+    uint32_t * d_rows = reinterpret_cast<uint32_t *>(take(4 * P));
+    double * d_matrix = reinterpret_cast<double *>(take(8 * Mx));
+    double * d_noise = reinterpret_cast<double *>(take(8 * R));
+    double * d_counts = reinterpret_cast<double *>(take(8 * R));
+
+    cudaError_t err = cudaSuccess;
+    auto up = [&](void * dst, const void * src, size_t n) {
+        if (err == cudaSuccess && n > 0) { err = cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, s); }
+    };
+
+    up(d_row_offset, pr->row_offset, 8 * (P + 1));
+    up(d_path_offset, pr->path_offset, 8 * (P + 1));
+    up(d_matrix_offset, pr->matrix_offset, 8 * (P + 1));
+    up(d_rows, rows.data(), 4 * P);
+    up(d_matrix, pr->matrix, 8 * Mx);
+    up(d_noise, pr->noise, 8 * R);
+    up(d_counts, pr->counts, 8 * R);
+
+    if (err == cudaSuccess) { err = cudaStreamSynchronize(s); }   // `rows` and the caller's arrays may go away
+
+    if (err != cudaSuccess) {
+        cudaFreeAsync(base, s);
+        return rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("rpvg_b200_grouped_upload: ") + cudaGetErrorString(err));
+    }
+
+    auto * grouped = new rpvg_b200_grouped();
+    grouped->n_clusters = P;
+    grouped->base = base;
+    grouped->d_matrix = d_matrix;
+    grouped->d_noise = d_noise;
+    grouped->d_counts = d_counts;
+    grouped->d_row_offset = d_row_offset;
+    grouped->d_group_offset = d_path_offset;
+    grouped->d_matrix_offset = d_matrix_offset;
+    grouped->d_n_classes = d_rows;
+    *out = grouped;
+
+    return RPVG_B200_OK;
 }

@@ -432,3 +432,130 @@ void NestedPathAbundanceEstimator::estimateBatch(const vector<PathClusterEstimat
 
     lap("F accumulate");
 }
+
+// haplotypes model (posteriors over the raw matrix, rpvg:src/path_posterior_estimator.cpp:9-71): dense matrices of all
+// clusters built on all cores and uploaded once, then the rounds of the staged posterior calculation
+void PathEstimator::posteriorsBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const uint32_t group_size, const bool bounded, const double min_rel_likelihood) const {
+
+    vector<size_t> members;
+    for (size_t i = 0; i < estimates.size(); ++i) {
+        if (!cluster_probs[i]->empty()) { members.push_back(i); }
+    }
+
+    if (members.empty()) { return; }
+
+    const size_t n = members.size();
+
+    vector<uint64_t> row_offset = {0}, path_offset = {0}, matrix_offset = {0};
+
+    for (auto i: members) {
+        const uint64_t rows = cluster_probs[i]->size();
+        const uint64_t num_paths = estimates[i]->paths.size();
+        row_offset.push_back(row_offset.back() + rows);
+        path_offset.push_back(path_offset.back() + num_paths);
+        matrix_offset.push_back(matrix_offset.back() + rows * num_paths);
+    }
+
+    vector<double> matrix(matrix_offset.back(), 0), noise(row_offset.back()), counts(row_offset.back());
+    vector<GroupPosteriorPlan> plans(n);
+
+    #pragma omp parallel for schedule(dynamic, 8)
+    for (size_t k = 0; k < n; ++k) {
+
+        const auto & probs = *cluster_probs[members[k]];
+        PathClusterEstimates * est = estimates[members[k]];
+
+        const size_t rows = probs.size();
+        const size_t num_paths = est->paths.size();
+
+        double * block = matrix.data() + matrix_offset[k];   // column-major rows x paths, as denseMatrix leaves it
+
+        for (size_t r = 0; r < rows; ++r) {
+
+            for (auto & path_probs: probs[r].pathProbs()) {
+                for (auto & path: path_probs.second) {
+                    assert(path < num_paths);
+                    block[static_cast<size_t>(path) * rows + r] = path_probs.first;
+                }
+            }
+
+            noise[row_offset[k] + r] = probs[r].noiseProb();
+            counts[row_offset[k] + r] = probs[r].readCount();
+        }
+
+        vector<uint32_t> path_counts;
+        path_counts.reserve(num_paths);
+        for (auto & path: est->paths) { path_counts.emplace_back(path.source_count); }
+
+        planPathGroupPosteriors(&plans[k], est, num_paths, path_counts, group_size, bounded, min_rel_likelihood);
+    }
+
+    auto * ctx = threadContext();
+
+    rpvg_b200_loglik_problems problems;
+    problems.n_problems = static_cast<uint32_t>(n);
+    problems.row_offset = row_offset.data();
+    problems.path_offset = path_offset.data();
+    problems.matrix_offset = matrix_offset.data();
+    problems.set_offset = nullptr;
+    problems.matrix = matrix.data();
+    problems.noise = noise.data();
+    problems.counts = counts.data();
+    problems.group_size = group_size;
+    problems.sets = nullptr;
+
+    rpvg_b200_grouped * resident = nullptr;
+    if (rpvg_b200_grouped_upload(ctx, &problems, &resident) != RPVG_B200_OK) { fatalBatch(ctx, "rpvg_b200_grouped_upload"); }
+
+    bool more_rounds = true;
+
+    while (more_rounds) {
+
+        const uint32_t set_size = plans.front().set_size;
+
+        vector<uint64_t> set_offset = {0};
+        vector<uint32_t> sets;
+
+        for (auto & plan: plans) {
+            assert(plan.set_size == set_size);
+            sets.insert(sets.end(), plan.flat_sets.begin(), plan.flat_sets.end());
+            set_offset.push_back(sets.size() / set_size);
+        }
+
+        vector<double> loglik(set_offset.back(), 0);
+        if (rpvg_b200_grouped_loglik(ctx, resident, set_size, set_offset.data(), sets.data(), loglik.data()) != RPVG_B200_OK) { fatalBatch(ctx, "rpvg_b200_grouped_loglik"); }
+
+        vector<char> more(n, 0);
+
+        #pragma omp parallel for schedule(dynamic, 8)
+        for (size_t k = 0; k < n; ++k) { more[k] = advancePathGroupPosteriors(&plans[k], estimates[members[k]], loglik.data() + set_offset[k]) ? 1 : 0; }
+
+        more_rounds = more.front() != 0;
+        for (auto m: more) { assert((m != 0) == more_rounds); }
+    }
+
+    rpvg_b200_grouped_free(ctx, resident);
+}
+
+void PathPosteriorEstimator::estimateBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const vector<mt19937 *> & rngs) {
+
+    assert(estimates.size() == cluster_probs.size());
+
+    for (auto & est: estimates) { est->resetEstimates(est->paths.size(), 1); }
+    posteriorsBatch(estimates, cluster_probs, 1, false, 1);
+}
+
+void PathGroupPosteriorEstimator::estimateBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const vector<mt19937 *> & rngs) {
+
+    assert(estimates.size() == cluster_probs.size());
+
+    if (use_group_post_gibbs) {
+        PathEstimator::estimateBatch(estimates, cluster_probs, rngs);
+        return;
+    }
+
+    for (auto & est: estimates) { est->resetEstimates(0, 0); }
+
+    // rpvg:src/path_posterior_estimator.cpp:5 — min_rel_likelihood of the bounded calculation
+    posteriorsBatch(estimates, cluster_probs, group_size, group_size == 2, 1e-8);
+}

@@ -180,6 +180,10 @@ class PathEstimator {
         // are in path_cluster_estimates.
         bool advancePathGroupPosteriors(GroupPosteriorPlan * plan, PathClusterEstimates * path_cluster_estimates, const double * loglik) const;
 
+        // Full (any k) or Bounded (k = 2) posteriors over the raw probability matrices of many clusters: the matrices go
+        // to the device once, every round of log-likelihoods is one call for all clusters (batch.cpp).
+        void posteriorsBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const uint32_t group_size, const bool bounded, const double min_rel_likelihood) const;
+
         // One context per calling thread: estimate() is re-entrant on a shared object (rpvg:src/main.cpp:829-830).
         static rpvg_b200_ctx * threadContext();
 
@@ -291,6 +295,7 @@ class PathPosteriorEstimator : public PathEstimator {
         virtual ~PathPosteriorEstimator() {};
 
         void estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng);
+        void estimateBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const vector<mt19937 *> & rngs);
 };
 
 class PathGroupPosteriorEstimator : public PathPosteriorEstimator {
@@ -301,6 +306,9 @@ class PathGroupPosteriorEstimator : public PathPosteriorEstimator {
         ~PathGroupPosteriorEstimator() {};
 
         void estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng);
+
+        // (--use-hap-gibbs samples on the host between the device calls of a cluster: looped)
+        void estimateBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const vector<mt19937 *> & rngs);
 
     private:
 

@@ -77,3 +77,17 @@ def test_other_models_fall_back_to_the_loop(b200_harness):
         _, batched = loader.harness_estimate_batched(b200_harness, cfg, arena, rng_seed=9)
         for a, b in zip(batched, one_by_one):
             same(a, b, exact=True)
+
+
+@pytest.mark.parametrize("model, k", [(loader.MODEL_PATH_POSTERIOR, 1), (loader.MODEL_HAPLOTYPES, 2), (loader.MODEL_HAPLOTYPES, 3), (loader.MODEL_HAPLOTYPES, 1)])
+def test_posterior_batch_equals_per_cluster_and_reference(b200_harness, reference, model, k):
+    """Haplotypes model: raw matrices of all clusters on the device once, one log-likelihood call per round."""
+    arena = hap_arena(90 + k, n=9)
+    cfg = loader.make_config(model, group_size=k)
+    _, one_by_one = loader.harness_estimate_batch(b200_harness, cfg, arena, rng_seed=2, num_threads=1)
+    _, batched = loader.harness_estimate_batched(b200_harness, cfg, arena, rng_seed=2)
+    _, ref = loader.harness_estimate_batch(reference, cfg, arena, rng_seed=2)
+    for a, b, r in zip(batched, one_by_one, ref):
+        same(a, b, exact=True)
+        assert a["sets"] == r["sets"]
+        assert np.max(np.abs(a["posteriors"] - r["posteriors"]), initial=0) < 1e-9
