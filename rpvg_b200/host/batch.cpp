@@ -559,3 +559,111 @@ void PathGroupPosteriorEstimator::estimateBatch(const vector<PathClusterEstimate
     // rpvg:src/path_posterior_estimator.cpp:5 — min_rel_likelihood of the bounded calculation
     posteriorsBatch(estimates, cluster_probs, group_size, group_size == 2, 1e-8);
 }
+
+// strains model (rpvg:src/path_abundance_estimator.cpp:217-295): covers of all clusters in one call, then the EM on every
+// cluster's cover (partial matrix, normalise, collapse, EM, Gibbs) in one call
+void MinimumPathAbundanceEstimator::estimateBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const vector<mt19937 *> & rngs) {
+
+    assert(estimates.size() == cluster_probs.size());
+    assert(estimates.size() == rngs.size());
+
+    vector<size_t> members;
+
+    for (size_t i = 0; i < estimates.size(); ++i) {
+        estimates[i]->resetEstimates(estimates[i]->paths.size(), 1);
+        if (!cluster_probs[i]->empty()) { members.push_back(i); }
+    }
+
+    if (members.empty()) { return; }
+
+    BatchArena arena;
+    {
+        vector<const vector<ReadPathProbabilities> *> member_probs;
+        vector<uint32_t> member_paths;
+        for (auto i: members) {
+            member_probs.push_back(cluster_probs[i]);
+            member_paths.push_back(estimates[i]->paths.size());
+        }
+        arena.build(member_probs, member_paths);
+    }
+
+    rpvg_b200_clusters clusters = arena.view();
+    auto * ctx = threadContext();
+
+    // rpvg:src/path_abundance_estimator.cpp:229-252
+    vector<uint8_t> in_cover(arena.path_offset.back(), 0);
+    if (rpvg_b200_path_cover(ctx, &clusters, in_cover.data()) != RPVG_B200_OK) { fatalBatch(ctx, "rpvg_b200_path_cover"); }
+
+    // :254-282 one subset (the cover) per cluster that has one
+    vector<uint32_t> subset_cluster, subset_paths, gibbs_counts;
+    vector<uint64_t> subset_offset = {0}, gibbs_seeds;
+    size_t total_values = 0;
+
+    for (size_t k = 0; k < members.size(); ++k) {
+
+        const size_t p0 = arena.path_offset[k], p1 = arena.path_offset[k + 1];
+        const size_t before = subset_paths.size();
+
+        for (size_t j = p0; j < p1; ++j) {
+            if (in_cover[j]) { subset_paths.push_back(static_cast<uint32_t>(j - p0)); }
+        }
+
+        if (subset_paths.size() == before) { continue; }   // empty cover: the reset estimates stand
+
+        subset_cluster.push_back(static_cast<uint32_t>(k));
+        subset_offset.push_back(subset_paths.size());
+        gibbs_counts.push_back(num_gibbs_samples);
+
+        uint64_t seed = 0;
+        if (num_gibbs_samples > 0) {
+            mt19937 * mt_rng = rngs[members[k]];
+            seed = (static_cast<uint64_t>((*mt_rng)()) << 32) | (*mt_rng)();
+        }
+        gibbs_seeds.push_back(seed);
+        total_values += static_cast<size_t>(num_gibbs_samples) * (subset_paths.size() - before);
+    }
+
+    if (subset_cluster.empty()) { return; }
+
+    rpvg_b200_subsets subsets = {static_cast<uint32_t>(subset_cluster.size()), subset_cluster.data(), subset_offset.data(), subset_paths.data()};
+
+    rpvg_b200_em_params params;
+    rpvg_b200_em_params_default(&params);
+    params.max_em_its = max_em_its;
+    params.max_rel_em_conv = max_rel_em_conv;
+
+    vector<double> cover_abundances(subset_paths.size(), 0), noise_counts(subset_cluster.size(), 0), total_counts(subset_cluster.size(), 0);
+    vector<double> gibbs_abundances(total_values), gibbs_noise(static_cast<size_t>(num_gibbs_samples) * subset_cluster.size());
+
+    rpvg_b200_gibbs gibbs = {gibbs_counts.data(), gibbs_thin_its, gibbs_seeds.data(), gibbs_abundances.data(), gibbs_noise.data()};
+
+    if (rpvg_b200_subset_em_gibbs(ctx, &clusters, &subsets, &params, prob_precision, num_gibbs_samples > 0 ? &gibbs : nullptr, cover_abundances.data(), noise_counts.data(),
+                                  total_counts.data(), nullptr, nullptr) != RPVG_B200_OK) {
+        fatalBatch(ctx, "rpvg_b200_subset_em");
+    }
+
+    size_t value_pos = 0;
+
+    for (size_t s = 0; s < subset_cluster.size(); ++s) {
+
+        PathClusterEstimates * est = estimates[members[subset_cluster[s]]];
+        const size_t c0 = subset_offset[s], c1 = subset_offset[s + 1];
+
+        if (num_gibbs_samples > 0) {
+
+            CountSamples samples;
+            samples.path_ids.assign(subset_paths.begin() + c0, subset_paths.begin() + c1);
+            samples.noise_samples.assign(gibbs_noise.begin() + s * num_gibbs_samples, gibbs_noise.begin() + (s + 1) * num_gibbs_samples);
+            samples.abundance_samples.assign(gibbs_abundances.begin() + value_pos, gibbs_abundances.begin() + value_pos + static_cast<size_t>(num_gibbs_samples) * (c1 - c0));
+            value_pos += static_cast<size_t>(num_gibbs_samples) * (c1 - c0);
+
+            est->gibbs_read_count_samples.emplace_back(std::move(samples));
+        }
+
+        // :286-292
+        for (size_t i = c0; i < c1; ++i) { est->abundances.at(subset_paths[i]) += cover_abundances[i]; }
+
+        est->noise_count = noise_counts[s];
+        est->total_count = total_counts[s];
+    }
+}

@@ -230,10 +230,8 @@ class MinimumPathAbundanceEstimator : public PathAbundanceEstimator {
 
         void estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng);
 
-        // (the greedy cover couples the phases of a cluster; clusters are looped over)
-        void estimateBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const vector<mt19937 *> & rngs) {
-            PathEstimator::estimateBatch(estimates, cluster_probs, rngs);
-        }
+        // two device calls for the whole batch: the path covers of all clusters, then the EMs (and Gibbs samples) on them
+        void estimateBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const vector<mt19937 *> & rngs);
 };
 
 class NestedPathAbundanceEstimator : public PathAbundanceEstimator {

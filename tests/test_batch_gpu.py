@@ -91,3 +91,17 @@ def test_posterior_batch_equals_per_cluster_and_reference(b200_harness, referenc
         same(a, b, exact=True)
         assert a["sets"] == r["sets"]
         assert np.max(np.abs(a["posteriors"] - r["posteriors"]), initial=0) < 1e-9
+
+
+@pytest.mark.parametrize("gibbs", [0, 8])
+def test_strains_batch_equals_per_cluster(b200_harness, gibbs):
+    arena = concat([synth.transcripts_arena(seed=33, n_paths=500, n_reads=3000, n_max=70), hap_arena(95, n=5)])
+    cfg = loader.make_config(loader.MODEL_STRAINS, num_gibbs_samples=gibbs)
+    _, one_by_one = loader.harness_estimate_batch(b200_harness, cfg, arena, rng_seed=4, num_threads=1)
+    _, batched = loader.harness_estimate_batched(b200_harness, cfg, arena, rng_seed=4)
+    for a, b in zip(batched, one_by_one):
+        same(a, b, exact=True)
+        assert len(a["gibbs"]) == len(b["gibbs"])
+        for ga, gb in zip(a["gibbs"], b["gibbs"]):
+            assert np.array_equal(ga["path_ids"], gb["path_ids"])
+            assert np.array_equal(ga["noise_samples"], gb["noise_samples"]) and np.array_equal(ga["abundance_samples"], gb["abundance_samples"])
