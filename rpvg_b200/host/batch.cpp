@@ -277,6 +277,8 @@ void NestedPathAbundanceEstimator::estimateBatch(const vector<PathClusterEstimat
 
     // (the host stages are independent per cluster: all cores, like the reference's loop; the device calls are made by
     // this thread)
+    lap("A flatten");
+
     #pragma omp parallel for schedule(dynamic, 8)
     for (size_t k = 0; k < items.size(); ++k) { items[k].source_groups = findPathSourceGroups(estimates[items[k].index]->paths); }
 
@@ -327,13 +329,15 @@ void NestedPathAbundanceEstimator::estimateBatch(const vector<PathClusterEstimat
             const uint32_t set_size = items.front().plan.set_size;
 
             vector<uint64_t> set_offset = {0};
-            vector<uint32_t> sets;
-
             for (auto & item: items) {
                 assert(item.plan.set_size == set_size);
-                sets.insert(sets.end(), item.plan.flat_sets.begin(), item.plan.flat_sets.end());
-                set_offset.push_back(sets.size() / set_size);
+                set_offset.push_back(set_offset.back() + item.plan.flat_sets.size() / set_size);
             }
+
+            vector<uint32_t> sets(set_offset.back() * set_size);
+
+            #pragma omp parallel for schedule(dynamic, 8)
+            for (size_t k = 0; k < items.size(); ++k) { copy(items[k].plan.flat_sets.begin(), items[k].plan.flat_sets.end(), sets.begin() + set_offset[k] * set_size); }
 
             lap("C   concatenate");
 
@@ -514,13 +518,15 @@ void PathEstimator::posteriorsBatch(const vector<PathClusterEstimates *> & estim
         const uint32_t set_size = plans.front().set_size;
 
         vector<uint64_t> set_offset = {0};
-        vector<uint32_t> sets;
-
         for (auto & plan: plans) {
             assert(plan.set_size == set_size);
-            sets.insert(sets.end(), plan.flat_sets.begin(), plan.flat_sets.end());
-            set_offset.push_back(sets.size() / set_size);
+            set_offset.push_back(set_offset.back() + plan.flat_sets.size() / set_size);
         }
+
+        vector<uint32_t> sets(set_offset.back() * set_size);
+
+        #pragma omp parallel for schedule(dynamic, 8)
+        for (size_t k = 0; k < n; ++k) { copy(plans[k].flat_sets.begin(), plans[k].flat_sets.end(), sets.begin() + set_offset[k] * set_size); }
 
         vector<double> loglik(set_offset.back(), 0);
         if (rpvg_b200_grouped_loglik(ctx, resident, set_size, set_offset.data(), sets.data(), loglik.data()) != RPVG_B200_OK) { fatalBatch(ctx, "rpvg_b200_grouped_loglik"); }

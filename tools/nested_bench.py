@@ -28,7 +28,12 @@ else:
 print(f"{n_clusters} clusters, {arena.n_paths} paths, {arena.n_reads} read classes, ready in {time.time() - t0:.1f} s", flush=True)
 if len(sys.argv) > 3 and sys.argv[3] == "generate-only":
     raise SystemExit(0)
-cfg = loader.make_config(loader.MODEL_HAPLOTYPE_TRANSCRIPTS, group_size=2)
+model = os.environ.get("RPVG_BENCH_MODEL", "haplotype-transcripts")
+cfg = {"haplotype-transcripts": loader.make_config(loader.MODEL_HAPLOTYPE_TRANSCRIPTS, group_size=2),
+       "haplotypes": loader.make_config(loader.MODEL_HAPLOTYPES, group_size=2),
+       "strains": loader.make_config(loader.MODEL_STRAINS),
+       "transcripts": loader.make_config(loader.MODEL_TRANSCRIPTS)}[model]
+print("inference model:", model, flush=True)
 
 b200 = loader.load_harness(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "_build", "libharness_b200.so"))
 batch_only = len(sys.argv) > 3 and sys.argv[3] == "batch-only"
