@@ -195,6 +195,16 @@ int rpvg_b200_grouped_loglik(rpvg_b200_ctx * ctx, const rpvg_b200_grouped * grou
 /* Dense matrices the caller built itself (the layout of rpvg_b200_loglik_problems; its `sets` is not used), put on the
  * device once for several rounds of rpvg_b200_grouped_loglik: the batched driver of the haplotype posterior classes. */
 int rpvg_b200_grouped_upload(rpvg_b200_ctx * ctx, const rpvg_b200_loglik_problems * problems, rpvg_b200_grouped ** grouped);
+/* The pair walk of calculatePathGroupPosteriorsBounded (rpvg:src/path_estimator.cpp:424-450) on the resident matrices:
+ * for each cluster all pairs (i, j >= i) of order[] (its groups in the caller's order, at group_offset[c]) get
+ * ll = rpvg_b200_grouped_loglik's sum + log_freq[a] + log_freq[b] + log(numPermutations); a pair is a candidate unless
+ * ll - (largest ll of the pairs before it) < min_log_diff. Returned: per cluster the candidates in pair order —
+ * cand_pair = index of the pair in that enumeration, cand_loglik = its sum over the read classes (without the
+ * frequency terms) — in memory owned by the handle (valid until the next call on it or its release). Pass
+ * min_log_diff a little below log(min_rel_likelihood) and replay the reference's walk on the candidates: pairs left
+ * out fail the exact test as well and never hold the running maximum. */
+int rpvg_b200_grouped_bounded_pairs(rpvg_b200_ctx * ctx, rpvg_b200_grouped * grouped, const uint64_t * group_offset, const uint32_t * order, const double * log_freq,
+                                    double min_log_diff, const uint64_t ** cand_offset, const uint32_t ** cand_pair, const double ** cand_loglik);
 void rpvg_b200_grouped_free(rpvg_b200_ctx * ctx, rpvg_b200_grouped * grouped);
 
 /* ---- strains model: greedy weighted minimum path cover ----

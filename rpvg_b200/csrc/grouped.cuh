@@ -3,6 +3,7 @@
 #pragma once
 
 #include <cstdint>
+#include <vector>
 
 struct rpvg_b200_grouped {
 
@@ -15,4 +16,9 @@ struct rpvg_b200_grouped {
     const uint64_t * d_group_offset = nullptr; // [n_clusters + 1]
     const uint64_t * d_matrix_offset = nullptr;
     const uint32_t * d_n_classes = nullptr;    // [n_clusters]
+
+    // results of the last rpvg_b200_grouped_bounded_pairs on this handle (host memory, valid until the next one / free)
+    std::vector<uint64_t> h_cand_offset;
+    std::vector<uint32_t> h_cand_pair;
+    std::vector<double> h_cand_loglik;
 };

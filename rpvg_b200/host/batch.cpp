@@ -12,6 +12,7 @@
 #include <chrono>
 #include <cstdlib>
 #include <iostream>
+#include <memory>
 #include <numeric>
 
 #include "rpvg_b200.h"
@@ -28,35 +29,12 @@ namespace {
 // class sorted by path — the flattening estimate() does for one cluster.
 struct BatchArena {
 
-    vector<uint64_t> read_offset = {0}, path_offset = {0}, row_ptr = {0};
-    vector<uint32_t> col, count;
-    vector<double> prob, noise;
+    vector<uint64_t> read_offset = {0}, path_offset = {0};
 
-    void add(const vector<ReadPathProbabilities> & cluster_probs, const uint32_t num_paths) {
-
-        vector<pair<uint32_t, double> > row;
-
-        for (auto & read_probs: cluster_probs) {
-
-            row.clear();
-            for (auto & path_probs: read_probs.pathProbs()) {
-                for (auto & path: path_probs.second) { row.emplace_back(path, path_probs.first); }
-            }
-            sort(row.begin(), row.end());
-
-            for (auto & entry: row) {
-                col.push_back(entry.first);
-                prob.push_back(entry.second);
-            }
-
-            row_ptr.push_back(col.size());
-            noise.push_back(read_probs.noiseProb());
-            count.push_back(read_probs.readCount());
-        }
-
-        read_offset.push_back(noise.size());
-        path_offset.push_back(path_offset.back() + num_paths);
-    }
+    // filled completely by build(): plain arrays, so that nothing is value-initialised first
+    unique_ptr<uint64_t[]> row_ptr;
+    unique_ptr<uint32_t[]> col, count;
+    unique_ptr<double[]> prob, noise;
 
     // all clusters at once, the clusters filled in parallel
     void build(const vector<const vector<ReadPathProbabilities> *> & members, const vector<uint32_t> & num_paths) {
@@ -83,11 +61,12 @@ struct BatchArena {
             entry_offset.push_back(entry_offset.back() + entries[k]);
         }
 
-        row_ptr.assign(read_offset.back() + 1, 0);
-        col.resize(entry_offset.back());
-        prob.resize(entry_offset.back());
-        noise.resize(read_offset.back());
-        count.resize(read_offset.back());
+        row_ptr.reset(new uint64_t[read_offset.back() + 1]);
+        col.reset(new uint32_t[entry_offset.back() + 1]);
+        prob.reset(new double[entry_offset.back() + 1]);
+        noise.reset(new double[read_offset.back() + 1]);
+        count.reset(new uint32_t[read_offset.back() + 1]);
+        row_ptr[0] = 0;
 
         #pragma omp parallel for schedule(dynamic, 8)
         for (size_t k = 0; k < n; ++k) {
@@ -121,10 +100,78 @@ struct BatchArena {
     uint32_t size() const { return static_cast<uint32_t>(read_offset.size() - 1); }
 
     rpvg_b200_clusters view() const {
-        return rpvg_b200_clusters{size(), read_offset.data(), path_offset.data(), row_ptr.data(), col.data(), prob.data(), noise.data(), count.data()};
+        return rpvg_b200_clusters{size(), read_offset.data(), path_offset.data(), row_ptr.get(), col.get(), prob.get(), noise.get(), count.get()};
     }
 };
 
+}
+
+void PathEstimator::runPosteriorRounds(rpvg_b200_ctx * ctx, rpvg_b200_grouped * resident, const vector<uint64_t> & group_offset, vector<GroupPosteriorPlan> * plans, const vector<PathClusterEstimates *> & outs) const {
+
+    const size_t n = plans->size();
+    if (n == 0) { return; }
+
+    const bool bounded = plans->front().bounded;
+    for (auto & plan: *plans) { plan.device_pairs = bounded; }
+
+    // round 1: the first request of every plan (Full: all multisets; Bounded: the single groups)
+    {
+        const uint32_t set_size = plans->front().set_size;
+
+        vector<uint64_t> set_offset = {0};
+        for (auto & plan: *plans) {
+            assert(plan.set_size == set_size && plan.bounded == bounded);
+            set_offset.push_back(set_offset.back() + plan.flat_sets.size() / set_size);
+        }
+
+        vector<uint32_t> sets(set_offset.back() * set_size);
+
+        #pragma omp parallel for schedule(dynamic, 8)
+        for (size_t k = 0; k < n; ++k) { copy((*plans)[k].flat_sets.begin(), (*plans)[k].flat_sets.end(), sets.begin() + set_offset[k] * set_size); }
+
+        vector<double> loglik(set_offset.back(), 0);
+        if (rpvg_b200_grouped_loglik(ctx, resident, set_size, set_offset.data(), sets.data(), loglik.data()) != RPVG_B200_OK) { fatalBatch(ctx, "rpvg_b200_grouped_loglik"); }
+
+        #pragma omp parallel for schedule(dynamic, 8)
+        for (size_t k = 0; k < n; ++k) {
+            const bool more = advancePathGroupPosteriors(&(*plans)[k], outs[k], loglik.data() + set_offset[k]);
+            assert(more == bounded);
+            (void) more;
+        }
+    }
+
+    if (!bounded) { return; }
+
+    // round 2 (Bounded): the pairs are enumerated, evaluated and pre-filtered on the device from each cluster's order of
+    // groups; the reference's walk is replayed over the candidates (a margin of 1e-6 in log space keeps every pair the
+    // exact test could keep)
+    vector<uint32_t> order(group_offset.back());
+    vector<double> log_freq(group_offset.back());
+
+    #pragma omp parallel for schedule(dynamic, 8)
+    for (size_t k = 0; k < n; ++k) {
+        const auto & plan = (*plans)[k];
+        assert(plan.marginal_posteriors.size() == group_offset[k + 1] - group_offset[k]);
+        for (size_t i = 0; i < plan.marginal_posteriors.size(); ++i) {
+            order[group_offset[k] + i] = plan.marginal_posteriors[i].second;
+            log_freq[group_offset[k] + i] = plan.path_log_freqs[i];
+        }
+    }
+
+    const uint64_t * cand_offset = nullptr;
+    const uint32_t * cand_pair = nullptr;
+    const double * cand_loglik = nullptr;
+
+    if (rpvg_b200_grouped_bounded_pairs(ctx, resident, group_offset.data(), order.data(), log_freq.data(), plans->front().min_log_likelihood_diff - 1e-6, &cand_offset, &cand_pair,
+                                        &cand_loglik) != RPVG_B200_OK) {
+        fatalBatch(ctx, "rpvg_b200_grouped_bounded_pairs");
+    }
+
+    #pragma omp parallel for schedule(dynamic, 8)
+    for (size_t k = 0; k < n; ++k) {
+        const uint64_t c0 = cand_offset[k];
+        finishBoundedPathGroupPosteriors(&(*plans)[k], outs[k], cand_offset[k + 1] - c0, cand_pair ? cand_pair + c0 : nullptr, cand_loglik ? cand_loglik + c0 : nullptr);
+    }
 }
 
 void PathEstimator::estimateBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const vector<mt19937 *> & rngs) {
@@ -237,7 +284,6 @@ void NestedPathAbundanceEstimator::estimateBatch(const vector<PathClusterEstimat
         size_t index;
         pair<vector<vector<uint32_t> >, vector<uint32_t> > source_groups;
         PathClusterEstimates group_estimates;
-        GroupPosteriorPlan plan;
         vector<SubsetJob> jobs;
     };
 
@@ -289,8 +335,11 @@ void NestedPathAbundanceEstimator::estimateBatch(const vector<PathClusterEstimat
 
     // ---- stage B: grouped + normalised + collapsed matrix of every cluster; they stay on the device for stage C
     rpvg_b200_grouped * grouped = nullptr;
+    vector<uint64_t> group_offset = {0};
+    vector<GroupPosteriorPlan> plans(items.size());
+    vector<PathClusterEstimates *> group_outs(items.size());
     {
-        vector<uint64_t> group_offset = {0}, group_path_ptr = {0};
+        vector<uint64_t> group_path_ptr = {0};
         vector<uint32_t> group_paths;
 
         for (size_t k = 0; k < items.size(); ++k) {
@@ -311,57 +360,17 @@ void NestedPathAbundanceEstimator::estimateBatch(const vector<PathClusterEstimat
         #pragma omp parallel for schedule(dynamic, 8)
         for (size_t k = 0; k < items.size(); ++k) {
             assert(n_classes[k] > 0);
-            planPathGroupPosteriors(&items[k].plan, &items[k].group_estimates, items[k].source_groups.first.size(), items[k].source_groups.second, group_size, group_size == 2,
-                                    min_hap_prob);
+            group_outs[k] = &items[k].group_estimates;
+            planPathGroupPosteriors(&plans[k], group_outs[k], items[k].source_groups.first.size(), items[k].source_groups.second, group_size, group_size == 2, min_hap_prob);
         }
     }
 
     lap("B grouped collapse");
 
-    // ---- stage C: posteriors of the haplotype combinations; every round is one log-likelihood call for all clusters
-    // (Full: one round; Bounded: marginals, then the pairs). All clusters run the same kind of plan, so they have a
-    // request in the same rounds.
-    {
-        bool more_rounds = true;
-
-        while (more_rounds) {
-
-            const uint32_t set_size = items.front().plan.set_size;
-
-            vector<uint64_t> set_offset = {0};
-            for (auto & item: items) {
-                assert(item.plan.set_size == set_size);
-                set_offset.push_back(set_offset.back() + item.plan.flat_sets.size() / set_size);
-            }
-
-            vector<uint32_t> sets(set_offset.back() * set_size);
-
-            #pragma omp parallel for schedule(dynamic, 8)
-            for (size_t k = 0; k < items.size(); ++k) { copy(items[k].plan.flat_sets.begin(), items[k].plan.flat_sets.end(), sets.begin() + set_offset[k] * set_size); }
-
-            lap("C   concatenate");
-
-            vector<double> loglik(set_offset.back(), 0);
-            if (rpvg_b200_grouped_loglik(ctx, grouped, set_size, set_offset.data(), sets.data(), loglik.data()) != RPVG_B200_OK) { fatalBatch(ctx, "rpvg_b200_grouped_loglik"); }
-
-            if (trace) { cerr << "[rpvg_b200 batch]     " << set_offset.back() << " sets of " << set_size << endl; }
-            lap("C   device log-likelihoods");
-
-            vector<char> more(items.size(), 0);
-
-            #pragma omp parallel for schedule(dynamic, 8)
-            for (size_t k = 0; k < items.size(); ++k) {
-                more[k] = advancePathGroupPosteriors(&items[k].plan, &items[k].group_estimates, loglik.data() + set_offset[k]) ? 1 : 0;
-            }
-
-            lap("C   advance");
-
-            more_rounds = more.front() != 0;
-            for (auto m: more) { assert((m != 0) == more_rounds); }
-        }
-
-        rpvg_b200_grouped_free(ctx, grouped);
-    }
+    // ---- stage C: posteriors of the haplotype combinations (Full: one log-likelihood call for all clusters; Bounded: the
+    // marginals, then the pair walk on the device)
+    runPosteriorRounds(ctx, grouped, group_offset, &plans, group_outs);
+    rpvg_b200_grouped_free(ctx, grouped);
 
     lap("C posteriors");
 
@@ -511,34 +520,10 @@ void PathEstimator::posteriorsBatch(const vector<PathClusterEstimates *> & estim
     rpvg_b200_grouped * resident = nullptr;
     if (rpvg_b200_grouped_upload(ctx, &problems, &resident) != RPVG_B200_OK) { fatalBatch(ctx, "rpvg_b200_grouped_upload"); }
 
-    bool more_rounds = true;
+    vector<PathClusterEstimates *> outs(n);
+    for (size_t k = 0; k < n; ++k) { outs[k] = estimates[members[k]]; }
 
-    while (more_rounds) {
-
-        const uint32_t set_size = plans.front().set_size;
-
-        vector<uint64_t> set_offset = {0};
-        for (auto & plan: plans) {
-            assert(plan.set_size == set_size);
-            set_offset.push_back(set_offset.back() + plan.flat_sets.size() / set_size);
-        }
-
-        vector<uint32_t> sets(set_offset.back() * set_size);
-
-        #pragma omp parallel for schedule(dynamic, 8)
-        for (size_t k = 0; k < n; ++k) { copy(plans[k].flat_sets.begin(), plans[k].flat_sets.end(), sets.begin() + set_offset[k] * set_size); }
-
-        vector<double> loglik(set_offset.back(), 0);
-        if (rpvg_b200_grouped_loglik(ctx, resident, set_size, set_offset.data(), sets.data(), loglik.data()) != RPVG_B200_OK) { fatalBatch(ctx, "rpvg_b200_grouped_loglik"); }
-
-        vector<char> more(n, 0);
-
-        #pragma omp parallel for schedule(dynamic, 8)
-        for (size_t k = 0; k < n; ++k) { more[k] = advancePathGroupPosteriors(&plans[k], estimates[members[k]], loglik.data() + set_offset[k]) ? 1 : 0; }
-
-        more_rounds = more.front() != 0;
-        for (auto m: more) { assert((m != 0) == more_rounds); }
-    }
+    runPosteriorRounds(ctx, resident, path_offset, &plans, outs);
 
     rpvg_b200_grouped_free(ctx, resident);
 }

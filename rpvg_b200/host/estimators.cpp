@@ -286,6 +286,12 @@ bool PathEstimator::advancePathGroupPosteriors(GroupPosteriorPlan * plan, PathCl
         // have skipped has a log-likelihood below the bound, so the replay drops it as well: the list comes out the same.
         plan->set_size = 2;
         plan->flat_sets.clear();
+
+        if (plan->device_pairs) {   // the caller enumerates the pairs on the device from marginal_posteriors
+            plan->stage = 1;
+            return true;
+        }
+
         plan->flat_sets.reserve(static_cast<size_t>(plan->num_paths) * (plan->num_paths + 1));
 
         for (uint32_t i = 0; i < plan->marginal_posteriors.size(); ++i) {
@@ -337,6 +343,56 @@ bool PathEstimator::advancePathGroupPosteriors(GroupPosteriorPlan * plan, PathCl
 
     plan->stage = 2;
     return false;
+}
+
+void PathEstimator::finishBoundedPathGroupPosteriors(GroupPosteriorPlan * plan, PathClusterEstimates * path_cluster_estimates, const size_t n_candidates, const uint32_t * cand_pair, const double * cand_loglik) const {
+
+    assert(plan->bounded && plan->stage == 1);
+
+    const uint32_t G = plan->marginal_posteriors.size();
+
+    vector<double> log_likelihoods;
+    double max_log_likelihood = numeric_limits<double>::lowest();
+
+    // pair index -> (i, j): row i of the enumeration starts at i * G - i (i - 1) / 2; the candidates come ascending
+    uint32_t i = 0;
+    uint64_t row_start = 0;
+
+    for (size_t k = 0; k < n_candidates; ++k) {
+
+        const uint64_t pair_idx = cand_pair[k];
+        while (i + 1 < G && row_start + (G - i) <= pair_idx) {
+            row_start += G - i;
+            ++i;
+        }
+
+        const uint32_t j = i + static_cast<uint32_t>(pair_idx - row_start);
+        assert(j < G);
+
+        const uint32_t first_path_idx = plan->marginal_posteriors.at(i).second;
+        const uint32_t second_path_idx = plan->marginal_posteriors.at(j).second;
+
+        double log_likelihood = cand_loglik[k];
+        log_likelihood += plan->path_log_freqs.at(first_path_idx) + plan->path_log_freqs.at(second_path_idx) + log(numPermutations(vector<uint32_t>({first_path_idx, second_path_idx})));
+
+        if (log_likelihood - max_log_likelihood < plan->min_log_likelihood_diff) { continue; }
+
+        log_likelihoods.emplace_back(log_likelihood);
+        max_log_likelihood = max(max_log_likelihood, log_likelihood);
+        path_cluster_estimates->path_group_sets.emplace_back(vector<uint32_t>({first_path_idx, second_path_idx}));
+    }
+
+    double sum_log_posterior = numeric_limits<double>::lowest();
+
+    for (size_t k = 0; k < log_likelihoods.size(); ++k) {
+
+        if (log_likelihoods.at(k) - max_log_likelihood < plan->min_log_likelihood_diff) { log_likelihoods.at(k) = numeric_limits<double>::lowest(); }
+        sum_log_posterior = add_log(sum_log_posterior, log_likelihoods.at(k));
+    }
+
+    for (auto & ll: log_likelihoods) { path_cluster_estimates->posteriors.emplace_back(exp(ll - sum_log_posterior)); }
+
+    plan->stage = 2;
 }
 
 void PathEstimator::calculatePathGroupPosteriorsFull(PathClusterEstimates * path_cluster_estimates, const vector<double> & matrix, const vector<double> & noise, const vector<double> & counts, const uint32_t num_paths, const vector<uint32_t> & path_counts, const uint32_t group_size) const {

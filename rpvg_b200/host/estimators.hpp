@@ -137,6 +137,7 @@ namespace std {
 #endif
 
 struct rpvg_b200_ctx;
+struct rpvg_b200_grouped;
 
 class PathEstimator {
 
@@ -166,6 +167,7 @@ class PathEstimator {
             double min_log_likelihood_diff = 0;
             vector<double> path_log_freqs;
 
+            bool device_pairs = false;   // bounded: the pair round is left to rpvg_b200_grouped_bounded_pairs (batch.cpp)
             int stage = 0;
             uint32_t set_size = 0;
             vector<uint32_t> flat_sets;
@@ -180,8 +182,17 @@ class PathEstimator {
         // are in path_cluster_estimates.
         bool advancePathGroupPosteriors(GroupPosteriorPlan * plan, PathClusterEstimates * path_cluster_estimates, const double * loglik) const;
 
+        // Last stage of a bounded plan with device_pairs: the reference's walk over the candidate pairs the device kept
+        // (index in the (i, j >= i) enumeration of plan->marginal_posteriors, log-likelihood sum), in pair order.
+        void finishBoundedPathGroupPosteriors(GroupPosteriorPlan * plan, PathClusterEstimates * path_cluster_estimates, const size_t n_candidates, const uint32_t * cand_pair, const double * cand_loglik) const;
+
         // Full (any k) or Bounded (k = 2) posteriors over the raw probability matrices of many clusters: the matrices go
         // to the device once, every round of log-likelihoods is one call for all clusters (batch.cpp).
+        // The device rounds of a batch of plans (all of the same kind) on resident matrices: one log-likelihood call for
+        // the first request of all plans; for bounded plans the pair walk on the device, then the exact walk over its
+        // candidates. group_offset [plans + 1]: columns (paths or groups) of each plan's matrix.
+        void runPosteriorRounds(rpvg_b200_ctx * ctx, rpvg_b200_grouped * resident, const vector<uint64_t> & group_offset, vector<GroupPosteriorPlan> * plans, const vector<PathClusterEstimates *> & outs) const;
+
         void posteriorsBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const uint32_t group_size, const bool bounded, const double min_rel_likelihood) const;
 
         // One context per calling thread: estimate() is re-entrant on a shared object (rpvg:src/main.cpp:829-830).
