@@ -105,3 +105,18 @@ def test_strains_batch_equals_per_cluster(b200_harness, gibbs):
         for ga, gb in zip(a["gibbs"], b["gibbs"]):
             assert np.array_equal(ga["path_ids"], gb["path_ids"])
             assert np.array_equal(ga["noise_samples"], gb["noise_samples"]) and np.array_equal(ga["abundance_samples"], gb["abundance_samples"])
+
+
+def test_posterior_batch_on_single_path_and_mixed_clusters(b200_harness, reference):
+    """Diploid posteriors on clusters of 1 to ~60 paths (a single path has a single pair): the device pair walk and the
+    per-cluster path agree exactly, and with the reference class."""
+    arena = synth.transcripts_arena(seed=37, n_paths=600, n_reads=3500, n_max=60)
+    cfg = loader.make_config(loader.MODEL_HAPLOTYPES, group_size=2)
+    _, one_by_one = loader.harness_estimate_batch(b200_harness, cfg, arena, rng_seed=6, num_threads=1)
+    _, batched = loader.harness_estimate_batched(b200_harness, cfg, arena, rng_seed=6)
+    _, ref = loader.harness_estimate_batch(reference, cfg, arena, rng_seed=6)
+    assert min(len(r["sets"]) for r in ref if r["total_count"] > 0 or r["sets"]) >= 1
+    for a, b, r in zip(batched, one_by_one, ref):
+        same(a, b, exact=True)
+        assert a["sets"] == r["sets"]
+        assert np.max(np.abs(a["posteriors"] - r["posteriors"]), initial=0) < 1e-9
