@@ -192,6 +192,11 @@ int rpvg_b200_grouped_create(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * clu
                              uint32_t * n_classes, rpvg_b200_grouped ** grouped);
 int rpvg_b200_grouped_loglik(rpvg_b200_ctx * ctx, const rpvg_b200_grouped * grouped, uint32_t group_size, const uint64_t * set_offset, const uint32_t * sets,
                              double * loglik);
+/* The raw matrices of the haplotypes model (constructProbabilityMatrix, rpvg:src/path_estimator.cpp:55-77: the
+ * probabilities as they are, noise apart, neither normalised nor collapsed) built on the device from the arena and kept
+ * there: problem c = cluster c, its columns = its paths. Every cluster needs at least one read class. */
+int rpvg_b200_grouped_raw(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * clusters, rpvg_b200_grouped ** grouped);
+
 /* Dense matrices the caller built itself (the layout of rpvg_b200_loglik_problems; its `sets` is not used), put on the
  * device once for several rounds of rpvg_b200_grouped_loglik: the batched driver of the haplotype posterior classes. */
 int rpvg_b200_grouped_upload(rpvg_b200_ctx * ctx, const rpvg_b200_loglik_problems * problems, rpvg_b200_grouped ** grouped);

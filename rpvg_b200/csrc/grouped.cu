@@ -372,6 +372,128 @@ extern "C" int rpvg_b200_grouped_create(rpvg_b200_ctx * ctx, const rpvg_b200_clu
     return groupedCollapse(ctx, cl, gr, prob_precision, n_classes, nullptr, nullptr, nullptr, grouped);
 }
 
+namespace {
+
+// one thread per read class: its probabilities scattered into the zero-filled dense block of its cluster
+__global__ void rawRowsKernel(const uint32_t n_clusters, const uint64_t n_reads, const uint64_t * __restrict__ read_offset, const uint64_t * __restrict__ path_offset,
+                              const uint64_t * __restrict__ matrix_offset, const uint64_t * __restrict__ row_ptr, const uint32_t * __restrict__ col,
+                              const double * __restrict__ prob, const uint32_t * __restrict__ count, double * __restrict__ matrix, double * __restrict__ counts,
+                              uint32_t * __restrict__ rows_of_cluster) {
+
+    const uint64_t r = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (r >= n_reads) { return; }
+
+    const uint32_t c = clusterOf(read_offset, n_clusters, r);
+    const uint64_t rows = read_offset[c + 1] - read_offset[c];
+    const uint64_t num_paths = path_offset[c + 1] - path_offset[c];
+    const uint64_t local = r - read_offset[c];
+
+    double * row = matrix + matrix_offset[c] + local;
+
+    for (uint64_t e = row_ptr[r]; e < row_ptr[r + 1]; ++e) {
+        const uint32_t j = col[e];
+        if (j < num_paths) { row[j * rows] = prob[e]; }
+    }
+
+    counts[r] = static_cast<double>(count[r]);
+    if (local == 0) { rows_of_cluster[c] = static_cast<uint32_t>(rows); }
+}
+
+}
+
+// The raw matrices of the haplotypes model (constructProbabilityMatrix, rpvg:src/path_estimator.cpp:55-77: probabilities
+// as they are, noise apart, no normalisation, no collapse) built on the device from the arena and kept there.
+extern "C" int rpvg_b200_grouped_raw(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, rpvg_b200_grouped ** out) {
+
+    if (!ctx || !cl || !out) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "NULL argument"); }
+    *out = nullptr;
+    if (cl->n_clusters == 0) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "no clusters"); }
+
+    const uint32_t C = cl->n_clusters;
+    const uint64_t R = cl->read_offset[C];
+    if (R == 0) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "rpvg_b200_grouped_raw: no read classes"); }
+    const uint64_t Z = cl->row_ptr[R];
+
+    std::vector<uint64_t> matrix_offset(C + 1, 0);
+    for (uint32_t c = 0; c < C; ++c) {
+        const uint64_t rows = cl->read_offset[c + 1] - cl->read_offset[c];
+        const uint64_t num_paths = cl->path_offset[c + 1] - cl->path_offset[c];
+        if (rows == 0) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "rpvg_b200_grouped_raw: a cluster has no read classes"); }
+        matrix_offset[c + 1] = matrix_offset[c] + rows * num_paths;
+    }
+
+    const uint64_t MX = matrix_offset[C];
+    if (R >= 0xffffffffull || MX >= (uint64_t(1) << 33)) { return rpvgFail(ctx, RPVG_B200_ERR_LIMIT, "dense matrices too large for one call (rows x paths)"); }
+
+    RPVG_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+
+    auto pad = [](size_t b) { return (b + 255) & ~size_t(255); };
+    const size_t bytes = 3 * pad(8 * (C + 1)) + pad(8 * (R + 1)) + pad(4 * Z) + pad(8 * Z) + 2 * pad(8 * R) + pad(4 * R) + pad(8 * MX) + pad(4 * C) + 4096;
+
+    char * base = nullptr;
+    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&base), bytes, s));
+
+    size_t used = 0;
+    auto take = [&](size_t b) { char * q = base + used; used += pad(b); return q; };
+
+    uint64_t * d_read_offset = reinterpret_cast<uint64_t *>(take(8 * (C + 1)));
+    uint64_t * d_path_offset = reinterpret_cast<uint64_t *>(take(8 * (C + 1)));
+    uint64_t * d_matrix_offset = reinterpret_cast<uint64_t *>(take(8 * (C + 1)));
+    uint64_t * d_row_ptr = reinterpret_cast<uint64_t *>(take(8 * (R + 1)));
+    uint32_t * d_col = reinterpret_cast<uint32_t *>(take(4 * Z));
+    double * d_prob = reinterpret_cast<double *>(take(8 * Z));
+    double * d_noise = reinterpret_cast<double *>(take(8 * R));
+    double * d_counts = reinterpret_cast<double *>(take(8 * R));
+    uint32_t * d_count = reinterpret_cast<uint32_t *>(take(4 * R));
+    double * d_matrix = reinterpret_cast<double *>(take(8 * MX));
+    uint32_t * d_rows = reinterpret_cast<uint32_t *>(take(4 * C));
+
+    cudaError_t err = cudaSuccess;
+    auto up = [&](void * dst, const void * src, size_t n) {
+        if (err == cudaSuccess && n > 0) { err = cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, s); }
+    };
+
+    up(d_read_offset, cl->read_offset, 8 * (C + 1));
+    up(d_path_offset, cl->path_offset, 8 * (C + 1));
+    up(d_matrix_offset, matrix_offset.data(), 8 * (C + 1));
+    up(d_row_ptr, cl->row_ptr, 8 * (R + 1));
+    up(d_col, cl->col, 4 * Z);
+    up(d_prob, cl->prob, 8 * Z);
+    up(d_noise, cl->noise, 8 * R);
+    up(d_count, cl->count, 4 * R);
+
+    if (err == cudaSuccess) { err = cudaMemsetAsync(d_matrix, 0, 8 * MX, s); }
+
+    if (err == cudaSuccess) {
+        rawRowsKernel<<<static_cast<unsigned>((R + 255) / 256), 256, 0, s>>>(C, R, d_read_offset, d_path_offset, d_matrix_offset, d_row_ptr, d_col, d_prob, d_count, d_matrix,
+                                                                            d_counts, d_rows);
+        ctx->launches++;
+        err = cudaGetLastError();
+    }
+
+    if (err == cudaSuccess) { err = cudaStreamSynchronize(s); }   // matrix_offset and the caller's arrays may go away
+
+    if (err != cudaSuccess) {
+        cudaFreeAsync(base, s);
+        return rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("rpvg_b200_grouped_raw: ") + cudaGetErrorString(err));
+    }
+
+    auto * grouped = new rpvg_b200_grouped();
+    grouped->n_clusters = C;
+    grouped->base = base;
+    grouped->d_matrix = d_matrix;
+    grouped->d_noise = d_noise;
+    grouped->d_counts = d_counts;
+    grouped->d_row_offset = d_read_offset;
+    grouped->d_group_offset = d_path_offset;
+    grouped->d_matrix_offset = d_matrix_offset;
+    grouped->d_n_classes = d_rows;
+    *out = grouped;
+
+    return RPVG_B200_OK;
+}
+
 extern "C" void rpvg_b200_grouped_free(rpvg_b200_ctx * ctx, rpvg_b200_grouped * grouped) {
 
     if (!grouped) { return; }

@@ -459,66 +459,38 @@ void PathEstimator::posteriorsBatch(const vector<PathClusterEstimates *> & estim
 
     const size_t n = members.size();
 
-    vector<uint64_t> row_offset = {0}, path_offset = {0}, matrix_offset = {0};
-
-    for (auto i: members) {
-        const uint64_t rows = cluster_probs[i]->size();
-        const uint64_t num_paths = estimates[i]->paths.size();
-        row_offset.push_back(row_offset.back() + rows);
-        path_offset.push_back(path_offset.back() + num_paths);
-        matrix_offset.push_back(matrix_offset.back() + rows * num_paths);
+    BatchArena arena;
+    {
+        vector<const vector<ReadPathProbabilities> *> member_probs;
+        vector<uint32_t> member_paths;
+        for (auto i: members) {
+            member_probs.push_back(cluster_probs[i]);
+            member_paths.push_back(estimates[i]->paths.size());
+        }
+        arena.build(member_probs, member_paths);
     }
 
-    vector<double> matrix(matrix_offset.back(), 0), noise(row_offset.back()), counts(row_offset.back());
+    const vector<uint64_t> & path_offset = arena.path_offset;
     vector<GroupPosteriorPlan> plans(n);
 
     #pragma omp parallel for schedule(dynamic, 8)
     for (size_t k = 0; k < n; ++k) {
 
-        const auto & probs = *cluster_probs[members[k]];
         PathClusterEstimates * est = estimates[members[k]];
 
-        const size_t rows = probs.size();
-        const size_t num_paths = est->paths.size();
-
-        double * block = matrix.data() + matrix_offset[k];   // column-major rows x paths, as denseMatrix leaves it
-
-        for (size_t r = 0; r < rows; ++r) {
-
-            for (auto & path_probs: probs[r].pathProbs()) {
-                for (auto & path: path_probs.second) {
-                    assert(path < num_paths);
-                    block[static_cast<size_t>(path) * rows + r] = path_probs.first;
-                }
-            }
-
-            noise[row_offset[k] + r] = probs[r].noiseProb();
-            counts[row_offset[k] + r] = probs[r].readCount();
-        }
-
         vector<uint32_t> path_counts;
-        path_counts.reserve(num_paths);
+        path_counts.reserve(est->paths.size());
         for (auto & path: est->paths) { path_counts.emplace_back(path.source_count); }
 
-        planPathGroupPosteriors(&plans[k], est, num_paths, path_counts, group_size, bounded, min_rel_likelihood);
+        planPathGroupPosteriors(&plans[k], est, est->paths.size(), path_counts, group_size, bounded, min_rel_likelihood);
     }
 
     auto * ctx = threadContext();
 
-    rpvg_b200_loglik_problems problems;
-    problems.n_problems = static_cast<uint32_t>(n);
-    problems.row_offset = row_offset.data();
-    problems.path_offset = path_offset.data();
-    problems.matrix_offset = matrix_offset.data();
-    problems.set_offset = nullptr;
-    problems.matrix = matrix.data();
-    problems.noise = noise.data();
-    problems.counts = counts.data();
-    problems.group_size = group_size;
-    problems.sets = nullptr;
-
+    // the dense matrices (rows x paths of every cluster, as denseMatrix makes them) are built on the device
+    rpvg_b200_clusters clusters = arena.view();
     rpvg_b200_grouped * resident = nullptr;
-    if (rpvg_b200_grouped_upload(ctx, &problems, &resident) != RPVG_B200_OK) { fatalBatch(ctx, "rpvg_b200_grouped_upload"); }
+    if (rpvg_b200_grouped_raw(ctx, &clusters, &resident) != RPVG_B200_OK) { fatalBatch(ctx, "rpvg_b200_grouped_raw"); }
 
     vector<PathClusterEstimates *> outs(n);
     for (size_t k = 0; k < n; ++k) { outs[k] = estimates[members[k]]; }
