@@ -28,6 +28,7 @@
 #include "common.cuh"
 #include "em_kernels.cuh"
 #include "em_sell.cuh"
+#include "em_dense.cuh"
 #include "em_batch.cuh"
 
 namespace {
@@ -178,6 +179,14 @@ uint32_t envKnob(const char * name, uint32_t fallback) {
 
 constexpr int kNumTiers = 5;
 
+// sides of the dense kernels (em_dense.cuh), descending; a cluster goes to the smallest that holds max(M, N + 1)
+constexpr uint32_t kDenseDims[4] = {128, 64, 32, 16};
+
+// Largest side that goes to the dense kernels unless RPVG_B200_EM_DENSE_MAX says otherwise. Measured on B200 (config 2,
+// per-CTA timeline): 0.39-0.45 us per iteration at side 16 and 0.66-0.81 at 32, against 1.1-1.3 on the sliced-ELL
+// kernels; at 64 (1.15-1.4 vs 1.6-1.9) the gain no longer pays for the shared memory and at 128 there is none.
+constexpr uint32_t kDenseDefaultMax = 32;
+
 // Shared-memory tiers of the EM launches and the CTA size that goes with each; RPVG_B200_EM_TIERS="kb:threads,..." (five
 // pairs, ascending) overrides them for tuning runs.
 struct SellTiers {
@@ -223,8 +232,11 @@ void planEmLaunches(const rpvg_b200_ctx * ctx, rpvg_b200_batch * b, std::vector<
 
     std::vector<GroupPlan> items(b->n_clusters);
 
-    // bin index = ((4 - log2 group) * tiers + (tiers - 1 - tier)) * 2 + (index_bytes == 4); last bin = fallback
+    // bin index = ((4 - log2 group) * tiers + (tiers - 1 - tier)) * 2 + (index_bytes == 4); then the fallback, then the
+    // dense kernels (largest first)
     const int fallback_bin = 5 * kNumTiers * 2;
+    const int dense_bin0 = fallback_bin + 1;
+    const uint32_t dense_max = std::min(envKnob("RPVG_B200_EM_DENSE_MAX", kDenseDefaultMax), kDenseDims[0]);
 
     for (uint32_t c = 0; c < b->n_clusters; ++c) {
 
@@ -258,7 +270,16 @@ void planEmLaunches(const rpvg_b200_ctx * ctx, rpvg_b200_batch * b, std::vector<
         plan.bin = fallback_bin;
         plan.cta_bytes = 0;
 
-        if (fixed + 4096 <= smem_cap) {
+        // small clusters: dense in shared memory, one thread per read class / path (em_dense.cuh)
+        const uint64_t dense_side = std::max(M, N + 1);
+
+        if (dense_side <= dense_max) {
+
+            int k = 3;
+            while (kDenseDims[k] < dense_side) { k--; }
+            plan.bin = dense_bin0 + k;
+
+        } else if (fixed + 4096 <= smem_cap) {
 
             const uint64_t need_typical = std::max(fixed + 4096, sellSmemBytes(m_b, z_b, N, cols_typical, index_bytes, multi, false));
             const uint64_t need_worst = std::max(fixed + 4096, sellSmemBytes(m_b, z_b, N, cols_worst, index_bytes, multi, true));
@@ -312,7 +333,17 @@ void planEmLaunches(const rpvg_b200_ctx * ctx, rpvg_b200_batch * b, std::vector<
             bin.first = k;
             bin.count = 0;
 
-            if (items[k].bin == fallback_bin) {
+            bin.dense_dim = 0;
+
+            if (items[k].bin >= dense_bin0) {
+
+                bin.dense_dim = kDenseDims[items[k].bin - dense_bin0];
+                bin.group_size = 1;
+                bin.threads = std::max(32u, bin.dense_dim);
+                bin.smem = static_cast<uint32_t>(sizeof(double) * (bin.dense_dim * (bin.dense_dim + 1) + 2 * bin.dense_dim));
+                bin.index_bytes = 0;
+
+            } else if (items[k].bin == fallback_bin) {
 
                 bin.group_size = 0;
                 bin.threads = kEmThreads;
@@ -400,6 +431,17 @@ cudaError_t launchSellBin(const SellArgs & sa, const rpvg_b200_batch::EmBin & bi
         case 1024: return launchSell<512, 1024, false, uint16_t>(sa, 1, bin.count, stream);
         default: return launchSell<512, 512, false, uint16_t>(sa, 1, bin.count, stream);
     }
+}
+
+cudaError_t launchDenseBin(const EmArgs & args, const uint32_t * clusters, const rpvg_b200_batch::EmBin & bin, cudaStream_t stream) {
+
+    switch (bin.dense_dim) {
+        case 16: emDenseKernel<16><<<bin.count, DenseShape<16>::kThreads, DenseShape<16>::kSmemBytes, stream>>>(args, clusters); break;
+        case 32: emDenseKernel<32><<<bin.count, DenseShape<32>::kThreads, DenseShape<32>::kSmemBytes, stream>>>(args, clusters); break;
+        case 64: emDenseKernel<64><<<bin.count, DenseShape<64>::kThreads, DenseShape<64>::kSmemBytes, stream>>>(args, clusters); break;
+        default: emDenseKernel<128><<<bin.count, DenseShape<128>::kThreads, DenseShape<128>::kSmemBytes, stream>>>(args, clusters); break;
+    }
+    return cudaGetLastError();
 }
 
 template <typename Kernel>
@@ -499,6 +541,8 @@ int rpvgEmInit(rpvg_b200_ctx * ctx) {
     RPVG_CUDA(ctx, (configureSell<512, 1024, true, uint16_t>(ctx, &max_group)));
     RPVG_CUDA(ctx, (configureSell<512, 512, true, uint32_t>(ctx, &max_group)));
     RPVG_CUDA(ctx, (configureSell<512, 1024, true, uint32_t>(ctx, &max_group)));
+
+    RPVG_CUDA(ctx, cudaFuncSetAttribute(emDenseKernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(DenseShape<128>::kSmemBytes)));
 
     ctx->max_group_size = max_group;
     return RPVG_B200_OK;
@@ -816,12 +860,15 @@ int rpvg_b200_batch_em(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const rpvg_b200
         if (k < stream_map.size()) { return stream_map[k]; }
         const auto & bin = b->bins[k];
         const uint32_t top_smem = std::min<uint32_t>(sellTiers().smem[kNumTiers - 1], static_cast<uint32_t>(ctx->max_smem_optin) - kStaticSmemReserve);
+        // the dense kernels share the last stream of the lowest class: their CTAs are many and small, a launch of
+        // theirs queued behind a sliced-ELL bin would start when that bin has drained
+        if (bin.dense_dim > 0) { return ctx->side_streams.size() - 1; }
         size_t cls = 4;
         if (bin.group_size == 2) { cls = 0; }
         else if (bin.group_size == 4) { cls = 1; }
         else if (bin.group_size == 1 && bin.smem >= top_smem) { cls = 2; }
         else if (bin.group_size >= 8) { cls = 3; }
-        const size_t width = cls == 4 ? 4 : 2;
+        const size_t width = cls == 4 ? 3 : 2;
         return 2 * cls + (class_cursor[cls]++ % width);
     };
 
@@ -847,7 +894,15 @@ int rpvg_b200_batch_em(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const rpvg_b200
             RPVG_LAUNCHED(ctx);
         }
 
-        if (bin.group_size == 0) {
+        if (bin.dense_dim > 0) {
+
+            const cudaError_t launch_err = launchDenseBin(args, b->d_order + bin.first, bin, bs);
+            if (launch_err != cudaSuccess) {
+                return rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("emDenseKernel launch (side ") + std::to_string(bin.dense_dim) + "): " + cudaGetErrorString(launch_err));
+            }
+            RPVG_LAUNCHED(ctx);
+
+        } else if (bin.group_size == 0) {
 
             EmArgs fallback_args = args;
             fallback_args.order = b->d_order + bin.first;

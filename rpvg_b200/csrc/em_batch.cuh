@@ -46,6 +46,7 @@ struct rpvg_b200_batch {
         uint32_t index_bytes;  // 2 or 4
         uint32_t first;        // offset into d_order / d_group_scratch / d_group_cta_bytes
         uint32_t count;
+        uint32_t dense_dim;    // > 0: emDenseKernel of this side (one CTA per cluster, no scratch)
     };
     std::vector<EmBin> bins;
     uint64_t scratch_bytes = 0;

@@ -167,3 +167,39 @@ def test_em_wide_clusters(ctx):
     ]
     arena = concat(parts)
     check_against_port(ctx, arena)
+
+
+def test_em_dense_kernels(ctx, monkeypatch):
+    """Small clusters run on the dense kernels (em_dense.cuh; max(read classes, paths + 1) <= 32 by default): sizes on
+    both sides of every kernel side, full matrices, a path nobody maps to, a cluster without read classes — against the
+    oracle, and against the sliced-ELL kernels on the same arena (RPVG_B200_EM_DENSE_MAX=0), also with every side the
+    library has (128)."""
+    rng = np.random.default_rng(123)
+    parts = []
+    for m, n in [(1, 1), (2, 1), (15, 15), (16, 15), (16, 16), (17, 3), (3, 17), (31, 31), (32, 31), (32, 32), (33, 31), (40, 12),
+                 (63, 63), (64, 63), (65, 20), (100, 127), (128, 127), (128, 128), (129, 5)]:
+        parts.append(_random_cluster(rng, m, n, max(1, n // 3)))
+    parts.append(_random_cluster(rng, 16, 15, 0, dense=True))
+    parts.append(_random_cluster(rng, 32, 31, 0, dense=True))
+    parts.append(_random_cluster(rng, 128, 127, 0, dense=True))
+
+    # a path without entries (column 2 removed from every read class) and a cluster without read classes
+    holed = _random_cluster(rng, 12, 6, 2)
+    keep = holed.col != 2
+    lens = np.add.reduceat(keep.astype(np.int64), holed.row_ptr[:-1].astype(np.int64))
+    row_ptr = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    parts.append(ClusterArena(holed.read_offset, holed.path_offset, row_ptr, holed.col[keep], holed.prob[keep], holed.noise, holed.count))
+    parts.append(ClusterArena(np.array([0, 0], dtype=np.uint64), np.array([0, 3], dtype=np.uint64), np.array([0], dtype=np.uint64), np.zeros(0, dtype=np.uint32),
+                              np.zeros(0), np.zeros(0), np.zeros(0, dtype=np.uint32)))
+
+    arena = concat(parts)
+
+    results = {}
+    for dense_max in ("0", "32", "128"):
+        monkeypatch.setenv("RPVG_B200_EM_DENSE_MAX", dense_max)
+        results[dense_max] = check_against_port(ctx, arena)
+
+    for dense_max in ("32", "128"):
+        for mine, sell in zip(results[dense_max], results["0"]):
+            assert np.allclose(mine, sell, rtol=REL_TOL, atol=1e-9)
+        assert np.array_equal(results[dense_max][3], results["0"][3])
