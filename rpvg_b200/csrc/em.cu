@@ -360,7 +360,7 @@ void planEmLaunches(const rpvg_b200_ctx * ctx, rpvg_b200_batch * b, std::vector<
                 bin.smem = std::min(sellTiers().smem[tier], smem_cap);
                 bin.threads = sellTiers().threads[tier];
 
-                // instantiations that exist: one CTA {64,128,256,512,1024} x u16; groups {256,512,1024} x u16; 512 x u32
+                // instantiations that exist (build threads): one CTA {64,128,256,512} x u16; groups {256,512} x u16; 512 x u32
                 if (tier == kNumTiers - 1 && big_threads == 1024) { bin.threads = 1024; }
                 if (bin.index_bytes == 4) { bin.threads = 512; }
                 if (bin.group_size > 1) { bin.threads = std::max(bin.threads, 256u); }
@@ -424,10 +424,15 @@ cudaError_t launchSellBin(const SellArgs & sa, const rpvg_b200_batch::EmBin & bi
         return launchSell<512, 512, true, uint16_t>(sa, bin.group_size, bin.count, stream);
     }
 
+    // Where shared memory, not threads, limits the CTAs of a tier per SM (4 x 52 KB, 2 x 104 KB) the run kernel gets
+    // twice the build kernel's threads: 32 warps per SM again, and half the latency per iteration for a cluster that
+    // is alone on its SM at the end of a batch (measured: 57.7 -> 57.0 ms/step on config 2).
     switch (bin.threads) {
         case 64: return launchSell<64, 64, false, uint16_t>(sa, 1, bin.count, stream);
-        case 128: return launchSell<128, 128, false, uint16_t>(sa, 1, bin.count, stream);
-        case 256: return launchSell<256, 256, false, uint16_t>(sa, 1, bin.count, stream);
+        case 128:
+            if (bin.smem > 32 * 1024) { return launchSell<128, 256, false, uint16_t>(sa, 1, bin.count, stream); }
+            return launchSell<128, 128, false, uint16_t>(sa, 1, bin.count, stream);
+        case 256: return launchSell<256, 512, false, uint16_t>(sa, 1, bin.count, stream);
         case 1024: return launchSell<512, 1024, false, uint16_t>(sa, 1, bin.count, stream);
         default: return launchSell<512, 512, false, uint16_t>(sa, 1, bin.count, stream);
     }
@@ -531,7 +536,8 @@ int rpvgEmInit(rpvg_b200_ctx * ctx) {
 
     RPVG_CUDA(ctx, (configureSell<64, 64, false, uint16_t>(ctx, &unused)));
     RPVG_CUDA(ctx, (configureSell<128, 128, false, uint16_t>(ctx, &unused)));
-    RPVG_CUDA(ctx, (configureSell<256, 256, false, uint16_t>(ctx, &unused)));
+    RPVG_CUDA(ctx, (configureSell<128, 256, false, uint16_t>(ctx, &unused)));
+    RPVG_CUDA(ctx, (configureSell<256, 512, false, uint16_t>(ctx, &unused)));
     RPVG_CUDA(ctx, (configureSell<512, 512, false, uint16_t>(ctx, &unused)));
     RPVG_CUDA(ctx, (configureSell<512, 1024, false, uint16_t>(ctx, &unused)));
     RPVG_CUDA(ctx, (configureSell<512, 512, false, uint32_t>(ctx, &unused)));
