@@ -67,6 +67,13 @@ const char * rpvg_b200_version(void);
 /* Number of kernel launches this ctx has enqueued so far (for bench.py's gpu_launches). */
 uint64_t rpvg_b200_launch_count(const rpvg_b200_ctx * ctx);
 
+/* Page-locked host memory owned by the ctx, for callers that flatten a batch right before handing it over (the batched
+ * drivers of rpvg_b200/host): an arena built in it uploads at the full host-link rate instead of going through the
+ * driver's staging copy. `slot` < 8 names one grow-only buffer; the pointer stays valid until the next call for the
+ * same slot with a larger size, or rpvg_b200_destroy. NULL on failure (rpvg_b200_last_error). No counterpart in the
+ * reference (its estimators never leave the host). */
+void * rpvg_b200_pinned_scratch(rpvg_b200_ctx * ctx, uint32_t slot, uint64_t bytes);
+
 /* ---- transcripts model: matrix build + EM ----
  * Replaces, for a batch of clusters, the body of PathAbundanceEstimator::estimate
  * (rpvg:src/path_abundance_estimator.cpp:18-33): constructProbabilityMatrix (rpvg:src/path_estimator.cpp:55-77),

@@ -72,6 +72,8 @@ def lib():
         l.rpvg_b200_last_error.argtypes = [C.c_void_p]
         l.rpvg_b200_launch_count.restype = C.c_uint64
         l.rpvg_b200_launch_count.argtypes = [C.c_void_p]
+        l.rpvg_b200_pinned_scratch.restype = C.c_void_p
+        l.rpvg_b200_pinned_scratch.argtypes = [C.c_void_p, C.c_uint32, C.c_uint64]
         l.rpvg_b200_create.argtypes = [C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]
         l.rpvg_b200_destroy.argtypes = [C.c_void_p]
         l.rpvg_b200_em_params_default.argtypes = [C.POINTER(EmParams)]
@@ -152,6 +154,13 @@ class Context:
     @property
     def launches(self) -> int:
         return int(lib().rpvg_b200_launch_count(self._h))
+
+    def pinned_scratch(self, slot: int, nbytes: int) -> int:
+        """rpvg_b200_pinned_scratch: address of the slot's page-locked buffer (>= nbytes); raises on failure."""
+        address = lib().rpvg_b200_pinned_scratch(self._h, slot, nbytes)
+        if not address:
+            raise RpvgB200Error(lib().rpvg_b200_last_error(self._h).decode())
+        return int(address)
 
     # -- transcripts model --------------------------------------------------------------------------------------------
     def em_abundances(self, arena: ClusterArena, params: EmParams | None = None):

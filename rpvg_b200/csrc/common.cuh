@@ -29,6 +29,11 @@ struct rpvg_b200_ctx {
     std::vector<cudaEvent_t> lane_events;
     cudaEvent_t fork_event = nullptr;
     uint32_t max_group_size = 1;
+
+    // rpvg_b200_pinned_scratch: grow-only page-locked host buffers, one per slot
+    static constexpr uint32_t kPinnedSlots = 8;
+    void * pinned[kPinnedSlots] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    uint64_t pinned_bytes[kPinnedSlots] = {0, 0, 0, 0, 0, 0, 0, 0};
 };
 
 // em.cu: sets the kernel attributes of the EM kernels and probes the largest usable thread-block cluster.

@@ -129,8 +129,45 @@ void rpvg_b200_destroy(rpvg_b200_ctx * ctx) {
     for (auto ev: ctx->lane_events) { cudaEventDestroy(ev); }
     if (ctx->fork_event) { cudaEventDestroy(ctx->fork_event); }
     if (ctx->own_stream) { cudaStreamDestroy(ctx->stream); }
+    for (auto buffer: ctx->pinned) {
+        if (buffer) { cudaFreeHost(buffer); }
+    }
 
     delete ctx;
+}
+
+void * rpvg_b200_pinned_scratch(rpvg_b200_ctx * ctx, uint32_t slot, uint64_t bytes) {
+
+    if (!ctx || slot >= rpvg_b200_ctx::kPinnedSlots) {
+        rpvgFail(ctx, RPVG_B200_ERR_INVALID, "rpvg_b200_pinned_scratch: bad slot");
+        return nullptr;
+    }
+
+    if (bytes <= ctx->pinned_bytes[slot] && ctx->pinned[slot]) { return ctx->pinned[slot]; }
+
+    cudaSetDevice(ctx->device);
+
+    if (ctx->pinned[slot]) {
+        cudaStreamSynchronize(ctx->stream);   // a copy from the old buffer may still be in flight
+        cudaFreeHost(ctx->pinned[slot]);
+        ctx->pinned[slot] = nullptr;
+        ctx->pinned_bytes[slot] = 0;
+    }
+
+    // a quarter of headroom: batches of a run are of similar, not equal, size
+    const uint64_t want = std::max<uint64_t>(bytes + bytes / 4, 1 << 16);
+    void * buffer = nullptr;
+    const cudaError_t err = cudaHostAlloc(&buffer, want, cudaHostAllocDefault);
+
+    if (err != cudaSuccess) {
+        rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("cudaHostAlloc(") + std::to_string(want) + "): " + cudaGetErrorString(err));
+        cudaGetLastError();
+        return nullptr;
+    }
+
+    ctx->pinned[slot] = buffer;
+    ctx->pinned_bytes[slot] = want;
+    return buffer;
 }
 
 const char * rpvg_b200_last_error(const rpvg_b200_ctx * ctx) {

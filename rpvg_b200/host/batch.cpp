@@ -31,13 +31,14 @@ struct BatchArena {
 
     vector<uint64_t> read_offset = {0}, path_offset = {0};
 
-    // filled completely by build(): plain arrays, so that nothing is value-initialised first
-    unique_ptr<uint64_t[]> row_ptr;
-    unique_ptr<uint32_t[]> col, count;
-    unique_ptr<double[]> prob, noise;
+    // filled completely by build(), in page-locked memory of the thread's context (rpvg_b200_pinned_scratch: the
+    // arena goes to the device right away, twice for the nested model, and pageable memory would halve that rate)
+    uint64_t * row_ptr = nullptr;
+    uint32_t * col = nullptr, * count = nullptr;
+    double * prob = nullptr, * noise = nullptr;
 
     // all clusters at once, the clusters filled in parallel
-    void build(const vector<const vector<ReadPathProbabilities> *> & members, const vector<uint32_t> & num_paths) {
+    void build(rpvg_b200_ctx * ctx, const vector<const vector<ReadPathProbabilities> *> & members, const vector<uint32_t> & num_paths) {
 
         const size_t n = members.size();
         vector<uint64_t> entries(n, 0);
@@ -61,11 +62,12 @@ struct BatchArena {
             entry_offset.push_back(entry_offset.back() + entries[k]);
         }
 
-        row_ptr.reset(new uint64_t[read_offset.back() + 1]);
-        col.reset(new uint32_t[entry_offset.back() + 1]);
-        prob.reset(new double[entry_offset.back() + 1]);
-        noise.reset(new double[read_offset.back() + 1]);
-        count.reset(new uint32_t[read_offset.back() + 1]);
+        row_ptr = static_cast<uint64_t *>(rpvg_b200_pinned_scratch(ctx, 0, sizeof(uint64_t) * (read_offset.back() + 1)));
+        col = static_cast<uint32_t *>(rpvg_b200_pinned_scratch(ctx, 1, sizeof(uint32_t) * (entry_offset.back() + 1)));
+        prob = static_cast<double *>(rpvg_b200_pinned_scratch(ctx, 2, sizeof(double) * (entry_offset.back() + 1)));
+        noise = static_cast<double *>(rpvg_b200_pinned_scratch(ctx, 3, sizeof(double) * (read_offset.back() + 1)));
+        count = static_cast<uint32_t *>(rpvg_b200_pinned_scratch(ctx, 4, sizeof(uint32_t) * (read_offset.back() + 1)));
+        if (!row_ptr || !col || !prob || !noise || !count) { fatalBatch(ctx, "rpvg_b200_pinned_scratch"); }
         row_ptr[0] = 0;
 
         #pragma omp parallel for schedule(dynamic, 8)
@@ -100,7 +102,7 @@ struct BatchArena {
     uint32_t size() const { return static_cast<uint32_t>(read_offset.size() - 1); }
 
     rpvg_b200_clusters view() const {
-        return rpvg_b200_clusters{size(), read_offset.data(), path_offset.data(), row_ptr.get(), col.get(), prob.get(), noise.get(), count.get()};
+        return rpvg_b200_clusters{size(), read_offset.data(), path_offset.data(), row_ptr, col, prob, noise, count};
     }
 };
 
@@ -207,7 +209,7 @@ void PathAbundanceEstimator::estimateBatch(const vector<PathClusterEstimates *> 
             member_probs.push_back(cluster_probs[i]);
             member_paths.push_back(estimates[i]->paths.size());
         }
-        arena.build(member_probs, member_paths);
+        arena.build(threadContext(), member_probs, member_paths);
     }
 
     rpvg_b200_em_params params;
@@ -318,7 +320,7 @@ void NestedPathAbundanceEstimator::estimateBatch(const vector<PathClusterEstimat
             members.push_back(cluster_probs[item.index]);
             member_paths.push_back(estimates[item.index]->paths.size());
         }
-        arena.build(members, member_paths);
+        arena.build(threadContext(), members, member_paths);
     }
 
     // (the host stages are independent per cluster: all cores, like the reference's loop; the device calls are made by
@@ -467,7 +469,7 @@ void PathEstimator::posteriorsBatch(const vector<PathClusterEstimates *> & estim
             member_probs.push_back(cluster_probs[i]);
             member_paths.push_back(estimates[i]->paths.size());
         }
-        arena.build(member_probs, member_paths);
+        arena.build(threadContext(), member_probs, member_paths);
     }
 
     const vector<uint64_t> & path_offset = arena.path_offset;
@@ -547,7 +549,7 @@ void MinimumPathAbundanceEstimator::estimateBatch(const vector<PathClusterEstima
             member_probs.push_back(cluster_probs[i]);
             member_paths.push_back(estimates[i]->paths.size());
         }
-        arena.build(member_probs, member_paths);
+        arena.build(threadContext(), member_probs, member_paths);
     }
 
     rpvg_b200_clusters clusters = arena.view();

@@ -5,7 +5,7 @@ import numpy as np
 import pytest
 
 from oracle import loader
-from rpvg_b200 import synth
+from rpvg_b200 import capi, synth
 from rpvg_b200.arena import concat
 
 pytestmark = pytest.mark.gpu
@@ -120,3 +120,29 @@ def test_posterior_batch_on_single_path_and_mixed_clusters(b200_harness, referen
         same(a, b, exact=True)
         assert a["sets"] == r["sets"]
         assert np.max(np.abs(a["posteriors"] - r["posteriors"]), initial=0) < 1e-9
+
+
+def test_pinned_scratch(ctx):
+    """rpvg_b200_pinned_scratch: a slot keeps its buffer while requests fit, grows otherwise, slots are independent,
+    the memory is writable host memory, and a slot outside 0..7 is refused."""
+    import ctypes as C
+
+    a = ctx.pinned_scratch(0, 1000)
+    assert ctx.pinned_scratch(0, 500) == a
+    assert ctx.pinned_scratch(0, 1000) == a
+    b = ctx.pinned_scratch(1, 1 << 20)
+    assert b != a
+
+    view = (C.c_ubyte * (1 << 20)).from_address(b)
+    view[0] = 7
+    view[(1 << 20) - 1] = 9
+    assert view[0] == 7 and view[(1 << 20) - 1] == 9
+
+    big = ctx.pinned_scratch(0, 8 << 20)     # beyond the first allocation and its headroom
+    view = (C.c_ubyte * (8 << 20)).from_address(big)
+    view[(8 << 20) - 1] = 1
+    assert ctx.pinned_scratch(0, 1000) == big
+    assert ctx.pinned_scratch(1, 1000) == b
+
+    with pytest.raises(capi.RpvgB200Error):
+        ctx.pinned_scratch(8, 16)
