@@ -183,7 +183,7 @@ constexpr int kNumTiers = 5;
 constexpr uint32_t kDenseDims[4] = {128, 64, 32, 16};
 
 // Largest side that goes to the dense kernels unless RPVG_B200_EM_DENSE_MAX says otherwise. Measured on B200 (config 2,
-// per-CTA timeline): 0.39-0.45 us per iteration at side 16 and 0.66-0.81 at 32, against 1.1-1.3 on the sliced-ELL
+// per-CTA timeline): 0.33-0.39 us per iteration at side 16 and 0.52-0.55 at 32, against 1.1-1.3 on the sliced-ELL
 // kernels; at 64 (1.15-1.4 vs 1.6-1.9) the gain no longer pays for the shared memory and at 128 there is none.
 constexpr uint32_t kDenseDefaultMax = 32;
 

@@ -13,7 +13,7 @@
 //   M: a_j = a_j * (sum_r P[r][j] w_r) / total, j <= N        (rpvg:src/path_abundance_estimator.cpp:82-98)
 //   one barrier after each step; the second one carries the convergence vote.
 //
-// Zero entries add exactly nothing, so with one running sum (DIM <= 16) the E-step sum has the bits of the sparse
+// Zero entries add exactly nothing, so with one running sum (sides 16 and 32) the E-step sum has the bits of the sparse
 // sequential one. Deterministic like the other kernels (fixed order, no atomics).
 #pragma once
 
@@ -24,7 +24,9 @@
 template <int DIM> struct DenseShape {
     static constexpr int kThreads = DIM < 32 ? 32 : DIM;
     static constexpr int kStride = DIM + 1;
-    static constexpr int kWays = DIM > 16 ? 4 : 1;   // running sums per thread (the dependent fp64 chain is 9 cycles a step)
+    // running sums per thread: one for the single-warp kernels (measured: the four-way loop's remainder handling costs a
+    // short sum more than the 9-cycle dependent chain it saves: 0.74 vs 0.45 us per iteration at side 16)
+    static constexpr int kWays = DIM > 32 ? 4 : 1;
     static constexpr size_t kSmemBytes = sizeof(double) * (static_cast<size_t>(DIM) * kStride + 2 * DIM);
 };
 
@@ -55,6 +57,24 @@ __device__ __forceinline__ double denseDot(const double * x, const uint32_t x_st
     #pragma unroll
     for (int u = 1; u < WAYS; ++u) { total += s[u]; }
     return total;
+}
+
+// The two barriers of an iteration; a CTA of one warp needs no hardware barrier for them.
+template <int THREADS>
+__device__ __forceinline__ void denseBarrier() {
+
+    if (THREADS == 32) { __syncwarp(); } else { __syncthreads(); }
+}
+
+template <int THREADS>
+__device__ __forceinline__ bool denseVote(const bool ok) {
+
+    if (THREADS == 32) {
+        const bool all = __all_sync(0xffffffffu, ok);
+        __syncwarp();
+        return all;
+    }
+    return __syncthreads_and(ok) != 0;
 }
 
 template <int DIM>
@@ -138,7 +158,7 @@ __global__ void __launch_bounds__(DenseShape<DIM>::kThreads) emDenseKernel(const
 
         if (tid < M) { w[tid] = count * sellReciprocal(denseDot<Shape::kWays>(P + tid * stride, 1, a, N + 1)); }
 
-        __syncthreads();
+        denseBarrier<THREADS>();
 
         bool ok = true;
 
@@ -155,7 +175,7 @@ __global__ void __launch_bounds__(DenseShape<DIM>::kThreads) emDenseKernel(const
 
         ++it;
 
-        if (__syncthreads_and(ok)) {
+        if (denseVote<THREADS>(ok)) {
             if (++conv_its == args.params.min_em_conv_its) { break; }
         } else {
             conv_its = 0;
