@@ -285,6 +285,19 @@ int rpvg_b200_merge_read_records(rpvg_b200_ctx * ctx, const rpvg_b200_read_recor
 int rpvg_b200_tpm(rpvg_b200_ctx * ctx, uint64_t n_paths, const double * abundances, const double * effective_lengths, double * tpm,
                   double * total_transcript_count);
 
+/* ---- per-path haplotype probabilities and read counts (the reducer behind the haplotype abundance table) ----
+ * HaplotypeAbundanceEstimatesWriter::addEstimates, rpvg:src/threaded_output_writer.cpp:355-391, for all clusters of a run:
+ * the estimates of cluster c are the path sets set_offset[c] .. set_offset[c+1]; set i has the members
+ * members[member_offset[i] .. member_offset[i+1]) (cluster-local path indices, at most `ploidy`, repeats adjacent),
+ * the posterior posteriors[i] and one abundance per member (abundances is parallel to members).
+ *   read_counts[p]     = sum of the abundances of the members equal to p
+ *   haplotype_probs[p] = sum of the posteriors of the sets p is a member of (a member equal to its predecessor in the set
+ *                        adds nothing)
+ * both over the paths of all clusters (path_offset[c] + local index), added in the order of the sets: bit-identical to
+ * the reference's loop. Host memory in and out. */
+int rpvg_b200_haplotype_marginals(rpvg_b200_ctx * ctx, uint32_t n_clusters, const uint64_t * path_offset, const uint64_t * set_offset, const uint64_t * member_offset,
+                                  const uint32_t * members, const double * posteriors, const double * abundances, double * haplotype_probs, double * read_counts);
+
 /* ---- EM of one cluster for callers that must not allocate ----
  * No counterpart in the reference (rpvg runs on the host and allocates freely); it exists for callers of this library
  * that cannot call cudaMalloc while they run: code under a fixed device-memory budget sized at start-up, real-time

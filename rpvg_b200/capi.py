@@ -86,6 +86,7 @@ def lib():
         l.rpvg_b200_batch_free.argtypes = [C.c_void_p, C.c_void_p]
         l.rpvg_b200_merge_read_records.argtypes = [C.c_void_p, C.POINTER(ReadRecords), C.c_double] + [C.c_void_p] * 4
         l.rpvg_b200_tpm.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_double)]
+        l.rpvg_b200_haplotype_marginals.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 8
         l.rpvg_b200_collapse.argtypes = [C.c_void_p, C.POINTER(CollapseProblems), C.c_double] + [C.c_void_p] * 4
         l.rpvg_b200_subset_em.argtypes = [C.c_void_p, C.POINTER(Clusters), C.POINTER(Subsets), C.POINTER(EmParams), C.c_double] + [C.c_void_p] * 5
         l.rpvg_b200_path_cover.argtypes = [C.c_void_p, C.POINTER(Clusters), C.c_void_p]
@@ -233,6 +234,21 @@ class Context:
         merged_count = np.zeros(R, dtype=np.uint32)
         self._check(lib().rpvg_b200_merge_read_records(self._h, C.byref(rec), prob_precision, _ptr(n_merged), _ptr(record_class), _ptr(merged_rep), _ptr(merged_count)))
         return n_merged, record_class, merged_rep, merged_count
+
+    def haplotype_marginals(self, path_offset, set_offset, member_offset, members, posteriors, abundances):
+        """rpvg_b200_haplotype_marginals: (haplotype_probs[n_paths], read_counts[n_paths])."""
+        path_offset = np.ascontiguousarray(path_offset, dtype=np.uint64)
+        set_offset = np.ascontiguousarray(set_offset, dtype=np.uint64)
+        member_offset = np.ascontiguousarray(member_offset, dtype=np.uint64)
+        members = np.ascontiguousarray(members, dtype=np.uint32)
+        posteriors = np.ascontiguousarray(posteriors, dtype=np.float64)
+        abundances = np.ascontiguousarray(abundances, dtype=np.float64)
+        n_paths = int(path_offset[-1])
+        probs = np.zeros(n_paths, dtype=np.float64)
+        counts = np.zeros(n_paths, dtype=np.float64)
+        self._check(lib().rpvg_b200_haplotype_marginals(self._h, path_offset.size - 1, _ptr(path_offset), _ptr(set_offset), _ptr(member_offset), _ptr(members),
+                                                        _ptr(posteriors), _ptr(abundances), _ptr(probs), _ptr(counts)))
+        return probs, counts
 
     def tpm(self, abundances, effective_lengths):
         """rpvg_b200_tpm: (tpm[n_paths], total_transcript_count)."""
