@@ -308,12 +308,18 @@ int rpvg_b200_haplotype_marginals(rpvg_b200_ctx * ctx, uint32_t n_clusters, cons
  *   limit   : 8 * (nnz + 2 * (n_paths + 1)) <= 4 MiB, else RPVG_B200_ERR_LIMIT (message in error_message) and no launch.
  *   inputs  : one cluster in the arena layout above: d_row_ptr[n_reads + 1] (entry offsets, any base), d_col/d_prob
  *             indexed by those offsets, d_noise[n_reads], d_count[n_reads]; nnz = d_row_ptr[n_reads] - d_row_ptr[0].
- *   outputs : d_abundances[n_paths], d_noise_count[1], d_total_count[1], d_iterations[1] (0xffffffff = a path index was
- *             out of range). The kernel is enqueued on `stream` (a cudaStream_t, NULL = default stream); the call does
- *             not synchronize. Same semantics as rpvg_b200_em_abundances for one cluster, equal to it up to rounding.
+ *   outputs : d_abundances[n_paths], d_noise_count[1], d_total_count[1], d_iterations[1]. The kernel is enqueued on
+ *             `stream` (a cudaStream_t, NULL = default stream); the call does not synchronize and leaves `device` the
+ *             calling thread's current device. Same semantics as rpvg_b200_em_abundances for one cluster, equal to it
+ *             up to rounding.
+ *   checks  : made on the device, like the regular entry point's: nnz must equal d_row_ptr[n_reads] - d_row_ptr[0] (the
+ *             host sizes the work area from it), offsets non-decreasing, path indices < n_paths and strictly ascending
+ *             within a read class, probabilities finite and >= 0. On failure d_iterations[0] = 0xffffffff and nothing
+ *             else is written (neither the outputs nor the work area).
  *   sharing : all calls on a device use the same work area and find the previous call's contents in it (the kernel clears
  *             what it accumulates into); calls whose kernels could overlap on the GPU race — serialise them per device.
- *   set-up  : the first call on a device resolves the work area's device address; make it before any stream capture. */
+ *   set-up  : the first call on a device resolves the work area's device address (the runtime may load the library's
+ *             device code on that GPU at this point); make it before any stream capture. */
 int rpvg_b200_em_cluster_noalloc(int device, void * stream, uint32_t n_reads, uint32_t n_paths, uint64_t nnz, const uint64_t * d_row_ptr,
                                  const uint32_t * d_col, const double * d_prob, const double * d_noise, const uint32_t * d_count,
                                  const rpvg_b200_em_params * params, double * d_abundances, double * d_noise_count, double * d_total_count,

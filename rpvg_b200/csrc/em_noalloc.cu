@@ -17,8 +17,13 @@
 //     what it reads first and zeroes its accumulators at the start of every iteration, so stale contents are harmless;
 //   * two calls whose kernels may overlap on the GPU (different streams, no dependency) race on the array: serialise
 //     calls per device;
-//   * the first call on a device looks the array's device address up (cudaGetSymbolAddress). Make that first call
-//     before starting any stream capture on the device; later calls only launch a kernel on the caller's stream.
+//   * the first call on a device looks the array's device address up (cudaGetSymbolAddress), which may also make the
+//     CUDA runtime load this library's device code on that GPU. Make that first call before starting any stream capture
+//     on the device; later calls only launch a kernel on the caller's stream;
+//   * the call makes `device` the calling thread's current device and leaves it so;
+//   * the inputs get the same checks as the regular entry point (offsets consistent with the nnz the caller states, path
+//     indices in range and strictly ascending within a read class, probabilities finite and non-negative). A failed check
+//     is reported on the device: d_iterations[0] = 0xffffffff, nothing else written.
 // Column sums are accumulated with atomics (there is no column-major copy to gather from, building one would need more
 // memory), so results agree with the regular entry points to rounding (~1e-15 relative), not bit for bit.
 
@@ -44,7 +49,7 @@ void noallocMessage(char * buffer, size_t buffer_len, const char * text) {
     if (buffer && buffer_len > 0) { snprintf(buffer, buffer_len, "%s", text); }
 }
 
-__global__ void __launch_bounds__(kNoAllocThreads) emNoAllocKernel(const uint32_t M, const uint32_t N, const uint64_t * __restrict__ row_ptr,
+__global__ void __launch_bounds__(kNoAllocThreads) emNoAllocKernel(const uint32_t M, const uint32_t N, const uint64_t host_nnz, const uint64_t * __restrict__ row_ptr,
                                                                    const uint32_t * __restrict__ col, const double * __restrict__ prob,
                                                                    const double * __restrict__ noise, const uint32_t * __restrict__ count,
                                                                    const rpvg_b200_em_params params, unsigned char * scratch, double * abundances,
@@ -55,6 +60,13 @@ __global__ void __launch_bounds__(kNoAllocThreads) emNoAllocKernel(const uint32_
     const int tid = threadIdx.x;
     const uint64_t e_base = row_ptr[0];
     const uint64_t nnz = row_ptr[M] - e_base;
+
+    // The host sized the work area from the caller's nnz; the layout below follows row_ptr. If the two disagree (or
+    // row_ptr runs backwards) nothing is written: every thread sees the same values, so the exit is uniform.
+    if (nnz != host_nnz || row_ptr[M] < e_base) {
+        if (tid == 0) { *iterations = 0xffffffffu; }
+        return;
+    }
 
     double * val = reinterpret_cast<double *>(scratch);   // [nnz] normalised probabilities
     double * a = val + nnz;                               // [N + 1] relative abundances, noise last
@@ -70,18 +82,39 @@ __global__ void __launch_bounds__(kNoAllocThreads) emNoAllocKernel(const uint32_
         return;
     }
 
-    // rpvg:src/path_estimator.cpp:156-166 on the non-zeros; a path index out of range stops the call (iterations = ~0)
+    // First a pass that only reads: the checks the regular entry point makes in buildRowsKernel (em.cu) — entry offsets
+    // non-decreasing and inside [row_ptr[0], row_ptr[M]], path indices in range and strictly ascending within a read
+    // class, probabilities finite and non-negative. Any failure stops the call (iterations = ~0) before the work area or
+    // the outputs are touched.
     int bad = 0;
+
+    for (uint32_t i = tid; i < M; i += kNoAllocThreads) {
+
+        const uint64_t e0 = row_ptr[i], e1 = row_ptr[i + 1];
+        if (e0 < e_base || e1 < e0 || e1 - e_base > nnz) { bad = 1; continue; }
+
+        int64_t prev_col = -1;
+        for (uint64_t e = e0; e < e1; ++e) {
+            const uint32_t j = col[e];
+            const double p = prob[e];
+            if (j >= N || static_cast<int64_t>(j) <= prev_col || !(p >= 0) || isinf(p)) { bad = 1; }
+            prev_col = j;
+        }
+    }
+
+    if (__syncthreads_or(bad)) {
+        if (tid == 0) { *iterations = 0xffffffffu; }
+        return;
+    }
+
+    // rpvg:src/path_estimator.cpp:156-166 on the non-zeros
     double count_sum = 0;
 
     for (uint32_t i = tid; i < M; i += kNoAllocThreads) {
 
         const uint64_t e0 = row_ptr[i], e1 = row_ptr[i + 1];
         double row_sum = 0;
-        for (uint64_t e = e0; e < e1; ++e) {
-            row_sum += prob[e];
-            if (col[e] >= N) { bad = 1; }
-        }
+        for (uint64_t e = e0; e < e1; ++e) { row_sum += prob[e]; }
 
         const double scale = 1 - noise[i];
         for (uint64_t e = e0; e < e1; ++e) {
@@ -90,11 +123,6 @@ __global__ void __launch_bounds__(kNoAllocThreads) emNoAllocKernel(const uint32_
             val[e - e_base] = v;
         }
         count_sum += static_cast<double>(count[i]);
-    }
-
-    if (__syncthreads_or(bad)) {
-        if (tid == 0) { *iterations = 0xffffffffu; }
-        return;
     }
 
     const double total = blockSum(count_sum, red);
@@ -183,9 +211,12 @@ extern "C" int rpvg_b200_em_cluster_noalloc(int device, void * stream, uint32_t 
         return RPVG_B200_ERR_INVALID;
     }
 
-    const unsigned long long needed = 8ull * (nnz + 2ull * (static_cast<unsigned long long>(n_paths) + 1));
+    // (compare before multiplying: 8 * nnz wraps for nnz >= 2^61)
+    const unsigned long long slots = kNoAllocScratchBytes / 8;
+    const unsigned long long vector_slots = 2ull * (static_cast<unsigned long long>(n_paths) + 1);
+    const unsigned long long needed = (nnz > slots) ? ~0ull : 8ull * (nnz + vector_slots);
 
-    if (needed > kNoAllocScratchBytes) {
+    if (nnz > slots || needed > kNoAllocScratchBytes) {
         char text[256];
         snprintf(text, sizeof(text), "rpvg_b200_em_cluster_noalloc: cluster needs %llu bytes of work area (8 * (nnz + 2 * (n_paths + 1))), the fixed area holds %zu; "
                                      "use rpvg_b200_em_abundances for clusters this large", needed, kNoAllocScratchBytes);
@@ -216,7 +247,7 @@ extern "C" int rpvg_b200_em_cluster_noalloc(int device, void * stream, uint32_t 
         scratch = scratch_address[device];
     }
 
-    emNoAllocKernel<<<1, kNoAllocThreads, 0, static_cast<cudaStream_t>(stream)>>>(n_reads, n_paths, d_row_ptr, d_col, d_prob, d_noise, d_count, *params, scratch,
+    emNoAllocKernel<<<1, kNoAllocThreads, 0, static_cast<cudaStream_t>(stream)>>>(n_reads, n_paths, nnz, d_row_ptr, d_col, d_prob, d_noise, d_count, *params, scratch,
                                                                                   d_abundances, d_noise_count, d_total_count, d_iterations);
     err = cudaGetLastError();
     if (err != cudaSuccess) {
