@@ -276,6 +276,43 @@ typedef struct rpvg_b200_read_records {
 int rpvg_b200_merge_read_records(rpvg_b200_ctx * ctx, const rpvg_b200_read_records * records, double prob_precision, uint32_t * n_merged, uint32_t * record_class,
                                  uint32_t * merged_rep, uint32_t * merged_count);
 
+/* ---- per-read path probabilities: the step right before the estimators' boundary ----
+ * ReadPathProbabilities::addPathProbs (rpvg:src/read_path_probabilities.cpp:74-221) with calcAlignPathLogProbs (:39-67)
+ * for all reads of a batch of clusters. Read r (of the cluster whose read_offset range holds it) owns the alignment paths
+ * align_ptr[r] .. align_ptr[r+1]; the LAST of them is the noise alignment path (AlignmentPath with an empty search state:
+ * score_sum <= 0, no path ids), every other one lists the paths it was found on (ids[id_ptr[a] .. id_ptr[a+1]), indices
+ * into the cluster's paths, i.e. after rpvg's clustered_path_index lookup; any order, repeats across alignment paths
+ * allowed). frag_log_prob[a] = FragmentLengthDist::logProb(frag_length) of alignment path a (rpvg:src/fragment_length_dist.cpp:385;
+ * the distribution stays with the caller), NULL for single-end reads. path_group != NULL switches collapse_groups on:
+ * path_group[p] = index of the path's group among the groups of its cluster (rpvg's group_name_index), source_count[p] its
+ * weight (NULL = 1); the output ids are then group indices.
+ * Output, for read r: noise[r] = ReadPathProbabilities::noiseProb(), and pathProbs() as groups group_ptr[r] .. group_ptr[r+1]
+ * — group g has the probability group_prob[g] and the ascending ids group_ids[group_id_ptr[g] .. group_id_ptr[g+1]) — i.e.
+ * the layout rpvg_b200_read_records takes (read counts are the caller's: 1 per read before the merge). Capacities:
+ * noise [n_reads], group_ptr [n_reads + 1], group_prob and group_ids [number of input ids], group_id_ptr [that + 1].
+ * Same arithmetic as the reference except that exp/log/log1p are the device's: values agree to ~1e-14 relative. A read
+ * with mapping quality 0 keeps noise 1 and no groups; one whose noise alignment path has score 0 gets its noise (~1) and
+ * no groups; malformed input (index out of range, a read whose paths all have effective length 0, which rpvg asserts
+ * against) is RPVG_B200_ERR_INVALID. Host pointers in and out. */
+typedef struct {
+    uint32_t n_clusters;
+    const uint64_t * read_offset;      /* [n_clusters + 1] reads of cluster c */
+    const uint64_t * path_offset;      /* [n_clusters + 1] paths of cluster c */
+    const double * effective_length;   /* [n_paths] PathInfo::effective_length */
+    const uint32_t * path_group;       /* [n_paths] or NULL */
+    const uint32_t * source_count;     /* [n_paths] or NULL */
+    const uint8_t * min_mapq;          /* [n_reads] AlignmentPath::min_mapq (equal over the alignment paths of a read) */
+    const uint64_t * align_ptr;        /* [n_reads + 1] */
+    const int32_t * score_sum;         /* [n_align] AlignmentPath::score_sum */
+    const uint32_t * align_length;     /* [n_align] AlignmentPath::align_length */
+    const double * frag_log_prob;      /* [n_align] or NULL */
+    const uint64_t * id_ptr;           /* [n_align + 1] */
+    const uint32_t * ids;              /* cluster-local path indices */
+} rpvg_b200_alignments;
+
+int rpvg_b200_add_path_probs(rpvg_b200_ctx * ctx, const rpvg_b200_alignments * alignments, double min_noise_prob, double prob_precision, double * noise,
+                             uint64_t * group_ptr, double * group_prob, uint64_t * group_id_ptr, uint32_t * group_ids);
+
 /* ---- transcripts per million (the reducer behind the abundance table) ----
  * total_transcript_count = sum over all paths with effective_length > 0 of abundance / effective_length
  * (rpvg:src/main.cpp:1029-1057); tpm[i] = abundance[i] / effective_length[i] / total_transcript_count * 10^6, 0 for a

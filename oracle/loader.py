@@ -48,6 +48,18 @@ class HarnessResult(C.Structure):
                 ("gibbs_abund_ptr", C.POINTER(C.c_uint64)), ("gibbs_abund", C.POINTER(C.c_double))]
 
 
+class HarnessAlignments(C.Structure):
+    _fields_ = [("num_paths", C.c_uint32), ("effective_length", C.c_void_p), ("path_group", C.c_void_p), ("source_count", C.c_void_p),
+                ("num_groups", C.c_uint32), ("num_reads", C.c_uint32), ("min_mapq", C.c_void_p), ("align_ptr", C.c_void_p), ("score_sum", C.c_void_p),
+                ("align_length", C.c_void_p), ("frag_length", C.c_void_p), ("id_ptr", C.c_void_p), ("ids", C.c_void_p)]
+
+
+class HarnessEstimates(C.Structure):
+    _fields_ = [("cluster_id", C.c_uint32), ("num_paths", C.c_uint32), ("length", C.c_void_p), ("effective_length", C.c_void_p),
+                ("n_sets", C.c_uint64), ("set_ptr", C.c_void_p), ("set_ids", C.c_void_p), ("posteriors", C.c_void_p),
+                ("n_abundances", C.c_uint64), ("abundances", C.c_void_p), ("noise_count", C.c_double), ("total_count", C.c_double)]
+
+
 MODEL_TRANSCRIPTS, MODEL_STRAINS, MODEL_HAPLOTYPE_TRANSCRIPTS, MODEL_PATH_POSTERIOR, MODEL_HAPLOTYPES = range(5)
 
 
@@ -151,6 +163,14 @@ def reference():
         l.ref_group_posteriors.argtypes = [C.c_int32, C.c_uint32, C.c_double, C.c_uint32, C.c_uint32, C.c_uint32] + [C.c_void_p] * 4
         l.ref_path_cover.restype = C.c_uint32
         l.ref_path_cover.argtypes = [C.c_uint32, C.c_uint32] + [C.c_void_p] * 4
+        l.ref_frag_log_prob.restype = C.c_double
+        l.ref_frag_log_prob.argtypes = [C.c_double, C.c_double, C.c_uint32, C.c_uint32]
+        l.ref_add_path_probs.restype = C.c_uint64
+        l.ref_add_path_probs.argtypes = [C.POINTER(HarnessAlignments), C.c_double, C.c_double, C.c_uint32, C.c_int32, C.c_double, C.c_double, C.c_int32] + [C.c_void_p] * 5
+        l.ref_write_probs.restype = C.c_int32
+        l.ref_write_probs.argtypes = [C.c_char_p, C.c_double, C.c_uint32, C.POINTER(HarnessCluster), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+        l.ref_write_estimates.restype = C.c_int32
+        l.ref_write_estimates.argtypes = [C.c_int32, C.c_char_p, C.c_uint32, C.c_double, C.c_double, C.c_uint32, C.POINTER(HarnessEstimates), C.c_uint32]
         _reference = l
     return _reference
 
@@ -325,3 +345,31 @@ def ref_merge_read_records(ref, num_paths, count, noise, entry_ptr, entry_prob, 
                                    o_path_ptr.ctypes.data, o_ids.ctypes.data)
     ne = int(o_entry_ptr[n])
     return o_noise[:n], o_count[:n], o_entry_ptr[:n + 1], o_entry_prob[:ne], o_path_ptr[:ne + 1], o_ids[:int(o_path_ptr[ne])]
+
+
+def ref_add_path_probs(ref, effective_length, min_mapq, align_ptr, score_sum, align_length, frag_length, id_ptr, ids, frag_mean=10.0, frag_sd=2.0,
+                       sd_max_multi=10, is_single_end=False, min_noise_prob=0.0, prob_precision=1e-8, path_group=None, source_count=None, num_groups=0):
+    """The reference's own ReadPathProbabilities::addPathProbs (rpvg:src/read_path_probabilities.cpp:74-221) on the reads of one
+    cluster. -> (noise, group_ptr, group_prob, group_id_ptr, group_ids)."""
+    def arr(a, t):
+        return None if a is None else np.ascontiguousarray(a, dtype=t)
+
+    def p(a):
+        return None if a is None else a.ctypes.data
+
+    effective_length = arr(effective_length, np.float64)
+    min_mapq, score_sum = arr(min_mapq, np.uint8), arr(score_sum, np.int32)
+    align_ptr, id_ptr = arr(align_ptr, np.uint64), arr(id_ptr, np.uint64)
+    align_length, frag_length, ids = arr(align_length, np.uint32), arr(frag_length, np.uint32), arr(ids, np.uint32)
+    path_group, source_count = arr(path_group, np.uint32), arr(source_count, np.uint32)
+    R, T = len(min_mapq), len(ids)
+    al = HarnessAlignments(len(effective_length), p(effective_length), p(path_group), p(source_count), num_groups, R, p(min_mapq), p(align_ptr), p(score_sum),
+                           p(align_length), p(frag_length), p(id_ptr), p(ids))
+    noise = np.zeros(R, dtype=np.float64)
+    group_ptr = np.zeros(R + 1, dtype=np.uint64)
+    group_prob = np.zeros(T + 1, dtype=np.float64)
+    group_id_ptr = np.zeros(T + 2, dtype=np.uint64)
+    group_ids = np.zeros(T + 1, dtype=np.uint32)
+    G = ref.ref_add_path_probs(C.byref(al), frag_mean, frag_sd, sd_max_multi, int(is_single_end), min_noise_prob, prob_precision, int(path_group is not None),
+                               noise.ctypes.data, group_ptr.ctypes.data, group_prob.ctypes.data, group_id_ptr.ctypes.data, group_ids.ctypes.data)
+    return noise, group_ptr, group_prob[:G], group_id_ptr[:G + 1], group_ids[:int(group_id_ptr[G])]

@@ -51,6 +51,12 @@ class ReadRecords(C.Structure):
     _fields_ = [("n_clusters", C.c_uint32)] + [(n, C.c_void_p) for n in ("read_offset", "group_ptr", "group_prob", "id_ptr", "ids", "noise", "count")]
 
 
+class Alignments(C.Structure):
+    _fields_ = [("n_clusters", C.c_uint32)] + [(n, C.c_void_p) for n in (
+        "read_offset", "path_offset", "effective_length", "path_group", "source_count", "min_mapq", "align_ptr", "score_sum", "align_length",
+        "frag_log_prob", "id_ptr", "ids")]
+
+
 class Subsets(C.Structure):
     _fields_ = [("n_subsets", C.c_uint32), ("subset_cluster", C.c_void_p), ("subset_offset", C.c_void_p), ("subset_paths", C.c_void_p)]
 
@@ -85,6 +91,7 @@ def lib():
         l.rpvg_b200_batch_em_timings.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_float)]
         l.rpvg_b200_batch_free.argtypes = [C.c_void_p, C.c_void_p]
         l.rpvg_b200_merge_read_records.argtypes = [C.c_void_p, C.POINTER(ReadRecords), C.c_double] + [C.c_void_p] * 4
+        l.rpvg_b200_add_path_probs.argtypes = [C.c_void_p, C.POINTER(Alignments), C.c_double, C.c_double] + [C.c_void_p] * 5
         l.rpvg_b200_tpm.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_double)]
         l.rpvg_b200_haplotype_marginals.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 8
         l.rpvg_b200_collapse.argtypes = [C.c_void_p, C.POINTER(CollapseProblems), C.c_double] + [C.c_void_p] * 4
@@ -234,6 +241,28 @@ class Context:
         merged_count = np.zeros(R, dtype=np.uint32)
         self._check(lib().rpvg_b200_merge_read_records(self._h, C.byref(rec), prob_precision, _ptr(n_merged), _ptr(record_class), _ptr(merged_rep), _ptr(merged_count)))
         return n_merged, record_class, merged_rep, merged_count
+
+    def add_path_probs(self, read_offset, path_offset, effective_length, min_mapq, align_ptr, score_sum, align_length, frag_log_prob, id_ptr, ids,
+                       path_group=None, source_count=None, min_noise_prob=1e-4, prob_precision=1e-8):
+        """rpvg_b200_add_path_probs: (noise[R], group_ptr[R + 1], group_prob, group_id_ptr, group_ids)."""
+        def arr(a, t):
+            return None if a is None else np.ascontiguousarray(a, dtype=t)
+        read_offset, path_offset, align_ptr, id_ptr = (arr(a, np.uint64) for a in (read_offset, path_offset, align_ptr, id_ptr))
+        effective_length, frag_log_prob = arr(effective_length, np.float64), arr(frag_log_prob, np.float64)
+        min_mapq, score_sum = arr(min_mapq, np.uint8), arr(score_sum, np.int32)
+        align_length, ids, path_group, source_count = (arr(a, np.uint32) for a in (align_length, ids, path_group, source_count))
+        al = Alignments(len(read_offset) - 1, _ptr(read_offset), _ptr(path_offset), _ptr(effective_length), _ptr(path_group), _ptr(source_count), _ptr(min_mapq),
+                        _ptr(align_ptr), _ptr(score_sum), _ptr(align_length), _ptr(frag_log_prob), _ptr(id_ptr), _ptr(ids))
+        R, T = int(read_offset[-1]), len(ids)
+        noise = np.zeros(R, dtype=np.float64)
+        group_ptr = np.zeros(R + 1, dtype=np.uint64)
+        group_prob = np.zeros(T + 1, dtype=np.float64)
+        group_id_ptr = np.zeros(T + 2, dtype=np.uint64)
+        group_ids = np.zeros(T + 1, dtype=np.uint32)
+        self._check(lib().rpvg_b200_add_path_probs(self._h, C.byref(al), min_noise_prob, prob_precision, _ptr(noise), _ptr(group_ptr), _ptr(group_prob),
+                                                   _ptr(group_id_ptr), _ptr(group_ids)))
+        G = int(group_ptr[-1])
+        return noise, group_ptr, group_prob[:G], group_id_ptr[:G + 1], group_ids[:int(group_id_ptr[G])]
 
     def haplotype_marginals(self, path_offset, set_offset, member_offset, members, posteriors, abundances):
         """rpvg_b200_haplotype_marginals: (haplotype_probs[n_paths], read_counts[n_paths])."""
