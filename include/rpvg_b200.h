@@ -335,6 +335,21 @@ int rpvg_b200_tpm(rpvg_b200_ctx * ctx, uint64_t n_paths, const double * abundanc
 int rpvg_b200_haplotype_marginals(rpvg_b200_ctx * ctx, uint32_t n_clusters, const uint64_t * path_offset, const uint64_t * set_offset, const uint64_t * member_offset,
                                   const uint32_t * members, const double * posteriors, const double * abundances, double * haplotype_probs, double * read_counts);
 
+/* ---- read counts and TPM per member of every haplotype combination (the reducer behind the joint haplotype abundance table) ----
+ * JointHaplotypeAbundanceEstimatesWriter::addEstimates, rpvg:src/threaded_output_writer.cpp:456-525, for all clusters of a
+ * run; sets, members and posteriors as in rpvg_b200_haplotype_marginals. Only sets with posterior >= min_posterior are
+ * written (written[i] = 1), and — like the reference's iterator, :473-502 — the abundances of a cluster are consumed by the
+ * members of its WRITTEN sets only: abundances[member_offset[set_offset[c]] + k] belongs to the k-th member of cluster c's
+ * written sets (with every set written this is the k-th member, the layout of rpvg_b200_haplotype_marginals).
+ *   read_counts[e], tpm[e] : per member e of a written set (0 for the others): that abundance, and
+ *                            (abundance / effective_lengths[path], 0 without effective length) / total_transcript_count * 10^6
+ *   noise_counts[ploidy]   : each slot = sum over the clusters, in order, of noise_count[c] / ploidy (:517-520)
+ * total_transcript_count is rpvg_b200_tpm's. Bit-identical to the reference's arithmetic. Host memory in and out. */
+int rpvg_b200_joint_haplotype_estimates(rpvg_b200_ctx * ctx, uint32_t n_clusters, const uint64_t * path_offset, const uint64_t * set_offset,
+                                        const uint64_t * member_offset, const uint32_t * members, const double * posteriors, const double * abundances,
+                                        const double * effective_lengths, const double * noise_count, uint32_t ploidy, double min_posterior,
+                                        double total_transcript_count, uint8_t * written, double * read_counts, double * tpm, double * noise_counts);
+
 /* ---- EM of one cluster for callers that must not allocate ----
  * No counterpart in the reference (rpvg runs on the host and allocates freely); it exists for callers of this library
  * that cannot call cudaMalloc while they run: code under a fixed device-memory budget sized at start-up, real-time

@@ -373,3 +373,42 @@ def ref_add_path_probs(ref, effective_length, min_mapq, align_ptr, score_sum, al
     G = ref.ref_add_path_probs(C.byref(al), frag_mean, frag_sd, sd_max_multi, int(is_single_end), min_noise_prob, prob_precision, int(path_group is not None),
                                noise.ctypes.data, group_ptr.ctypes.data, group_prob.ctypes.data, group_id_ptr.ctypes.data, group_ids.ctypes.data)
     return noise, group_ptr, group_prob[:G], group_id_ptr[:G + 1], group_ids[:int(group_id_ptr[G])]
+
+
+def ref_write_probs(ref, prefix, arena, lengths, effective_lengths, prob_precision=1e-8):
+    """rpvg's own ProbabilityClusterWriter (rpvg:src/threaded_output_writer.cpp:40-95) on every cluster of the arena, in order
+    -> ``<prefix>.txt.gz``. Path p of cluster c is named ``c<c>_p<p>``."""
+    datas = [HarnessClusterData(arena, c) for c in range(arena.n_clusters)]
+    structs = (HarnessCluster * arena.n_clusters)(*[d.struct for d in datas])
+    lens, effs = [], []
+    for c in range(arena.n_clusters):
+        p0, p1 = int(arena.path_offset[c]), int(arena.path_offset[c + 1])
+        lens.append(np.ascontiguousarray(lengths[p0:p1], dtype=np.uint32))
+        effs.append(np.ascontiguousarray(effective_lengths[p0:p1], dtype=np.float64))
+    len_ptrs = (C.c_void_p * arena.n_clusters)(*[a.ctypes.data for a in lens])
+    eff_ptrs = (C.c_void_p * arena.n_clusters)(*[a.ctypes.data for a in effs])
+    status = ref.ref_write_probs(os.fsencode(prefix), prob_precision, arena.n_clusters, structs, len_ptrs, eff_ptrs)
+    assert status == 0
+    return prefix + ".txt.gz"
+
+
+def ref_write_estimates(ref, kind, prefix, clusters, ploidy=2, min_posterior=1e-8, total_transcript_count=1.0, unaligned_read_count=0):
+    """rpvg's own estimate writers (rpvg:src/threaded_output_writer.cpp:237-548) -> ``<prefix>.txt``. kind 0: abundance table,
+    1: haplotype abundance table, 2: joint haplotype abundance table, 3: joint haplotype table. ``clusters``: list of dicts
+    with cluster_id, length, effective_length, sets (list of tuples), posteriors, abundances, noise_count, total_count."""
+    keep, structs = [], []
+    for cl in clusters:
+        length = np.ascontiguousarray(cl["length"], dtype=np.uint32)
+        eff = np.ascontiguousarray(cl["effective_length"], dtype=np.float64)
+        set_ptr = np.zeros(len(cl["sets"]) + 1, dtype=np.uint64)
+        set_ptr[1:] = np.cumsum([len(s) for s in cl["sets"]])
+        set_ids = np.ascontiguousarray([x for s in cl["sets"] for x in s], dtype=np.uint32)
+        post = np.ascontiguousarray(cl["posteriors"], dtype=np.float64)
+        ab = np.ascontiguousarray(cl["abundances"], dtype=np.float64)
+        keep.append((length, eff, set_ptr, set_ids, post, ab))
+        structs.append(HarnessEstimates(cl["cluster_id"], len(length), length.ctypes.data, eff.ctypes.data, len(cl["sets"]), set_ptr.ctypes.data,
+                                        set_ids.ctypes.data, post.ctypes.data, len(ab), ab.ctypes.data, float(cl["noise_count"]), float(cl["total_count"])))
+    arr = (HarnessEstimates * len(structs))(*structs)
+    status = ref.ref_write_estimates(kind, os.fsencode(prefix), ploidy, min_posterior, total_transcript_count, len(structs), arr, unaligned_read_count)
+    assert status == 0
+    return prefix + ".txt"

@@ -94,6 +94,7 @@ def lib():
         l.rpvg_b200_add_path_probs.argtypes = [C.c_void_p, C.POINTER(Alignments), C.c_double, C.c_double] + [C.c_void_p] * 5
         l.rpvg_b200_tpm.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_double)]
         l.rpvg_b200_haplotype_marginals.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 8
+        l.rpvg_b200_joint_haplotype_estimates.argtypes = [C.c_void_p, C.c_uint32] + [C.c_void_p] * 8 + [C.c_uint32, C.c_double, C.c_double] + [C.c_void_p] * 4
         l.rpvg_b200_collapse.argtypes = [C.c_void_p, C.POINTER(CollapseProblems), C.c_double] + [C.c_void_p] * 4
         l.rpvg_b200_subset_em.argtypes = [C.c_void_p, C.POINTER(Clusters), C.POINTER(Subsets), C.POINTER(EmParams), C.c_double] + [C.c_void_p] * 5
         l.rpvg_b200_path_cover.argtypes = [C.c_void_p, C.POINTER(Clusters), C.c_void_p]
@@ -278,6 +279,22 @@ class Context:
         self._check(lib().rpvg_b200_haplotype_marginals(self._h, path_offset.size - 1, _ptr(path_offset), _ptr(set_offset), _ptr(member_offset), _ptr(members),
                                                         _ptr(posteriors), _ptr(abundances), _ptr(probs), _ptr(counts)))
         return probs, counts
+
+    def joint_haplotype_estimates(self, path_offset, set_offset, member_offset, members, posteriors, abundances, effective_lengths, noise_count, ploidy,
+                                  min_posterior, total_transcript_count):
+        """rpvg_b200_joint_haplotype_estimates: (written[n_sets] bool, read_counts[n_members], tpm[n_members], noise_counts[ploidy])."""
+        path_offset, set_offset, member_offset = (np.ascontiguousarray(a, dtype=np.uint64) for a in (path_offset, set_offset, member_offset))
+        members = np.ascontiguousarray(members, dtype=np.uint32)
+        posteriors, abundances, effective_lengths, noise_count = (np.ascontiguousarray(a, dtype=np.float64) for a in (posteriors, abundances, effective_lengths, noise_count))
+        S, E = int(set_offset[-1]), int(member_offset[-1])
+        written = np.zeros(max(S, 1), dtype=np.uint8)
+        read_counts = np.zeros(max(E, 1), dtype=np.float64)
+        tpm = np.zeros(max(E, 1), dtype=np.float64)
+        noise_counts = np.zeros(ploidy, dtype=np.float64)
+        self._check(lib().rpvg_b200_joint_haplotype_estimates(self._h, path_offset.size - 1, _ptr(path_offset), _ptr(set_offset), _ptr(member_offset), _ptr(members),
+                                                              _ptr(posteriors), _ptr(abundances), _ptr(effective_lengths), _ptr(noise_count), ploidy, min_posterior,
+                                                              total_transcript_count, _ptr(written), _ptr(read_counts), _ptr(tpm), _ptr(noise_counts)))
+        return written[:S].astype(bool), read_counts[:E], tpm[:E], noise_counts
 
     def tpm(self, abundances, effective_lengths):
         """rpvg_b200_tpm: (tpm[n_paths], total_transcript_count)."""
