@@ -2,7 +2,10 @@
 """Headline benchmark: EM throughput (nnz x iterations / s) of the transcripts-model hot path on config 2 of
 BASELINE.json ("transcripts model EM on synthetic clusters: 1M read classes, 200k paths, power-law cluster sizes").
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--config c1|c2|c3|c4|c5]
+
+--config (default c2, the headline) names the BASELINE.json configuration that runs; c1/c3/c4/c5 run the model classes
+through the batched driver and report the inference-stage wall time (see run_model_config).
 
 One process per GPU (torchrun for N > 1). A step = one pass of the hot path (matrix build + EM of every cluster) over
 one synthetic arena of the named shape. Clusters are independent, so ranks are sharded with no data-path collective:
@@ -16,7 +19,11 @@ max-over-ranks device time.
 * roofline : the EM kernel's algorithmic bytes (12 nnz_path + 20 M + 16 (N+1) per cluster per iteration)
            / its own device time, against MEASURED_PEAKS.json's HBM GB/s.
 * cpu_baseline / --impl reference : the reference's own estimator objects (oracle/_ref, rpvg's unmodified translation
-           units, OpenMP over clusters like rpvg:src/main.cpp:829) on a bounded sample of the same arena.
+           units, OpenMP over clusters like rpvg:src/main.cpp:829) on a bounded sample of the same arena, sized from the
+           clusters' own cost (dense entries x iterations) so that every host thread stays busy; `same_work` is the GPU on
+           exactly that sample; `cpu_port` is the sparse CPU restatement (oracle/rpvg_oracle.cpp) on the WHOLE arena, so the
+           share of the ratio that is sparse-vs-dense algorithmics is visible next to the hardware's.
+* strong   : (N > 1) one config-2 arena, and a job of 8 of them, dealt over the N ranks by LPT: fixed total work.
 """
 
 from __future__ import annotations
@@ -95,24 +102,23 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def reference_sample(arena, max_dense_entries=1.5e6, max_clusters=400, max_total_dense=1.2e8):
-    """A bounded sample of the arena's clusters for the CPU arm. The reference is dense: a cluster
-    costs M x (N+1) x iterations, so the sample keeps clusters whose dense matrix has at most ``max_dense_entries``
-    entries, evenly spaced over the size-sorted list, within a total dense budget."""
-    shapes = [arena.cluster_shape(c) for c in range(arena.n_clusters)]
-    dense = np.array([m * (n + 1) for m, n, _ in shapes], dtype=np.float64)
-    eligible = np.nonzero((dense <= max_dense_entries) & (np.array([m for m, _, _ in shapes]) > 0))[0]
-    eligible = eligible[np.argsort(-dense[eligible], kind="stable")]
-    picks = eligible[np.linspace(0, len(eligible) - 1, min(max_clusters, len(eligible))).astype(int)]
-    picks = np.unique(picks)
-    picks = picks[np.argsort(-dense[picks], kind="stable")]
+def reference_sample(arena, iterations, threads, target_seconds=12.0, dense_rate=2.5e8, seed=7):
+    """A bounded sample of the arena's clusters for the CPU arm. The reference is dense: a cluster costs
+    M x (N + 1) x iterations there. The sample is drawn at random (seeded) among the clusters whose cost is at most 1/(4 x
+    threads) of the budget — so that rpvg's dynamic largest-first loop keeps every thread busy to the end — until about
+    ``target_seconds`` x threads of single-thread work (at ``dense_rate`` dense entries x iterations per second) is reached."""
+    shapes = np.array([arena.cluster_shape(c) for c in range(arena.n_clusters)], dtype=np.float64)
+    cost = shapes[:, 0] * (shapes[:, 1] + 1) * np.asarray(iterations, dtype=np.float64)
+    budget = target_seconds * threads * dense_rate
+    eligible = np.nonzero((cost > 0) & (cost <= budget / (4.0 * threads)))[0]
+    order = np.random.default_rng(seed).permutation(eligible)
     keep, total = [], 0.0
-    for c in picks[::-1]:   # smallest first until the budget is used, so the sample is never empty
-        if total + dense[c] > max_total_dense and keep:
+    for c in order:
+        if total + cost[c] > budget:
             continue
         keep.append(int(c))
-        total += dense[c]
-    return sorted(keep)
+        total += cost[c]
+    return sorted(keep), float(total)
 
 
 def host_threads() -> int:
@@ -123,24 +129,108 @@ def host_threads() -> int:
         return os.cpu_count() or 1
 
 
-def run_reference_sample(arena, sample_ids, threads=0):
+def cpu_seconds():
+    t = os.times()
+    return t.user + t.system
+
+
+def run_reference_sample(sub, its, threads=0):
     """Times the reference's own PathAbundanceEstimator (oracle/_ref) — or, if that library is absent, the CPU port — on
-    the sample. Returns (nnz*it/s, seconds, kind, cores)."""
+    the clusters of ``sub`` (iteration counts ``its`` from the port: the reference does not report them).
+    Returns (nnz*it/s, seconds, kind, cores, host-core utilisation during the run)."""
     from oracle import loader
     threads = threads or host_threads()
-    sub = arena.select(sample_ids)
-    _, _, _, its, _ = loader.port_em_abundances(sub, num_threads=threads)     # iteration counts (the reference does not report them)
     work = 0.0
     for k in range(sub.n_clusters):
         m, _, nnz_path = sub.cluster_shape(k)
         work += float(its[k]) * (nnz_path + m)
+    c0 = cpu_seconds()
     if loader.reference_available():
         lib = loader.reference()
         cfg = loader.make_config(loader.MODEL_TRANSCRIPTS)
         seconds, _ = loader.harness_estimate_batch(lib, cfg, sub, rng_seed=1, num_threads=threads)
-        return work / seconds, seconds, "reference", threads
-    _, _, _, _, seconds = loader.port_em_abundances(sub, num_threads=threads)
-    return work / seconds, seconds, "port", threads
+        kind = "reference"
+    else:
+        _, _, _, _, seconds = loader.port_em_abundances(sub, num_threads=threads)
+        kind = "port"
+    busy = (cpu_seconds() - c0) / max(seconds * threads, 1e-9)
+    return work / seconds, seconds, kind, threads, busy
+
+
+def run_port_full(arena, threads=0):
+    """The sparse CPU restatement on the whole arena, all host threads: (nnz*it/s, seconds, iterations)."""
+    from oracle import loader
+    threads = threads or host_threads()
+    _, _, _, its, seconds = loader.port_em_abundances(arena, num_threads=threads)
+    work = 0.0
+    for c in range(arena.n_clusters):
+        m, _, nnz_path = arena.cluster_shape(c)
+        work += float(its[c]) * (nnz_path + m)
+    return work / seconds, seconds, its
+
+
+def pin_arena(torch, arena):
+    """Pinned host copies of an arena's arrays (the e2e legs upload from these)."""
+    class Pinned:
+        pass
+    pinned = Pinned()
+    for name in ("read_offset", "path_offset", "row_ptr", "col", "prob", "noise", "count"):
+        a = getattr(arena, name)
+        signed = {np.dtype(np.uint64): np.int64, np.dtype(np.uint32): np.int32}.get(a.dtype)
+        setattr(pinned, name, torch.from_numpy(a.view(signed) if signed else a).pin_memory())
+    return pinned
+
+
+def pinned_outputs(torch, arena):
+    return (torch.empty(arena.n_paths, dtype=torch.float64).pin_memory(), torch.empty(arena.n_clusters, dtype=torch.float64).pin_memory(),
+            torch.empty(arena.n_clusters, dtype=torch.float64).pin_memory(), torch.empty(arena.n_clusters, dtype=torch.int32).pin_memory())
+
+
+def time_resident(torch, ctx, stream, flush, params, pinned, outs, steps, warmup):
+    """EM on an arena resident in HBM: per-step device time (CUDA events on the launching stream, L2 flushed before every
+    step). Returns (step_ms list, em_ms list, build_ms list, work, algorithmic bytes, launches)."""
+    batch = ctx.upload(pinned)
+    for _ in range(warmup):
+        batch.em(params)
+    batch.download(*outs)
+    work, alg_bytes = batch.em_work()
+    launches_before = ctx.launches
+    step_ms, em_ms, build_ms = [], [], []
+    for _ in range(steps):
+        flush.fill_(1)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        batch.em(params)
+        e1.record(stream)
+        e1.synchronize()
+        step_ms.append(e0.elapsed_time(e1))
+        b_ms, k_ms = batch.em_timings()
+        build_ms.append(b_ms)
+        em_ms.append(k_ms)
+    launches = ctx.launches - launches_before
+    batch.download(*outs)
+    batch.free()
+    return step_ms, em_ms, build_ms, work, alg_bytes, launches
+
+
+def time_e2e(torch, ctx, flush, params, pinned, outs, steps, warmup):
+    """Host buffers -> C ABI -> host buffers: upload + build + EM + download per step, wall clock around synchronous calls."""
+    for _ in range(warmup):
+        b = ctx.upload(pinned)
+        b.em(params)
+        b.download(*outs)
+        b.free()
+    times = []
+    for _ in range(steps):
+        flush.fill_(1)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        b = ctx.upload(pinned)
+        b.em(params)
+        b.download(*outs)
+        times.append(1e3 * (time.perf_counter() - t0))
+        b.free()
+    return times
 
 
 def main():
@@ -149,13 +239,19 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="c2", choices=["c1", "c2", "c3", "c4", "c5"])
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the workload (debug only; a scaled run is not a bench number)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-strong", action="store_true", help="N > 1: skip the fixed-work (strong scaling) legs")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+
+    if args.config != "c2":
+        from rpvg_b200 import model_bench
+        return model_bench.run(args, rank, local_rank, world, ClockSampler, host_threads)
 
     from rpvg_b200 import synth
 
@@ -166,26 +262,38 @@ def main():
               "read_classes_per_gpu": n_reads, "paths_per_gpu": n_paths, "max_em_its": 10000, "max_rel_em_conv": 0.001,
               "sharding": f"{world} arena(s) of this shape; clusters dealt to {world} rank(s) by LPT on nnz x E[iterations], no collective", "l2": "flushed between timed steps (256 MiB write)"}
 
+    def headline_arena(k=0):
+        return synth.transcripts_arena(seed=synth.BASE_SEED + 2 + k, n_paths=n_paths, n_reads=n_reads, n_max=n_max)
+
     # ------------------------------------------------------------------------------------------------ reference arm
     if args.impl == "reference":
         if rank != 0:
             return 0
-        arena = synth.transcripts_arena(seed=synth.BASE_SEED + 2, n_paths=n_paths, n_reads=n_reads, n_max=n_max)
-        sample = reference_sample(arena)
+        arena = headline_arena()
+        threads = host_threads()
+        port_value, port_seconds, its = run_port_full(arena, threads)           # iteration counts + the sparse CPU number
+        sample, _ = reference_sample(arena, its, threads)
+        sub = arena.select(sample)
+        sub_its = its[sample]
+        small = list(range(0, sub.n_clusters, 8))
         for _ in range(args.warmup):
-            run_reference_sample(arena, sample[: max(1, len(sample) // 8)])
-        values, secs = [], []
-        kind, cores = "reference", 0
+            run_reference_sample(sub.select(small), sub_its[small], threads)
+        values, secs, busy = [], [], []
+        kind, cores = "reference", threads
         for _ in range(args.steps):
-            v, s, kind, cores = run_reference_sample(arena, sample)
+            v, s_, kind, cores, b_ = run_reference_sample(sub, sub_its, threads)
             values.append(v)
-            secs.append(s)
-        value = float(np.sum([v * s for v, s in zip(values, secs)]) / np.sum(secs))
-        sample_desc = f"{len(sample)} of {arena.n_clusters} clusters (dense M x (N+1) <= 1.5e6 each), all host threads"
+            secs.append(s_)
+            busy.append(b_)
+        value = float(np.sum([v * s_ for v, s_ in zip(values, secs)]) / np.sum(secs))
+        sample_desc = (f"{len(sample)} of {arena.n_clusters} clusters drawn at random among those costing <= 1/(4 x threads) of the budget "
+                       f"(dense M x (N+1) x iterations), all host threads")
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": 1e3 * float(np.mean(secs)), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f64", "data": "synthetic", "config": config, "impl": "reference",
-                "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample_desc},
+                "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample_desc, "host_core_utilisation": float(np.mean(busy))},
+                "cpu_port": {"value": port_value, "unit": UNIT, "cores": threads, "kind": "port", "seconds": port_seconds,
+                             "sample": "the whole arena (sparse CPU restatement, oracle/rpvg_oracle.cpp)"},
                 "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
         print(json.dumps(line))
         return 0
@@ -193,7 +301,8 @@ def main():
     # ------------------------------------------------------------------------------------------------------ B200 arm
     import torch
     import torch.distributed as dist
-    from rpvg_b200 import capi
+    from rpvg_b200 import capi, multi_gpu
+    from rpvg_b200.arena import concat
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the hot path has no CPU fallback")
@@ -202,34 +311,20 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
+    first = headline_arena()
     if world == 1:
-        arena = synth.transcripts_arena(seed=synth.BASE_SEED + 2, n_paths=n_paths, n_reads=n_reads, n_max=n_max)
+        arena = first
     else:
         # weak scaling: the job is `world` arenas of the config-2 shape; its clusters are dealt to the ranks by LPT on the
         # nnz x E[iterations] cost model (rpvg_b200/multi_gpu.py). No data-path collective: clusters are independent.
-        from rpvg_b200 import multi_gpu
-        from rpvg_b200.arena import concat
-        job = concat([synth.transcripts_arena(seed=synth.BASE_SEED + 2 + r, n_paths=n_paths, n_reads=n_reads, n_max=n_max) for r in range(world)])
+        job = concat([first] + [headline_arena(r) for r in range(1, world)])
         arena = job.select(multi_gpu.lpt_partition(multi_gpu.cluster_costs(job), world)[rank])
         del job
 
-    # pinned host copies of the arena: the e2e leg uploads from these every step
-    class Pinned:
-        pass
-
-    pinned = Pinned()
-    for name in ("read_offset", "path_offset", "row_ptr", "col", "prob", "noise", "count"):
-        a = getattr(arena, name)
-        signed = {np.dtype(np.uint64): np.int64, np.dtype(np.uint32): np.int32}.get(a.dtype)
-        t = torch.from_numpy(a.view(signed) if signed else a).pin_memory()
-        setattr(pinned, name, t)
+    pinned = pin_arena(torch, arena)
     h2d_bytes = arena.input_bytes()
-
-    out_ab = torch.empty(arena.n_paths, dtype=torch.float64).pin_memory()
-    out_noise = torch.empty(arena.n_clusters, dtype=torch.float64).pin_memory()
-    out_total = torch.empty(arena.n_clusters, dtype=torch.float64).pin_memory()
-    out_its = torch.empty(arena.n_clusters, dtype=torch.int32).pin_memory()
-    d2h_bytes = out_ab.numel() * 8 + out_noise.numel() * 8 + out_total.numel() * 8 + out_its.numel() * 4
+    outs = pinned_outputs(torch, arena)
+    d2h_bytes = outs[0].numel() * 8 + outs[1].numel() * 8 + outs[2].numel() * 8 + outs[3].numel() * 4
 
     # a dedicated (non-default) stream shared by torch (events, L2 flush) and the library (kernels, copies)
     stream = torch.cuda.Stream()
@@ -244,64 +339,59 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- device-resident leg ("value")
-    batch = ctx.upload(pinned)
-    for _ in range(args.warmup):
-        batch.em(params)
-    batch.download(out_ab, out_noise, out_total, out_its)
-    work, alg_bytes = batch.em_work()
+    def max_over_ranks(values):
+        t = torch.tensor(values, dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return [float(x) for x in t.cpu()]
 
+    def sum_over_ranks(values):
+        t = torch.tensor(values, dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return [float(x) for x in t.cpu()]
+
+    # ---- device-resident leg ("value")
     sampler = ClockSampler(local_rank)
     barrier()
     sampler.start()
-    launches_before = ctx.launches
-    step_ms, em_ms, build_ms = [], [], []
-    for _ in range(args.steps):
-        flush.fill_(1)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(stream)
-        batch.em(params)
-        e1.record(stream)
-        e1.synchronize()
-        step_ms.append(e0.elapsed_time(e1))
-        b_ms, k_ms = batch.em_timings()
-        build_ms.append(b_ms)
-        em_ms.append(k_ms)
-    launches = ctx.launches - launches_before
+    step_ms, em_ms, build_ms, work, alg_bytes, launches = time_resident(torch, ctx, stream, flush, params, pinned, outs, args.steps, args.warmup)
     barrier()
     clocks = sampler.stop()
-    batch.download(out_ab, out_noise, out_total, out_its)
-    checksum = float(out_ab.sum())
-    batch.free()
+    checksum = float(outs[0].sum())
+    max_its = int(outs[3].max())
+    its_all = outs[3].numpy().astype(np.int64).copy()
 
     # ---- end-to-end leg ("e2e"): host buffers -> C ABI -> host buffers
-    for _ in range(min(2, args.warmup)):
-        b = ctx.upload(pinned)
-        b.em(params)
-        b.download(out_ab, out_noise, out_total, out_its)
-        b.free()
     barrier()
-    e2e_ms = []
-    for _ in range(args.steps):
-        flush.fill_(1)
-        torch.cuda.synchronize()
-        t0 = time.perf_counter()
-        b = ctx.upload(pinned)
-        b.em(params)
-        b.download(out_ab, out_noise, out_total, out_its)
-        e2e_ms.append(1e3 * (time.perf_counter() - t0))
-        b.free()
+    e2e_ms = time_e2e(torch, ctx, flush, params, pinned, outs, args.steps, min(2, args.warmup))
     barrier()
 
-    total_ms = float(np.sum(step_ms))
-    total_e2e_ms = float(np.sum(e2e_ms))
-    stats = torch.tensor([total_ms, total_e2e_ms], dtype=torch.float64, device="cuda")
-    works = torch.tensor([work], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(stats, op=dist.ReduceOp.MAX)
-        dist.all_reduce(works, op=dist.ReduceOp.SUM)
-    max_ms, max_e2e_ms = [float(x) for x in stats.cpu()]
-    all_work = float(works.cpu()[0])
+    max_ms, max_e2e_ms = max_over_ranks([float(np.sum(step_ms)), float(np.sum(e2e_ms))])
+    all_work = sum_over_ranks([work])[0]
+
+    # ---- fixed total work over the N ranks (strong scaling): one arena, and a job of 8 arenas, dealt by LPT
+    strong = None
+    if world > 1 and not args.no_strong and args.scale == 1.0:
+        strong = {}
+        for name, n_arenas in (("one_arena", 1), ("eight_arenas", 8)):
+            job = first if n_arenas == 1 else concat([first] + [headline_arena(r) for r in range(1, n_arenas)])
+            share = job.select(multi_gpu.lpt_partition(multi_gpu.cluster_costs(job), world)[rank])
+            sp, so = pin_arena(torch, share), pinned_outputs(torch, share)
+            barrier()
+            ms, _, _, w_share, _, _ = time_resident(torch, ctx, stream, flush, params, sp, so, 3, 2)
+            barrier()
+            ms_n = max_over_ranks([float(np.mean(ms))])[0]
+            ms_1 = 0.0
+            if rank == 0:   # the same job on one GPU, measured in the same run
+                jp, jo = pin_arena(torch, job), pinned_outputs(torch, job)
+                ms1, _, _, _, _, _ = time_resident(torch, ctx, stream, flush, params, jp, jo, 3, 2)
+                ms_1 = float(np.mean(ms1))
+                del jp, jo
+            barrier()
+            ms_1 = max_over_ranks([ms_1])[0]
+            strong[name] = {"ms_n1": ms_1, f"ms_n{world}": ms_n, "speedup": ms_1 / ms_n, "work_nnz_iterations": sum_over_ranks([w_share])[0]}
+            del job, share, sp, so
 
     if rank == 0:
         value = all_work * args.steps / (max_ms * 1e-3)
@@ -309,14 +399,14 @@ def main():
         peak, peak_src = measured_peak_hbm()
         em_ms_mean = float(np.mean(em_ms))
         achieved = alg_bytes / (em_ms_mean * 1e-3) / 1e9
-        # DRAM bytes the EM launches of one step really move (ncu, same workload): the slices live in shared memory, so
-        # this is a small fraction of the algorithmic bytes the HBM roofline is quoted on (profiles/r01d_*).
+        # DRAM bytes the EM launches of one step really move (ncu, same workload, round-1 build): the slices live in shared
+        # memory, so this is a small fraction of the algorithmic bytes the HBM roofline is quoted on.
         traffic, traffic_src = None, None
         try:
-            with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01d_em_traffic.json")) as fh:
+            with open(os.path.join(ROOT, "profiles", "r01d_em_traffic.json")) as fh:
                 measured = json.load(fh)
             if world == 1:
-                traffic, traffic_src = measured["em_dram_bytes_per_step"], measured["source"]
+                traffic, traffic_src = measured["em_dram_bytes_per_step"], measured["source"] + " (ncu capture of the round-1 build, not of this run)"
         except OSError:
             pass
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -325,22 +415,39 @@ def main():
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                         "ms_per_step": max_e2e_ms / args.steps},
                 "gpu_launches": int(launches),
-                "roofline": {"bound": "hbm", "kernel": "emSellKernel (all bins, concurrent streams)", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                             "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
-                             "limiter": "shared-memory data pipe: 76% busy over a whole single-cluster launch (ncu, profiles/r01c_ncu_single_cluster_metrics.txt); the rest is barriers",
-                             "shared_pipe_busy_frac": 0.76,
+                "roofline": {"bound": "hbm", "kernel": "emSellRunKernel + emSellBuildKernel + emDenseKernel (all bins, concurrent streams)", "achieved": achieved,
+                             "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                             "meaning": "algorithmic-bytes equivalent (12 nnz_path + 20 M + 16 (N+1) per cluster and iteration / EM device time): the slices are "
+                                        "resident in shared memory, real DRAM traffic is ~0.2% of it; the binding resource is the shared-memory data pipe "
+                                        "(profiles/r02c_ncu_single_cluster.md: 74% busy over a whole single-cluster launch, 9.6 wavefronts per 32 entries)",
                              "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": em_ms_mean, "build_ms": float(np.mean(build_ms)),
                              "kernel_share_of_step": em_ms_mean / (max_ms / args.steps)},
                 "inference_stage_wall_ms": max_e2e_ms / args.steps,
                 "work_per_step": {"nnz_iterations": all_work, "nnz": arena.nnz, "clusters": arena.n_clusters,
-                                  "max_iterations": int(out_its.max()), "checksum": checksum}}
+                                  "max_iterations": max_its, "checksum": checksum}}
+        if strong:
+            line["strong"] = strong
+
         if not args.no_cpu_baseline:
-            sample = reference_sample(arena, max_clusters=200, max_total_dense=4e7)
-            v, s, kind, cores = run_reference_sample(arena, sample)
-            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "seconds": s,
-                                    "sample": f"{len(sample)} of {arena.n_clusters} clusters (dense M x (N+1) <= 1.5e6 each)"}
+            threads = host_threads()
+            port_value, port_seconds, port_its = run_port_full(arena, threads)
+            line["cpu_port"] = {"value": port_value, "unit": UNIT, "cores": threads, "kind": "port", "seconds": port_seconds,
+                                "sample": "the whole arena of this rank (sparse CPU restatement, oracle/rpvg_oracle.cpp)",
+                                "iterations_identical_to_gpu": bool(np.array_equal(port_its.astype(np.int64), its_all))}
+            sample, _ = reference_sample(arena, its_all, threads)
+            sub = arena.select(sample)
+            v, s_, kind, cores, busy = run_reference_sample(sub, its_all[sample], threads)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "seconds": s_, "host_core_utilisation": busy,
+                                    "sample": f"{len(sample)} of {arena.n_clusters} clusters drawn at random among those costing <= 1/(4 x threads) of the "
+                                              f"budget (dense M x (N+1) x iterations)"}
+            # the GPU on exactly that sample, through the host-facing call
+            sp, so = pin_arena(torch, sub), pinned_outputs(torch, sub)
+            gpu_ms = float(np.mean(time_e2e(torch, ctx, flush, params, sp, so, 3, 2)))
+            line["same_work"] = {"clusters": len(sample), "gpu_ms": gpu_ms, "cpu_ms": 1e3 * s_, "ratio": 1e3 * s_ / gpu_ms,
+                                 "cpu": f"{kind}, {cores} threads", "gpu": "rpvg_b200_batch_upload + _em + _download from pinned host buffers"}
         print(json.dumps(line))
 
+    barrier()
     ctx.close()
     if world > 1:
         dist.destroy_process_group()

@@ -9,8 +9,14 @@
 // safety margin; the caller replays the reference's exact walk on those few (any pair dropped here fails the exact test
 // too and cannot move the maximum), which gives the same list and the same numbers as walking all pairs.
 //
-// One CTA per cluster: pairs of a cluster are few thousand; a warp per pair for the sum over read classes (as in
-// posterior.cu), then a block-wide scan. fp64 log bound.
+// Values: pairTileKernel. The pairs of all clusters are cut into tiles of 32 x 32 (first group x second group, upper
+// triangle of tiles only) and, when the tiles alone would not fill the GPU, into row ranges as well; one 256-thread CTA per
+// (tile, row range). The CTA stages the 64 columns of its tile 32 read classes at a time in shared memory (coalesced
+// column reads, 0.5 B of L2 traffic per log) and every thread owns 4 pairs: one column read serves 32 pairs, and the
+// kernel is bound by the fp64 log, not by memory. Sums run over the read classes in order, 32 at a time,
+// the partial sums added with compensation: the result is within an ulp or two of the exact sum whatever the number of
+// read classes (the reference's own Eigen reduction is no closer), and deterministic.
+// Scan: boundedScanKernel, one CTA per cluster: exclusive prefix maximum in pair order, test, compaction.
 
 #include <cfloat>
 #include <string>
@@ -54,7 +60,197 @@ __device__ __forceinline__ void pairOfIndex(const uint32_t G, const uint32_t ind
     *j_out = i + (index - row_start(i));
 }
 
-__global__ void __launch_bounds__(kBoundedThreads) boundedPairsKernel(const BoundedArgs args) {
+constexpr uint32_t kPairTile = 32;        // pairs per tile side
+constexpr uint32_t kPairRowChunk = 32;    // read classes staged at a time
+constexpr int kPairThreads = 256;         // 32 first groups x 8 threads, each thread 4 second groups
+
+struct PairTileArgs {
+
+    BoundedArgs b;
+    uint32_t n_clusters;
+    const uint64_t * item_offset;      // [n_clusters + 1] work items (tiles x row ranges) of each cluster
+    uint32_t rows_per_split;           // read classes per row range (multiple of kPairRowChunk); >= the largest cluster: no split
+    double * partial;                  // [n_items x 1024] when rows are split, else NULL
+    unsigned long long * log_count;    // logs evaluated (for the roofline)
+};
+
+__global__ void __launch_bounds__(kPairThreads) pairTileKernel(const PairTileArgs args) {
+
+    __shared__ double col_s[2 * kPairTile][kPairRowChunk + 1];   // [column of the tile][read class]: 32 first, then 32 second groups
+    __shared__ double noise_s[kPairRowChunk];
+    __shared__ double count_s[kPairRowChunk];
+
+    const BoundedArgs & b = args.b;
+
+    const uint32_t tid = threadIdx.x;
+    const uint32_t lane = tid & 31;
+    const uint32_t warp = tid >> 5;
+
+    const uint64_t item = blockIdx.x;
+    const uint32_t c = clusterOf(args.item_offset, args.n_clusters, item);
+
+    const uint64_t g0 = b.group_offset[c];
+    const uint32_t G = static_cast<uint32_t>(b.group_offset[c + 1] - g0);
+    const uint64_t r0 = b.row_offset[c];
+    const uint32_t rows = b.n_classes[c];
+    const double * matrix = b.matrix + b.matrix_offset[c];
+    const double * noise = b.noise + r0;
+    const double * counts = b.counts + r0;
+    const uint32_t * order = b.order + g0;
+
+    const uint32_t tiles_side = (G + kPairTile - 1) / kPairTile;
+    const uint32_t n_tiles = tiles_side * (tiles_side + 1) / 2;
+    const uint32_t local = static_cast<uint32_t>(item - args.item_offset[c]);
+    const uint32_t split = local / n_tiles;
+
+    uint32_t ti, tj;
+    pairOfIndex(tiles_side, local % n_tiles, &ti, &tj);
+
+    const uint32_t row_begin = split * args.rows_per_split;
+    const uint32_t row_end = min(rows, row_begin + args.rows_per_split);
+
+    // this thread's pairs: first group i, second groups j0 .. j0 + 3 (positions in `order`)
+    const uint32_t li = tid >> 3;
+    const uint32_t lj = (tid & 7) * 4;
+    const uint32_t i = ti * kPairTile + li;
+    const uint32_t j0 = tj * kPairTile + lj;
+
+    double acc[4] = {0, 0, 0, 0};
+    double comp[4] = {0, 0, 0, 0};
+
+    for (uint32_t base = row_begin; base < row_end; base += kPairRowChunk) {
+
+        const uint32_t n_chunk = min(kPairRowChunk, row_end - base);
+
+        __syncthreads();   // the previous chunk has been consumed
+
+        // stage: warp w loads columns w, w + 8, ..: lane = read class (coalesced), padded rows against bank conflicts
+        for (uint32_t k = warp; k < 2 * kPairTile; k += kPairThreads / 32) {
+            const uint32_t pos = (k < kPairTile ? ti * kPairTile + k : tj * kPairTile + (k - kPairTile));
+            double v = 0;
+            if (pos < G && lane < n_chunk) { v = matrix[static_cast<uint64_t>(order[pos]) * rows + base + lane]; }
+            col_s[k][lane] = v;
+        }
+        if (tid < kPairRowChunk) {
+            noise_s[tid] = tid < n_chunk ? noise[base + tid] : 1.0;
+            count_s[tid] = tid < n_chunk ? counts[base + tid] : 0.0;   // padding rows add count 0 * log(1)
+        }
+
+        __syncthreads();
+
+        double sum[4] = {0, 0, 0, 0};
+
+        #pragma unroll 2
+        for (uint32_t r = 0; r < kPairRowChunk; ++r) {
+
+            // noise + col_first / 2 + col_second / 2, in the reference's order
+            const double first = noise_s[r] + col_s[li][r] / 2.0;
+            const double cnt = count_s[r];
+
+            #pragma unroll
+            for (uint32_t q = 0; q < 4; ++q) {
+                const double prob = first + col_s[kPairTile + lj + q][r] / 2.0;
+                sum[q] = fma(cnt, log(prob), sum[q]);
+            }
+        }
+
+        // compensated addition of the chunk's sums
+        #pragma unroll
+        for (uint32_t q = 0; q < 4; ++q) {
+            const double y = sum[q] - comp[q];
+            const double t = acc[q] + y;
+            comp[q] = (t - acc[q]) - y;
+            acc[q] = t;
+        }
+    }
+
+    if (tid == 0 && args.log_count) {
+        const uint32_t ni = min(kPairTile, G - ti * kPairTile), nj = min(kPairTile, G - tj * kPairTile);
+        const unsigned long long pairs = (ti == tj) ? static_cast<unsigned long long>(ni) * (ni + 1) / 2 : static_cast<unsigned long long>(ni) * nj;
+        atomicAdd(args.log_count, pairs * (row_end > row_begin ? row_end - row_begin : 0));
+    }
+
+    if (args.partial) {
+
+        double * out = args.partial + item * (kPairTile * kPairTile) + tid * 4;
+        #pragma unroll
+        for (uint32_t q = 0; q < 4; ++q) { out[q] = acc[q]; }
+        return;
+    }
+
+    if (i >= G) { return; }
+
+    const uint64_t p0 = b.pair_offset[c];
+    const uint32_t a = order[i];
+    const uint64_t row_start = static_cast<uint64_t>(i) * G - (static_cast<uint64_t>(i) * (i - 1)) / 2;
+
+    #pragma unroll
+    for (uint32_t q = 0; q < 4; ++q) {
+        const uint32_t j = j0 + q;
+        if (j < G && j >= i) {
+            const uint32_t bb = order[j];
+            const uint64_t p = p0 + row_start + (j - i);
+            b.cand_loglik[p] = acc[q];
+            b.pair_ll[p] = acc[q] + (b.log_freq[g0 + a] + b.log_freq[g0 + bb] + (a == bb ? 0.0 : 0.6931471805599453));
+        }
+    }
+}
+
+// Row ranges were summed apart: add them in order, per pair, and write the values (one thread per pair slot of a tile).
+__global__ void __launch_bounds__(kPairThreads) pairCombineKernel(const PairTileArgs args) {
+
+    const BoundedArgs & b = args.b;
+
+    // one CTA per (cluster, tile): the first-split item of the tile
+    const uint64_t tile_item = blockIdx.x;
+    const uint32_t c = clusterOf(args.item_offset, args.n_clusters, tile_item);   // item_offset here counts tiles x splits; see the launch
+
+    const uint64_t g0 = b.group_offset[c];
+    const uint32_t G = static_cast<uint32_t>(b.group_offset[c + 1] - g0);
+    const uint32_t rows = b.n_classes[c];
+    const uint32_t * order = b.order + g0;
+
+    const uint32_t tiles_side = (G + kPairTile - 1) / kPairTile;
+    const uint32_t n_tiles = tiles_side * (tiles_side + 1) / 2;
+    const uint32_t n_splits = max(1u, (rows + args.rows_per_split - 1) / args.rows_per_split);
+    const uint32_t local = static_cast<uint32_t>(tile_item - args.item_offset[c]);
+
+    if (local >= n_tiles) { return; }   // only the items of the first row range combine
+
+    uint32_t ti, tj;
+    pairOfIndex(tiles_side, local, &ti, &tj);
+
+    const uint32_t tid = threadIdx.x;
+    const uint32_t i = ti * kPairTile + (tid >> 3);
+    const uint32_t j0 = tj * kPairTile + (tid & 7) * 4;
+
+    if (i >= G) { return; }
+
+    const uint64_t p0 = b.pair_offset[c];
+    const uint32_t a = order[i];
+    const uint64_t row_start = static_cast<uint64_t>(i) * G - (static_cast<uint64_t>(i) * (i - 1)) / 2;
+
+    for (uint32_t q = 0; q < 4; ++q) {
+
+        const uint32_t j = j0 + q;
+        if (j >= G || j < i) { continue; }
+
+        double acc = 0, comp = 0;
+        for (uint32_t sp = 0; sp < n_splits; ++sp) {
+            const double y = args.partial[(args.item_offset[c] + static_cast<uint64_t>(sp) * n_tiles + local) * (kPairTile * kPairTile) + tid * 4 + q] - comp;
+            const double t = acc + y;
+            comp = (t - acc) - y;
+            acc = t;
+        }
+
+        const uint32_t bb = order[j];
+        const uint64_t p = p0 + row_start + (j - i);
+        b.cand_loglik[p] = acc;
+        b.pair_ll[p] = acc + (b.log_freq[g0 + a] + b.log_freq[g0 + bb] + (a == bb ? 0.0 : 0.6931471805599453));
+    }
+}
+
+__global__ void __launch_bounds__(kBoundedThreads) boundedScanKernel(const BoundedArgs args) {
 
     __shared__ double warp_max[kBoundedThreads / 32];
     __shared__ double carry;
@@ -67,46 +263,11 @@ __global__ void __launch_bounds__(kBoundedThreads) boundedPairsKernel(const Boun
     const uint32_t warp = tid >> 5;
     constexpr uint32_t num_warps = kBoundedThreads / 32;
 
-    const uint64_t g0 = args.group_offset[c];
-    const uint32_t G = static_cast<uint32_t>(args.group_offset[c + 1] - g0);
-    const uint64_t r0 = args.row_offset[c];
-    const uint32_t rows = args.n_classes[c];
-    const double * matrix = args.matrix + args.matrix_offset[c];
-    const double * noise = args.noise + r0;
-    const double * counts = args.counts + r0;
-    const uint32_t * order = args.order + g0;
-    const double * log_freq = args.log_freq + g0;
-
     const uint64_t p0 = args.pair_offset[c];
     const uint32_t n_pairs = static_cast<uint32_t>(args.pair_offset[c + 1] - p0);
 
     double * pair_ll = args.pair_ll + p0;
-    double * raw = args.cand_loglik + p0;   // raw sums of all pairs first, compacted in place at the end
-
-    // ---- values: a warp per pair
-    for (uint32_t p = warp; p < n_pairs; p += num_warps) {
-
-        uint32_t i, j;
-        pairOfIndex(G, p, &i, &j);
-        const uint32_t a = order[i], b = order[j];
-
-        const double * col_a = matrix + static_cast<uint64_t>(a) * rows;
-        const double * col_b = matrix + static_cast<uint64_t>(b) * rows;
-
-        double acc = 0;
-        for (uint32_t r = lane; r < rows; r += 32) {
-            double prob = noise[r];
-            prob += col_a[r] / 2.0;
-            prob += col_b[r] / 2.0;
-            acc += counts[r] * log(prob);
-        }
-        acc = warpSum(acc);
-
-        if (lane == 0) {
-            raw[p] = acc;
-            pair_ll[p] = acc + (log_freq[a] + log_freq[b] + (a == b ? 0.0 : 0.6931471805599453));
-        }
-    }
+    double * raw = args.cand_loglik + p0;   // raw sums of all pairs first, compacted in place
 
     if (tid == 0) {
         carry = -DBL_MAX;
@@ -261,9 +422,98 @@ extern "C" int rpvg_b200_grouped_bounded_pairs(rpvg_b200_ctx * ctx, rpvg_b200_gr
         args.cand_pair = d_cand_pair;
         args.cand_loglik = d_cand_loglik;
 
-        boundedPairsKernel<<<C, kBoundedThreads, 0, s>>>(args);
-        ctx->launches++;
-        err = cudaGetLastError();
+        // ---- plan: tiles of 32 x 32 pairs per cluster; row ranges as well while the tiles alone leave SMs idle
+        std::vector<uint32_t> n_classes(C, 0);
+        err = cudaMemcpyAsync(n_classes.data(), grouped->d_n_classes, 4 * static_cast<size_t>(C), cudaMemcpyDeviceToHost, s);
+        if (err == cudaSuccess) { err = cudaStreamSynchronize(s); }
+
+        uint64_t n_tiles_total = 0;
+        uint32_t most_rows = 0;
+        for (uint32_t c = 0; c < C; ++c) {
+            const uint64_t side = (group_offset[c + 1] - group_offset[c] + kPairTile - 1) / kPairTile;
+            n_tiles_total += side * (side + 1) / 2;
+            most_rows = std::max(most_rows, n_classes[c]);
+        }
+
+        const uint64_t want_items = 4ull * static_cast<uint64_t>(ctx->num_sms);
+        uint32_t rows_per_split = std::max(most_rows, kPairRowChunk);
+
+        if (n_tiles_total < want_items) {
+            const uint64_t splits = (want_items + n_tiles_total - 1) / n_tiles_total;
+            rows_per_split = static_cast<uint32_t>((most_rows + splits - 1) / splits);
+            rows_per_split = std::max(8 * kPairRowChunk, ((rows_per_split + kPairRowChunk - 1) / kPairRowChunk) * kPairRowChunk);
+        }
+
+        std::vector<uint64_t> item_offset(C + 1, 0);
+        bool split_rows = false;
+        for (uint32_t c = 0; c < C; ++c) {
+            const uint64_t side = (group_offset[c + 1] - group_offset[c] + kPairTile - 1) / kPairTile;
+            const uint64_t splits = std::max<uint64_t>(1, (static_cast<uint64_t>(n_classes[c]) + rows_per_split - 1) / rows_per_split);
+            split_rows = split_rows || splits > 1;
+            item_offset[c + 1] = item_offset[c] + side * (side + 1) / 2 * splits;
+        }
+        const uint64_t n_items = item_offset[C];
+
+        if (n_items >= (1ull << 31)) { err = cudaErrorInvalidValue; }
+
+        char * extra = nullptr;
+        const size_t extra_bytes = pad(8 * (C + 1)) + (split_rows ? pad(8 * n_items * kPairTile * kPairTile) : 0) + 256;
+        if (err == cudaSuccess) { err = cudaMallocAsync(reinterpret_cast<void **>(&extra), extra_bytes, s); }
+
+        if (err == cudaSuccess) {
+
+            uint64_t * d_item_offset = reinterpret_cast<uint64_t *>(extra);
+            double * d_partial = split_rows ? reinterpret_cast<double *>(extra + pad(8 * (C + 1))) : nullptr;
+            unsigned long long * d_log_count = reinterpret_cast<unsigned long long *>(extra + extra_bytes - 256);
+
+            err = cudaMemcpyAsync(d_item_offset, item_offset.data(), 8 * (C + 1), cudaMemcpyHostToDevice, s);
+            if (err == cudaSuccess) { err = cudaMemsetAsync(d_log_count, 0, 8, s); }
+
+            PairTileArgs tile_args;
+            tile_args.b = args;
+            tile_args.n_clusters = C;
+            tile_args.item_offset = d_item_offset;
+            tile_args.rows_per_split = rows_per_split;
+            tile_args.partial = d_partial;
+            tile_args.log_count = d_log_count;
+
+            cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+            if (err == cudaSuccess) { err = cudaEventCreate(&ev0); }
+            if (err == cudaSuccess) { err = cudaEventCreate(&ev1); }
+
+            if (err == cudaSuccess && n_items > 0) {
+
+                cudaEventRecord(ev0, s);
+                pairTileKernel<<<static_cast<unsigned>(n_items), kPairThreads, 0, s>>>(tile_args);
+                ctx->launches++;
+
+                if (split_rows) {
+                    pairCombineKernel<<<static_cast<unsigned>(n_items), kPairThreads, 0, s>>>(tile_args);
+                    ctx->launches++;
+                }
+                cudaEventRecord(ev1, s);
+
+                boundedScanKernel<<<C, kBoundedThreads, 0, s>>>(args);
+                ctx->launches++;
+                err = cudaGetLastError();
+            }
+
+            unsigned long long log_count = 0;
+            if (err == cudaSuccess) { err = cudaMemcpyAsync(&log_count, d_log_count, 8, cudaMemcpyDeviceToHost, s); }
+            if (err == cudaSuccess) { err = cudaStreamSynchronize(s); }
+
+            if (err == cudaSuccess && n_items > 0) {
+                float ms = 0;
+                cudaEventElapsedTime(&ms, ev0, ev1);
+                grouped->pair_ms += ms;
+                grouped->pair_logs += static_cast<double>(log_count);
+            }
+
+            if (ev0) { cudaEventDestroy(ev0); }
+            if (ev1) { cudaEventDestroy(ev1); }
+        }
+
+        if (extra) { cudaFreeAsync(extra, s); }
     }
 
     if (err == cudaSuccess) { err = cudaMemcpyAsync(n_candidates.data(), d_n_candidates, 4 * C, cudaMemcpyDeviceToHost, s); }
@@ -301,5 +551,14 @@ extern "C" int rpvg_b200_grouped_bounded_pairs(rpvg_b200_ctx * ctx, rpvg_b200_gr
 
     *cand_pair = grouped->h_cand_pair.data();
     *cand_loglik = grouped->h_cand_loglik.data();
+    return RPVG_B200_OK;
+}
+
+
+extern "C" int rpvg_b200_grouped_pair_stats(const rpvg_b200_grouped * grouped, double * kernel_ms, double * log_evaluations) {
+
+    if (!grouped) { return RPVG_B200_ERR_INVALID; }
+    if (kernel_ms) { *kernel_ms = grouped->pair_ms; }
+    if (log_evaluations) { *log_evaluations = grouped->pair_logs; }
     return RPVG_B200_OK;
 }

@@ -21,4 +21,8 @@ struct rpvg_b200_grouped {
     std::vector<uint64_t> h_cand_offset;
     std::vector<uint32_t> h_cand_pair;
     std::vector<double> h_cand_loglik;
+
+    // device time and log evaluations of the pair kernels of all rpvg_b200_grouped_bounded_pairs calls on this handle
+    double pair_ms = 0;
+    double pair_logs = 0;
 };

@@ -11,6 +11,7 @@
 // problem are shared by all of its sets and stay in L2/L1), fp64 log, fixed summation tree (deterministic).
 // Bound: fp64 ALU / log throughput, not HBM.
 
+#include <algorithm>
 #include <cmath>
 #include <string>
 #include <vector>
@@ -307,5 +308,73 @@ extern "C" int rpvg_b200_grouped_upload(rpvg_b200_ctx * ctx, const rpvg_b200_log
     grouped->d_n_classes = d_rows;
     *out = grouped;
 
+    return RPVG_B200_OK;
+}
+
+
+// ---- fp64 log throughput of this GPU: the roofline denominator of the log-likelihood kernels ---------------------------
+namespace {
+
+// Every thread evaluates 4 independent chains of log(): the instruction mix of the pair kernel's inner loop (one add,
+// one log, one fused multiply-add per evaluation) without any memory traffic.
+__global__ void logPeakKernel(const uint32_t iterations, const double seed, double * __restrict__ sink) {
+
+    double x[4];
+    #pragma unroll
+    for (int q = 0; q < 4; ++q) { x[q] = seed + 1e-3 * (threadIdx.x * 4 + q) + 1e-6 * blockIdx.x; }
+
+    double acc[4] = {0, 0, 0, 0};
+
+    for (uint32_t it = 0; it < iterations; ++it) {
+        #pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            acc[q] = fma(1.000001, log(x[q] + acc[q] * 1e-9), acc[q]);
+        }
+    }
+
+    const double total = (acc[0] + acc[1]) + (acc[2] + acc[3]);
+    if (total == 12345.678) { sink[0] = total; }   // never true: keeps the loop alive
+}
+
+}
+
+extern "C" int rpvg_b200_log_peak(rpvg_b200_ctx * ctx, double * logs_per_second) {
+
+    if (!ctx || !logs_per_second) { return RPVG_B200_ERR_INVALID; }
+
+    RPVG_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+
+    double * d_sink = nullptr;
+    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&d_sink), 256, s));
+
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaError_t err = cudaEventCreate(&ev0);
+    if (err == cudaSuccess) { err = cudaEventCreate(&ev1); }
+
+    const uint32_t iterations = 2000;
+    const unsigned grid = 8u * static_cast<unsigned>(ctx->num_sms), block = 256;
+    double best = 0;
+
+    for (int rep = 0; rep < 4 && err == cudaSuccess; ++rep) {   // first repetition = warm-up
+
+        cudaEventRecord(ev0, s);
+        logPeakKernel<<<grid, block, 0, s>>>(iterations, 0.5, d_sink);
+        ctx->launches++;
+        cudaEventRecord(ev1, s);
+        err = cudaEventSynchronize(ev1);
+
+        float ms = 0;
+        if (err == cudaSuccess) { err = cudaEventElapsedTime(&ms, ev0, ev1); }
+        if (err == cudaSuccess && rep > 0 && ms > 0) { best = std::max(best, 4.0 * iterations * grid * block / (ms * 1e-3)); }
+    }
+
+    if (ev0) { cudaEventDestroy(ev0); }
+    if (ev1) { cudaEventDestroy(ev1); }
+    cudaFreeAsync(d_sink, s);
+
+    if (err != cudaSuccess) { return rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("rpvg_b200_log_peak: ") + cudaGetErrorString(err)); }
+
+    *logs_per_second = best;
     return RPVG_B200_OK;
 }

@@ -119,6 +119,50 @@ struct FlatCluster {
     }
 };
 
+// One cluster's dense matrix put on the device once (rpvg_b200_grouped_upload), for every log-likelihood request that follows.
+struct ResidentCluster {
+
+    rpvg_b200_ctx * ctx;
+    rpvg_b200_grouped * handle = nullptr;
+    uint32_t num_paths;
+
+    ResidentCluster(rpvg_b200_ctx * ctx_in, const vector<double> & matrix, const vector<double> & noise, const vector<double> & counts, const uint32_t num_paths_in) : ctx(ctx_in), num_paths(num_paths_in) {
+
+        const uint64_t rows = noise.size();
+        const uint64_t row_offset[2] = {0, rows};
+        const uint64_t path_offset[2] = {0, num_paths};
+        const uint64_t matrix_offset[2] = {0, rows * num_paths};
+        const uint64_t set_offset[2] = {0, 0};
+
+        rpvg_b200_loglik_problems problems;
+        problems.n_problems = 1;
+        problems.row_offset = row_offset;
+        problems.path_offset = path_offset;
+        problems.matrix_offset = matrix_offset;
+        problems.set_offset = set_offset;
+        problems.matrix = matrix.data();
+        problems.noise = noise.data();
+        problems.counts = counts.data();
+        problems.group_size = 1;
+        problems.sets = nullptr;
+
+        if (rpvg_b200_grouped_upload(ctx, &problems, &handle) != RPVG_B200_OK) { fatal(ctx, "rpvg_b200_grouped_upload"); }
+    }
+
+    ~ResidentCluster() { rpvg_b200_grouped_free(ctx, handle); }
+
+    ResidentCluster(const ResidentCluster &) = delete;
+    ResidentCluster & operator=(const ResidentCluster &) = delete;
+
+    vector<double> logLikelihoods(const uint32_t group_size, const vector<uint32_t> & flat_sets) const {
+
+        const uint64_t set_offset[2] = {0, flat_sets.size() / group_size};
+        vector<double> loglik(set_offset[1], 0);
+        if (set_offset[1] > 0 && rpvg_b200_grouped_loglik(ctx, handle, group_size, set_offset, flat_sets.data(), loglik.data()) != RPVG_B200_OK) { fatal(ctx, "rpvg_b200_grouped_loglik"); }
+        return loglik;
+    }
+};
+
 // sum_r count_r log(noise_r + sum_p col_p / k) for each set, on the device
 vector<double> deviceLogLikelihoods(rpvg_b200_ctx * ctx, const vector<double> & matrix, const vector<double> & noise, const vector<double> & counts,
                                     const uint32_t num_paths, const uint32_t group_size, const vector<uint32_t> & flat_sets) {
@@ -410,14 +454,14 @@ void PathEstimator::calculatePathGroupPosteriorsBounded(PathClusterEstimates * p
 
     assert(group_size == 2);
 
-    GroupPosteriorPlan plan;
-    planPathGroupPosteriors(&plan, path_cluster_estimates, num_paths, path_counts, group_size, true, min_rel_likelihood);
+    // the matrix goes up once; marginals, then the pair walk on the device (the same two rounds the batched drivers run)
+    vector<GroupPosteriorPlan> plans(1);
+    planPathGroupPosteriors(&plans[0], path_cluster_estimates, num_paths, path_counts, group_size, true, min_rel_likelihood);
 
-    bool more = true;
-    while (more) {
-        auto loglik = deviceLogLikelihoods(threadContext(), matrix, noise, counts, num_paths, plan.set_size, plan.flat_sets);
-        more = advancePathGroupPosteriors(&plan, path_cluster_estimates, loglik.data());
-    }
+    auto * ctx = threadContext();
+    const ResidentCluster resident(ctx, matrix, noise, counts, num_paths);
+
+    runPosteriorRounds(ctx, resident.handle, {0, num_paths}, &plans, {path_cluster_estimates});
 }
 
 void PathEstimator::estimatePathGroupPosteriorsGibbs(PathClusterEstimates * path_cluster_estimates, const vector<double> & matrix, const vector<double> & noise, const vector<double> & counts, const uint32_t num_paths, const vector<uint32_t> & path_counts, const uint32_t group_size, mt19937 * mt_rng) const {
@@ -442,6 +486,7 @@ void PathEstimator::estimatePathGroupPosteriorsGibbs(PathClusterEstimates * path
     const uint32_t num_gibbs_its = 100 + round(0.05 * group_size * num_paths);
 
     auto * ctx = threadContext();
+    const ResidentCluster resident(ctx, matrix, noise, counts, num_paths);   // the matrix goes up once for the whole chain
 
     // Conditional of one slot given the others: log-likelihood of {others} + {k} for every path k. The device adds
     // noise + col / group_size over the set in the order given: the other slots first, the candidate last, like the
@@ -456,7 +501,7 @@ void PathEstimator::estimatePathGroupPosteriorsGibbs(PathClusterEstimates * path
             flat_sets.push_back(k);
         }
 
-        auto group_probs = deviceLogLikelihoods(ctx, matrix, noise, counts, num_paths, group_size, flat_sets);
+        auto group_probs = resident.logLikelihoods(group_size, flat_sets);
 
         double sum_log_group_probs = numeric_limits<double>::lowest();
 
