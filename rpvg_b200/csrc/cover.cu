@@ -8,9 +8,9 @@
 // largest (sum of uncovered counts it covers) / weight_j, then zeroes the read classes it covers; one path -> {0}.
 //
 // Device: entries sorted by (global path, read class) with a stable radix sort, so that a column's weight is summed in
-// read-class order like the reference does; one CTA per cluster runs the pick loop: a warp per column for the covered
-// counts (integers, exact in fp64), a block arg-max that prefers the lower index among equal scores, a pass over the
-// picked column to zero its rows. No atomics, deterministic.
+// read-class order like the reference does; one CTA per cluster runs the pick loop on uncovered counts that are kept up
+// to date per column (see coverKernel): a block arg-max that prefers the lower index among equal scores, then the rows of
+// the picked column leave the counts of every column they are in. Sums of integers: exact, hence deterministic.
 
 #include <cfloat>
 #include <vector>
@@ -83,14 +83,19 @@ __global__ void coverWeightsKernel(uint64_t n_paths, const uint64_t * __restrict
     weight[j] = w * -1;
 }
 
-// one CTA per cluster
+// One CTA per cluster. The reference recomputes every column's uncovered count for every pick (O(picks x entries)); here
+// the counts are kept up to date instead: a read class is zeroed exactly once, and when it is, its count is taken off
+// every column that holds it (the entries of its row). All sums are sums of integers below 2^53 — exact in fp64 whatever
+// the order, atomics included — so the scores, and with them the picks, are the reference's. Work: O(entries + picks x N).
 __global__ void __launch_bounds__(kCoverThreads) coverKernel(const uint64_t * __restrict__ read_offset, const uint64_t * __restrict__ path_offset,
+                                                             const uint64_t * __restrict__ row_ptr, const uint32_t * __restrict__ col,
                                                              const uint64_t * __restrict__ col_ptr, const uint32_t * __restrict__ csc_row,
-                                                             const double * __restrict__ weight, double * uncovered, uint8_t * __restrict__ in_cover,
+                                                             const double * __restrict__ weight, double * uncovered, double * covered, uint8_t * __restrict__ in_cover,
                                                              const uint32_t * __restrict__ error) {
 
     __shared__ double best_score[kCoverThreads / 32];
     __shared__ uint32_t best_index[kCoverThreads / 32];
+    __shared__ double red[32];
     __shared__ int pick_shared;
 
     if (*error) { return; }
@@ -112,28 +117,44 @@ __global__ void __launch_bounds__(kCoverThreads) coverKernel(const uint64_t * __
         return;
     }
 
+    // uncovered count of every column, and the total still uncovered
+    for (uint32_t j = warp; j < N; j += num_warps) {
+        double sum = 0;
+        for (uint64_t k = col_ptr[p0 + j] + lane; k < col_ptr[p0 + j + 1]; k += 32) { sum += uncovered[csc_row[k]]; }
+        sum = warpSum(sum);
+        if (lane == 0) { covered[p0 + j] = sum; }
+    }
+
+    double mine = 0;
+    for (uint64_t r = r0 + tid; r < r1; r += kCoverThreads) { mine += uncovered[r]; }
+    double remaining = blockSum(mine, red);
+
     __syncthreads();
 
     for (uint32_t pick_round = 0; pick_round < N; ++pick_round) {
 
-        // while (uncovered_read_counts.maxCoeff() > 0)
-        int any = 0;
-        for (uint64_t r = r0 + tid; r < r1; r += kCoverThreads) { any |= uncovered[r] > 0; }
-        if (!__syncthreads_or(any)) { break; }
+        // while (uncovered_read_counts.maxCoeff() > 0): counts are non-negative integers
+        if (!(remaining > 0)) { break; }
 
         double score = 0;            // strictly-greater-than-0 is what the reference's scan starts from
         uint32_t index = 0xffffffffu;
 
-        for (uint32_t j = warp; j < N; j += num_warps) {
-
-            double covered = 0;
-            for (uint64_t k = col_ptr[p0 + j] + lane; k < col_ptr[p0 + j + 1]; k += 32) { covered += uncovered[csc_row[k]]; }
-            covered = warpSum(covered);   // integers: exact, order does not matter
-
-            const double s = covered / weight[p0 + j];
-            if (s > score) {   // ascending j per warp: the first maximum of this warp's columns stays
+        for (uint32_t j = tid; j < N; j += kCoverThreads) {   // ascending j per thread: its first maximum stays
+            const double s = covered[p0 + j] / weight[p0 + j];
+            if (s > score) {
                 score = s;
                 index = j;
+            }
+        }
+
+        // first strict maximum of the block: larger score, or the same score at a lower index
+        #pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            const double other_score = __shfl_xor_sync(0xffffffffu, score, off);
+            const uint32_t other_index = __shfl_xor_sync(0xffffffffu, index, off);
+            if (other_index != 0xffffffffu && (index == 0xffffffffu || other_score > score || (other_score == score && other_index < index))) {
+                score = other_score;
+                index = other_index;
             }
         }
 
@@ -147,7 +168,7 @@ __global__ void __launch_bounds__(kCoverThreads) coverKernel(const uint64_t * __
             double s = 0;
             uint32_t best = 0xffffffffu;
             for (int wi = 0; wi < num_warps; ++wi) {
-                if (best_index[wi] != 0xffffffffu && (best_score[wi] > s || (best_score[wi] == s && best_index[wi] < best))) {
+                if (best_index[wi] != 0xffffffffu && (best == 0xffffffffu || best_score[wi] > s || (best_score[wi] == s && best_index[wi] < best))) {
                     s = best_score[wi];
                     best = best_index[wi];
                 }
@@ -160,7 +181,23 @@ __global__ void __launch_bounds__(kCoverThreads) coverKernel(const uint64_t * __
         if (pick == 0xffffffffu) { break; }   // the reference asserts here (no positive score)
 
         if (tid == 0) { in_cover[p0 + pick] = 1; }
-        for (uint64_t k = col_ptr[p0 + pick] + tid; k < col_ptr[p0 + pick + 1]; k += kCoverThreads) { uncovered[csc_row[k]] = 0; }
+
+        // the read classes the pick covers leave every column that holds them
+        double taken = 0;
+
+        for (uint64_t k = col_ptr[p0 + pick] + tid; k < col_ptr[p0 + pick + 1]; k += kCoverThreads) {
+
+            const uint64_t r = csc_row[k];   // global read class (rows of a column are distinct: no two threads meet on one)
+            const double cnt = uncovered[r];
+
+            if (cnt > 0) {
+                uncovered[r] = 0;
+                taken += cnt;
+                for (uint64_t e = row_ptr[r]; e < row_ptr[r + 1]; ++e) { atomicAdd(&covered[p0 + col[e]], -cnt); }
+            }
+        }
+
+        remaining -= blockSum(taken, red);   // (barriers inside: the updates are done before the next scan)
         __syncthreads();
     }
 }
@@ -191,7 +228,7 @@ extern "C" int rpvg_b200_path_cover(rpvg_b200_ctx * ctx, const rpvg_b200_cluster
 
     auto pad = [](size_t b) { return (b + 255) & ~size_t(255); };
     const size_t bytes = 2 * pad(8 * (C + 1)) + pad(8 * (R + 1)) + pad(4 * Z) + pad(8 * Z) + pad(8 * R) + pad(4 * R) + 6 * pad(4 * Z) + pad(8 * R) + pad(8 * (P + 1)) +
-                         pad(8 * P) + pad(P) + pad(sort_bytes) + 1024;
+                         2 * pad(8 * P) + pad(P) + pad(sort_bytes) + 1024;
 
     char * base = nullptr;
     RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&base), bytes, s));
@@ -215,6 +252,7 @@ extern "C" int rpvg_b200_path_cover(rpvg_b200_ctx * ctx, const rpvg_b200_cluster
     double * d_cnt = reinterpret_cast<double *>(take(8 * R));
     uint64_t * d_col_ptr = reinterpret_cast<uint64_t *>(take(8 * (P + 1)));
     double * d_weight = reinterpret_cast<double *>(take(8 * P));
+    double * d_covered = reinterpret_cast<double *>(take(8 * P));
     uint8_t * d_in_cover = reinterpret_cast<uint8_t *>(take(P));
     void * d_sort_temp = take(sort_bytes);
     uint32_t * d_error = reinterpret_cast<uint32_t *>(take(4));
@@ -250,7 +288,7 @@ extern "C" int rpvg_b200_path_cover(rpvg_b200_ctx * ctx, const rpvg_b200_cluster
     if (err == cudaSuccess) {
         coverColumnPointerKernel<<<static_cast<unsigned>((P + 1 + 255) / 256), 256, 0, s>>>(P, Z, d_key_out, d_col_ptr);
         coverWeightsKernel<<<static_cast<unsigned>((P + 255) / 256), 256, 0, s>>>(P, d_col_ptr, d_idx_out, d_entry_row, d_prob, d_cnt, d_csc_row, d_weight);
-        coverKernel<<<C, kCoverThreads, 0, s>>>(d_read_offset, d_path_offset, d_col_ptr, d_csc_row, d_weight, d_cnt, d_in_cover, d_error);
+        coverKernel<<<C, kCoverThreads, 0, s>>>(d_read_offset, d_path_offset, d_row_ptr, d_col, d_col_ptr, d_csc_row, d_weight, d_cnt, d_covered, d_in_cover, d_error);
         ctx->launches += 3;
         err = cudaGetLastError();
     }
