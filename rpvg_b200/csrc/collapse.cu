@@ -35,8 +35,11 @@ int rpvgCollapseDevice(rpvg_b200_ctx * ctx, CollapseRows rows, uint32_t * d_row_
     collapseSortKernel<<<rows.n_problems, kCollapseSortThreads, 0, s>>>(rows, d_sorted);
     RPVG_LAUNCHED(ctx);
 
-    const unsigned pgrid = (rows.n_problems + 127) / 128;
-    collapseScanKernel<<<pgrid, 128, 0, s>>>(rows, d_sorted, prob_precision, d_sorted_class, d_n_classes);
+    collapseBoundaryKernel<<<grid, 256, 0, s>>>(rows, d_sorted, prob_precision, d_sorted_class);
+    RPVG_LAUNCHED(ctx);
+    collapseStretchKernel<<<grid, 256, 0, s>>>(rows, d_sorted, prob_precision, d_sorted_class);
+    RPVG_LAUNCHED(ctx);
+    collapseIndexKernel<<<rows.n_problems, kCollapseIndexThreads, 0, s>>>(rows, d_sorted_class, d_n_classes);
     RPVG_LAUNCHED(ctx);
 
     return RPVG_B200_OK;

@@ -13,8 +13,8 @@
 //      and a merge-path sort fed such a comparator can partition out of bounds (seen with cub::DeviceMergeSort); a
 //      network always yields a permutation. Ties under the comparator are broken by row id, so the result is the one a
 //      stable sort would give whenever the comparator is consistent;
-//   2. greedy scan, one thread per problem (sequential by definition: the predicate is against the running
-//      representative, which is not an equivalence relation);
+//   2. greedy scan (sequential by definition: the predicate is against the running representative, which is not an
+//      equivalence relation), cut into independent stretches at the rows that certainly start a class;
 //   3. class ids / representatives / class counts.
 // What is exact: the partition into classes, the class counts and the class order. Rows the comparator calls equal
 // (all columns within 100 eps, same count) are ordered arbitrarily by the reference's unstable std::sort; here they keep
@@ -153,32 +153,120 @@ __device__ __forceinline__ bool collapseWithinPrecision(const CollapseRows & row
     return fabs(rows.noise[a] - rows.noise[b]) < prob_precision;
 }
 
-// One thread per problem. sorted[] holds the row ids of every problem in sorted order (problems contiguous).
-// Writes, per sorted position: class index within its problem; per problem: number of classes.
-static __global__ void collapseScanKernel(const CollapseRows rows, const uint32_t * __restrict__ sorted, const double prob_precision,
-                                   uint32_t * __restrict__ sorted_class, uint32_t * __restrict__ n_classes) {
+// The greedy scan, in three parallel passes. sorted[] holds the row ids of every problem in sorted order (problems
+// contiguous); sorted_class[] receives, per sorted position, the class index within its problem; n_classes per problem.
+//
+// A row joins the CURRENT representative iff all columns are within the precision of the representative's — sequential by
+// definition. But the chain is cut wherever a row is certainly not within the precision of any representative it could
+// meet: if it differs from its predecessor by at least twice the precision in some column, then (triangle inequality) it
+// differs from the predecessor's representative by more than the precision, and from the predecessor itself too — it
+// starts a class whatever happened before. Pass 1 marks these certain starts (one thread per adjacent pair of rows);
+// pass 2 walks every stretch between two certain starts with the exact sequential rule (one thread per stretch: in real
+// data nearly every start is a certain one, or the rows are duplicates within the precision, so the stretches are short
+// or cheap); pass 3 numbers the classes (one CTA per problem). The result is the sequential scan's, bit for bit.
 
-    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= rows.n_problems) { return; }
+// true iff some column (absent = 0) or the noise value of rows a and b differ by at least `distance`
+__device__ __forceinline__ bool collapseFartherThan(const CollapseRows & rows, const uint32_t a, const uint32_t b, const double distance) {
 
+    uint64_t ea = rows.row_ptr[a], eb = rows.row_ptr[b];
+    const uint64_t ea1 = rows.row_ptr[a + 1], eb1 = rows.row_ptr[b + 1];
+
+    while (ea < ea1 || eb < eb1) {
+
+        const uint32_t ca = ea < ea1 ? rows.col[ea] : 0xffffffffu;
+        const uint32_t cb = eb < eb1 ? rows.col[eb] : 0xffffffffu;
+
+        double va = 0, vb = 0;
+        if (ca <= cb) { va = rows.val[ea++]; }
+        if (cb <= ca) { vb = rows.val[eb++]; }
+
+        if (fabs(va - vb) >= distance) { return true; }
+    }
+
+    return fabs(rows.noise[a] - rows.noise[b]) >= distance;
+}
+
+// pass 1: flag[s] = 1 where a class certainly starts (first row of a problem, or farther than twice the precision, with a
+// hair of slack for the rounding of the differences, from the row before), else 0
+static __global__ void collapseBoundaryKernel(const CollapseRows rows, const uint32_t * __restrict__ sorted, const double prob_precision, uint32_t * __restrict__ flag) {
+
+    const uint64_t s = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (s >= rows.n_rows) { return; }
+
+    const uint32_t row = sorted[s];
+    const uint32_t p = rows.row_problem[row];
+
+    bool start = (s == rows.problem_row_offset[p]);
+    if (!start) { start = collapseFartherThan(rows, sorted[s - 1], row, 2.0 * prob_precision * (1.0 + 1e-9)); }
+
+    flag[s] = start ? 1u : 0u;
+}
+
+// pass 2: the thread of a certain start walks its stretch (up to the next certain start or the end of the problem) with
+// the sequential rule; rows that become representatives inside the stretch get flag 2
+static __global__ void collapseStretchKernel(const CollapseRows rows, const uint32_t * __restrict__ sorted, const double prob_precision, uint32_t * flag) {
+
+    const uint64_t s = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (s >= rows.n_rows || flag[s] != 1u) { return; }
+
+    uint32_t rep = sorted[s];
+    const uint64_t s1 = rows.problem_row_offset[rows.row_problem[rep] + 1];
+
+    for (uint64_t t = s + 1; t < s1; ++t) {
+
+        if (flag[t] == 1u) { break; }   // written by pass 1 only; this thread alone writes inside its stretch
+
+        const uint32_t row = sorted[t];
+        if (!collapseWithinPrecision(rows, rep, row, prob_precision)) {
+            rep = row;
+            flag[t] = 2u;
+        }
+    }
+}
+
+constexpr int kCollapseIndexThreads = 256;
+
+// pass 3: class index = number of starts up to and including the position, minus one (in place), and the class count
+static __global__ void __launch_bounds__(kCollapseIndexThreads) collapseIndexKernel(const CollapseRows rows, uint32_t * sorted_class, uint32_t * __restrict__ n_classes) {
+
+    __shared__ uint32_t warp_total[kCollapseIndexThreads / 32];
+    __shared__ uint32_t carry;
+
+    const uint32_t p = blockIdx.x;
     const uint64_t s0 = rows.problem_row_offset[p];
     const uint64_t s1 = rows.problem_row_offset[p + 1];
 
-    uint32_t classes = 0;
-    uint32_t rep = 0;
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
-    for (uint64_t s = s0; s < s1; ++s) {
+    if (tid == 0) { carry = 0; }
+    __syncthreads();
 
-        const uint32_t row = sorted[s];
+    for (uint64_t base = s0; base < s1; base += kCollapseIndexThreads) {
 
-        if (s == s0 || !collapseWithinPrecision(rows, rep, row, prob_precision)) {
-            rep = row;
-            classes++;
+        const uint64_t s = base + tid;
+        const uint32_t start = (s < s1 && sorted_class[s] != 0u) ? 1u : 0u;
+
+        uint32_t incl = start;
+        #pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t up = __shfl_up_sync(0xffffffffu, incl, off);
+            if (lane >= off) { incl += up; }
         }
-        sorted_class[s] = classes - 1;
+
+        if (lane == 31) { warp_total[warp] = incl; }
+        __syncthreads();
+
+        uint32_t before = carry;
+        for (uint32_t w = 0; w < warp; ++w) { before += warp_total[w]; }
+
+        if (s < s1) { sorted_class[s] = before + incl - 1; }
+
+        __syncthreads();
+        if (tid == kCollapseIndexThreads - 1) { carry = before + incl; }
+        __syncthreads();
     }
 
-    n_classes[p] = classes;
+    if (tid == 0) { n_classes[p] = carry; }
 }
 
 // Per sorted position: scatter to per-row class ids, mark representatives, add the counts up per class (in sorted
