@@ -5,7 +5,7 @@ BASELINE.json ("transcripts model EM on synthetic clusters: 1M read classes, 200
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--config c1|c2|c3|c4|c5]
 
 --config (default c2, the headline) names the BASELINE.json configuration that runs; c1/c3/c4/c5 run the model classes
-through the batched driver and report the inference-stage wall time (see run_model_config).
+through the batched driver and report the inference-stage wall time (bench_models.py).
 
 One process per GPU (torchrun for N > 1). A step = one pass of the hot path (matrix build + EM of every cluster) over
 one synthetic arena of the named shape. Clusters are independent, so ranks are sharded with no data-path collective:
@@ -250,8 +250,8 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
 
     if args.config != "c2":
-        from rpvg_b200 import model_bench
-        return model_bench.run(args, rank, local_rank, world, ClockSampler, host_threads)
+        import bench_models
+        return bench_models.run(args, rank, local_rank, world, ClockSampler, host_threads)
 
     from rpvg_b200 import synth
 

@@ -1,4 +1,4 @@
-"""bench.py --config c1|c3|c4|c5: the model classes of the other BASELINE.json configurations through the batched driver.
+"""bench.py --config c1|c3|c4|c5 (part of bench.py, kept in a file of its own): the model classes of the other BASELINE.json configurations through the batched driver.
 
 A step = one ``estimateBatch`` call of the drop-in class over the whole (per-rank share of the) configuration: flatten ->
 H2D -> kernels -> D2H -> fill of every PathClusterEstimates, i.e. the inference stage the reference times at
@@ -26,12 +26,12 @@ import time
 
 import numpy as np
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.abspath(__file__))
 
 
 def build_config(name, scale):
     from rpvg_b200 import synth
-    from oracle import loader
+    from tests.harness import binding as loader
     if name == "c1":
         arena = synth.example_arena(n_reads=int(100_000 * scale))
         cfg = loader.make_config(loader.MODEL_HAPLOTYPE_TRANSCRIPTS, group_size=2)
@@ -72,7 +72,7 @@ def dense_cost(arena, model_is_nested):
 
 def run(args, rank, local_rank, world, ClockSampler, host_threads):
     sys.path.insert(0, ROOT)
-    from oracle import loader
+    from tests.harness import binding as loader   # marshalling for the estimator harness (this repository's classes)
     from rpvg_b200 import multi_gpu
 
     arena, cfg, what = build_config(args.config, args.scale)
@@ -94,8 +94,9 @@ def run(args, rank, local_rank, world, ClockSampler, host_threads):
     if args.impl == "reference":
         if rank != 0:
             return 0
+        from oracle import loader as oracle_loader   # the reference arm: rpvg's own classes
         threads = host_threads()
-        ref = loader.reference()
+        ref = oracle_loader.reference()
         order = sample_clusters(threads)
         chunk = 4 * threads
         sample, seconds = [], 0.0
@@ -172,9 +173,10 @@ def run(args, rank, local_rank, world, ClockSampler, host_threads):
         if args.config == "c4":
             line["roofline"] = pair_kernel_roofline(ctx, arena)
 
-        if not args.no_cpu_baseline and loader.reference_available():
+        from oracle import loader as oracle_loader   # cpu_baseline leg only
+        if not args.no_cpu_baseline and oracle_loader.reference_available():
             threads = host_threads()
-            ref = loader.reference()
+            ref = oracle_loader.reference()
             order = sample_clusters(threads)
             chunk = 4 * threads
             sample, cpu_s = [], 0.0

@@ -67,9 +67,9 @@ constexpr int kPairThreads = 256;         // 32 first groups x 8 threads, each t
 struct PairTileArgs {
 
     BoundedArgs b;
-    uint32_t n_clusters;
-    const uint64_t * item_offset;      // [n_clusters + 1] work items (tiles x row ranges) of each cluster
-    uint32_t rows_per_split;           // read classes per row range (multiple of kPairRowChunk); >= the largest cluster: no split
+    const uint4 * items;               // work items: x = cluster, y = tile row | tile column << 16, z = row range, w = row ranges of the tile;
+                                       // the row ranges of a tile are adjacent items
+    uint32_t rows_per_split;           // read classes per row range (multiple of kPairRowChunk)
     double * partial;                  // [n_items x 1024] when rows are split, else NULL
     unsigned long long * log_count;    // logs evaluated (for the roofline)
 };
@@ -87,7 +87,8 @@ __global__ void __launch_bounds__(kPairThreads) pairTileKernel(const PairTileArg
     const uint32_t warp = tid >> 5;
 
     const uint64_t item = blockIdx.x;
-    const uint32_t c = clusterOf(args.item_offset, args.n_clusters, item);
+    const uint4 what = args.items[item];
+    const uint32_t c = what.x;
 
     const uint64_t g0 = b.group_offset[c];
     const uint32_t G = static_cast<uint32_t>(b.group_offset[c + 1] - g0);
@@ -98,13 +99,8 @@ __global__ void __launch_bounds__(kPairThreads) pairTileKernel(const PairTileArg
     const double * counts = b.counts + r0;
     const uint32_t * order = b.order + g0;
 
-    const uint32_t tiles_side = (G + kPairTile - 1) / kPairTile;
-    const uint32_t n_tiles = tiles_side * (tiles_side + 1) / 2;
-    const uint32_t local = static_cast<uint32_t>(item - args.item_offset[c]);
-    const uint32_t split = local / n_tiles;
-
-    uint32_t ti, tj;
-    pairOfIndex(tiles_side, local % n_tiles, &ti, &tj);
+    const uint32_t ti = what.y & 0xffffu, tj = what.y >> 16;
+    const uint32_t split = what.z;
 
     const uint32_t row_begin = split * args.rows_per_split;
     const uint32_t row_end = min(rows, row_begin + args.rows_per_split);
@@ -196,29 +192,24 @@ __global__ void __launch_bounds__(kPairThreads) pairTileKernel(const PairTileArg
     }
 }
 
-// Row ranges were summed apart: add them in order, per pair, and write the values (one thread per pair slot of a tile).
+// Row ranges were summed apart: add them in order, per pair, and write the values (one CTA per tile: launched over all
+// items, only the first row range of a tile works).
 __global__ void __launch_bounds__(kPairThreads) pairCombineKernel(const PairTileArgs args) {
 
     const BoundedArgs & b = args.b;
 
-    // one CTA per (cluster, tile): the first-split item of the tile
-    const uint64_t tile_item = blockIdx.x;
-    const uint32_t c = clusterOf(args.item_offset, args.n_clusters, tile_item);   // item_offset here counts tiles x splits; see the launch
+    const uint64_t item = blockIdx.x;
+    const uint4 what = args.items[item];
+    if (what.z != 0) { return; }
+
+    const uint32_t c = what.x;
+    const uint32_t n_splits = what.w;
 
     const uint64_t g0 = b.group_offset[c];
     const uint32_t G = static_cast<uint32_t>(b.group_offset[c + 1] - g0);
-    const uint32_t rows = b.n_classes[c];
     const uint32_t * order = b.order + g0;
 
-    const uint32_t tiles_side = (G + kPairTile - 1) / kPairTile;
-    const uint32_t n_tiles = tiles_side * (tiles_side + 1) / 2;
-    const uint32_t n_splits = max(1u, (rows + args.rows_per_split - 1) / args.rows_per_split);
-    const uint32_t local = static_cast<uint32_t>(tile_item - args.item_offset[c]);
-
-    if (local >= n_tiles) { return; }   // only the items of the first row range combine
-
-    uint32_t ti, tj;
-    pairOfIndex(tiles_side, local, &ti, &tj);
+    const uint32_t ti = what.y & 0xffffu, tj = what.y >> 16;
 
     const uint32_t tid = threadIdx.x;
     const uint32_t i = ti * kPairTile + (tid >> 3);
@@ -237,7 +228,7 @@ __global__ void __launch_bounds__(kPairThreads) pairCombineKernel(const PairTile
 
         double acc = 0, comp = 0;
         for (uint32_t sp = 0; sp < n_splits; ++sp) {
-            const double y = args.partial[(args.item_offset[c] + static_cast<uint64_t>(sp) * n_tiles + local) * (kPairTile * kPairTile) + tid * 4 + q] - comp;
+            const double y = args.partial[(item + sp) * (kPairTile * kPairTile) + tid * 4 + q] - comp;
             const double t = acc + y;
             comp = (t - acc) - y;
             acc = t;
@@ -247,6 +238,85 @@ __global__ void __launch_bounds__(kPairThreads) pairCombineKernel(const PairTile
         const uint64_t p = p0 + row_start + (j - i);
         b.cand_loglik[p] = acc;
         b.pair_ll[p] = acc + (b.log_freq[g0 + a] + b.log_freq[g0 + bb] + (a == bb ? 0.0 : 0.6931471805599453));
+    }
+}
+
+// ---- the reference's bound on a whole row of pairs (rpvg:src/path_estimator.cpp:414, 427-433) ---------------------------
+// max over the columns of every read class, halved (read_path_probs.rowwise().maxCoeff() / group_size): one thread per
+// read class, coalesced over the read classes of a column
+__global__ void pairRowMaxKernel(const BoundedArgs b, const uint32_t n_clusters, const uint64_t n_rows_total, double * __restrict__ row_max) {
+
+    const uint64_t r = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (r >= n_rows_total) { return; }
+
+    const uint32_t c = clusterOf(b.row_offset, n_clusters, r);
+    const uint32_t local = static_cast<uint32_t>(r - b.row_offset[c]);
+    const uint32_t rows = b.n_classes[c];
+    if (local >= rows) { return; }
+
+    const uint32_t G = static_cast<uint32_t>(b.group_offset[c + 1] - b.group_offset[c]);
+    const double * matrix = b.matrix + b.matrix_offset[c];
+
+    double best = matrix[local];
+    for (uint32_t g = 1; g < G; ++g) { best = fmax(best, matrix[static_cast<uint64_t>(g) * rows + local]); }
+
+    row_max[r] = best / 2.0;
+}
+
+// optimal log-likelihood of any pair whose first group is order[i]: one warp per (cluster, i)
+__global__ void __launch_bounds__(kBoundedThreads) pairRowBoundKernel(const BoundedArgs b, const uint32_t n_clusters, const uint64_t n_groups_total,
+                                                                      const double * __restrict__ row_max, double * __restrict__ bound) {
+
+    const uint32_t lane = threadIdx.x & 31;
+    const uint64_t k = (blockIdx.x * static_cast<uint64_t>(kBoundedThreads) + threadIdx.x) >> 5;
+    if (k >= n_groups_total) { return; }
+
+    const uint32_t c = clusterOf(b.group_offset, n_clusters, k);
+    const uint64_t g0 = b.group_offset[c];
+    const uint64_t r0 = b.row_offset[c];
+    const uint32_t rows = b.n_classes[c];
+    const uint32_t a = b.order[k];
+
+    const double * col = b.matrix + b.matrix_offset[c] + static_cast<uint64_t>(a) * rows;
+
+    double acc = 0;
+    for (uint32_t r = lane; r < rows; r += 32) {
+        const double base = b.noise[r0 + r] + col[r] / 2.0;
+        acc += b.counts[r0 + r] * log(base + row_max[r0 + r]);
+    }
+    acc = warpSum(acc);
+
+    if (lane == 0) { bound[k] = acc + (b.log_freq[g0 + a] + 0.6931471805599453); }
+}
+
+__global__ void pairFillKernel(const uint64_t n, double * __restrict__ pair_ll) {
+
+    const uint64_t p = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (p < n) { pair_ll[p] = -DBL_MAX; }
+}
+
+// largest value among the pairs of the first `head_rows` rows of every cluster (a prefix of its pairs): one CTA per cluster
+__global__ void __launch_bounds__(kBoundedThreads) pairHeadMaxKernel(const BoundedArgs b, const uint32_t head_rows, double * __restrict__ head_max) {
+
+    __shared__ double red[kBoundedThreads / 32];
+
+    const uint32_t c = blockIdx.x;
+    const uint64_t G = b.group_offset[c + 1] - b.group_offset[c];
+    const uint64_t h = G < head_rows ? G : head_rows;
+    const uint64_t n = h * G - (h * (h - 1)) / 2;
+    const double * pair_ll = b.pair_ll + b.pair_offset[c];
+
+    double best = -DBL_MAX;
+    for (uint64_t p = threadIdx.x; p < n; p += kBoundedThreads) { best = fmax(best, pair_ll[p]); }
+
+    #pragma unroll
+    for (int off = 16; off > 0; off >>= 1) { best = fmax(best, __shfl_xor_sync(0xffffffffu, best, off)); }
+    if ((threadIdx.x & 31) == 0) { red[threadIdx.x >> 5] = best; }
+    __syncthreads();
+
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < kBoundedThreads / 32; ++w) { best = fmax(best, red[w]); }
+        head_max[c] = best;
     }
 }
 
@@ -422,77 +492,150 @@ extern "C" int rpvg_b200_grouped_bounded_pairs(rpvg_b200_ctx * ctx, rpvg_b200_gr
         args.cand_pair = d_cand_pair;
         args.cand_loglik = d_cand_loglik;
 
-        // ---- plan: tiles of 32 x 32 pairs per cluster; row ranges as well while the tiles alone leave SMs idle
+        // ---- plan. The reference skips all pairs of a first group whose bound (its log-likelihood with the best column of
+        // every read class as partner) is already out of reach of the running maximum. The running maximum is the prefix
+        // maximum over the pairs in enumeration order, so any maximum over an initial stretch of rows is a lower bound
+        // of it for every later row: rows whose bound fails against it (with the margin) are skipped by the reference
+        // as well. Two waves: the first 32 groups of every cluster (the most probable ones: the caller orders them by
+        // marginal posterior), then only the tile rows that still hold a row in reach. Pairs never evaluated stay at the
+        // most negative value and drop out in the scan.
         std::vector<uint32_t> n_classes(C, 0);
         err = cudaMemcpyAsync(n_classes.data(), grouped->d_n_classes, 4 * static_cast<size_t>(C), cudaMemcpyDeviceToHost, s);
         if (err == cudaSuccess) { err = cudaStreamSynchronize(s); }
 
-        uint64_t n_tiles_total = 0;
-        uint32_t most_rows = 0;
-        for (uint32_t c = 0; c < C; ++c) {
-            const uint64_t side = (group_offset[c + 1] - group_offset[c] + kPairTile - 1) / kPairTile;
-            n_tiles_total += side * (side + 1) / 2;
-            most_rows = std::max(most_rows, n_classes[c]);
-        }
-
-        const uint64_t want_items = 4ull * static_cast<uint64_t>(ctx->num_sms);
-        uint32_t rows_per_split = std::max(most_rows, kPairRowChunk);
-
-        if (n_tiles_total < want_items) {
-            const uint64_t splits = (want_items + n_tiles_total - 1) / n_tiles_total;
-            rows_per_split = static_cast<uint32_t>((most_rows + splits - 1) / splits);
-            rows_per_split = std::max(8 * kPairRowChunk, ((rows_per_split + kPairRowChunk - 1) / kPairRowChunk) * kPairRowChunk);
-        }
-
-        std::vector<uint64_t> item_offset(C + 1, 0);
-        bool split_rows = false;
-        for (uint32_t c = 0; c < C; ++c) {
-            const uint64_t side = (group_offset[c + 1] - group_offset[c] + kPairTile - 1) / kPairTile;
-            const uint64_t splits = std::max<uint64_t>(1, (static_cast<uint64_t>(n_classes[c]) + rows_per_split - 1) / rows_per_split);
-            split_rows = split_rows || splits > 1;
-            item_offset[c + 1] = item_offset[c] + side * (side + 1) / 2 * splits;
-        }
-        const uint64_t n_items = item_offset[C];
-
-        if (n_items >= (1ull << 31)) { err = cudaErrorInvalidValue; }
+        const uint64_t R_total = grouped->h_rows_total;
 
         char * extra = nullptr;
-        const size_t extra_bytes = pad(8 * (C + 1)) + (split_rows ? pad(8 * n_items * kPairTile * kPairTile) : 0) + 256;
+        const size_t extra_bytes = pad(8 * R_total) + pad(8 * G) + pad(8 * C) + 256;
         if (err == cudaSuccess) { err = cudaMallocAsync(reinterpret_cast<void **>(&extra), extra_bytes, s); }
 
-        if (err == cudaSuccess) {
+        double * d_row_max = reinterpret_cast<double *>(extra);
+        double * d_bound = reinterpret_cast<double *>(extra + pad(8 * R_total));
+        double * d_head_max = reinterpret_cast<double *>(extra + pad(8 * R_total) + pad(8 * G));
+        unsigned long long * d_log_count = reinterpret_cast<unsigned long long *>(extra + extra_bytes - 256);
 
-            uint64_t * d_item_offset = reinterpret_cast<uint64_t *>(extra);
-            double * d_partial = split_rows ? reinterpret_cast<double *>(extra + pad(8 * (C + 1))) : nullptr;
-            unsigned long long * d_log_count = reinterpret_cast<unsigned long long *>(extra + extra_bytes - 256);
+        cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+        if (err == cudaSuccess) { err = cudaEventCreate(&ev0); }
+        if (err == cudaSuccess) { err = cudaEventCreate(&ev1); }
+        float pair_ms = 0;
 
-            err = cudaMemcpyAsync(d_item_offset, item_offset.data(), 8 * (C + 1), cudaMemcpyHostToDevice, s);
-            if (err == cudaSuccess) { err = cudaMemsetAsync(d_log_count, 0, 8, s); }
+        std::vector<double> bound(G, 0), head_max(C, 0);
+
+        // one wave: the tiles in `tiles` (cluster, tile row, tile column), cut into row ranges while they leave SMs idle
+        auto run_wave = [&](const std::vector<uint4> & tiles) {
+
+            if (tiles.empty() || err != cudaSuccess) { return; }
+
+            uint32_t most_rows = 0;
+            for (auto & t: tiles) { most_rows = std::max(most_rows, n_classes[t.x]); }
+
+            const uint64_t want_items = 4ull * static_cast<uint64_t>(ctx->num_sms);
+            uint32_t rows_per_split = std::max(most_rows, kPairRowChunk);
+
+            if (tiles.size() < want_items) {
+                const uint64_t splits = (want_items + tiles.size() - 1) / tiles.size();
+                rows_per_split = static_cast<uint32_t>((most_rows + splits - 1) / splits);
+                rows_per_split = std::max(8 * kPairRowChunk, ((rows_per_split + kPairRowChunk - 1) / kPairRowChunk) * kPairRowChunk);
+            }
+
+            std::vector<uint4> items;
+            items.reserve(tiles.size());
+            bool split_rows = false;
+
+            for (auto & t: tiles) {
+                const uint32_t splits = std::max(1u, (n_classes[t.x] + rows_per_split - 1) / rows_per_split);
+                split_rows = split_rows || splits > 1;
+                for (uint32_t sp = 0; sp < splits; ++sp) { items.push_back(make_uint4(t.x, t.y, sp, splits)); }
+            }
+
+            if (items.size() >= (1ull << 31)) { err = cudaErrorInvalidValue; return; }
+
+            char * wave = nullptr;
+            const size_t wave_bytes = pad(16 * items.size()) + (split_rows ? pad(8 * items.size() * kPairTile * kPairTile) : 0);
+            err = cudaMallocAsync(reinterpret_cast<void **>(&wave), wave_bytes, s);
+            if (err != cudaSuccess) { return; }
+
+            uint4 * d_items = reinterpret_cast<uint4 *>(wave);
+            err = cudaMemcpyAsync(d_items, items.data(), 16 * items.size(), cudaMemcpyHostToDevice, s);
 
             PairTileArgs tile_args;
             tile_args.b = args;
-            tile_args.n_clusters = C;
-            tile_args.item_offset = d_item_offset;
+            tile_args.items = d_items;
             tile_args.rows_per_split = rows_per_split;
-            tile_args.partial = d_partial;
+            tile_args.partial = split_rows ? reinterpret_cast<double *>(wave + pad(16 * items.size())) : nullptr;
             tile_args.log_count = d_log_count;
 
-            cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-            if (err == cudaSuccess) { err = cudaEventCreate(&ev0); }
-            if (err == cudaSuccess) { err = cudaEventCreate(&ev1); }
-
-            if (err == cudaSuccess && n_items > 0) {
+            if (err == cudaSuccess) {
 
                 cudaEventRecord(ev0, s);
-                pairTileKernel<<<static_cast<unsigned>(n_items), kPairThreads, 0, s>>>(tile_args);
+                pairTileKernel<<<static_cast<unsigned>(items.size()), kPairThreads, 0, s>>>(tile_args);
                 ctx->launches++;
-
                 if (split_rows) {
-                    pairCombineKernel<<<static_cast<unsigned>(n_items), kPairThreads, 0, s>>>(tile_args);
+                    pairCombineKernel<<<static_cast<unsigned>(items.size()), kPairThreads, 0, s>>>(tile_args);
                     ctx->launches++;
                 }
                 cudaEventRecord(ev1, s);
+                err = cudaGetLastError();
+            }
 
+            // (the item list is a host vector: done with it before it goes)
+            if (err == cudaSuccess) { err = cudaEventSynchronize(ev1); }
+            if (err == cudaSuccess) {
+                float ms = 0;
+                cudaEventElapsedTime(&ms, ev0, ev1);
+                pair_ms += ms;
+            }
+
+            cudaFreeAsync(wave, s);
+        };
+
+        if (err == cudaSuccess) {
+
+            err = cudaMemsetAsync(d_log_count, 0, 8, s);
+
+            if (err == cudaSuccess && R_total > 0) {
+                pairRowMaxKernel<<<static_cast<unsigned>((R_total + 255) / 256), 256, 0, s>>>(args, C, R_total, d_row_max);
+                pairRowBoundKernel<<<static_cast<unsigned>((G * 32 + kBoundedThreads - 1) / kBoundedThreads), kBoundedThreads, 0, s>>>(args, C, G, d_row_max, d_bound);
+                pairFillKernel<<<static_cast<unsigned>((NP + 255) / 256), 256, 0, s>>>(NP, d_pair_ll);
+                ctx->launches += 3;
+                err = cudaGetLastError();
+            }
+
+            // wave 1: tile row 0 of every cluster
+            std::vector<uint4> tiles;
+            for (uint32_t c = 0; c < C; ++c) {
+                const uint32_t side = static_cast<uint32_t>((group_offset[c + 1] - group_offset[c] + kPairTile - 1) / kPairTile);
+                for (uint32_t tj = 0; tj < side; ++tj) { tiles.push_back(make_uint4(c, tj << 16, 0, 1)); }
+            }
+            run_wave(tiles);
+
+            if (err == cudaSuccess) {
+                pairHeadMaxKernel<<<C, kBoundedThreads, 0, s>>>(args, kPairTile, d_head_max);
+                ctx->launches++;
+                err = cudaGetLastError();
+            }
+            if (err == cudaSuccess) { err = cudaMemcpyAsync(bound.data(), d_bound, 8 * G, cudaMemcpyDeviceToHost, s); }
+            if (err == cudaSuccess) { err = cudaMemcpyAsync(head_max.data(), d_head_max, 8 * static_cast<size_t>(C), cudaMemcpyDeviceToHost, s); }
+            if (err == cudaSuccess) { err = cudaStreamSynchronize(s); }
+
+            // wave 2: the other tile rows that hold a first group still in reach
+            tiles.clear();
+            for (uint32_t c = 0; c < C && err == cudaSuccess; ++c) {
+                const uint64_t g0 = group_offset[c];
+                const uint32_t Gc = static_cast<uint32_t>(group_offset[c + 1] - g0);
+                const uint32_t side = (Gc + kPairTile - 1) / kPairTile;
+                for (uint32_t ti = 1; ti < side; ++ti) {
+                    bool in_reach = false;
+                    for (uint32_t i = ti * kPairTile; i < std::min(Gc, (ti + 1) * kPairTile) && !in_reach; ++i) {
+                        in_reach = !(bound[g0 + i] - head_max[c] < min_log_diff);
+                    }
+                    if (!in_reach) { continue; }
+                    for (uint32_t tj = ti; tj < side; ++tj) { tiles.push_back(make_uint4(c, ti | (tj << 16), 0, 1)); }
+                }
+            }
+            run_wave(tiles);
+
+            if (err == cudaSuccess) {
                 boundedScanKernel<<<C, kBoundedThreads, 0, s>>>(args);
                 ctx->launches++;
                 err = cudaGetLastError();
@@ -502,17 +645,14 @@ extern "C" int rpvg_b200_grouped_bounded_pairs(rpvg_b200_ctx * ctx, rpvg_b200_gr
             if (err == cudaSuccess) { err = cudaMemcpyAsync(&log_count, d_log_count, 8, cudaMemcpyDeviceToHost, s); }
             if (err == cudaSuccess) { err = cudaStreamSynchronize(s); }
 
-            if (err == cudaSuccess && n_items > 0) {
-                float ms = 0;
-                cudaEventElapsedTime(&ms, ev0, ev1);
-                grouped->pair_ms += ms;
+            if (err == cudaSuccess) {
+                grouped->pair_ms += pair_ms;
                 grouped->pair_logs += static_cast<double>(log_count);
             }
-
-            if (ev0) { cudaEventDestroy(ev0); }
-            if (ev1) { cudaEventDestroy(ev1); }
         }
 
+        if (ev0) { cudaEventDestroy(ev0); }
+        if (ev1) { cudaEventDestroy(ev1); }
         if (extra) { cudaFreeAsync(extra, s); }
     }
 

@@ -350,6 +350,7 @@ static int groupedCollapse(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, c
         grouped->d_group_offset = d_group_offset;
         grouped->d_matrix_offset = d_matrix_offset;
         grouped->d_n_classes = d_n_classes;
+        grouped->h_rows_total = cl->read_offset[C];
         *keep = grouped;
         return status;
     }
@@ -489,6 +490,7 @@ extern "C" int rpvg_b200_grouped_raw(rpvg_b200_ctx * ctx, const rpvg_b200_cluste
     grouped->d_group_offset = d_path_offset;
     grouped->d_matrix_offset = d_matrix_offset;
     grouped->d_n_classes = d_rows;
+    grouped->h_rows_total = cl->read_offset[C];
     *out = grouped;
 
     return RPVG_B200_OK;

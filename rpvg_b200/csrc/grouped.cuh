@@ -16,6 +16,7 @@ struct rpvg_b200_grouped {
     const uint64_t * d_group_offset = nullptr; // [n_clusters + 1]
     const uint64_t * d_matrix_offset = nullptr;
     const uint32_t * d_n_classes = nullptr;    // [n_clusters]
+    uint64_t h_rows_total = 0;                 // d_row_offset[n_clusters] (host copy): extent of the per-row arrays
 
     // results of the last rpvg_b200_grouped_bounded_pairs on this handle (host memory, valid until the next one / free)
     std::vector<uint64_t> h_cand_offset;

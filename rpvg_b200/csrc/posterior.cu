@@ -306,6 +306,7 @@ extern "C" int rpvg_b200_grouped_upload(rpvg_b200_ctx * ctx, const rpvg_b200_log
     grouped->d_group_offset = d_path_offset;
     grouped->d_matrix_offset = d_matrix_offset;
     grouped->d_n_classes = d_rows;
+    grouped->h_rows_total = R;
     *out = grouped;
 
     return RPVG_B200_OK;

@@ -37,50 +37,90 @@ struct BatchArena {
     uint32_t * col = nullptr, * count = nullptr;
     double * prob = nullptr, * noise = nullptr;
 
-    // all clusters at once, the clusters filled in parallel
+    // all clusters at once, filled in parallel over stretches of read classes (a cluster may hold most of the batch: the
+    // unit of work is 256 read classes, not a cluster)
     void build(rpvg_b200_ctx * ctx, const vector<const vector<ReadPathProbabilities> *> & members, const vector<uint32_t> & num_paths) {
 
         const size_t n = members.size();
-        vector<uint64_t> entries(n, 0);
-
-        #pragma omp parallel for schedule(dynamic, 8)
-        for (size_t k = 0; k < n; ++k) {
-            uint64_t e = 0;
-            for (auto & read_probs: *members[k]) {
-                for (auto & path_probs: read_probs.pathProbs()) { e += path_probs.second.size(); }
-            }
-            entries[k] = e;
-        }
 
         read_offset.assign(1, 0);
         path_offset.assign(1, 0);
-        vector<uint64_t> entry_offset = {0};
 
         for (size_t k = 0; k < n; ++k) {
             read_offset.push_back(read_offset.back() + members[k]->size());
             path_offset.push_back(path_offset.back() + num_paths[k]);
-            entry_offset.push_back(entry_offset.back() + entries[k]);
         }
 
-        row_ptr = static_cast<uint64_t *>(rpvg_b200_pinned_scratch(ctx, 0, sizeof(uint64_t) * (read_offset.back() + 1)));
-        col = static_cast<uint32_t *>(rpvg_b200_pinned_scratch(ctx, 1, sizeof(uint32_t) * (entry_offset.back() + 1)));
-        prob = static_cast<double *>(rpvg_b200_pinned_scratch(ctx, 2, sizeof(double) * (entry_offset.back() + 1)));
-        noise = static_cast<double *>(rpvg_b200_pinned_scratch(ctx, 3, sizeof(double) * (read_offset.back() + 1)));
-        count = static_cast<uint32_t *>(rpvg_b200_pinned_scratch(ctx, 4, sizeof(uint32_t) * (read_offset.back() + 1)));
-        if (!row_ptr || !col || !prob || !noise || !count) { fatalBatch(ctx, "rpvg_b200_pinned_scratch"); }
-        row_ptr[0] = 0;
+        const uint64_t R = read_offset.back();
 
-        #pragma omp parallel for schedule(dynamic, 8)
+        struct Stretch { uint32_t cluster; uint32_t begin, end; };
+        constexpr uint32_t kStretchRows = 256;
+
+        vector<Stretch> stretches;
         for (size_t k = 0; k < n; ++k) {
+            const uint32_t m = members[k]->size();
+            for (uint32_t b = 0; b < m; b += kStretchRows) { stretches.push_back({static_cast<uint32_t>(k), b, min(m, b + kStretchRows)}); }
+        }
+
+        row_ptr = static_cast<uint64_t *>(rpvg_b200_pinned_scratch(ctx, 0, sizeof(uint64_t) * (R + 1)));
+        noise = static_cast<double *>(rpvg_b200_pinned_scratch(ctx, 3, sizeof(double) * (R + 1)));
+        count = static_cast<uint32_t *>(rpvg_b200_pinned_scratch(ctx, 4, sizeof(uint32_t) * (R + 1)));
+        if (!row_ptr || !noise || !count) { fatalBatch(ctx, "rpvg_b200_pinned_scratch"); }
+
+        // pass 1: entries of every read class (into row_ptr[r + 1]), its noise and count
+        #pragma omp parallel for schedule(dynamic, 4)
+        for (size_t q = 0; q < stretches.size(); ++q) {
+
+            const auto & st = stretches[q];
+            const auto & probs = *members[st.cluster];
+            uint64_t r = read_offset[st.cluster] + st.begin;
+
+            for (uint32_t i = st.begin; i < st.end; ++i, ++r) {
+                uint64_t e = 0;
+                for (auto & path_probs: probs[i].pathProbs()) { e += path_probs.second.size(); }
+                row_ptr[r + 1] = e;
+                noise[r] = probs[i].noiseProb();
+                count[r] = probs[i].readCount();
+            }
+        }
+
+        row_ptr[0] = 0;
+        for (uint64_t r = 0; r < R; ++r) { row_ptr[r + 1] += row_ptr[r]; }
+
+        const uint64_t Z = row_ptr[R];
+
+        col = static_cast<uint32_t *>(rpvg_b200_pinned_scratch(ctx, 1, sizeof(uint32_t) * (Z + 1)));
+        prob = static_cast<double *>(rpvg_b200_pinned_scratch(ctx, 2, sizeof(double) * (Z + 1)));
+        if (!col || !prob) { fatalBatch(ctx, "rpvg_b200_pinned_scratch"); }
+
+        // pass 2: the entries, ascending by path within a read class. A read class comes as a few groups of ascending ids:
+        // one group is copied as it is, several are merged by a sort
+        #pragma omp parallel for schedule(dynamic, 4)
+        for (size_t q = 0; q < stretches.size(); ++q) {
+
+            const auto & st = stretches[q];
+            const auto & probs = *members[st.cluster];
+            uint64_t r = read_offset[st.cluster] + st.begin;
 
             vector<pair<uint32_t, double> > row;
-            uint64_t e = entry_offset[k];
-            uint64_t r = read_offset[k];
 
-            for (auto & read_probs: *members[k]) {
+            for (uint32_t i = st.begin; i < st.end; ++i, ++r) {
+
+                uint64_t e = row_ptr[r];
+                const auto & groups = probs[i].pathProbs();
+
+                if (groups.size() == 1 && is_sorted(groups.front().second.begin(), groups.front().second.end())) {
+
+                    for (auto & path: groups.front().second) {
+                        col[e] = path;
+                        prob[e] = groups.front().first;
+                        ++e;
+                    }
+                    continue;
+                }
 
                 row.clear();
-                for (auto & path_probs: read_probs.pathProbs()) {
+                for (auto & path_probs: groups) {
                     for (auto & path: path_probs.second) { row.emplace_back(path, path_probs.first); }
                 }
                 sort(row.begin(), row.end());
@@ -90,11 +130,6 @@ struct BatchArena {
                     prob[e] = entry.second;
                     ++e;
                 }
-
-                row_ptr[r + 1] = e;
-                noise[r] = read_probs.noiseProb();
-                count[r] = read_probs.readCount();
-                ++r;
             }
         }
     }
