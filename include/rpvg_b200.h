@@ -234,6 +234,14 @@ void rpvg_b200_grouped_free(rpvg_b200_ctx * ctx, rpvg_b200_grouped * grouped);
  * (A cluster with one path gets {0}; a cluster whose read classes are all noise-only gets the empty cover.) */
 int rpvg_b200_path_cover(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * clusters, uint8_t * in_cover);
 
+/* MinimumPathAbundanceEstimator::weightedMinimumPathCover itself (rpvg:src/path_abundance_estimator.cpp:297-340; the public
+ * method the reference's own test calls, rpvg:src/tests/path_abundance_estimator_test.cpp:8-28) on a cover the caller made:
+ * read class r covers the paths col[row_ptr[r] .. row_ptr[r+1]) (the true entries of row r of the boolean matrix),
+ * read_counts[n_reads] and path_weights[n_paths] as the reference takes them. in_cover[n_paths]: 1 for the picked paths
+ * (ascending index = the reference's sorted result). One cluster per call. */
+int rpvg_b200_weighted_path_cover(rpvg_b200_ctx * ctx, uint32_t n_reads, uint32_t n_paths, const uint64_t * row_ptr, const uint32_t * col,
+                                  const double * read_counts, const double * path_weights, uint8_t * in_cover);
+
 /* ---- Gibbs read-count sampler ----
  * gibbsReadCountSampler (rpvg:src/path_abundance_estimator.cpp:116-212), started from the EM result of each cluster
  * (or path subset): num_samples[c] samples, one every thin_its iterations. Random numbers are counter-based

@@ -98,6 +98,7 @@ def lib():
         l.rpvg_b200_collapse.argtypes = [C.c_void_p, C.POINTER(CollapseProblems), C.c_double] + [C.c_void_p] * 4
         l.rpvg_b200_subset_em.argtypes = [C.c_void_p, C.POINTER(Clusters), C.POINTER(Subsets), C.POINTER(EmParams), C.c_double] + [C.c_void_p] * 5
         l.rpvg_b200_path_cover.argtypes = [C.c_void_p, C.POINTER(Clusters), C.c_void_p]
+        l.rpvg_b200_weighted_path_cover.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32] + [C.c_void_p] * 5
         l.rpvg_b200_em_cluster_noalloc.argtypes = ([C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint64] + [C.c_void_p] * 5 + [C.POINTER(EmParams)] +
                                                    [C.c_void_p] * 4 + [C.c_char_p, C.c_size_t])
         _lib = l
@@ -229,6 +230,19 @@ class Context:
         cl = clusters_struct(arena)
         self._check(lib().rpvg_b200_path_cover(self._h, C.byref(cl), in_cover.ctypes.data))
         return in_cover.astype(bool)
+
+    def weighted_path_cover(self, cover, read_counts, path_weights):
+        """rpvg_b200_weighted_path_cover on a dense boolean cover (rows x paths): sorted list of the picked paths."""
+        cover = np.asarray(cover, dtype=bool)
+        rows, n_paths = cover.shape
+        row_ptr = np.zeros(rows + 1, dtype=np.uint64)
+        row_ptr[1:] = np.cumsum(cover.sum(axis=1))
+        col = np.ascontiguousarray(np.nonzero(cover)[1], dtype=np.uint32)
+        read_counts = np.ascontiguousarray(read_counts, dtype=np.float64)
+        path_weights = np.ascontiguousarray(path_weights, dtype=np.float64)
+        in_cover = np.zeros(n_paths, dtype=np.uint8)
+        self._check(lib().rpvg_b200_weighted_path_cover(self._h, rows, n_paths, _ptr(row_ptr), _ptr(col), _ptr(read_counts), _ptr(path_weights), _ptr(in_cover)))
+        return [int(j) for j in np.nonzero(in_cover)[0]]
 
     def merge_read_records(self, read_offset, group_ptr, group_prob, id_ptr, ids, noise, count, prob_precision=1e-8):
         """rpvg_b200_merge_read_records: (n_merged[C], record_class[R], merged_rep[R], merged_count[R])."""

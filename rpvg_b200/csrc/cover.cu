@@ -307,3 +307,132 @@ extern "C" int rpvg_b200_path_cover(rpvg_b200_ctx * ctx, const rpvg_b200_cluster
     cudaFreeAsync(base, s);
     return status;
 }
+
+
+// ---- weightedMinimumPathCover itself (rpvg:src/path_abundance_estimator.cpp:297-340) on a caller-made cover ---------------
+namespace {
+
+// one thread per read class: keys of its cover entries (the read classes come with their counts as they are)
+__global__ void coverGivenRowsKernel(uint64_t n_reads, const uint64_t * __restrict__ row_ptr, const uint32_t * __restrict__ col, const uint32_t n_paths,
+                                     uint32_t * __restrict__ key, uint32_t * __restrict__ idx, uint32_t * __restrict__ entry_row, uint32_t * __restrict__ error) {
+
+    const uint64_t r = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (r >= n_reads) { return; }
+
+    for (uint64_t e = row_ptr[r]; e < row_ptr[r + 1]; ++e) {
+        uint32_t j = col[e];
+        if (j >= n_paths) {
+            atomicOr(error, RPVG_DEV_ERR_COL_RANGE);
+            j = 0;
+        }
+        key[e] = j;
+        idx[e] = static_cast<uint32_t>(e);
+        entry_row[e] = static_cast<uint32_t>(r);
+    }
+}
+
+__global__ void coverGivenColumnsKernel(uint64_t nnz, const uint32_t * __restrict__ sorted_idx, const uint32_t * __restrict__ entry_row, uint32_t * __restrict__ csc_row) {
+
+    const uint64_t k = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (k < nnz) { csc_row[k] = entry_row[sorted_idx[k]]; }
+}
+
+}
+
+extern "C" int rpvg_b200_weighted_path_cover(rpvg_b200_ctx * ctx, uint32_t n_reads, uint32_t n_paths, const uint64_t * row_ptr, const uint32_t * col,
+                                             const double * read_counts, const double * path_weights, uint8_t * in_cover) {
+
+    if (!ctx || !row_ptr || !read_counts || !path_weights || !in_cover) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "rpvg_b200_weighted_path_cover: NULL argument"); }
+    if (n_paths == 0) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "rpvg_b200_weighted_path_cover: no paths"); }
+
+    if (n_reads == 0) {   // nothing uncovered: the reference's loop does not run (one path -> {0} all the same)
+        for (uint32_t j = 0; j < n_paths; ++j) { in_cover[j] = (n_paths == 1) ? 1 : 0; }
+        return RPVG_B200_OK;
+    }
+
+    const uint64_t R = n_reads, P = n_paths, Z = row_ptr[R];
+    if (row_ptr[0] != 0) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "rpvg_b200_weighted_path_cover: row_ptr must start at 0"); }
+    if (Z >= 0x7fffffffull) { return rpvgFail(ctx, RPVG_B200_ERR_LIMIT, "rpvg_b200_weighted_path_cover: too many entries"); }
+    if (Z > 0 && !col) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "rpvg_b200_weighted_path_cover: col is NULL"); }
+
+    RPVG_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+
+    int sort_bits = 1;
+    while ((uint64_t(1) << sort_bits) < P + 1 && sort_bits < 32) { sort_bits++; }
+
+    size_t sort_bytes = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, static_cast<uint32_t *>(nullptr), static_cast<uint32_t *>(nullptr), static_cast<uint32_t *>(nullptr),
+                                    static_cast<uint32_t *>(nullptr), static_cast<int>(Z), 0, sort_bits, s);
+
+    auto pad = [](size_t b) { return (b + 255) & ~size_t(255); };
+    const size_t bytes = 2 * pad(16) + pad(8 * (R + 1)) + 7 * pad(4 * (Z + 1)) + pad(8 * R) + pad(8 * (P + 1)) + 2 * pad(8 * P) + pad(P) + pad(sort_bytes) + 1024;
+
+    char * base = nullptr;
+    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&base), bytes, s));
+
+    size_t used = 0;
+    auto take = [&](size_t b) { char * q = base + used; used += pad(b); return q; };
+
+    uint64_t * d_read_offset = reinterpret_cast<uint64_t *>(take(16));
+    uint64_t * d_path_offset = reinterpret_cast<uint64_t *>(take(16));
+    uint64_t * d_row_ptr = reinterpret_cast<uint64_t *>(take(8 * (R + 1)));
+    uint32_t * d_col = reinterpret_cast<uint32_t *>(take(4 * (Z + 1)));
+    uint32_t * d_key_in = reinterpret_cast<uint32_t *>(take(4 * (Z + 1)));
+    uint32_t * d_key_out = reinterpret_cast<uint32_t *>(take(4 * (Z + 1)));
+    uint32_t * d_idx_in = reinterpret_cast<uint32_t *>(take(4 * (Z + 1)));
+    uint32_t * d_idx_out = reinterpret_cast<uint32_t *>(take(4 * (Z + 1)));
+    uint32_t * d_entry_row = reinterpret_cast<uint32_t *>(take(4 * (Z + 1)));
+    uint32_t * d_csc_row = reinterpret_cast<uint32_t *>(take(4 * (Z + 1)));
+    double * d_cnt = reinterpret_cast<double *>(take(8 * R));
+    uint64_t * d_col_ptr = reinterpret_cast<uint64_t *>(take(8 * (P + 1)));
+    double * d_weight = reinterpret_cast<double *>(take(8 * P));
+    double * d_covered = reinterpret_cast<double *>(take(8 * P));
+    uint8_t * d_in_cover = reinterpret_cast<uint8_t *>(take(P));
+    void * d_sort_temp = take(sort_bytes);
+    uint32_t * d_error = reinterpret_cast<uint32_t *>(take(4));
+
+    const uint64_t read_offset[2] = {0, R}, path_offset[2] = {0, P};
+
+    cudaError_t err = cudaMemcpyAsync(d_read_offset, read_offset, 16, cudaMemcpyHostToDevice, s);
+    #define RPVG_STEP(call) if (err == cudaSuccess) { err = (call); }
+    RPVG_STEP(cudaMemcpyAsync(d_path_offset, path_offset, 16, cudaMemcpyHostToDevice, s))
+    RPVG_STEP(cudaMemcpyAsync(d_row_ptr, row_ptr, 8 * (R + 1), cudaMemcpyHostToDevice, s))
+    if (Z > 0) { RPVG_STEP(cudaMemcpyAsync(d_col, col, 4 * Z, cudaMemcpyHostToDevice, s)) }
+    RPVG_STEP(cudaMemcpyAsync(d_cnt, read_counts, 8 * R, cudaMemcpyHostToDevice, s))
+    RPVG_STEP(cudaMemcpyAsync(d_weight, path_weights, 8 * P, cudaMemcpyHostToDevice, s))
+    RPVG_STEP(cudaMemsetAsync(d_error, 0, 4, s))
+    RPVG_STEP(cudaStreamSynchronize(s))   // (the two offset pairs are on this frame)
+
+    if (err == cudaSuccess) {
+        coverGivenRowsKernel<<<static_cast<unsigned>((R + 255) / 256), 256, 0, s>>>(R, d_row_ptr, d_col, n_paths, d_key_in, d_idx_in, d_entry_row, d_error);
+        ctx->launches++;
+        err = cudaGetLastError();
+    }
+
+    if (err == cudaSuccess && Z > 0) {
+        size_t temp = sort_bytes;
+        err = cub::DeviceRadixSort::SortPairs(d_sort_temp, temp, d_key_in, d_key_out, d_idx_in, d_idx_out, static_cast<int>(Z), 0, sort_bits, s);
+        ctx->launches += 2 + (sort_bits + 7) / 8;
+    }
+
+    if (err == cudaSuccess) {
+        coverColumnPointerKernel<<<static_cast<unsigned>((P + 1 + 255) / 256), 256, 0, s>>>(P, Z, d_key_out, d_col_ptr);
+        if (Z > 0) { coverGivenColumnsKernel<<<static_cast<unsigned>((Z + 255) / 256), 256, 0, s>>>(Z, d_idx_out, d_entry_row, d_csc_row); }
+        coverKernel<<<1, kCoverThreads, 0, s>>>(d_read_offset, d_path_offset, d_row_ptr, d_col, d_col_ptr, d_csc_row, d_weight, d_cnt, d_covered, d_in_cover, d_error);
+        ctx->launches += 3;
+        err = cudaGetLastError();
+    }
+
+    uint32_t dev_error = 0;
+    RPVG_STEP(cudaMemcpyAsync(in_cover, d_in_cover, P, cudaMemcpyDeviceToHost, s))
+    RPVG_STEP(cudaMemcpyAsync(&dev_error, d_error, 4, cudaMemcpyDeviceToHost, s))
+    RPVG_STEP(cudaStreamSynchronize(s))
+    #undef RPVG_STEP
+
+    cudaFreeAsync(base, s);
+
+    if (err != cudaSuccess) { return rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("rpvg_b200_weighted_path_cover: ") + cudaGetErrorString(err)); }
+    if (dev_error) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "rpvg_b200_weighted_path_cover: path index out of range"); }
+    return RPVG_B200_OK;
+}

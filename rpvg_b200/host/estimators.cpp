@@ -684,6 +684,49 @@ void MinimumPathAbundanceEstimator::estimate(PathClusterEstimates * path_cluster
     path_cluster_estimates->total_count = total_count;
 }
 
+// rpvg:src/path_abundance_estimator.cpp:297-340, the greedy picks on the device (rpvg_b200_weighted_path_cover)
+vector<uint32_t> MinimumPathAbundanceEstimator::weightedMinimumPathCover(const uint32_t rows, const uint32_t n_paths, const uint8_t * read_path_cover, const double * read_counts, const double * path_weights) const {
+
+    vector<uint64_t> row_ptr = {0};
+    vector<uint32_t> col;
+
+    for (uint32_t i = 0; i < rows; ++i) {
+        for (uint32_t j = 0; j < n_paths; ++j) {
+            if (read_path_cover[static_cast<size_t>(j) * rows + i]) { col.push_back(j); }
+        }
+        row_ptr.push_back(col.size());
+    }
+
+    auto * ctx = threadContext();
+    vector<uint8_t> in_cover(n_paths, 0);
+
+    if (rpvg_b200_weighted_path_cover(ctx, rows, n_paths, row_ptr.data(), col.data(), read_counts, path_weights, in_cover.data()) != RPVG_B200_OK) {
+        fatal(ctx, "rpvg_b200_weighted_path_cover");
+    }
+
+    vector<uint32_t> min_path_cover;
+    for (uint32_t j = 0; j < n_paths; ++j) {
+        if (in_cover[j]) { min_path_cover.push_back(j); }
+    }
+
+    return min_path_cover;
+}
+
+#ifdef RPVG_B200_WITH_RPVG_HEADERS
+vector<uint32_t> MinimumPathAbundanceEstimator::weightedMinimumPathCover(const Utils::ColMatrixXb & read_path_cover, const Utils::RowVectorXd & read_counts, const Utils::RowVectorXd & path_weights) const {
+
+    assert(read_path_cover.rows() == read_counts.cols());
+    assert(read_path_cover.cols() == path_weights.cols());
+
+    vector<uint8_t> cover(static_cast<size_t>(read_path_cover.rows()) * read_path_cover.cols());
+    for (Eigen::Index j = 0; j < read_path_cover.cols(); ++j) {
+        for (Eigen::Index i = 0; i < read_path_cover.rows(); ++i) { cover[static_cast<size_t>(j) * read_path_cover.rows() + i] = read_path_cover(i, j) ? 1 : 0; }
+    }
+
+    return weightedMinimumPathCover(read_path_cover.rows(), read_path_cover.cols(), cover.data(), read_counts.data(), path_weights.data());
+}
+#endif
+
 // ---- haplotypes ------------------------------------------------------------------------------------------------------
 
 static const double min_rel_likelihood = 1e-8;   // rpvg:src/path_posterior_estimator.cpp:5

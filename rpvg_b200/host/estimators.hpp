@@ -3,8 +3,11 @@
 // rpvg:src/main.cpp:766-788,977 compiles unchanged. Everything O(data) runs on the GPU through the C ABI
 // (include/rpvg_b200.h); what stays here is the O(#sets) combinatorics whose order is observable in the output.
 //
-// Inside rpvg's tree, compile with -DRPVG_B200_WITH_RPVG_HEADERS: the value types then come from rpvg's own headers.
-// Stand-alone (this repository's tests) the same public types are declared below.
+// Inside rpvg's tree this header takes the place of path_estimator.hpp, path_abundance_estimator.hpp and
+// path_posterior_estimator.hpp; compile with -DRPVG_B200_WITH_RPVG_HEADERS: the value types (PathInfo, PathClusterEstimates,
+// ReadPathProbabilities, the Eigen typedefs of utils.hpp) then come from rpvg's own headers. oracle/Makefile builds
+// that configuration against the reference tree (oracle/_ref/dropin_catch_tests: the reference's own test of the path
+// cover compiled against these classes). Stand-alone (this repository's tests) the same public types are declared below.
 #ifndef RPVG_B200_HOST_ESTIMATORS_HPP
 #define RPVG_B200_HOST_ESTIMATORS_HPP
 
@@ -19,12 +22,16 @@
 #include "sparsepp/spp.h"
 #include "path_cluster_estimates.hpp"
 #include "read_path_probabilities.hpp"
-#include "path_estimator.hpp"   // std::hash<vector<uint32_t>>
+#include "utils.hpp"
+
+#define RPVG_B200_HAVE_SPARSEPP 1
 
 namespace rpvg_b200_host {
 template <class K> using hash_set = spp::sparse_hash_set<K>;
 template <class K, class V> using hash_map = spp::sparse_hash_map<K, V>;
 }
+
+using namespace std;
 
 #else
 
@@ -114,6 +121,8 @@ class ReadPathProbabilities {
         double prob_precision;
 };
 
+#endif
+
 // rpvg:src/path_estimator.hpp:51-68 — the hash the nested model's maps of path lists are keyed with; it decides their
 // iteration order, which is observable in the output.
 namespace std {
@@ -133,8 +142,6 @@ namespace std {
         }
     };
 }
-
-#endif
 
 struct rpvg_b200_ctx;
 struct rpvg_b200_grouped;
@@ -240,6 +247,13 @@ class MinimumPathAbundanceEstimator : public PathAbundanceEstimator {
         ~MinimumPathAbundanceEstimator() {};
 
         void estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng);
+
+#ifdef RPVG_B200_WITH_RPVG_HEADERS
+        // rpvg:src/path_abundance_estimator.hpp:48 — public in the reference (its test calls it); the picks run on the device
+        vector<uint32_t> weightedMinimumPathCover(const Utils::ColMatrixXb & read_path_cover, const Utils::RowVectorXd & read_counts, const Utils::RowVectorXd & path_weights) const;
+#endif
+        // the same on flat arrays: cover column-major, rows x n_paths, non-zero = the read class has the path
+        vector<uint32_t> weightedMinimumPathCover(const uint32_t rows, const uint32_t n_paths, const uint8_t * read_path_cover, const double * read_counts, const double * path_weights) const;
 
         // two device calls for the whole batch: the path covers of all clusters, then the EMs (and Gibbs samples) on them
         void estimateBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const vector<mt19937 *> & rngs);

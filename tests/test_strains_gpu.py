@@ -106,3 +106,27 @@ def test_strains_class_matches_golden(b200_harness):
         assert np.array_equal(res["abundances"] == 0, ab == 0)
         assert np.allclose(res["abundances"], ab, rtol=REL_TOL, atol=0)
         assert abs(res["noise_count"] - noise) <= REL_TOL * max(1.0, total) and res["total_count"] == total
+
+
+def test_public_weighted_minimum_path_cover_known_answers(ctx):
+    """The reference's own test of the hot path (rpvg:src/tests/path_abundance_estimator_test.cpp:8-28) through the C entry
+    point behind the public method MinimumPathAbundanceEstimator::weightedMinimumPathCover."""
+    cover = np.array([[1, 0, 1], [0, 1, 0], [1, 0, 0], [0, 1, 1]], dtype=bool)
+    counts = [1, 3, 1, 5]
+    assert ctx.weighted_path_cover(cover, counts, [1, 1, 1]) == [0, 1]
+    assert ctx.weighted_path_cover(cover, counts, [1, 1, 0.01]) == [0, 1, 2]
+    assert ctx.weighted_path_cover(np.ones((3, 1), dtype=bool), [1, 1, 1], [2.0]) == [0]
+
+
+def test_reference_catch2_test_compiled_against_the_drop_in_classes():
+    """oracle/_ref/dropin_catch_tests: rpvg's own path_abundance_estimator_test.cpp compiled against this repository's
+    classes inside rpvg's type system (-DRPVG_B200_WITH_RPVG_HEADERS, built by oracle/Makefile where the reference tree
+    exists; the binary travels to the GPU box)."""
+    import os
+    import subprocess
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "dropin_catch_tests")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/dropin_catch_tests is not built")
+    out = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)
+    assert out.returncode == 0, out.stdout[-2000:]
+    assert "All tests passed" in out.stdout
