@@ -61,6 +61,8 @@ void rpvg_b200_em_params_default(rpvg_b200_em_params * params);
  * let the ctx create its own non-blocking stream. One ctx per host thread that calls in (rpvg calls estimate() from
  * OpenMP threads, rpvg:src/main.cpp:829-830,977); a ctx is not re-entrant. */
 int rpvg_b200_create(int device, void * stream, rpvg_b200_ctx ** out_ctx);
+/* CUDA devices visible to the process (0 without a usable driver): what the host library shards a batch over. */
+int rpvg_b200_device_count(void);
 void rpvg_b200_destroy(rpvg_b200_ctx * ctx);
 const char * rpvg_b200_last_error(const rpvg_b200_ctx * ctx);
 const char * rpvg_b200_version(void);
@@ -112,7 +114,8 @@ int rpvg_b200_batch_em_timings(rpvg_b200_ctx * ctx, rpvg_b200_batch * batch, flo
  * estimatePathGroupPosteriorsGibbs (:527-555): for every set s of group_size paths of its problem (cluster)
  *   loglik[s] = sum_r counts[r] * log(noise[r] + sum_{p in s} matrix[r, p] / group_size).
  * Log frequencies, log(numPermutations), the log-sum-exp and Bounded's sequential pruning are O(#sets) and stay with the
- * caller (rpvg_b200/host does them in the reference's order). Host pointers in and out. */
+ * caller (rpvg_b200/host does them in the reference's order). Host pointers in and out. A set with a member outside its
+ * problem's columns gets NaN. */
 typedef struct {
     uint32_t n_problems;
     const uint64_t * row_offset;    /* [n_problems + 1] read classes of problem p */

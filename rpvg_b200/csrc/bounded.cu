@@ -451,7 +451,7 @@ extern "C" int rpvg_b200_grouped_bounded_pairs(rpvg_b200_ctx * ctx, rpvg_b200_gr
     const size_t bytes = 2 * pad(8 * (C + 1)) + pad(4 * G) + pad(8 * G) + 2 * pad(8 * NP) + 2 * pad(4 * NP) + pad(4 * C) + 1024;
 
     char * base = nullptr;
-    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&base), bytes, s));
+    RPVG_CUDA(ctx, cudaMallocFromPoolAsync(reinterpret_cast<void **>(&base), bytes, ctx->pool, s));
 
     size_t used = 0;
     auto take = [&](size_t b) { char * q = base + used; used += pad(b); return q; };
@@ -507,7 +507,7 @@ extern "C" int rpvg_b200_grouped_bounded_pairs(rpvg_b200_ctx * ctx, rpvg_b200_gr
 
         char * extra = nullptr;
         const size_t extra_bytes = pad(8 * R_total) + pad(8 * G) + pad(8 * C) + 256;
-        if (err == cudaSuccess) { err = cudaMallocAsync(reinterpret_cast<void **>(&extra), extra_bytes, s); }
+        if (err == cudaSuccess) { err = cudaMallocFromPoolAsync(reinterpret_cast<void **>(&extra), extra_bytes, ctx->pool, s); }
 
         double * d_row_max = reinterpret_cast<double *>(extra);
         double * d_bound = reinterpret_cast<double *>(extra + pad(8 * R_total));
@@ -552,7 +552,7 @@ extern "C" int rpvg_b200_grouped_bounded_pairs(rpvg_b200_ctx * ctx, rpvg_b200_gr
 
             char * wave = nullptr;
             const size_t wave_bytes = pad(16 * items.size()) + (split_rows ? pad(8 * items.size() * kPairTile * kPairTile) : 0);
-            err = cudaMallocAsync(reinterpret_cast<void **>(&wave), wave_bytes, s);
+            err = cudaMallocFromPoolAsync(reinterpret_cast<void **>(&wave), wave_bytes, ctx->pool, s);
             if (err != cudaSuccess) { return; }
 
             uint4 * d_items = reinterpret_cast<uint4 *>(wave);

@@ -69,7 +69,7 @@ extern "C" int rpvg_b200_collapse(rpvg_b200_ctx * ctx, const rpvg_b200_collapse_
     const size_t bytes = 2 * pad(8 * (P + 1)) + pad(8 * (R + 1)) + pad(4 * Z) + pad(8 * Z) + 2 * pad(8 * R) + 5 * pad(4 * R) + pad(4 * P) + pad(8 * R) + 1024;
 
     char * base = nullptr;
-    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&base), bytes, s));
+    RPVG_CUDA(ctx, cudaMallocFromPoolAsync(reinterpret_cast<void **>(&base), bytes, ctx->pool, s));
 
     size_t used = 0;
     auto take = [&](size_t b) { char * q = base + used; used += pad(b); return q; };

@@ -22,6 +22,11 @@ struct rpvg_b200_ctx {
     uint64_t launches = 0;
     std::string error;
 
+    // Every device allocation of the library comes out of this pool (cudaMallocFromPoolAsync) and goes back to it with
+    // cudaFreeAsync: freed batch memory stays with the ctx for the next batch, and the device's default pool — which
+    // belongs to the host application — is left alone.
+    cudaMemPool_t pool = nullptr;
+
     // EM launch machinery (em.cu): side streams for concurrent bins, largest thread-block cluster this device accepts
     std::vector<cudaStream_t> side_streams;   // kNumSideStreams: pairs of equal priority, the last four lowest
     std::vector<cudaEvent_t> join_events;
@@ -35,6 +40,10 @@ struct rpvg_b200_ctx {
     void * pinned[kPinnedSlots] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     uint64_t pinned_bytes[kPinnedSlots] = {0, 0, 0, 0, 0, 0, 0, 0};
 };
+
+// em.cu: host-side shape checks of a cluster arena (offsets start at 0 and never decrease — over all read classes, not
+// only at cluster boundaries —, no cluster without paths, sizes within the 32-bit limits of the device code).
+int rpvgCheckClusters(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * clusters);
 
 // em.cu: sets the kernel attributes of the EM kernels and probes the largest usable thread-block cluster.
 int rpvgEmInit(rpvg_b200_ctx * ctx);
@@ -62,6 +71,17 @@ inline int rpvgFail(rpvg_b200_ctx * ctx, int status, const std::string & message
             return rpvgFail((ctx), RPVG_B200_ERR_CUDA, std::string("kernel launch: ") + cudaGetErrorString(rpvg_launch_err)); \
         }                                                                                                        \
     } while (0)
+
+// Returns a stream-ordered allocation on every way out of a function (the RPVG_CUDA / RPVG_LAUNCHED early returns included).
+struct DeviceAllocationGuard {
+
+    cudaStream_t stream;
+    void * ptr;
+
+    ~DeviceAllocationGuard() {
+        if (ptr) { cudaFreeAsync(ptr, stream); }
+    }
+};
 
 // Device error flags a kernel may raise (checked at download).
 enum : uint32_t {

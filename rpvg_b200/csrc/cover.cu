@@ -208,6 +208,7 @@ extern "C" int rpvg_b200_path_cover(rpvg_b200_ctx * ctx, const rpvg_b200_cluster
 
     if (!ctx || !cl || !in_cover) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "NULL argument"); }
     if (cl->n_clusters == 0) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "no clusters"); }
+    { const int shape = rpvgCheckClusters(ctx, cl); if (shape != RPVG_B200_OK) { return shape; } }
 
     const uint32_t C = cl->n_clusters;
     const uint64_t R = cl->read_offset[C];
@@ -231,7 +232,7 @@ extern "C" int rpvg_b200_path_cover(rpvg_b200_ctx * ctx, const rpvg_b200_cluster
                          2 * pad(8 * P) + pad(P) + pad(sort_bytes) + 1024;
 
     char * base = nullptr;
-    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&base), bytes, s));
+    RPVG_CUDA(ctx, cudaMallocFromPoolAsync(reinterpret_cast<void **>(&base), bytes, ctx->pool, s));
 
     size_t used = 0;
     auto take = [&](size_t b) { char * q = base + used; used += pad(b); return q; };
@@ -369,7 +370,7 @@ extern "C" int rpvg_b200_weighted_path_cover(rpvg_b200_ctx * ctx, uint32_t n_rea
     const size_t bytes = 2 * pad(16) + pad(8 * (R + 1)) + 7 * pad(4 * (Z + 1)) + pad(8 * R) + pad(8 * (P + 1)) + 2 * pad(8 * P) + pad(P) + pad(sort_bytes) + 1024;
 
     char * base = nullptr;
-    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&base), bytes, s));
+    RPVG_CUDA(ctx, cudaMallocFromPoolAsync(reinterpret_cast<void **>(&base), bytes, ctx->pool, s));
 
     size_t used = 0;
     auto take = [&](size_t b) { char * q = base + used; used += pad(b); return q; };

@@ -13,6 +13,16 @@ const char * rpvg_b200_version(void) {
     return "rpvg_b200 0.1 (sm_100a)";
 }
 
+int rpvg_b200_device_count(void) {
+
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return count;
+}
+
 int rpvg_b200_create(int device, void * stream, rpvg_b200_ctx ** out_ctx) {
 
     if (!out_ctx) { return RPVG_B200_ERR_INVALID; }
@@ -57,11 +67,22 @@ int rpvg_b200_create(int device, void * stream, rpvg_b200_ctx ** out_ctx) {
         ctx->own_stream = true;
     }
 
-    // Keep freed batch memory in the pool: batches of similar size follow each other.
-    cudaMemPool_t pool;
-    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+    // A private memory pool that keeps freed batch memory: batches of similar size follow each other.
+    {
+        cudaMemPoolProps props = {};
+        props.allocType = cudaMemAllocationTypePinned;
+        props.handleTypes = cudaMemHandleTypeNone;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = device;
+
+        if (cudaMemPoolCreate(&ctx->pool, &props) != cudaSuccess) {
+            if (ctx->own_stream) { cudaStreamDestroy(ctx->stream); }
+            delete ctx;
+            return RPVG_B200_ERR_CUDA;
+        }
+
         uint64_t threshold = UINT64_MAX;
-        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold);
+        cudaMemPoolSetAttribute(ctx->pool, cudaMemPoolAttrReleaseThreshold, &threshold);
     }
 
     // Side streams for the concurrent launches of rpvg_b200_batch_em, two per priority level below the lanes' and four at
@@ -129,6 +150,7 @@ void rpvg_b200_destroy(rpvg_b200_ctx * ctx) {
     for (auto ev: ctx->lane_events) { cudaEventDestroy(ev); }
     if (ctx->fork_event) { cudaEventDestroy(ctx->fork_event); }
     if (ctx->own_stream) { cudaStreamDestroy(ctx->stream); }
+    if (ctx->pool) { cudaMemPoolDestroy(ctx->pool); }
     for (auto buffer: ctx->pinned) {
         if (buffer) { cudaFreeHost(buffer); }
     }

@@ -498,12 +498,16 @@ cudaError_t configureSell(const rpvg_b200_ctx * ctx, uint32_t * max_group) {
     return configureSellKernel(emSellRunKernel<RUN_THREADS, MULTI, IndexT>, RUN_THREADS, MULTI, smem_cap, max_group);
 }
 
-int checkClusters(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl) {
+}
+
+// Shape checks every entry point that takes a cluster arena makes on the host before anything goes to the device.
+int rpvgCheckClusters(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl) {
 
     if (!cl) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "clusters is NULL"); }
     if (cl->n_clusters == 0) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "empty batch (n_clusters == 0)"); }
-    if (!cl->read_offset || !cl->path_offset || !cl->row_ptr) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "offset arrays are NULL"); }
-    if (cl->read_offset[0] != 0 || cl->path_offset[0] != 0 || cl->row_ptr[0] != 0) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "offset arrays must start at 0"); }
+    if (!cl->read_offset || !cl->path_offset) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "offset arrays are NULL"); }
+    if (cl->read_offset[cl->n_clusters] > 0 && !cl->row_ptr) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "row_ptr is NULL"); }
+    if (cl->read_offset[0] != 0 || cl->path_offset[0] != 0 || (cl->row_ptr && cl->row_ptr[0] != 0)) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "offset arrays must start at 0"); }
 
     for (uint32_t c = 0; c < cl->n_clusters; ++c) {
         if (cl->read_offset[c + 1] < cl->read_offset[c] || cl->path_offset[c + 1] < cl->path_offset[c]) {
@@ -516,16 +520,24 @@ int checkClusters(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl) {
 
     const uint64_t n_reads = cl->read_offset[cl->n_clusters];
     const uint64_t n_paths = cl->path_offset[cl->n_clusters];
-    const uint64_t nnz = cl->row_ptr[n_reads];
+    const uint64_t nnz = n_reads > 0 ? cl->row_ptr[n_reads] : 0;
 
-    if (n_paths + cl->n_clusters >= 0xffffffffull || nnz >= 0xffffffffull || n_reads >= 0xffffffffull) {
-        return rpvgFail(ctx, RPVG_B200_ERR_LIMIT, "batch too large: paths, read classes and non-zeros must each stay below 2^32 per batch");
+    // (the sorts and scans of the matrix build take 32-bit signed item counts)
+    if (n_paths + cl->n_clusters >= 0x7fffffffull || nnz >= 0x7fffffffull || n_reads >= 0x7fffffffull) {
+        return rpvgFail(ctx, RPVG_B200_ERR_LIMIT, "batch too large: paths, read classes and non-zeros must each stay below 2^31 per batch");
+    }
+
+    // entry offsets non-decreasing over all read classes: the device lays its arrays out from them
+    for (uint64_t r = 0; r < n_reads; ++r) {
+        if (cl->row_ptr[r + 1] < cl->row_ptr[r]) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "malformed cluster arena: row_ptr decreases at read class " + std::to_string(r)); }
     }
     if (n_reads > 0 && (!cl->noise || !cl->count)) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "noise/count arrays are NULL"); }
     if (nnz > 0 && (!cl->col || !cl->prob)) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "col/prob arrays are NULL"); }
 
     return RPVG_B200_OK;
 }
+
+namespace {
 
 }
 
@@ -606,7 +618,7 @@ int rpvgBatchCreate(rpvg_b200_ctx * ctx, uint32_t n_clusters, const uint64_t * r
     bytes += ((b->scratch_bytes + 255) & ~size_t(255));
     bytes += padded<double>(R) + 8192;
 
-    cudaError_t err = cudaMallocAsync(reinterpret_cast<void **>(&b->pool.base), bytes, ctx->stream);
+    cudaError_t err = cudaMallocFromPoolAsync(reinterpret_cast<void **>(&b->pool.base), bytes, ctx->pool, ctx->stream);
     if (err != cudaSuccess) {
         delete b;
         return rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("cudaMallocAsync(") + std::to_string(bytes) + "): " + cudaGetErrorString(err));
@@ -707,7 +719,7 @@ int rpvg_b200_batch_upload(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, r
     if (!ctx || !out_batch) { return RPVG_B200_ERR_INVALID; }
     *out_batch = nullptr;
 
-    int status = checkClusters(ctx, cl);
+    int status = rpvgCheckClusters(ctx, cl);
     if (status != RPVG_B200_OK) { return status; }
 
     std::vector<uint64_t> cluster_nnz(cl->n_clusters);
@@ -743,7 +755,27 @@ int rpvg_b200_batch_upload(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, r
     return RPVG_B200_OK;
 }
 
+static int batchEmLaunch(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const rpvg_b200_em_params * params);
+
 int rpvg_b200_batch_em(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const rpvg_b200_em_params * params) {
+
+    const int status = batchEmLaunch(ctx, b, params);
+
+    // A failure between the fork and the join leaves side and lane streams with work the ctx stream does not wait for: the
+    // caller may free the batch next, so everything is drained here before the error goes back.
+    if (status != RPVG_B200_OK && ctx) {
+        const std::string message = ctx->error;
+        for (auto side: ctx->side_streams) { cudaStreamSynchronize(side); }
+        for (auto lane: ctx->lane_streams) { cudaStreamSynchronize(lane); }
+        cudaStreamSynchronize(ctx->stream);
+        cudaGetLastError();
+        ctx->error = message;
+    }
+
+    return status;
+}
+
+static int batchEmLaunch(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const rpvg_b200_em_params * params) {
 
     if (!ctx || !b || !params) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "NULL argument"); }
     if (params->min_em_conv_its == 0) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "min_em_conv_its must be > 0"); }

@@ -319,7 +319,7 @@ int rpvgBatchGibbs(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const uint32_t * nu
     const size_t bytes = pad(4 * cluster_list.size()) + pad(4 * C) + 3 * pad(8 * (C + 1)) + pad(4 * (b->n_paths + C)) + pad(8 * abundance_offset[C]) + pad(8 * sample_offset[C]) + 1024;
 
     char * base = nullptr;
-    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&base), bytes, s));
+    RPVG_CUDA(ctx, cudaMallocFromPoolAsync(reinterpret_cast<void **>(&base), bytes, ctx->pool, s));
 
     size_t used = 0;
     auto take = [&](size_t n) { char * q = base + used; used += pad(n); return q; };

@@ -144,6 +144,7 @@ static int groupedCollapse(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, c
 
     if (!ctx || !cl || !gr || !n_classes || (!keep && (!matrix || !noise || !counts))) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "NULL argument"); }
     if (cl->n_clusters == 0) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "no clusters"); }
+    { const int shape = rpvgCheckClusters(ctx, cl); if (shape != RPVG_B200_OK) { return shape; } }
 
     const uint32_t C = cl->n_clusters;
     const uint64_t R = cl->read_offset[C];
@@ -208,7 +209,7 @@ static int groupedCollapse(rpvg_b200_ctx * ctx, const rpvg_b200_clusters * cl, c
     bytes += 2 * pad(8 * MX) + 2 * pad(8 * (R + 1)) + pad(4 * MX) + pad(8 * MX) + 3 * pad(8 * R) + 4 * pad(4 * R) + pad(4 * C) + pad(scan_bytes) + 4096;
 
     char * base = nullptr;
-    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&base), bytes, s));
+    RPVG_CUDA(ctx, cudaMallocFromPoolAsync(reinterpret_cast<void **>(&base), bytes, ctx->pool, s));
 
     size_t used = 0;
     auto take = [&](size_t b) { char * q = base + used; used += pad(b); return q; };
@@ -409,6 +410,7 @@ extern "C" int rpvg_b200_grouped_raw(rpvg_b200_ctx * ctx, const rpvg_b200_cluste
     if (!ctx || !cl || !out) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "NULL argument"); }
     *out = nullptr;
     if (cl->n_clusters == 0) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "no clusters"); }
+    { const int shape = rpvgCheckClusters(ctx, cl); if (shape != RPVG_B200_OK) { return shape; } }
 
     const uint32_t C = cl->n_clusters;
     const uint64_t R = cl->read_offset[C];
@@ -433,7 +435,7 @@ extern "C" int rpvg_b200_grouped_raw(rpvg_b200_ctx * ctx, const rpvg_b200_cluste
     const size_t bytes = 3 * pad(8 * (C + 1)) + pad(8 * (R + 1)) + pad(4 * Z) + pad(8 * Z) + 2 * pad(8 * R) + pad(4 * R) + pad(8 * MX) + pad(4 * C) + 4096;
 
     char * base = nullptr;
-    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&base), bytes, s));
+    RPVG_CUDA(ctx, cudaMallocFromPoolAsync(reinterpret_cast<void **>(&base), bytes, ctx->pool, s));
 
     size_t used = 0;
     auto take = [&](size_t b) { char * q = base + used; used += pad(b); return q; };

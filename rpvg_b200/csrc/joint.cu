@@ -122,7 +122,8 @@ extern "C" int rpvg_b200_joint_haplotype_estimates(rpvg_b200_ctx * ctx, uint32_t
                          padded<double>(n_clusters) + padded<uint8_t>(S) + padded<double>(ploidy) + padded<uint32_t>(1) + 4096;
 
     DevicePool pool;
-    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&pool.base), bytes, s));
+    RPVG_CUDA(ctx, cudaMallocFromPoolAsync(reinterpret_cast<void **>(&pool.base), bytes, ctx->pool, s));
+    const DeviceAllocationGuard allocation_guard{s, pool.base};
     pool.size = bytes;
 
     uint64_t * d_path_offset = pool.take<uint64_t>(n_clusters + 1);
@@ -180,7 +181,6 @@ extern "C" int rpvg_b200_joint_haplotype_estimates(rpvg_b200_ctx * ctx, uint32_t
     down(&dev_error, d_error, 4);
     if (err == cudaSuccess) { err = cudaStreamSynchronize(s); }
 
-    cudaFreeAsync(pool.base, s);
 
     if (err != cudaSuccess) { return rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("rpvg_b200_joint_haplotype_estimates: ") + cudaGetErrorString(err)); }
     if (dev_error) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "rpvg_b200_joint_haplotype_estimates: set member out of the cluster's path range"); }

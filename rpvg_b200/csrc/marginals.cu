@@ -118,7 +118,8 @@ extern "C" int rpvg_b200_haplotype_marginals(rpvg_b200_ctx * ctx, uint32_t n_clu
     const size_t bytes = pad(8 * (n_clusters + 1)) * 2 + pad(8 * (S + 1)) + pad(4 * E) * 5 + pad(8 * S) + pad(8 * E) * 2 + pad(8 * P) * 2 + pad(sort_bytes) + 256;
 
     char * base = nullptr;
-    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&base), bytes, s));
+    RPVG_CUDA(ctx, cudaMallocFromPoolAsync(reinterpret_cast<void **>(&base), bytes, ctx->pool, s));
+    const DeviceAllocationGuard allocation_guard{s, base};
 
     size_t used = 0;
     auto take = [&](size_t b) { char * q = base + used; used += pad(b); return q; };
@@ -173,7 +174,6 @@ extern "C" int rpvg_b200_haplotype_marginals(rpvg_b200_ctx * ctx, uint32_t n_clu
     RPVG_STEP(cudaStreamSynchronize(s))
     #undef RPVG_STEP
 
-    cudaFreeAsync(base, s);
 
     if (err != cudaSuccess) { return rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("rpvg_b200_haplotype_marginals: ") + cudaGetErrorString(err)); }
     if (dev_error) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "rpvg_b200_haplotype_marginals: set member out of the cluster's path range"); }

@@ -457,7 +457,8 @@ extern "C" int rpvg_b200_add_path_probs(rpvg_b200_ctx * ctx, const rpvg_b200_ali
                          ((sort_bytes + 255) & ~size_t(255)) + ((scan_bytes + 255) & ~size_t(255)) + ((scan64_bytes + 255) & ~size_t(255)) + padded<uint32_t>(1) + 8192;
 
     DevicePool pool;
-    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&pool.base), bytes, s));
+    RPVG_CUDA(ctx, cudaMallocFromPoolAsync(reinterpret_cast<void **>(&pool.base), bytes, ctx->pool, s));
+    const DeviceAllocationGuard allocation_guard{s, pool.base};
     pool.size = bytes;
 
     uint64_t * d_read_offset = pool.take<uint64_t>(C + 1);
@@ -623,7 +624,6 @@ extern "C" int rpvg_b200_add_path_probs(rpvg_b200_ctx * ctx, const rpvg_b200_ali
         if (err == cudaSuccess) { err = cudaStreamSynchronize(s); }
     }
 
-    cudaFreeAsync(pool.base, s);
 
     if (err != cudaSuccess) { return rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("rpvg_b200_add_path_probs: ") + cudaGetErrorString(err)); }
 

@@ -57,10 +57,19 @@ __global__ void __launch_bounds__(kLoglikThreads) groupLoglikKernel(const Loglik
     const uint32_t k = args.group_size;
     const double group_size = static_cast<double>(k);
 
+    // a set member outside the problem's columns cannot be evaluated: the set's result is NaN (nothing is read out of range)
+    const uint32_t n_cols = static_cast<uint32_t>(args.path_offset[p + 1] - args.path_offset[p]);
+    bool in_range = true;
+
     const double * cols[kMaxGroupSizeLoglik];
     #pragma unroll
     for (uint32_t q = 0; q < kMaxGroupSizeLoglik; ++q) {
-        cols[q] = (q < k) ? matrix + static_cast<uint64_t>(args.sets[set * k + q]) * rows : matrix;
+        uint32_t member = (q < k) ? args.sets[set * k + q] : 0;
+        if (member >= n_cols) {
+            in_range = false;
+            member = 0;
+        }
+        cols[q] = matrix + static_cast<uint64_t>(member) * rows;
     }
 
     double acc = 0;
@@ -77,7 +86,7 @@ __global__ void __launch_bounds__(kLoglikThreads) groupLoglikKernel(const Loglik
     }
 
     acc = warpSum(acc);
-    if (lane == 0) { args.loglik[set] = acc; }
+    if (lane == 0) { args.loglik[set] = in_range ? acc : nan(""); }
 }
 
 }
@@ -109,7 +118,7 @@ extern "C" int rpvg_b200_group_loglik(rpvg_b200_ctx * ctx, const rpvg_b200_logli
     const size_t bytes = 4 * pad(8 * (P + 1)) + pad(8 * Mx) + 2 * pad(8 * R) + pad(4 * S * pr->group_size) + pad(8 * S) + 1024;
 
     char * base = nullptr;
-    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&base), bytes, s));
+    RPVG_CUDA(ctx, cudaMallocFromPoolAsync(reinterpret_cast<void **>(&base), bytes, ctx->pool, s));
 
     size_t used = 0;
     auto take = [&](size_t b) { char * q = base + used; used += pad(b); return q; };
@@ -193,7 +202,7 @@ extern "C" int rpvg_b200_grouped_loglik(rpvg_b200_ctx * ctx, const rpvg_b200_gro
     const size_t bytes = pad(8 * (P + 1)) + pad(4 * S * group_size) + pad(8 * S) + 1024;
 
     char * base = nullptr;
-    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&base), bytes, s));
+    RPVG_CUDA(ctx, cudaMallocFromPoolAsync(reinterpret_cast<void **>(&base), bytes, ctx->pool, s));
 
     uint64_t * d_set_offset = reinterpret_cast<uint64_t *>(base);
     uint32_t * d_sets = reinterpret_cast<uint32_t *>(base + pad(8 * (P + 1)));
@@ -263,7 +272,7 @@ extern "C" int rpvg_b200_grouped_upload(rpvg_b200_ctx * ctx, const rpvg_b200_log
     const size_t bytes = 3 * pad(8 * (P + 1)) + pad(4 * P) + pad(8 * Mx) + 2 * pad(8 * R) + 1024;
 
     char * base = nullptr;
-    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&base), bytes, s));
+    RPVG_CUDA(ctx, cudaMallocFromPoolAsync(reinterpret_cast<void **>(&base), bytes, ctx->pool, s));
 
     size_t used = 0;
     auto take = [&](size_t b) { char * q = base + used; used += pad(b); return q; };
@@ -347,7 +356,7 @@ extern "C" int rpvg_b200_log_peak(rpvg_b200_ctx * ctx, double * logs_per_second)
     cudaStream_t s = ctx->stream;
 
     double * d_sink = nullptr;
-    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&d_sink), 256, s));
+    RPVG_CUDA(ctx, cudaMallocFromPoolAsync(reinterpret_cast<void **>(&d_sink), 256, ctx->pool, s));
 
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaError_t err = cudaEventCreate(&ev0);

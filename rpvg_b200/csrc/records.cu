@@ -191,7 +191,8 @@ extern "C" int rpvg_b200_merge_read_records(rpvg_b200_ctx * ctx, const rpvg_b200
                          padded<uint32_t>(R) + 4 * padded<uint32_t>(R) + padded<uint32_t>(C) + 4096;
 
     DevicePool pool;
-    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&pool.base), bytes, s));
+    RPVG_CUDA(ctx, cudaMallocFromPoolAsync(reinterpret_cast<void **>(&pool.base), bytes, ctx->pool, s));
+    const DeviceAllocationGuard allocation_guard{s, pool.base};
     pool.size = bytes;
 
     uint64_t * d_read_offset = pool.take<uint64_t>(C + 1);
@@ -257,7 +258,6 @@ extern "C" int rpvg_b200_merge_read_records(rpvg_b200_ctx * ctx, const rpvg_b200
 
     if (err == cudaSuccess) { err = cudaStreamSynchronize(s); }
 
-    cudaFreeAsync(pool.base, s);
 
     if (err != cudaSuccess) { return rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("rpvg_b200_merge_read_records: ") + cudaGetErrorString(err)); }
     return RPVG_B200_OK;

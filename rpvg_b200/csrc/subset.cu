@@ -171,6 +171,7 @@ extern "C" int rpvg_b200_subset_em_gibbs(rpvg_b200_ctx * ctx, const rpvg_b200_cl
 
     if (!ctx || !cl || !ss || !params) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "NULL argument"); }
     if (ss->n_subsets == 0 || cl->n_clusters == 0) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "no subsets / no clusters"); }
+    { const int shape = rpvgCheckClusters(ctx, cl); if (shape != RPVG_B200_OK) { return shape; } }
 
     const uint32_t S = ss->n_subsets;
     const uint32_t C = cl->n_clusters;
@@ -212,7 +213,7 @@ extern "C" int rpvg_b200_subset_em_gibbs(rpvg_b200_ctx * ctx, const rpvg_b200_cl
     bytes += 5 * pad(4 * RS) + pad(4 * S) + pad(8 * RS) + pad(scan_bytes) + pad(4) + 4096;                             // collapse + classes
 
     char * base = nullptr;
-    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&base), bytes, st));
+    RPVG_CUDA(ctx, cudaMallocFromPoolAsync(reinterpret_cast<void **>(&base), bytes, ctx->pool, st));
 
     size_t used = 0;
     auto take = [&](size_t b) { char * q = base + used; used += pad(b); return q; };

@@ -55,7 +55,8 @@ extern "C" int rpvg_b200_tpm(rpvg_b200_ctx * ctx, uint64_t n_paths, const double
     const size_t bytes = 3 * array_bytes + 256 + ((reduce_bytes + 255) & ~size_t(255));
 
     char * base = nullptr;
-    RPVG_CUDA(ctx, cudaMallocAsync(reinterpret_cast<void **>(&base), bytes, s));
+    RPVG_CUDA(ctx, cudaMallocFromPoolAsync(reinterpret_cast<void **>(&base), bytes, ctx->pool, s));
+    const DeviceAllocationGuard allocation_guard{s, base};
 
     double * d_abundances = reinterpret_cast<double *>(base);
     double * d_lengths = reinterpret_cast<double *>(base + array_bytes);
@@ -85,7 +86,6 @@ extern "C" int rpvg_b200_tpm(rpvg_b200_ctx * ctx, uint64_t n_paths, const double
     if (err == cudaSuccess) { err = cudaStreamSynchronize(s); }
     if (err == cudaSuccess) { err = cudaGetLastError(); }
 
-    cudaFreeAsync(base, s);
 
     if (err != cudaSuccess) { return rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("rpvg_b200_tpm: ") + cudaGetErrorString(err)); }
 

@@ -14,6 +14,9 @@
 #include <iostream>
 #include <memory>
 #include <numeric>
+#include <thread>
+
+#include <omp.h>
 
 #include "rpvg_b200.h"
 
@@ -217,6 +220,78 @@ void PathEstimator::estimateBatch(const vector<PathClusterEstimates *> & estimat
     assert(estimates.size() == rngs.size());
 
     for (size_t i = 0; i < estimates.size(); ++i) { estimate(estimates[i], *cluster_probs[i], rngs[i]); }
+}
+
+// One batch over the GPUs of the box: see estimators.hpp. The split mirrors the reference's own schedule — largest first,
+// each to the least loaded worker (rpvg:src/main.cpp:827-830) — with devices in place of threads.
+void PathEstimator::estimateBatchOnDevices(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const vector<mt19937 *> & rngs, int num_devices) {
+
+    assert(estimates.size() == cluster_probs.size());
+    assert(estimates.size() == rngs.size());
+
+    if (num_devices <= 0) {
+        const char * env = getenv("RPVG_B200_DEVICES");
+        num_devices = 1;
+        if (env && string(env) == "all") { num_devices = rpvg_b200_device_count(); } else if (env) { num_devices = atoi(env); }
+    }
+
+    num_devices = max(1, min(num_devices, rpvg_b200_device_count()));
+    num_devices = static_cast<int>(min<size_t>(num_devices, max<size_t>(1, estimates.size())));
+
+    if (num_devices == 1) {
+        estimateBatch(estimates, cluster_probs, rngs);
+        return;
+    }
+
+    const size_t n = estimates.size();
+    vector<double> cost(n, 0);
+
+    #pragma omp parallel for schedule(dynamic, 16)
+    for (size_t i = 0; i < n; ++i) { cost[i] = clusterCost(*estimates[i], *cluster_probs[i]); }
+
+    // longest processing time first; ties by index, so the split is deterministic
+    vector<size_t> order(n);
+    iota(order.begin(), order.end(), 0);
+    stable_sort(order.begin(), order.end(), [&](size_t a, size_t b) { return cost[a] > cost[b]; });
+
+    vector<vector<size_t> > share(num_devices);
+    vector<double> load(num_devices, 0);
+
+    for (auto i: order) {
+        const size_t d = min_element(load.begin(), load.end()) - load.begin();
+        share[d].push_back(i);
+        load[d] += cost[i];
+    }
+
+    const int first_device = threadDevice();
+    const int host_threads = max(1, omp_get_max_threads() / num_devices);
+
+    vector<thread> workers;
+
+    for (int d = 0; d < num_devices; ++d) {
+
+        workers.emplace_back([&, d]() {
+
+            sort(share[d].begin(), share[d].end());   // the caller's order within a share
+
+            vector<PathClusterEstimates *> est;
+            vector<const vector<ReadPathProbabilities> *> probs;
+            vector<mt19937 *> generators;
+
+            for (auto i: share[d]) {
+                est.push_back(estimates[i]);
+                probs.push_back(cluster_probs[i]);
+                generators.push_back(rngs[i]);
+            }
+
+            threadDevice() = (first_device + d) % rpvg_b200_device_count();
+            omp_set_num_threads(host_threads);
+
+            if (!est.empty()) { estimateBatch(est, probs, generators); }
+        });
+    }
+
+    for (auto & worker: workers) { worker.join(); }
 }
 
 // transcripts model: EM (and Gibbs read counts) of all clusters in one device batch
@@ -543,6 +618,24 @@ void PathPosteriorEstimator::estimateBatch(const vector<PathClusterEstimates *> 
 
     for (auto & est: estimates) { est->resetEstimates(est->paths.size(), 1); }
     posteriorsBatch(estimates, cluster_probs, 1, false, 1);
+}
+
+double PathGroupPosteriorEstimator::clusterCost(const PathClusterEstimates & estimates, const vector<ReadPathProbabilities> & cluster_probs) const {
+
+    const double paths = estimates.paths.size();
+    return (group_size == 2 ? paths * (paths + 1) / 2 : paths) * max<double>(1, cluster_probs.size()) + PathEstimator::clusterCost(estimates, cluster_probs);
+}
+
+double NestedPathAbundanceEstimator::clusterCost(const PathClusterEstimates & estimates, const vector<ReadPathProbabilities> & cluster_probs) const {
+
+    // at most one haplotype group per haplotype id of the cluster, at most as many as path combinations
+    rpvg_b200_host::hash_set<uint32_t> ids;
+    for (auto & path: estimates.paths) {
+        for (auto & id: path.source_ids) { ids.insert(id); }
+    }
+
+    const double groups = max<double>(1, ids.size());
+    return groups * (groups + 1) / 2 * max<double>(1, cluster_probs.size()) + PathEstimator::clusterCost(estimates, cluster_probs);
 }
 
 void PathGroupPosteriorEstimator::estimateBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const vector<mt19937 *> & rngs) {

@@ -222,22 +222,70 @@ void PathClusterEstimates::resetEstimates(uint32_t num_components, const uint32_
 
 PathEstimator::PathEstimator(const double prob_precision_in) : prob_precision(prob_precision_in) {}
 
+namespace {
+
+// The contexts of one host thread, one per device it has worked on; released when the thread ends.
+struct ThreadContexts {
+
+    static constexpr int kMaxDevices = 64;
+    rpvg_b200_ctx * ctx[kMaxDevices] = {};
+
+    ~ThreadContexts() {
+        for (auto & c: ctx) {
+            if (c) { rpvg_b200_destroy(c); }
+            c = nullptr;
+        }
+    }
+};
+
+}
+
+int & PathEstimator::threadDevice() {
+
+    thread_local int device = -1;
+
+    if (device < 0) {
+        const char * env = getenv("RPVG_B200_DEVICE");
+        device = env ? atoi(env) : 0;
+    }
+
+    return device;
+}
+
 rpvg_b200_ctx * PathEstimator::threadContext() {
 
-    thread_local rpvg_b200_ctx * ctx = nullptr;
+    thread_local ThreadContexts contexts;
 
-    if (!ctx) {
+    const int device = threadDevice();
 
-        const char * device = getenv("RPVG_B200_DEVICE");
-        const int status = rpvg_b200_create(device ? atoi(device) : 0, nullptr, &ctx);
+    if (device < 0 || device >= ThreadContexts::kMaxDevices) {
+        cerr << "ERROR: rpvg_b200: device ordinal " << device << " out of range" << endl;
+        abort();
+    }
+
+    if (!contexts.ctx[device]) {
+
+        const int status = rpvg_b200_create(device, nullptr, &contexts.ctx[device]);
 
         if (status != RPVG_B200_OK) {
-            cerr << "ERROR: rpvg_b200_create failed with status " << status << " (a CUDA device is required; there is no CPU fallback)" << endl;
+            cerr << "ERROR: rpvg_b200_create(device " << device << ") failed with status " << status << " (a CUDA device is required; there is no CPU fallback)" << endl;
             abort();
         }
     }
 
-    return ctx;
+    return contexts.ctx[device];
+}
+
+// entries x expected EM iterations; the iterations grow roughly with the square root of the cluster's size (config 2:
+// ~30 for a handful of entries, ~1000 at 1e4, 3000-5000 at 1e5), the stopping rule caps them
+double PathEstimator::clusterCost(const PathClusterEstimates & estimates, const vector<ReadPathProbabilities> & cluster_probs) const {
+
+    double weight = cluster_probs.size();
+    for (auto & read_probs: cluster_probs) {
+        for (auto & path_probs: read_probs.pathProbs()) { weight += path_probs.second.size(); }
+    }
+
+    return weight * min(5000.0, max(20.0, 12.0 * sqrt(weight)));
 }
 
 void PathEstimator::denseMatrix(vector<double> * matrix, vector<double> * noise, vector<double> * counts, const vector<ReadPathProbabilities> & cluster_probs, const uint32_t num_paths) {

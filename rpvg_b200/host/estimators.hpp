@@ -5,9 +5,9 @@
 //
 // Inside rpvg's tree this header takes the place of path_estimator.hpp, path_abundance_estimator.hpp and
 // path_posterior_estimator.hpp; compile with -DRPVG_B200_WITH_RPVG_HEADERS: the value types (PathInfo, PathClusterEstimates,
-// ReadPathProbabilities, the Eigen typedefs of utils.hpp) then come from rpvg's own headers. oracle/Makefile builds
-// that configuration against the reference tree (oracle/_ref/dropin_catch_tests: the reference's own test of the path
-// cover compiled against these classes). Stand-alone (this repository's tests) the same public types are declared below.
+// ReadPathProbabilities, the Eigen typedefs of utils.hpp) then come from rpvg's own headers. The test infrastructure builds
+// that configuration against the reference tree (the reference's own Catch2 test of the path cover compiled against these
+// classes). Stand-alone (this repository's tests) the same public types are declared below.
 #ifndef RPVG_B200_HOST_ESTIMATORS_HPP
 #define RPVG_B200_HOST_ESTIMATORS_HPP
 
@@ -160,7 +160,21 @@ class PathEstimator {
         // results, cluster by cluster, as estimate(estimates[i], *cluster_probs[i], rngs[i]); the default does just that.
         virtual void estimateBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const vector<mt19937 *> & rngs);
 
+        // Not in rpvg: estimateBatch over several GPUs of the box. Clusters are independent: they are dealt to
+        // the devices by longest-processing-time-first on a per-cluster cost (clusterCost), one host thread with its own
+        // context and streams per device runs estimateBatch on its share, and every result lands in the caller's own
+        // PathClusterEstimates object — the original order, nothing to gather, no collective. The results are those of
+        // the single-device call, bit for bit (a cluster's computation does not depend on what else is in its batch).
+        // num_devices <= 0: $RPVG_B200_DEVICES ("all" or a count), else 1; never more than the visible devices.
+        void estimateBatchOnDevices(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const vector<mt19937 *> & rngs, int num_devices = 0);
+
     protected:
+
+        // what a cluster costs, for the split over devices: entries x expected EM iterations by default
+        virtual double clusterCost(const PathClusterEstimates & estimates, const vector<ReadPathProbabilities> & cluster_probs) const;
+
+        // device of the calling thread's context: $RPVG_B200_DEVICE (default 0) unless estimateBatchOnDevices set it
+        static int & threadDevice();
 
         const double prob_precision;
 
@@ -272,6 +286,11 @@ class NestedPathAbundanceEstimator : public PathAbundanceEstimator {
         // one or two rounds of log-likelihoods, all sub-EMs of all clusters) instead of four per cluster.
         void estimateBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const vector<mt19937 *> & rngs);
 
+    protected:
+
+        // haplotype combinations x read classes dominate this model
+        double clusterCost(const PathClusterEstimates & estimates, const vector<ReadPathProbabilities> & cluster_probs) const;
+
     private:
 
         const uint32_t group_size;
@@ -332,6 +351,11 @@ class PathGroupPosteriorEstimator : public PathPosteriorEstimator {
 
         // (--use-hap-gibbs samples on the host between the device calls of a cluster: looped)
         void estimateBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const vector<mt19937 *> & rngs);
+
+    protected:
+
+        // path combinations x read classes
+        double clusterCost(const PathClusterEstimates & estimates, const vector<ReadPathProbabilities> & cluster_probs) const;
 
     private:
 

@@ -174,17 +174,18 @@ def harness_estimate_batch(lib_, config: HarnessConfig, arena, cluster_ids=None,
         lib_.harness_estimator_destroy(est)
 
 
-def harness_estimate_batched(lib_, config: HarnessConfig, arena, cluster_ids=None, rng_seed: int = 1):
-    """rpvg_b200 harness only: the same clusters, order and generators through the classes' estimateBatch (one call)."""
+def harness_estimate_batched(lib_, config: HarnessConfig, arena, cluster_ids=None, rng_seed: int = 1, num_devices: int = 1):
+    """rpvg_b200 harness only: the same clusters, order and generators through the classes' estimateBatch (one call), or,
+    with num_devices != 1, through estimateBatchOnDevices (the batch dealt over that many GPUs)."""
     ids = list(range(arena.n_clusters)) if cluster_ids is None else list(cluster_ids)
     datas = [HarnessClusterData(arena, c) for c in ids]
     structs = (HarnessCluster * len(ids))(*[d.struct for d in datas])
     handles = (C.c_void_p * len(ids))()
-    lib_.harness_estimate_batched.restype = C.c_double
-    lib_.harness_estimate_batched.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(HarnessCluster), C.c_uint32, C.POINTER(C.c_void_p)]
+    lib_.harness_estimate_batched_devices.restype = C.c_double
+    lib_.harness_estimate_batched_devices.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(HarnessCluster), C.c_uint32, C.c_int32, C.POINTER(C.c_void_p)]
     est = lib_.harness_estimator_create(C.byref(config))
     try:
-        seconds = lib_.harness_estimate_batched(est, len(ids), structs, rng_seed, handles)
+        seconds = lib_.harness_estimate_batched_devices(est, len(ids), structs, rng_seed, num_devices, handles)
         return seconds, [result_to_dict(lib_, handles[i]) for i in range(len(ids))]
     finally:
         lib_.harness_estimator_destroy(est)

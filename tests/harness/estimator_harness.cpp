@@ -259,6 +259,12 @@ double harness_estimate_batch(void * estimator, uint32_t n, const HarnessCluster
 // same generator per cluster as harness_estimate_batch, one call. Returns wall seconds of the call.
 double harness_estimate_batched(void * estimator, uint32_t n, const HarnessCluster * clusters, uint32_t rng_seed, void ** handles) {
 
+    return harness_estimate_batched_devices(estimator, n, clusters, rng_seed, 1, handles);
+}
+
+// ... over num_devices GPUs of the box (estimateBatchOnDevices): same inputs, same outputs.
+double harness_estimate_batched_devices(void * estimator, uint32_t n, const HarnessCluster * clusters, uint32_t rng_seed, int32_t num_devices, void ** handles) {
+
     auto * holder = static_cast<EstimatorHolder *>(estimator);
 
     vector<PathClusterEstimates> ests(n);
@@ -289,7 +295,11 @@ double harness_estimate_batched(void * estimator, uint32_t n, const HarnessClust
     }
 
     auto time_start = chrono::steady_clock::now();
-    holder->estimator->estimateBatch(est_ptrs, prob_ptrs, rng_ptrs);
+    if (num_devices == 1) {
+        holder->estimator->estimateBatch(est_ptrs, prob_ptrs, rng_ptrs);
+    } else {
+        holder->estimator->estimateBatchOnDevices(est_ptrs, prob_ptrs, rng_ptrs, num_devices);
+    }
     auto time_end = chrono::steady_clock::now();
 
     for (uint32_t i = 0; i < n; ++i) { handles[i] = flattenEstimates(ests[i]); }

@@ -91,6 +91,8 @@ double harness_estimate_batch(void * estimator, uint32_t n, const HarnessCluster
 #ifndef HARNESS_REFERENCE
 /* rpvg_b200 classes only: the same clusters, order and generators through estimateBatch (one call). */
 double harness_estimate_batched(void * estimator, uint32_t n, const HarnessCluster * clusters, uint32_t rng_seed, void ** handles);
+/* ... through estimateBatchOnDevices: the batch dealt over num_devices GPUs (0: $RPVG_B200_DEVICES). */
+double harness_estimate_batched_devices(void * estimator, uint32_t n, const HarnessCluster * clusters, uint32_t rng_seed, int32_t num_devices, void ** handles);
 #endif
 
 const HarnessResult * harness_result_view(void * handle);
