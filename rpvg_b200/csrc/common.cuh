@@ -34,6 +34,7 @@ struct rpvg_b200_ctx {
     std::vector<cudaEvent_t> lane_events;
     cudaEvent_t fork_event = nullptr;
     uint32_t max_group_size = 1;
+    uint32_t stream_grid = 0;                 // CTAs of a cooperative emStreamKernel launch that are resident at once
 
     // rpvg_b200_pinned_scratch: grow-only page-locked host buffers, one per slot
     static constexpr uint32_t kPinnedSlots = 8;

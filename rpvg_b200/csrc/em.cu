@@ -29,6 +29,7 @@
 #include "em_kernels.cuh"
 #include "em_sell.cuh"
 #include "em_dense.cuh"
+#include "em_stream.cuh"
 #include "em_batch.cuh"
 
 namespace {
@@ -236,6 +237,11 @@ void planEmLaunches(const rpvg_b200_ctx * ctx, rpvg_b200_batch * b, std::vector<
     // dense kernels (largest first)
     const int fallback_bin = 5 * kNumTiers * 2;
     const int dense_bin0 = fallback_bin + 1;
+    const int stream_bin = -1;   // first: one cooperative launch per cluster, before anything else is forked
+
+    // Above this weight a cluster gets the whole GPU (emStreamKernel): 16 slices of shared memory no longer hold it and
+    // what does not fit would be streamed through 16 SMs only. Also for clusters whose vectors alone outgrow a CTA.
+    const uint64_t stream_weight = std::max<uint64_t>(1000, envKnob("RPVG_B200_EM_STREAM_WEIGHT", 400000));
     const uint32_t dense_max = std::min(envKnob("RPVG_B200_EM_DENSE_MAX", kDenseDefaultMax), kDenseDims[0]);
 
     for (uint32_t c = 0; c < b->n_clusters; ++c) {
@@ -273,7 +279,11 @@ void planEmLaunches(const rpvg_b200_ctx * ctx, rpvg_b200_batch * b, std::vector<
         // small clusters: dense in shared memory, one thread per read class / path (em_dense.cuh)
         const uint64_t dense_side = std::max(M, N + 1);
 
-        if (dense_side <= dense_max) {
+        if (ctx->stream_grid > 0 && (weight > stream_weight || (fixed + 4096 > smem_cap && weight > 50000))) {
+
+            plan.bin = stream_bin;
+
+        } else if (dense_side <= dense_max) {
 
             int k = 3;
             while (kDenseDims[k] < dense_side) { k--; }
@@ -334,8 +344,17 @@ void planEmLaunches(const rpvg_b200_ctx * ctx, rpvg_b200_batch * b, std::vector<
             bin.count = 0;
 
             bin.dense_dim = 0;
+            bin.stream = false;
 
-            if (items[k].bin >= dense_bin0) {
+            if (items[k].bin == stream_bin) {
+
+                bin.stream = true;
+                bin.group_size = 0;
+                bin.threads = kStreamThreads;
+                bin.smem = 0;
+                bin.index_bytes = 4;
+
+            } else if (items[k].bin >= dense_bin0) {
 
                 bin.dense_dim = kDenseDims[items[k].bin - dense_bin0];
                 bin.group_size = 1;
@@ -563,6 +582,17 @@ int rpvgEmInit(rpvg_b200_ctx * ctx) {
     RPVG_CUDA(ctx, cudaFuncSetAttribute(emDenseKernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(DenseShape<128>::kSmemBytes)));
 
     ctx->max_group_size = max_group;
+
+    // cooperative grid of emStreamKernel: every CTA resident at once
+    {
+        int cooperative = 0, per_sm = 0;
+        cudaDeviceGetAttribute(&cooperative, cudaDevAttrCooperativeLaunch, ctx->device);
+        if (cooperative && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, emStreamKernel, kStreamThreads, 0) == cudaSuccess && per_sm > 0) {
+            ctx->stream_grid = std::min<uint32_t>(kStreamMaxCtas, static_cast<uint32_t>(std::min(per_sm, 2) * ctx->num_sms));
+        }
+        cudaGetLastError();
+    }
+
     return RPVG_B200_OK;
 }
 
@@ -617,6 +647,7 @@ int rpvgBatchCreate(rpvg_b200_ctx * ctx, uint32_t n_clusters, const uint64_t * r
     bytes += padded<double>(P + C) + padded<double>(R) + padded<double>(P) + 2 * padded<double>(C) + padded<uint32_t>(C) + padded<uint32_t>(1);
     bytes += ((b->scratch_bytes + 255) & ~size_t(255));
     bytes += padded<double>(R) + 8192;
+    bytes += padded<double>(2 * kStreamMaxCtas) + padded<uint32_t>(kStreamMaxCtas);
 
     cudaError_t err = cudaMallocFromPoolAsync(reinterpret_cast<void **>(&b->pool.base), bytes, ctx->pool, ctx->stream);
     if (err != cudaSuccess) {
@@ -666,6 +697,8 @@ int rpvgBatchCreate(rpvg_b200_ctx * ctx, uint32_t n_clusters, const uint64_t * r
     b->d_iterations = pool.take<uint32_t>(C);
     b->d_error = pool.take<uint32_t>(1);
     b->d_scratch = pool.take<unsigned char>(b->scratch_bytes);
+    b->d_stream_partial = pool.take<double>(2 * kStreamMaxCtas);
+    b->d_stream_flags = pool.take<uint32_t>(kStreamMaxCtas);
 
     if (pool.used > pool.size) {
         cudaFreeAsync(pool.base, ctx->stream);
@@ -866,6 +899,27 @@ static int batchEmLaunch(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const rpvg_b2
 
     RPVG_CUDA(ctx, cudaEventRecord(b->ev_built, s));
 
+    // Giant clusters first, one after the other on the ctx stream: each is a cooperative launch that fills the GPU.
+    for (size_t k = 0; k < b->bins.size(); ++k) {
+
+        const auto & bin = b->bins[k];
+        if (!bin.stream) { continue; }
+
+        for (uint32_t i = 0; i < bin.count; ++i) {
+
+            StreamArgs sargs;
+            sargs.em = args;
+            sargs.cluster = b->h_order[bin.first + i];
+            sargs.partial = b->d_stream_partial;
+            sargs.low_partial = b->d_stream_partial + kStreamMaxCtas;
+            sargs.flags = b->d_stream_flags;
+
+            void * kernel_args[] = {&sargs};
+            RPVG_CUDA(ctx, cudaLaunchCooperativeKernel(reinterpret_cast<void *>(emStreamKernel), dim3(ctx->stream_grid), dim3(kStreamThreads), kernel_args, 0, s));
+            RPVG_LAUNCHED(ctx);
+        }
+    }
+
     // Bins run concurrently on the ctx's side streams (fork after the build, join before ev_done), one stream priority
     // level per bin, larger groups higher: a thread-block cluster of 16 needs 16 idle SMs of one GPC at the same moment,
     // which it only gets if it is placed before anything smaller. Measured on B200 (tools/em_timeline.py): 7 of the 8
@@ -921,6 +975,8 @@ static int batchEmLaunch(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const rpvg_b2
             fprintf(stderr, "[rpvg_b200] em bin %zu: group %u threads %u smem %u index %u clusters %u (max group %u, scratch %.1f MB)\n", k, bin.group_size,
                     bin.threads, bin.smem, bin.index_bytes, bin.count, ctx->max_group_size, b->scratch_bytes / 1e6);
         }
+
+        if (bin.stream) { continue; }   // done above
 
         cudaStream_t bs = ctx->side_streams[stream_of_bin(k)];
         RPVG_CUDA(ctx, cudaStreamWaitEvent(bs, ctx->fork_event, 0));

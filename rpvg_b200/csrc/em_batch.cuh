@@ -47,6 +47,7 @@ struct rpvg_b200_batch {
         uint32_t first;        // offset into d_order / d_group_scratch / d_group_cta_bytes
         uint32_t count;
         uint32_t dense_dim;    // > 0: emDenseKernel of this side (one CTA per cluster, no scratch)
+        bool stream;           // emStreamKernel: one cooperative launch of the whole GPU per cluster (em_stream.cuh)
     };
     std::vector<EmBin> bins;
     uint64_t scratch_bytes = 0;
@@ -97,6 +98,8 @@ struct rpvg_b200_batch {
     double * d_abund = nullptr;   // fallback kernel only: per cluster N_c + 1 relative abundances (noise last)
     double * d_w = nullptr;       // fallback kernel only
     unsigned char * d_scratch = nullptr;
+    double * d_stream_partial = nullptr;      // emStreamKernel: [2 x kStreamMaxCtas] doubles + [kStreamMaxCtas] votes
+    uint32_t * d_stream_flags = nullptr;
     double * d_abundances = nullptr;
     double * d_noise_count = nullptr;
     double * d_total_count = nullptr;

@@ -41,15 +41,16 @@ def power_law_sizes(rng, total, n_max, alpha=1.8):
 
 
 def transcripts_arena(seed=BASE_SEED + 2, n_paths=200_000, n_reads=1_000_000, n_max=5000, geom_p=0.25,
-                      min_reads_per_cluster=1) -> ClusterArena:
+                      min_reads_per_cluster=1, sizes=None, reads_cap=1e5) -> ClusterArena:
     """Config 2 — "transcripts model EM on synthetic clusters: 1M read classes, 200k paths, power-law cluster
     sizes (1-5,000 paths)". N_c ~ power-law(1.8) on [1, n_max]; R_c = min(1e5, ceil(5 N_c^1.1)) rescaled to sum to
     ``n_reads``; per read class 1 + Geom(geom_p) distinct paths inside a window around a random centre; values
     Dirichlet(1) * (1 - noise); counts 1 + Geom(0.3)."""
     rng = np.random.default_rng(seed)
 
-    sizes = power_law_sizes(rng, n_paths, n_max)
-    raw_reads = np.minimum(1e5, np.ceil(5.0 * sizes.astype(np.float64) ** 1.1))
+    # (``sizes``: the paths of every cluster given outright instead of drawn; ``reads_cap``: the cap on R_c before rescaling)
+    sizes = power_law_sizes(rng, n_paths, n_max) if sizes is None else np.asarray(sizes, dtype=np.int64)
+    raw_reads = np.minimum(reads_cap, np.ceil(5.0 * sizes.astype(np.float64) ** 1.1))
     reads = np.maximum(min_reads_per_cluster, np.round(raw_reads * (n_reads / raw_reads.sum()))).astype(np.int64)
 
     C = len(sizes)

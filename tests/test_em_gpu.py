@@ -203,3 +203,49 @@ def test_em_dense_kernels(ctx, monkeypatch):
         for mine, sell in zip(results[dense_max], results["0"]):
             assert np.allclose(mine, sell, rtol=REL_TOL, atol=1e-9)
         assert np.array_equal(results[dense_max][3], results["0"][3])
+
+
+def giant_arena(n_paths_giant, n_reads, seed=5):
+    """One giant cluster and a handful of ordinary ones around it."""
+    sizes = [7, 300, n_paths_giant, 40, 1200]
+    return synth.transcripts_arena(seed=seed, n_reads=n_reads, sizes=sizes, reads_cap=1e9)
+
+
+def test_em_giant_cluster_streams_over_the_whole_gpu(ctx):
+    """A cluster far beyond 16 shared-memory slices goes to emStreamKernel (one cooperative launch of the whole GPU, the
+    matrix streamed every iteration, grid-wide barriers). To convergence against the oracle: abundances, zero set and the
+    stopping iteration."""
+    arena = giant_arena(8000, 100_000)
+    shapes = [arena.cluster_shape(c) for c in range(arena.n_clusters)]
+    weight = max(m + z for m, _, z in shapes)
+    assert weight > 500_000
+
+    ab, noise, total, its = ctx.em_abundances(arena)
+    o_ab, o_noise, o_total, o_its, _ = loader.port_em_abundances(arena, num_threads=0)
+
+    assert np.array_equal(total, o_total)
+    assert np.array_equal(ab == 0, o_ab == 0)
+    nz = o_ab != 0
+    assert np.max(np.abs(ab[nz] - o_ab[nz]) / o_ab[nz]) < 1e-6
+    assert np.allclose(noise, o_noise, rtol=1e-6, atol=1e-9)
+    assert np.array_equal(its, o_its)
+
+    # bit-reproducible
+    ab2, noise2, _, its2 = ctx.em_abundances(arena)
+    assert np.array_equal(ab, ab2) and np.array_equal(noise, noise2) and np.array_equal(its, its2)
+
+
+def test_em_giant_cluster_two_million_entries(ctx):
+    """More than 2 M entries in one cluster (48 MB in the two orientations), 250 iterations on both sides."""
+    arena = giant_arena(40000, 520_000, seed=6)
+    assert max(z for _, _, z in (arena.cluster_shape(c) for c in range(arena.n_clusters))) > 2_000_000
+
+    params = capi.default_em_params(max_em_its=250)
+    ab, noise, total, its = ctx.em_abundances(arena, params)
+    o_ab, o_noise, o_total, o_its, _ = loader.port_em_abundances(arena, max_em_its=250, num_threads=0)
+
+    assert np.array_equal(its, o_its) and int(its.max()) == 250
+    assert np.array_equal(ab == 0, o_ab == 0)
+    nz = o_ab != 0
+    assert np.max(np.abs(ab[nz] - o_ab[nz]) / o_ab[nz]) < 1e-6
+    assert np.allclose(noise, o_noise, rtol=1e-6, atol=1e-9)
