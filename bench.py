@@ -157,11 +157,11 @@ def run_reference_sample(sub, its, threads=0):
     return work / seconds, seconds, kind, threads, busy
 
 
-def run_port_full(arena, threads=0):
+def run_port_full(arena, threads=0, max_em_its=10000):
     """The sparse CPU restatement on the whole arena, all host threads: (nnz*it/s, seconds, iterations)."""
     from oracle import loader
     threads = threads or host_threads()
-    _, _, _, its, seconds = loader.port_em_abundances(arena, num_threads=threads)
+    _, _, _, its, seconds = loader.port_em_abundances(arena, max_em_its=max_em_its, num_threads=threads)
     work = 0.0
     for c in range(arena.n_clusters):
         m, _, nnz_path = arena.cluster_shape(c)
@@ -239,7 +239,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--config", default="c2", choices=["c1", "c2", "c3", "c4", "c5"])
+    ap.add_argument("--config", default="c2", choices=["c1", "c2", "c3", "c4", "c5", "giant"])
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the workload (debug only; a scaled run is not a bench number)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-strong", action="store_true", help="N > 1: skip the fixed-work (strong scaling) legs")
@@ -249,7 +249,7 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
 
-    if args.config != "c2":
+    if args.config not in ("c2", "giant"):
         import bench_models
         return bench_models.run(args, rank, local_rank, world, ClockSampler, host_threads)
 
@@ -262,7 +262,21 @@ def main():
               "read_classes_per_gpu": n_reads, "paths_per_gpu": n_paths, "max_em_its": 10000, "max_rel_em_conv": 0.001,
               "sharding": f"{world} arena(s) of this shape; clusters dealt to {world} rank(s) by LPT on nnz x E[iterations], no collective", "l2": "flushed between timed steps (256 MiB write)"}
 
+    giant = args.config == "giant"
+    max_em_its = 10000
+
+    if giant:
+        # one path cluster larger than the L2 cache in both orientations: the HBM-streaming regime (emStreamKernel)
+        giant_paths, giant_reads, max_em_its = max(2000, int(20_000 * args.scale)), max(20000, int(4_000_000 * args.scale)), 200
+        config = {"workload": ("giant: ONE path cluster of 20k paths x 4M read classes (~20M entries: 480 MB in the two orientations, beyond the 126 MB L2), "
+                               "EM capped at 200 iterations; not a BASELINE.json configuration: the streaming regime north_star asks for") if args.scale == 1.0
+                              else f"DEBUG scale={args.scale} of the giant cluster",
+                  "read_classes_per_gpu": giant_reads, "paths_per_gpu": giant_paths, "max_em_its": max_em_its, "max_rel_em_conv": 0.001,
+                  "sharding": f"{world} replica(s): a single cluster does not shard", "l2": "the cluster is larger than L2; flushed between timed steps all the same"}
+
     def headline_arena(k=0):
+        if giant:
+            return synth.transcripts_arena(seed=synth.BASE_SEED + 7 + k, n_reads=giant_reads, sizes=[giant_paths], reads_cap=1e12)
         return synth.transcripts_arena(seed=synth.BASE_SEED + 2 + k, n_paths=n_paths, n_reads=n_reads, n_max=n_max)
 
     # ------------------------------------------------------------------------------------------------ reference arm
@@ -331,7 +345,7 @@ def main():
     torch.cuda.set_stream(stream)
     assert stream.cuda_stream != 0
     ctx = capi.Context(local_rank, stream.cuda_stream)
-    params = capi.default_em_params()
+    params = capi.default_em_params(max_em_its=max_em_its)
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device="cuda")
 
     def barrier():
@@ -372,7 +386,7 @@ def main():
 
     # ---- fixed total work over the N ranks (strong scaling): one arena, and a job of 8 arenas, dealt by LPT
     strong = None
-    if world > 1 and not args.no_strong and args.scale == 1.0:
+    if world > 1 and not args.no_strong and args.scale == 1.0 and not giant:
         strong = {}
         for name, n_arenas in (("one_arena", 1), ("eight_arenas", 8)):
             job = first if n_arenas == 1 else concat([first] + [headline_arena(r) for r in range(1, n_arenas)])
@@ -428,7 +442,19 @@ def main():
         if strong:
             line["strong"] = strong
 
-        if not args.no_cpu_baseline:
+        if giant:
+            its = float(max_its)
+            reads, paths, entries = float(arena.n_reads), float(arena.n_paths), float(arena.nnz_path)
+            line["roofline"]["kernel"] = "emStreamKernel (cooperative, whole GPU)"
+            line["roofline"]["meaning"] = ("algorithmic bytes (12 nnz_path + 20 M + 16 (N+1) per iteration, the matrix counted once) / EM device time. The kernel reads "
+                                           "both orientations of the matrix every iteration (deterministic: no atomics), see bytes_read_per_iteration")
+            line["roofline"]["bytes_read_per_iteration"] = 24 * entries + 32 * reads + 24 * paths
+            line["roofline"]["hbm_frac_of_bytes_read"] = (24 * entries + 32 * reads + 24 * paths) * its / (em_ms_mean * 1e-3) / 1e9 / peak
+            line["roofline"]["us_per_iteration"] = 1e3 * em_ms_mean / its
+            line["roofline"]["traffic"] = None
+            line["roofline"]["traffic_source"] = None
+
+        if not args.no_cpu_baseline and not giant:
             threads = host_threads()
             port_value, port_seconds, port_its = run_port_full(arena, threads)
             line["cpu_port"] = {"value": port_value, "unit": UNIT, "cores": threads, "kind": "port", "seconds": port_seconds,

@@ -588,7 +588,7 @@ int rpvgEmInit(rpvg_b200_ctx * ctx) {
         int cooperative = 0, per_sm = 0;
         cudaDeviceGetAttribute(&cooperative, cudaDevAttrCooperativeLaunch, ctx->device);
         if (cooperative && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, emStreamKernel, kStreamThreads, 0) == cudaSuccess && per_sm > 0) {
-            ctx->stream_grid = std::min<uint32_t>(kStreamMaxCtas, static_cast<uint32_t>(std::min(per_sm, 2) * ctx->num_sms));
+            ctx->stream_grid = std::min<uint32_t>(kStreamMaxCtas, static_cast<uint32_t>(std::min(per_sm, 4) * ctx->num_sms));
         }
         cudaGetLastError();
     }

@@ -6,9 +6,10 @@
 // persistent grid, the read classes and the paths each cut into one contiguous range per CTA of about equal entries,
 // two grid-wide barriers per iteration:
 //
-//   E-step  rows of the CTA's range, a thread per read class (they hold ~5 entries, and neighbouring threads read
-//           neighbouring rows, so every 32-byte sector fetched from HBM is used in full): w_i = count_i / (sum_j p_ij a_j +
-//           noise_i a_noise) into global memory; the CTA's share of sum_i noise_i w_i into partial[cta]
+//   E-step  rows of the CTA's range, 32 read classes per warp at a time: the warp loads their (contiguous) entries
+//           together, coalesced, 128 per step, the products go through shared memory and every lane sums its own read
+//           class in entry order: w_i = count_i / (sum_j p_ij a_j + noise_i a_noise) into global memory; the CTA's share of
+//           sum_i noise_i w_i into partial[cta]
 //   grid barrier
 //   M-step  columns of the CTA's range, 8 lanes per path over the column-major copy: a_j <- a_j * sum_i p_ij w_i / total
 //           in place (the E-step is over); every CTA adds partial[] up in the same order and gets the same noise
@@ -31,6 +32,7 @@
 
 constexpr int kStreamThreads = 512;
 constexpr uint32_t kStreamMaxCtas = 2048;
+constexpr uint32_t kStreamStep = 128;   // entries a warp multiplies per step of the E-step
 
 struct StreamArgs {
 
@@ -41,9 +43,10 @@ struct StreamArgs {
     double * low_partial;    // [grid] mass below min_em_abundance (final pass)
 };
 
-__global__ void __launch_bounds__(kStreamThreads) emStreamKernel(const StreamArgs sa) {
+__global__ void __launch_bounds__(kStreamThreads, 3) emStreamKernel(const StreamArgs sa) {
 
     __shared__ double red[32];
+    __shared__ double product_area[kStreamThreads / 32][kStreamStep];
 
     namespace cg = cooperative_groups;
     cg::grid_group grid = cg::this_grid();
@@ -51,6 +54,9 @@ __global__ void __launch_bounds__(kStreamThreads) emStreamKernel(const StreamArg
     const EmArgs & args = sa.em;
 
     const uint32_t tid = threadIdx.x;
+    const uint32_t lane = tid & 31;
+    const uint32_t warp = tid >> 5;
+    double * products = product_area[warp];
     const uint32_t cta = blockIdx.x;
     const uint32_t n_ctas = gridDim.x;
 
@@ -97,10 +103,18 @@ __global__ void __launch_bounds__(kStreamThreads) emStreamKernel(const StreamArg
         col_hi = split(col_ptr, N, k0, Z + N, cta + 1, n_ctas);
     }
 
-    // ---- total read count: every CTA sums all rows in the same order, so all agree bit for bit
+    // ---- total read count: every CTA sums its own rows, then all add the partial sums in the same order (counts are
+    // integers: the sum is exact whatever the order)
     double count_sum = 0;
-    for (uint32_t i = tid; i < M; i += kStreamThreads) { count_sum += cnt[i]; }
-    const double total = blockSum(count_sum, red);
+    for (uint32_t i = row_lo + tid; i < row_hi; i += kStreamThreads) { count_sum += cnt[i]; }
+    const double cta_count = blockSum(count_sum, red);
+    if (tid == 0) { sa.low_partial[cta] = cta_count; }
+
+    grid.sync();
+
+    double count_part = 0;
+    for (uint32_t q = tid; q < n_ctas; q += kStreamThreads) { count_part += sa.low_partial[q]; }
+    const double total = blockSum(count_part, red);
 
     // rpvg:src/path_abundance_estimator.cpp:54 — single-precision quotient widened to double
     const double a_init = static_cast<double>(1 / static_cast<float>(N + 1));
@@ -121,16 +135,48 @@ __global__ void __launch_bounds__(kStreamThreads) emStreamKernel(const StreamArg
         // ---- E-step over this CTA's rows
         double noise_acc = 0;
 
-        for (uint32_t i = row_lo + tid; i < row_hi; i += kStreamThreads) {
+        // A warp takes 32 consecutive read classes at a time (lane = read class). Their entries are one contiguous stretch
+        // of the row-major arrays: the lanes load it together, 128 entries a step — fully coalesced, every load independent
+        // of the row offsets — multiply by the gathered abundances and park the products in shared memory; then every lane
+        // adds up the products of its own read class, in entry order (the order a sequential loop over the row has).
+        for (uint32_t tile = row_lo + warp * 32; tile < row_hi; tile += (kStreamThreads / 32) * 32) {
 
-            const uint64_t e1 = row_ptr[i + 1];
+            const uint32_t i = tile + lane;
+            const bool live = i < row_hi;
+
+            const uint64_t begin = live ? row_ptr[i] : 0;
+            const uint64_t end = live ? row_ptr[i + 1] : 0;
+            const double nz = live ? noise[i] : 0.0;
+            const double ct = live ? cnt[i] : 0.0;
+
+            const uint32_t last = min(31u, row_hi - 1 - tile);
+            const uint64_t tile_begin = __shfl_sync(0xffffffffu, begin, 0);
+            const uint64_t tile_end = __shfl_sync(0xffffffffu, end, last);
+
             double s = 0;
-            for (uint64_t e = row_ptr[i]; e < e1; ++e) { s += args.val[e] * a[args.col[e]]; }
-            s += noise[i] * a_noise;
 
-            const double wi = cnt[i] / s;
-            w[i] = wi;
-            noise_acc += noise[i] * wi;
+            for (uint64_t step = tile_begin; step < tile_end; step += kStreamStep) {
+
+                #pragma unroll
+                for (uint32_t u = 0; u < kStreamStep / 32; ++u) {
+                    const uint64_t e = step + u * 32 + lane;
+                    if (e < tile_end) { products[u * 32 + lane] = args.val[e] * a[args.col[e]]; }
+                }
+
+                __syncwarp();
+
+                const uint64_t from = max(begin, step);
+                const uint64_t to = min(end, step + kStreamStep);
+                for (uint64_t e = from; e < to; ++e) { s += products[e - step]; }
+
+                __syncwarp();
+            }
+
+            if (live) {
+                const double wi = ct / (s + nz * a_noise);
+                w[i] = wi;
+                noise_acc += nz * wi;
+            }
         }
 
         const double cta_noise = blockSum(noise_acc, red);
@@ -146,30 +192,53 @@ __global__ void __launch_bounds__(kStreamThreads) emStreamKernel(const StreamArg
         const double a_noise_new = (a_noise * noise_g) / total;
         bool ok = !(a_noise_new >= min_abundance && fabs(a_noise_new - a_noise) / a_noise_new > conv);
 
-        // ---- M-step over this CTA's columns: 8 lanes per path
-        const uint32_t sub = tid & 7;
+        // ---- M-step over this CTA's columns: 8 lanes per path, or a whole warp where the range holds few, long columns
+        // (with 8 lanes the last round of a short range would leave most groups idle)
+        if ((col_hi - col_lo) * 8 < 4 * kStreamThreads) {
 
-        // (the loop bound is the warp's: its four columns may end at different places, the shuffles want all lanes)
-        for (uint32_t jw = col_lo + (tid >> 5) * 4; jw < col_hi; jw += kStreamThreads / 8) {
+            for (uint32_t j = col_lo + warp; j < col_hi; j += kStreamThreads / 32) {
 
-            const uint32_t j = jw + ((tid & 31) >> 3);
-            const bool live = j < col_hi;
-
-            double gsum = 0;
-            if (live) {
                 const uint64_t k1 = col_ptr[j + 1];
-                for (uint64_t k = col_ptr[j] + sub; k < k1; k += 8) { gsum += args.csc_val[k] * w[args.csc_row[k]]; }
+                double gsum = 0;
+                #pragma unroll 4
+                for (uint64_t k = col_ptr[j] + lane; k < k1; k += 32) { gsum += args.csc_val[k] * w[args.csc_row[k]]; }
+                gsum = warpSum(gsum);
+
+                if (lane == 0) {
+                    const double a_old = a[j];
+                    const double a_new = (a_old * gsum) / total;
+                    a[j] = a_new;
+                    if (a_new >= min_abundance && fabs(a_new - a_old) / a_new > conv) { ok = false; }
+                }
             }
 
-            gsum += __shfl_xor_sync(0xffffffffu, gsum, 4);
-            gsum += __shfl_xor_sync(0xffffffffu, gsum, 2);
-            gsum += __shfl_xor_sync(0xffffffffu, gsum, 1);
+        } else {
 
-            if (live && sub == 0) {
-                const double a_old = a[j];
-                const double a_new = (a_old * gsum) / total;
-                a[j] = a_new;
-                if (a_new >= min_abundance && fabs(a_new - a_old) / a_new > conv) { ok = false; }
+            const uint32_t sub = tid & 7;
+
+            // (the loop bound is the warp's: its four columns may end at different places, the shuffles want all lanes)
+            for (uint32_t jw = col_lo + warp * 4; jw < col_hi; jw += kStreamThreads / 8) {
+
+                const uint32_t j = jw + (lane >> 3);
+                const bool live = j < col_hi;
+
+                double gsum = 0;
+                if (live) {
+                    const uint64_t k1 = col_ptr[j + 1];
+                    #pragma unroll 4
+                    for (uint64_t k = col_ptr[j] + sub; k < k1; k += 8) { gsum += args.csc_val[k] * w[args.csc_row[k]]; }
+                }
+
+                gsum += __shfl_xor_sync(0xffffffffu, gsum, 4);
+                gsum += __shfl_xor_sync(0xffffffffu, gsum, 2);
+                gsum += __shfl_xor_sync(0xffffffffu, gsum, 1);
+
+                if (live && sub == 0) {
+                    const double a_old = a[j];
+                    const double a_new = (a_old * gsum) / total;
+                    a[j] = a_new;
+                    if (a_new >= min_abundance && fabs(a_new - a_old) / a_new > conv) { ok = false; }
+                }
             }
         }
 
