@@ -219,7 +219,7 @@ void PathEstimator::estimateBatch(const vector<PathClusterEstimates *> & estimat
     assert(estimates.size() == cluster_probs.size());
     assert(estimates.size() == rngs.size());
 
-    for (size_t i = 0; i < estimates.size(); ++i) { estimate(estimates[i], *cluster_probs[i], rngs[i]); }
+    for (size_t i = 0; i < estimates.size(); ++i) { estimateOne(estimates[i], *cluster_probs[i], rngs[i]); }
 }
 
 // One batch over the GPUs of the box: see estimators.hpp. The split mirrors the reference's own schedule — largest first,

@@ -4,6 +4,9 @@
 
 #include "estimators.hpp"
 
+#include <condition_variable>
+#include <mutex>
+
 #include <algorithm>
 #include <cassert>
 #include <cmath>
@@ -220,7 +223,107 @@ void PathClusterEstimates::resetEstimates(uint32_t num_components, const uint32_
 
 #endif
 
-PathEstimator::PathEstimator(const double prob_precision_in) : prob_precision(prob_precision_in) {}
+// Callers of estimate() that found the device busy. One mutex: a request is two pointers, the queue is touched for
+// nanoseconds around device calls of hundreds of microseconds.
+struct PathEstimator::Combiner {
+
+    struct Request {
+        PathClusterEstimates * estimates;
+        const vector<ReadPathProbabilities> * cluster_probs;
+        mt19937 * rng;
+        bool done = false;
+    };
+
+    mutex lock;
+    condition_variable wake;
+    vector<Request *> waiting;
+    bool device_busy = false;
+    const bool enabled;
+    rpvg_b200_ctx * shared_ctx = nullptr;
+
+    Combiner() : enabled(!(getenv("RPVG_B200_COMBINE") && string(getenv("RPVG_B200_COMBINE")) == "0")) {}
+    ~Combiner() { if (shared_ctx) { rpvg_b200_destroy(shared_ctx); } }
+};
+
+PathEstimator::PathEstimator(const double prob_precision_in) : combiner(new Combiner()), prob_precision(prob_precision_in) {}
+
+PathEstimator::~PathEstimator() { delete combiner; }
+
+void PathEstimator::estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng) {
+
+    if (!combiner->enabled || !combinesCallers()) {
+        estimateOne(path_cluster_estimates, cluster_probs, mt_rng);
+        return;
+    }
+
+    Combiner::Request mine;
+    mine.estimates = path_cluster_estimates;
+    mine.cluster_probs = &cluster_probs;
+    mine.rng = mt_rng;
+
+    unique_lock<mutex> guard(combiner->lock);
+    combiner->waiting.push_back(&mine);
+
+    for (;;) {
+
+        // until somebody has done this request, or the device is free and this thread does the waiting ones itself
+        combiner->wake.wait(guard, [&]() { return mine.done || !combiner->device_busy; });
+        if (mine.done) { return; }
+
+        combiner->device_busy = true;
+
+        vector<Combiner::Request *> batch;
+        batch.swap(combiner->waiting);   // this thread's request is among them: it was queued before the wait
+
+        guard.unlock();
+
+        // One context serves all combined calls (only one thread is ever in here): the calling threads need none of
+        // their own.
+        if (!combiner->shared_ctx) {
+            const int status = rpvg_b200_create(threadDevice(), nullptr, &combiner->shared_ctx);
+            if (status != RPVG_B200_OK) {
+                cerr << "ERROR: rpvg_b200_create(device " << threadDevice() << ") failed with status " << status << " (a CUDA device is required; there is no CPU fallback)" << endl;
+                abort();
+            }
+        }
+
+        rpvg_b200_ctx * previous = contextOverride();
+        contextOverride() = combiner->shared_ctx;
+
+        if (batch.size() == 1) {
+
+            estimateOne(batch[0]->estimates, *batch[0]->cluster_probs, batch[0]->rng);
+
+        } else {
+
+            vector<PathClusterEstimates *> est;
+            vector<const vector<ReadPathProbabilities> *> probs;
+            vector<mt19937 *> generators;
+
+            for (auto request: batch) {
+                est.push_back(request->estimates);
+                probs.push_back(request->cluster_probs);
+                generators.push_back(request->rng);
+            }
+
+            estimateBatch(est, probs, generators);
+        }
+
+        contextOverride() = previous;
+
+        guard.lock();
+
+        for (auto request: batch) { request->done = true; }
+        combiner->device_busy = false;
+        combiner->wake.notify_all();
+    }
+}
+
+rpvg_b200_ctx *& PathEstimator::contextOverride() {
+
+    thread_local rpvg_b200_ctx * ctx = nullptr;
+    return ctx;
+}
 
 namespace {
 
@@ -253,6 +356,8 @@ int & PathEstimator::threadDevice() {
 }
 
 rpvg_b200_ctx * PathEstimator::threadContext() {
+
+    if (contextOverride()) { return contextOverride(); }
 
     thread_local ThreadContexts contexts;
 
@@ -619,7 +724,7 @@ void PathEstimator::estimatePathGroupPosteriorsGibbs(PathClusterEstimates * path
 
 PathAbundanceEstimator::PathAbundanceEstimator(const uint32_t max_em_its_in, const double max_rel_em_conv_in, const uint32_t num_gibbs_samples_in, const uint32_t gibbs_thin_its_in, const double prob_precision) : PathEstimator(prob_precision), max_em_its(max_em_its_in), max_rel_em_conv(max_rel_em_conv_in), num_gibbs_samples(num_gibbs_samples_in), gibbs_thin_its(gibbs_thin_its_in) {}
 
-void PathAbundanceEstimator::estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng) {
+void PathAbundanceEstimator::estimateOne(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng) {
 
     path_cluster_estimates->resetEstimates(path_cluster_estimates->paths.size(), 1);
 
@@ -665,7 +770,7 @@ void PathAbundanceEstimator::estimate(PathClusterEstimates * path_cluster_estima
 
 MinimumPathAbundanceEstimator::MinimumPathAbundanceEstimator(const uint32_t max_em_its, const double max_rel_em_conv, const uint32_t num_gibbs_samples, const uint32_t gibbs_thin_its, const double prob_precision) : PathAbundanceEstimator(max_em_its, max_rel_em_conv, num_gibbs_samples, gibbs_thin_its, prob_precision) {}
 
-void MinimumPathAbundanceEstimator::estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng) {
+void MinimumPathAbundanceEstimator::estimateOne(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng) {
 
     const uint32_t num_paths = path_cluster_estimates->paths.size();
     path_cluster_estimates->resetEstimates(num_paths, 1);
@@ -781,7 +886,7 @@ static const double min_rel_likelihood = 1e-8;   // rpvg:src/path_posterior_esti
 
 PathPosteriorEstimator::PathPosteriorEstimator(const double prob_precision) : PathEstimator(prob_precision) {}
 
-void PathPosteriorEstimator::estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng) {
+void PathPosteriorEstimator::estimateOne(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng) {
 
     path_cluster_estimates->resetEstimates(path_cluster_estimates->paths.size(), 1);
 
@@ -798,7 +903,7 @@ void PathPosteriorEstimator::estimate(PathClusterEstimates * path_cluster_estima
 
 PathGroupPosteriorEstimator::PathGroupPosteriorEstimator(const uint32_t group_size_in, const bool use_group_post_gibbs_in, const double prob_precision) : PathPosteriorEstimator(prob_precision), group_size(group_size_in), use_group_post_gibbs(use_group_post_gibbs_in) {}
 
-void PathGroupPosteriorEstimator::estimate(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng) {
+void PathGroupPosteriorEstimator::estimateOne(PathClusterEstimates * path_cluster_estimates, const vector<ReadPathProbabilities> & cluster_probs, mt19937 * mt_rng) {
 
     path_cluster_estimates->resetEstimates(0, 0);
 
