@@ -10,7 +10,7 @@
 //
 // Device side: the same three steps as the read-class collapse of the matrices (collapse.cuh): bitonic network per
 // cluster with the reference's comparator (data-oblivious, so the tolerance comparator cannot break it; ties keep input
-// order), sequential greedy scan per cluster, class representatives and counts. Exact: the partition, the order of the
+// order), the greedy scan cut into independent stretches, kept records and counts. Exact: the partition, the order of the
 // kept records and their counts. A record is a ragged list of lists, so this is pointer chasing, not streaming: the
 // bound is L2/HBM latency; the work is O(R log^2 R) comparisons per cluster.
 
@@ -115,42 +115,137 @@ __global__ void __launch_bounds__(kCollapseSortThreads) recordSortKernel(const R
     collapseBitonicNetwork(sorted + r0, n, less);
 }
 
-// One thread per cluster: the scan of main.cpp:959-972. Per sorted position: index of the kept record it ends up in; per
-// cluster: number of kept records; per kept record (compacted at the cluster's offset): the record it is and its count.
-__global__ void recordScanKernel(const ReadRecords rec, const uint32_t * __restrict__ sorted, const double prob_precision, uint32_t * __restrict__ record_class,
-                                 uint32_t * __restrict__ n_merged, uint32_t * __restrict__ merged_rep, uint32_t * __restrict__ merged_count) {
+// The scan of main.cpp:959-972 in three parallel passes, like the read-class collapse (collapse.cuh): a record that
+// certainly cannot be folded into whatever record is kept before it starts a kept record of its own whatever happened
+// earlier — it differs from its predecessor in structure (groups, path ids: a kept record and everything folded into it
+// share them), or by at least twice the precision in the noise or a group probability (triangle inequality against the
+// predecessor's kept record). Pass 1 flags these certain starts, pass 2 walks every stretch between two of them with the
+// exact sequential rule, pass 3 numbers the kept records and adds up their counts.
 
-    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= rec.n_clusters) { return; }
+// true iff record b certainly cannot be folded into a record that record a was folded into (or into a itself)
+__device__ bool recordsCertainlyApart(const ReadRecords & rec, const uint64_t a, const uint64_t b, const double distance) {
 
+    if (fabs(rec.noise[a] - rec.noise[b]) >= distance) { return true; }
+
+    const uint64_t ga = rec.group_ptr[a], gb = rec.group_ptr[b];
+    const uint64_t na = rec.group_ptr[a + 1] - ga;
+    if (na != rec.group_ptr[b + 1] - gb) { return true; }
+
+    for (uint64_t i = 0; i < na; ++i) {
+
+        if (fabs(rec.group_prob[ga + i] - rec.group_prob[gb + i]) >= distance) { return true; }
+
+        const uint64_t ia = rec.id_ptr[ga + i], ib = rec.id_ptr[gb + i];
+        const uint64_t sa = rec.id_ptr[ga + i + 1] - ia;
+        if (sa != rec.id_ptr[gb + i + 1] - ib) { return true; }
+
+        for (uint64_t j = 0; j < sa; ++j) {
+            if (rec.ids[ia + j] != rec.ids[ib + j]) { return true; }
+        }
+    }
+
+    return false;
+}
+
+// pass 1: one thread per sorted position
+__global__ void recordBoundaryKernel(const ReadRecords rec, const uint32_t * __restrict__ sorted, const double prob_precision, uint32_t * __restrict__ flag) {
+
+    const uint64_t s = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (s >= rec.n_records) { return; }
+
+    const uint32_t c = clusterOf(rec.read_offset, rec.n_clusters, s);
+    const uint64_t r0 = rec.read_offset[c];
+
+    bool start = (s == r0);
+    if (!start) { start = recordsCertainlyApart(rec, r0 + sorted[s - 1], r0 + sorted[s], 2.0 * prob_precision * (1.0 + 1e-9)); }
+
+    flag[s] = start ? 1u : 0u;
+}
+
+// pass 2: the thread of a certain start walks its stretch with the sequential rule; records kept inside it get flag 2
+__global__ void recordStretchKernel(const ReadRecords rec, const uint32_t * __restrict__ sorted, const double prob_precision, uint32_t * flag) {
+
+    const uint64_t s = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (s >= rec.n_records || flag[s] != 1u) { return; }
+
+    const uint32_t c = clusterOf(rec.read_offset, rec.n_clusters, s);
     const uint64_t r0 = rec.read_offset[c];
     const uint64_t r1 = rec.read_offset[c + 1];
 
-    uint32_t kept = 0;
-    uint64_t rep = 0;
-    uint32_t rep_count = 0;
+    uint64_t rep = r0 + sorted[s];
 
-    for (uint64_t s = r0; s < r1; ++s) {
+    for (uint64_t t = s + 1; t < r1; ++t) {
 
-        const uint64_t r = r0 + sorted[s];
+        if (flag[t] == 1u) { break; }
 
-        if (s == r0 || !recordsMergeable(rec, rep, r, prob_precision)) {
-
-            if (kept > 0) { merged_count[r0 + kept - 1] = rep_count; }
+        const uint64_t r = r0 + sorted[t];
+        if (!recordsMergeable(rec, rep, r, prob_precision)) {
             rep = r;
-            rep_count = rec.count[r];
-            merged_rep[r0 + kept] = sorted[s];
-            kept++;
+            flag[t] = 2u;
+        }
+    }
+}
 
-        } else {
-            rep_count += rec.count[r];   // uint32, like ReadPathProbabilities::addReadCount
+constexpr int kRecordIndexThreads = 256;
+
+// pass 3, one CTA per cluster: index of the kept record of every sorted position (block scan of the start flags), the kept
+// records themselves and — by the thread of each start — the sum of the counts folded into it (uint32 arithmetic, like
+// ReadPathProbabilities::addReadCount: exact whatever the order)
+__global__ void __launch_bounds__(kRecordIndexThreads) recordIndexKernel(const ReadRecords rec, const uint32_t * __restrict__ sorted, const uint32_t * __restrict__ flag,
+                                                                         uint32_t * __restrict__ record_class, uint32_t * __restrict__ n_merged,
+                                                                         uint32_t * __restrict__ merged_rep, uint32_t * __restrict__ merged_count) {
+
+    __shared__ uint32_t warp_total[kRecordIndexThreads / 32];
+    __shared__ uint32_t carry;
+
+    const uint32_t c = blockIdx.x;
+    const uint64_t r0 = rec.read_offset[c];
+    const uint64_t r1 = rec.read_offset[c + 1];
+
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    if (tid == 0) { carry = 0; }
+    __syncthreads();
+
+    for (uint64_t base = r0; base < r1; base += kRecordIndexThreads) {
+
+        const uint64_t s = base + tid;
+        const uint32_t start = (s < r1 && flag[s] != 0u) ? 1u : 0u;
+
+        uint32_t incl = start;
+        #pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t up = __shfl_up_sync(0xffffffffu, incl, off);
+            if (lane >= off) { incl += up; }
         }
 
-        record_class[r] = kept - 1;
+        if (lane == 31) { warp_total[warp] = incl; }
+        __syncthreads();
+
+        uint32_t before = carry;
+        for (uint32_t w = 0; w < warp; ++w) { before += warp_total[w]; }
+
+        if (s < r1) {
+
+            const uint32_t kept = before + incl - 1;
+            record_class[r0 + sorted[s]] = kept;
+
+            if (start) {
+
+                uint32_t total = rec.count[r0 + sorted[s]];
+                for (uint64_t t = s + 1; t < r1 && flag[t] == 0u; ++t) { total += rec.count[r0 + sorted[t]]; }
+
+                merged_rep[r0 + kept] = sorted[s];
+                merged_count[r0 + kept] = total;
+            }
+        }
+
+        __syncthreads();
+        if (tid == kRecordIndexThreads - 1) { carry = before + incl; }
+        __syncthreads();
     }
 
-    if (kept > 0) { merged_count[r0 + kept - 1] = rep_count; }
-    n_merged[c] = kept;
+    if (tid == 0) { n_merged[c] = carry; }
 }
 
 }
@@ -188,7 +283,7 @@ extern "C" int rpvg_b200_merge_read_records(rpvg_b200_ctx * ctx, const rpvg_b200
     cudaStream_t s = ctx->stream;
 
     const size_t bytes = padded<uint64_t>(C + 1) + padded<uint64_t>(R + 1) + padded<double>(G + 1) + padded<uint64_t>(G + 1) + padded<uint32_t>(I + 1) + padded<double>(R) +
-                         padded<uint32_t>(R) + 4 * padded<uint32_t>(R) + padded<uint32_t>(C) + 4096;
+                         padded<uint32_t>(R) + 5 * padded<uint32_t>(R) + padded<uint32_t>(C) + 4096;
 
     DevicePool pool;
     RPVG_CUDA(ctx, cudaMallocFromPoolAsync(reinterpret_cast<void **>(&pool.base), bytes, ctx->pool, s));
@@ -207,6 +302,7 @@ extern "C" int rpvg_b200_merge_read_records(rpvg_b200_ctx * ctx, const rpvg_b200
     uint32_t * d_rep = pool.take<uint32_t>(R);
     uint32_t * d_merged_count = pool.take<uint32_t>(R);
     uint32_t * d_n_merged = pool.take<uint32_t>(C);
+    uint32_t * d_flag = pool.take<uint32_t>(R);
 
     cudaError_t err = cudaSuccess;
     auto up = [&](void * dst, const void * src, size_t n) {
@@ -241,7 +337,12 @@ extern "C" int rpvg_b200_merge_read_records(rpvg_b200_ctx * ctx, const rpvg_b200
         RPVG_LAUNCHED(ctx);
         recordSortKernel<<<C, kCollapseSortThreads, 0, s>>>(rec, d_sorted);
         RPVG_LAUNCHED(ctx);
-        recordScanKernel<<<(C + 127) / 128, 128, 0, s>>>(rec, d_sorted, prob_precision, d_class, d_n_merged, d_rep, d_merged_count);
+        const unsigned rgrid = static_cast<unsigned>((R + 255) / 256);
+        recordBoundaryKernel<<<rgrid, 256, 0, s>>>(rec, d_sorted, prob_precision, d_flag);
+        RPVG_LAUNCHED(ctx);
+        recordStretchKernel<<<rgrid, 256, 0, s>>>(rec, d_sorted, prob_precision, d_flag);
+        RPVG_LAUNCHED(ctx);
+        recordIndexKernel<<<C, kRecordIndexThreads, 0, s>>>(rec, d_sorted, d_flag, d_class, d_n_merged, d_rep, d_merged_count);
         RPVG_LAUNCHED(ctx);
 
         err = cudaGetLastError();

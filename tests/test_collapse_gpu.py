@@ -86,3 +86,32 @@ def test_collapse_edge_cases(ctx, port):
     assert n == 2 and np.array_equal(class_count[1:3], cnt) and np.array_equal(row_class[50:55], cls)
     n, out, cnt, cls = oracle_collapse(port, *distinct)
     assert np.array_equal(row_class[55:], cls)
+
+
+def test_collapse_hundred_thousand_rows(ctx, port):
+    """One problem of 100,000 rows (a C5-sized cluster: 25k-100k read classes): near duplicates inside the precision,
+    ulp-level twins and rows just outside it, so that certain starts and ambiguous stretches both occur; plus a problem
+    made of one long chain of rows each within the precision of its predecessor (the worst case for the cut into
+    stretches: one thread walks it all)."""
+    rng = np.random.default_rng(11)
+    big = make_problem(rng, 100_000, 8, 6000)
+
+    chain_rows = 3000
+    chain = np.zeros((chain_rows, 3))
+    chain[:, 0] = 0.3 + 6e-9 * np.arange(chain_rows)       # 6e-9 < precision between neighbours, drifting far over the chain
+    chain[:, 2] = 0.2
+    chain_problem = (chain, np.full(chain_rows, 0.01), np.ones(chain_rows))
+
+    problems = [big, chain_problem]
+    row_class, n_classes, class_rep, class_count = ctx.collapse(*to_csr(problems))
+
+    r0 = c0 = 0
+    for p, (mat, noise, counts) in enumerate(problems):
+        rows = mat.shape[0]
+        n, out, cnt, cls = oracle_collapse(port, mat, noise, counts)
+        assert n_classes[p] == n
+        assert np.array_equal(row_class[r0:r0 + rows], cls), f"problem {p}: partition / class order differs"
+        assert np.array_equal(class_count[c0:c0 + n], cnt)
+        r0 += rows
+        c0 += n
+    assert n_classes[0] > 5000 and 100 < n_classes[1] < chain_rows
