@@ -320,24 +320,30 @@ __global__ void __launch_bounds__(kBoundedThreads) pairHeadMaxKernel(const Bound
     }
 }
 
-__global__ void __launch_bounds__(kBoundedThreads) boundedScanKernel(const BoundedArgs args) {
+constexpr int kScanThreads = 1024;
+constexpr uint32_t kScanItems = 4;   // consecutive pairs per thread and round
 
-    __shared__ double warp_max[kBoundedThreads / 32];
+// One CTA per cluster: exclusive prefix maximum in pair order, the test against it, compaction of the pairs that pass.
+// A round takes 4096 pairs (four consecutive ones per thread: a cluster of 5,000 groups has 12.5 M of them).
+__global__ void __launch_bounds__(kScanThreads) boundedScanKernel(const BoundedArgs args) {
+
+    __shared__ double warp_max[kScanThreads / 32];
+    __shared__ uint32_t warp_count[kScanThreads / 32];
     __shared__ double carry;
-    __shared__ uint32_t warp_count[kBoundedThreads / 32];
     __shared__ uint32_t kept_total;
 
     const uint32_t c = blockIdx.x;
     const uint32_t tid = threadIdx.x;
     const uint32_t lane = tid & 31;
     const uint32_t warp = tid >> 5;
-    constexpr uint32_t num_warps = kBoundedThreads / 32;
+    constexpr uint32_t num_warps = kScanThreads / 32;
 
     const uint64_t p0 = args.pair_offset[c];
-    const uint32_t n_pairs = static_cast<uint32_t>(args.pair_offset[c + 1] - p0);
+    const uint64_t n_pairs = args.pair_offset[c + 1] - p0;
 
     double * pair_ll = args.pair_ll + p0;
     double * raw = args.cand_loglik + p0;   // raw sums of all pairs first, compacted in place
+    uint32_t * cand_pair = args.cand_pair + p0;
 
     if (tid == 0) {
         carry = -DBL_MAX;
@@ -345,53 +351,76 @@ __global__ void __launch_bounds__(kBoundedThreads) boundedScanKernel(const Bound
     }
     __syncthreads();
 
-    // ---- exclusive prefix maximum in pair order, test, compaction (tiles of kBoundedThreads pairs)
-    uint32_t * cand_pair = args.cand_pair + p0;
+    for (uint64_t base = 0; base < n_pairs; base += kScanThreads * kScanItems) {
 
-    for (uint32_t base = 0; base < n_pairs; base += kBoundedThreads) {
+        const uint64_t first = base + static_cast<uint64_t>(tid) * kScanItems;
 
-        const uint32_t p = base + tid;
-        const double ll = p < n_pairs ? pair_ll[p] : -DBL_MAX;
-        const double raw_value = p < n_pairs ? raw[p] : 0.0;
+        double ll[kScanItems], raw_value[kScanItems];
+        #pragma unroll
+        for (uint32_t i = 0; i < kScanItems; ++i) {
+            const uint64_t p = first + i;
+            ll[i] = p < n_pairs ? pair_ll[p] : -DBL_MAX;
+            raw_value[i] = p < n_pairs ? raw[p] : 0.0;
+        }
 
-        // inclusive max within the warp, then across warps
-        double incl = ll;
+        // maximum of this thread's pairs, exclusive scan of the maxima over the warp and the warps before it
+        double mine = ll[0];
+        #pragma unroll
+        for (uint32_t i = 1; i < kScanItems; ++i) { mine = fmax(mine, ll[i]); }
+
+        double incl = mine;
         #pragma unroll
         for (int off = 1; off < 32; off <<= 1) {
             const double up = __shfl_up_sync(0xffffffffu, incl, off);
             if (lane >= off) { incl = fmax(incl, up); }
         }
-        double excl = __shfl_up_sync(0xffffffffu, incl, 1);
-        if (lane == 0) { excl = -DBL_MAX; }
+        double before = __shfl_up_sync(0xffffffffu, incl, 1);
+        if (lane == 0) { before = -DBL_MAX; }
 
         if (lane == 31) { warp_max[warp] = incl; }
         __syncthreads();
 
-        double before = carry;
+        before = fmax(before, carry);
         for (uint32_t w = 0; w < warp; ++w) { before = fmax(before, warp_max[w]); }
-        excl = fmax(excl, before);
 
-        const bool keep = p < n_pairs && !(ll - excl < args.min_log_diff);
-
-        const uint32_t ballot = __ballot_sync(0xffffffffu, keep);
-        if (lane == 0) { warp_count[warp] = __popc(ballot); }
-        __syncthreads();
-
-        uint32_t offset = kept_total;
-        for (uint32_t w = 0; w < warp; ++w) { offset += warp_count[w]; }
-        offset += __popc(ballot & ((1u << lane) - 1));
-
-        __syncthreads();   // all reads of raw[] / carry / kept_total of this tile are done
-
-        if (keep) {
-            cand_pair[offset] = p;
-            raw[offset] = raw_value;   // offset <= p: never overwrites a value a later tile still needs
+        // the test, pair by pair, against everything before the pair
+        bool keep[kScanItems];
+        uint32_t n_keep = 0;
+        #pragma unroll
+        for (uint32_t i = 0; i < kScanItems; ++i) {
+            keep[i] = (first + i < n_pairs) && !(ll[i] - before < args.min_log_diff);
+            n_keep += keep[i] ? 1 : 0;
+            before = fmax(before, ll[i]);
         }
 
-        if (tid == kBoundedThreads - 1) {
-            double tile_max = carry;
-            for (uint32_t w = 0; w < num_warps; ++w) { tile_max = fmax(tile_max, warp_max[w]); }
-            carry = tile_max;
+        uint32_t count_incl = n_keep;
+        #pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t up = __shfl_up_sync(0xffffffffu, count_incl, off);
+            if (lane >= off) { count_incl += up; }
+        }
+
+        if (lane == 31) { warp_count[warp] = count_incl; }
+        __syncthreads();   // (also: all reads of raw[] / carry / kept_total of this round are done)
+
+        uint32_t offset = kept_total + count_incl - n_keep;
+        for (uint32_t w = 0; w < warp; ++w) { offset += warp_count[w]; }
+
+        __syncthreads();
+
+        #pragma unroll
+        for (uint32_t i = 0; i < kScanItems; ++i) {
+            if (keep[i]) {
+                cand_pair[offset] = static_cast<uint32_t>(first + i);
+                raw[offset] = raw_value[i];   // offset <= pair index: never overwrites a value a later round still needs
+                ++offset;
+            }
+        }
+
+        if (tid == kScanThreads - 1) {
+            double round_max = carry;
+            for (uint32_t w = 0; w < num_warps; ++w) { round_max = fmax(round_max, warp_max[w]); }
+            carry = round_max;
             uint32_t total = kept_total;
             for (uint32_t w = 0; w < num_warps; ++w) { total += warp_count[w]; }
             kept_total = total;
@@ -636,7 +665,7 @@ extern "C" int rpvg_b200_grouped_bounded_pairs(rpvg_b200_ctx * ctx, rpvg_b200_gr
             run_wave(tiles);
 
             if (err == cudaSuccess) {
-                boundedScanKernel<<<C, kBoundedThreads, 0, s>>>(args);
+                boundedScanKernel<<<C, kScanThreads, 0, s>>>(args);
                 ctx->launches++;
                 err = cudaGetLastError();
             }
