@@ -43,7 +43,7 @@ struct StreamArgs {
     double * low_partial;    // [grid] mass below min_em_abundance (final pass)
 };
 
-__global__ void __launch_bounds__(kStreamThreads, 3) emStreamKernel(const StreamArgs sa) {
+__global__ void __launch_bounds__(kStreamThreads, 2) emStreamKernel(const StreamArgs sa) {
 
     __shared__ double red[32];
     __shared__ double product_area[kStreamThreads / 32][kStreamStep];
@@ -139,15 +139,34 @@ __global__ void __launch_bounds__(kStreamThreads, 3) emStreamKernel(const Stream
         // of the row-major arrays: the lanes load it together, 128 entries a step — fully coalesced, every load independent
         // of the row offsets — multiply by the gathered abundances and park the products in shared memory; then every lane
         // adds up the products of its own read class, in entry order (the order a sequential loop over the row has).
-        for (uint32_t tile = row_lo + warp * 32; tile < row_hi; tile += (kStreamThreads / 32) * 32) {
+        // (the next tile's offsets, noise and count are loaded while this tile is worked on; the entry arrays are read
+        // once per iteration and marked streaming, so that they do not push a and w out of the L2)
+        constexpr uint32_t kTileStride = (kStreamThreads / 32) * 32;
+
+        uint32_t tile = row_lo + warp * 32;
+        uint64_t begin = 0, end = 0;
+        double nz = 0, ct = 0;
+        if (tile + lane < row_hi) {
+            begin = row_ptr[tile + lane];
+            end = row_ptr[tile + lane + 1];
+            nz = noise[tile + lane];
+            ct = cnt[tile + lane];
+        }
+
+        for (; tile < row_hi; tile += kTileStride) {
 
             const uint32_t i = tile + lane;
             const bool live = i < row_hi;
 
-            const uint64_t begin = live ? row_ptr[i] : 0;
-            const uint64_t end = live ? row_ptr[i + 1] : 0;
-            const double nz = live ? noise[i] : 0.0;
-            const double ct = live ? cnt[i] : 0.0;
+            const uint32_t next = i + kTileStride;
+            uint64_t next_begin = 0, next_end = 0;
+            double next_nz = 0, next_ct = 0;
+            if (next < row_hi) {
+                next_begin = row_ptr[next];
+                next_end = row_ptr[next + 1];
+                next_nz = noise[next];
+                next_ct = cnt[next];
+            }
 
             const uint32_t last = min(31u, row_hi - 1 - tile);
             const uint64_t tile_begin = __shfl_sync(0xffffffffu, begin, 0);
@@ -157,11 +176,25 @@ __global__ void __launch_bounds__(kStreamThreads, 3) emStreamKernel(const Stream
 
             for (uint64_t step = tile_begin; step < tile_end; step += kStreamStep) {
 
+                // all loads of the step first, then all gathers: the lanes past the end repeat the last entry (their
+                // products are never added)
+                double v[kStreamStep / 32];
+                uint32_t x[kStreamStep / 32];
+
                 #pragma unroll
                 for (uint32_t u = 0; u < kStreamStep / 32; ++u) {
-                    const uint64_t e = step + u * 32 + lane;
-                    if (e < tile_end) { products[u * 32 + lane] = args.val[e] * a[args.col[e]]; }
+                    const uint64_t e = min(step + u * 32 + lane, tile_end - 1);
+                    v[u] = __ldcs(args.val + e);
+                    x[u] = __ldcs(args.col + e);
                 }
+
+                double g[kStreamStep / 32];
+
+                #pragma unroll
+                for (uint32_t u = 0; u < kStreamStep / 32; ++u) { g[u] = a[x[u]]; }
+
+                #pragma unroll
+                for (uint32_t u = 0; u < kStreamStep / 32; ++u) { products[u * 32 + lane] = v[u] * g[u]; }
 
                 __syncwarp();
 
@@ -177,6 +210,11 @@ __global__ void __launch_bounds__(kStreamThreads, 3) emStreamKernel(const Stream
                 w[i] = wi;
                 noise_acc += nz * wi;
             }
+
+            begin = next_begin;
+            end = next_end;
+            nz = next_nz;
+            ct = next_ct;
         }
 
         const double cta_noise = blockSum(noise_acc, red);
@@ -201,7 +239,7 @@ __global__ void __launch_bounds__(kStreamThreads, 3) emStreamKernel(const Stream
                 const uint64_t k1 = col_ptr[j + 1];
                 double gsum = 0;
                 #pragma unroll 4
-                for (uint64_t k = col_ptr[j] + lane; k < k1; k += 32) { gsum += args.csc_val[k] * w[args.csc_row[k]]; }
+                for (uint64_t k = col_ptr[j] + lane; k < k1; k += 32) { gsum += __ldcs(args.csc_val + k) * w[__ldcs(args.csc_row + k)]; }
                 gsum = warpSum(gsum);
 
                 if (lane == 0) {
@@ -226,7 +264,7 @@ __global__ void __launch_bounds__(kStreamThreads, 3) emStreamKernel(const Stream
                 if (live) {
                     const uint64_t k1 = col_ptr[j + 1];
                     #pragma unroll 4
-                    for (uint64_t k = col_ptr[j] + sub; k < k1; k += 8) { gsum += args.csc_val[k] * w[args.csc_row[k]]; }
+                    for (uint64_t k = col_ptr[j] + sub; k < k1; k += 8) { gsum += __ldcs(args.csc_val + k) * w[__ldcs(args.csc_row + k)]; }
                 }
 
                 gsum += __shfl_xor_sync(0xffffffffu, gsum, 4);

@@ -224,25 +224,43 @@ void PathClusterEstimates::resetEstimates(uint32_t num_components, const uint32_
 #endif
 
 // Callers of estimate() that found the device busy. One mutex: a request is two pointers, the queue is touched for
-// nanoseconds around device calls of hundreds of microseconds.
+// nanoseconds around device calls of hundreds of microseconds. Up to kLeaders batches are under way at a time, each on
+// its own context: the host stages of one overlap the device time of another, and a batch that holds one slowly
+// converging cluster does not keep every caller waiting (RPVG_B200_COMBINE_SLOTS, default 3).
 struct PathEstimator::Combiner {
 
     struct Request {
         PathClusterEstimates * estimates;
         const vector<ReadPathProbabilities> * cluster_probs;
         mt19937 * rng;
+        bool taken = false;   // a leader has it in its batch
         bool done = false;
     };
+
+    static constexpr size_t kMaxSlots = 8;
 
     mutex lock;
     condition_variable wake;
     vector<Request *> waiting;
-    bool device_busy = false;
     const bool enabled;
-    rpvg_b200_ctx * shared_ctx = nullptr;
+    size_t n_slots = 3;
+    bool slot_busy[kMaxSlots] = {false, false, false, false, false, false, false, false};
+    rpvg_b200_ctx * slot_ctx[kMaxSlots] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 
-    Combiner() : enabled(!(getenv("RPVG_B200_COMBINE") && string(getenv("RPVG_B200_COMBINE")) == "0")) {}
-    ~Combiner() { if (shared_ctx) { rpvg_b200_destroy(shared_ctx); } }
+    Combiner() : enabled(!(getenv("RPVG_B200_COMBINE") && string(getenv("RPVG_B200_COMBINE")) == "0")) {
+        if (const char * v = getenv("RPVG_B200_COMBINE_SLOTS")) { n_slots = min<size_t>(kMaxSlots, max<size_t>(1, strtoul(v, nullptr, 10))); }
+    }
+
+    ~Combiner() {
+        for (auto ctx: slot_ctx) { if (ctx) { rpvg_b200_destroy(ctx); } }
+    }
+
+    // (under the lock) index of a free slot, or n_slots
+    size_t freeSlot() const {
+        size_t k = 0;
+        while (k < n_slots && slot_busy[k]) { ++k; }
+        return k;
+    }
 };
 
 PathEstimator::PathEstimator(const double prob_precision_in) : combiner(new Combiner()), prob_precision(prob_precision_in) {}
@@ -266,21 +284,23 @@ void PathEstimator::estimate(PathClusterEstimates * path_cluster_estimates, cons
 
     for (;;) {
 
-        // until somebody has done this request, or the device is free and this thread does the waiting ones itself
-        combiner->wake.wait(guard, [&]() { return mine.done || !combiner->device_busy; });
+        // until somebody has done this request, or a slot is free and this thread does the waiting ones itself
+        combiner->wake.wait(guard, [&]() { return mine.done || (!mine.taken && combiner->freeSlot() < combiner->n_slots); });
         if (mine.done) { return; }
 
-        combiner->device_busy = true;
+        const size_t slot = combiner->freeSlot();
+        combiner->slot_busy[slot] = true;
 
         vector<Combiner::Request *> batch;
-        batch.swap(combiner->waiting);   // this thread's request is among them: it was queued before the wait
+        batch.swap(combiner->waiting);   // this thread's request is among them: queued before the wait, taken by nobody
+        for (auto request: batch) { request->taken = true; }
 
         guard.unlock();
 
-        // One context serves all combined calls (only one thread is ever in here): the calling threads need none of
-        // their own.
-        if (!combiner->shared_ctx) {
-            const int status = rpvg_b200_create(threadDevice(), nullptr, &combiner->shared_ctx);
+        // One context per slot serves all combined calls (only one thread is ever in a slot): the calling threads need
+        // none of their own.
+        if (!combiner->slot_ctx[slot]) {
+            const int status = rpvg_b200_create(threadDevice(), nullptr, &combiner->slot_ctx[slot]);
             if (status != RPVG_B200_OK) {
                 cerr << "ERROR: rpvg_b200_create(device " << threadDevice() << ") failed with status " << status << " (a CUDA device is required; there is no CPU fallback)" << endl;
                 abort();
@@ -288,7 +308,7 @@ void PathEstimator::estimate(PathClusterEstimates * path_cluster_estimates, cons
         }
 
         rpvg_b200_ctx * previous = contextOverride();
-        contextOverride() = combiner->shared_ctx;
+        contextOverride() = combiner->slot_ctx[slot];
 
         if (batch.size() == 1) {
 
@@ -314,7 +334,7 @@ void PathEstimator::estimate(PathClusterEstimates * path_cluster_estimates, cons
         guard.lock();
 
         for (auto request: batch) { request->done = true; }
-        combiner->device_busy = false;
+        combiner->slot_busy[slot] = false;
         combiner->wake.notify_all();
     }
 }

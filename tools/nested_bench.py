@@ -1,6 +1,8 @@
 """Inference-stage wall time of the haplotype-transcripts model (config-1-like synthetic clusters) through the SAME harness
 source compiled against the reference's classes (CPU, oracle/_ref) and against this repository's drop-in classes (GPU).
-python tools/nested_bench.py [n_clusters] [threads]"""
+python tools/nested_bench.py [n_clusters] [threads]
+RPVG_BENCH_GPU_THREADS="16,64,256": caller threads of the per-cluster estimate() loop on the GPU classes (they block while
+the device works, so more of them than cores is how a per-cluster interface keeps the device fed)."""
 import os, sys, time
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -41,12 +43,16 @@ results = None
 for name, lib_ in (("reference classes (CPU)", loader.reference()), ("rpvg_b200 classes (GPU)", b200)):
     if lib_ is None or batch_only:
         continue
-    best = None
-    for rep in range(2):
-        secs, results = loader.harness_estimate_batch(lib_, cfg, arena, rng_seed=1, num_threads=threads)
-        best = secs if best is None else min(best, secs)
-    n_sets = sum(len(r["sets"]) for r in results)
-    print(f"{name}: {best * 1e3:.1f} ms for {n_clusters} clusters with {threads} threads = {n_clusters / best:.0f} clusters/s ({n_sets} output tuples)", flush=True)
+    counts = [threads]
+    if lib_ is b200 and os.environ.get("RPVG_BENCH_GPU_THREADS"):
+        counts = [int(x) for x in os.environ["RPVG_BENCH_GPU_THREADS"].split(",")]
+    for n_threads in counts:
+        best = None
+        for rep in range(2):
+            secs, results = loader.harness_estimate_batch(lib_, cfg, arena, rng_seed=1, num_threads=n_threads)
+            best = secs if best is None else min(best, secs)
+        n_sets = sum(len(r["sets"]) for r in results)
+        print(f"{name}: {best * 1e3:.1f} ms for {n_clusters} clusters with {n_threads} threads = {n_clusters / best:.0f} clusters/s ({n_sets} output tuples)", flush=True)
 
 best = None
 for rep in range(3):
