@@ -587,8 +587,7 @@ int rpvgEmInit(rpvg_b200_ctx * ctx) {
     {
         int cooperative = 0, per_sm = 0;
         cudaDeviceGetAttribute(&cooperative, cudaDevAttrCooperativeLaunch, ctx->device);
-        if (cooperative && cudaFuncSetAttribute(emStreamKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kStreamSmemBytes)) == cudaSuccess &&
-            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, emStreamKernel, kStreamThreads, kStreamSmemBytes) == cudaSuccess && per_sm > 0) {
+        if (cooperative && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, emStreamKernel, kStreamThreads, 0) == cudaSuccess && per_sm > 0) {
             ctx->stream_grid = std::min<uint32_t>(kStreamMaxCtas, static_cast<uint32_t>(std::min(per_sm, 4) * ctx->num_sms));
         }
         cudaGetLastError();
@@ -916,7 +915,7 @@ static int batchEmLaunch(rpvg_b200_ctx * ctx, rpvg_b200_batch * b, const rpvg_b2
             sargs.flags = b->d_stream_flags;
 
             void * kernel_args[] = {&sargs};
-            RPVG_CUDA(ctx, cudaLaunchCooperativeKernel(reinterpret_cast<void *>(emStreamKernel), dim3(ctx->stream_grid), dim3(kStreamThreads), kernel_args, kStreamSmemBytes, s));
+            RPVG_CUDA(ctx, cudaLaunchCooperativeKernel(reinterpret_cast<void *>(emStreamKernel), dim3(ctx->stream_grid), dim3(kStreamThreads), kernel_args, 0, s));
             RPVG_LAUNCHED(ctx);
         }
     }

@@ -6,12 +6,10 @@
 // persistent grid, the read classes and the paths each cut into one contiguous range per CTA of about equal entries,
 // two grid-wide barriers per iteration:
 //
-//   E-step  rows of the CTA's range, cut once more into one contiguous range per warp. The entries of a warp's rows are ONE
-//           contiguous stretch of the row-major arrays: the warp streams it through a ring of shared-memory stages with
-//           asynchronous 16-byte copies (128 entries a stage, three stages always under way, whatever the rows look
-//           like), multiplies a landed stage by the gathered abundances in place, and every lane sums its own read class
-//           in entry order, 32 read classes at a time: w_i = count_i / (sum_j p_ij a_j + noise_i a_noise) into global
-//           memory; the CTA's share of sum_i noise_i w_i into partial[cta]
+//   E-step  rows of the CTA's range, 32 read classes per warp at a time: the warp loads their (contiguous) entries
+//           together, coalesced, 128 per step, the products go through shared memory and every lane sums its own read
+//           class in entry order: w_i = count_i / (sum_j p_ij a_j + noise_i a_noise) into global memory; the CTA's share of
+//           sum_i noise_i w_i into partial[cta]
 //   grid barrier
 //   M-step  columns of the CTA's range, 8 lanes per path over the column-major copy: a_j <- a_j * sum_i p_ij w_i / total
 //           in place (the E-step is over); every CTA adds partial[] up in the same order and gets the same noise
@@ -34,27 +32,7 @@
 
 constexpr int kStreamThreads = 512;
 constexpr uint32_t kStreamMaxCtas = 2048;
-constexpr uint32_t kStreamStep = 128;   // entries of one stage of a warp's ring
-constexpr uint32_t kStreamStages = 4;
-
-// One stage: 128 entries of the row-major arrays, aligned on a multiple of 128 entries (16-byte copies)
-struct alignas(16) StreamStage {
-    double val[kStreamStep];
-    uint32_t col[kStreamStep];
-};
-
-constexpr size_t kStreamSmemBytes = sizeof(StreamStage) * kStreamStages * (kStreamThreads / 32);
-
-// 16 bytes global -> shared without a register in between; bytes < 16: the rest is filled with zeros, 0: nothing is read
-__device__ __forceinline__ void streamCopy16(void * dst, const void * src, uint32_t bytes) {
-    const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(dst));
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(d), "l"(src), "r"(bytes) : "memory");
-}
-
-__device__ __forceinline__ void streamCommit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-
-template <int N>
-__device__ __forceinline__ void streamWait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
+constexpr uint32_t kStreamStep = 128;   // entries a warp multiplies per step of the E-step
 
 struct StreamArgs {
 
@@ -68,7 +46,7 @@ struct StreamArgs {
 __global__ void __launch_bounds__(kStreamThreads, 2) emStreamKernel(const StreamArgs sa) {
 
     __shared__ double red[32];
-    extern __shared__ __align__(16) unsigned char stream_smem[];
+    __shared__ double product_area[kStreamThreads / 32][kStreamStep];
 
     namespace cg = cooperative_groups;
     cg::grid_group grid = cg::this_grid();
@@ -78,7 +56,7 @@ __global__ void __launch_bounds__(kStreamThreads, 2) emStreamKernel(const Stream
     const uint32_t tid = threadIdx.x;
     const uint32_t lane = tid & 31;
     const uint32_t warp = tid >> 5;
-    StreamStage * ring = reinterpret_cast<StreamStage *>(stream_smem) + warp * kStreamStages;
+    double * products = product_area[warp];
     const uint32_t cta = blockIdx.x;
     const uint32_t n_ctas = gridDim.x;
 
@@ -125,56 +103,6 @@ __global__ void __launch_bounds__(kStreamThreads, 2) emStreamKernel(const Stream
         col_hi = split(col_ptr, N, k0, Z + N, cta + 1, n_ctas);
     }
 
-    // ---- rows of this warp: the CTA's range cut the same way; their entries are the stretch [E0, E1) of the arrays
-    uint32_t wrow_lo, wrow_hi;
-    {
-        constexpr uint32_t num_warps = kStreamThreads / 32;
-        const uint32_t n = row_hi - row_lo;
-        const uint64_t base = row_ptr[row_lo];
-        const uint64_t total = (row_ptr[row_hi] - base) + n;
-
-        auto cut = [&](uint32_t part) {
-            if (part == 0) { return 0u; }
-            if (part >= num_warps) { return n; }
-            const uint64_t target = (total * part) / num_warps;
-            uint32_t lo = 0, hi = n;
-            while (lo < hi) {
-                const uint32_t mid = (lo + hi) >> 1;
-                if ((row_ptr[row_lo + mid] - base) + mid >= target) { hi = mid; } else { lo = mid + 1; }
-            }
-            return lo;
-        };
-        wrow_lo = row_lo + cut(warp);
-        wrow_hi = row_lo + cut(warp + 1);
-    }
-
-    const uint64_t E0 = row_ptr[wrow_lo];
-    const uint64_t E1 = row_ptr[wrow_hi];
-    const uint64_t cluster_end = e0 + Z;
-    const uint64_t first_block = E0 & ~static_cast<uint64_t>(kStreamStep - 1);
-    const uint32_t n_blocks = E1 > E0 ? static_cast<uint32_t>((E1 - first_block + kStreamStep - 1) / kStreamStep) : 0;
-
-    // stage `slot` <- the 128 entries from `b` on (a multiple of 128: both arrays are read in aligned 16-byte pieces; what
-    // lies before E0 or after E1 belongs to somebody else and is masked when the stage is used, what lies after the
-    // cluster's last entry is not read)
-    auto issue = [&](uint64_t b, uint32_t slot) {
-
-        StreamStage & st = ring[slot];
-
-        #pragma unroll
-        for (uint32_t u = 0; u < 2; ++u) {
-            const uint32_t q = u * 32 + lane;
-            const uint64_t e = b + 2 * q;
-            const uint32_t bytes = e + 2 <= cluster_end ? 16u : (e < cluster_end ? 8u : 0u);
-            streamCopy16(st.val + 2 * q, args.val + (bytes ? e : b), bytes);
-        }
-        {
-            const uint64_t e = b + 4 * lane;
-            const uint32_t bytes = e + 4 <= cluster_end ? 16u : (e < cluster_end ? 4u * static_cast<uint32_t>(cluster_end - e) : 0u);
-            streamCopy16(st.col + 4 * lane, args.col + (bytes ? e : b), bytes);
-        }
-    };
-
     // ---- total read count: every CTA sums its own rows, then all add the partial sums in the same order (counts are
     // integers: the sum is exact whatever the order)
     double count_sum = 0;
@@ -211,113 +139,83 @@ __global__ void __launch_bounds__(kStreamThreads, 2) emStreamKernel(const Stream
         // of the row-major arrays: the lanes load it together, 128 entries a step — fully coalesced, every load independent
         // of the row offsets — multiply by the gathered abundances and park the products in shared memory; then every lane
         // adds up the products of its own read class, in entry order (the order a sequential loop over the row has).
-        // (the arrays are read once per iteration and go past the L1; a and w stay in the L2)
-        #pragma unroll
-        for (uint32_t p = 0; p + 1 < kStreamStages; ++p) {
-            if (p < n_blocks) { issue(first_block + static_cast<uint64_t>(p) * kStreamStep, p); }
-            streamCommit();
+        // (the next tile's offsets, noise and count are loaded while this tile is worked on; the entry arrays are read
+        // once per iteration and marked streaming, so that they do not push a and w out of the L2)
+        constexpr uint32_t kTileStride = (kStreamThreads / 32) * 32;
+
+        uint32_t tile = row_lo + warp * 32;
+        uint64_t begin = 0, end = 0;
+        double nz = 0, ct = 0;
+        if (tile + lane < row_hi) {
+            begin = row_ptr[tile + lane];
+            end = row_ptr[tile + lane + 1];
+            nz = noise[tile + lane];
+            ct = cnt[tile + lane];
         }
 
-        // the 32 read classes under way (lane = read class), and the 32 after them, loaded ahead
-        uint32_t group = wrow_lo;
-        uint64_t begin = 0, end = 0, next_begin = 0, next_end = 0;
-        double nz = 0, ct = 0, next_nz = 0, next_ct = 0;
+        for (; tile < row_hi; tile += kTileStride) {
 
-        if (group + lane < wrow_hi) {
-            begin = row_ptr[group + lane];
-            end = row_ptr[group + lane + 1];
-            nz = noise[group + lane];
-            ct = cnt[group + lane];
-        }
-        if (group + 32 + lane < wrow_hi) {
-            next_begin = row_ptr[group + 32 + lane];
-            next_end = row_ptr[group + 32 + lane + 1];
-            next_nz = noise[group + 32 + lane];
-            next_ct = cnt[group + 32 + lane];
-        }
+            const uint32_t i = tile + lane;
+            const bool live = i < row_hi;
 
-        double s = 0;
+            const uint32_t next = i + kTileStride;
+            uint64_t next_begin = 0, next_end = 0;
+            double next_nz = 0, next_ct = 0;
+            if (next < row_hi) {
+                next_begin = row_ptr[next];
+                next_end = row_ptr[next + 1];
+                next_nz = noise[next];
+                next_ct = cnt[next];
+            }
 
-        // closes the group under way (all its entries are in) and moves on to the next one
-        auto finish_group = [&]() {
+            const uint32_t last = min(31u, row_hi - 1 - tile);
+            const uint64_t tile_begin = __shfl_sync(0xffffffffu, begin, 0);
+            const uint64_t tile_end = __shfl_sync(0xffffffffu, end, last);
 
-            if (group + lane < wrow_hi) {
+            double s = 0;
+
+            for (uint64_t step = tile_begin; step < tile_end; step += kStreamStep) {
+
+                // all loads of the step first, then all gathers: the lanes past the end repeat the last entry (their
+                // products are never added)
+                double v[kStreamStep / 32];
+                uint32_t x[kStreamStep / 32];
+
+                #pragma unroll
+                for (uint32_t u = 0; u < kStreamStep / 32; ++u) {
+                    const uint64_t e = min(step + u * 32 + lane, tile_end - 1);
+                    v[u] = __ldcs(args.val + e);
+                    x[u] = __ldcs(args.col + e);
+                }
+
+                double g[kStreamStep / 32];
+
+                #pragma unroll
+                for (uint32_t u = 0; u < kStreamStep / 32; ++u) { g[u] = a[x[u]]; }
+
+                #pragma unroll
+                for (uint32_t u = 0; u < kStreamStep / 32; ++u) { products[u * 32 + lane] = v[u] * g[u]; }
+
+                __syncwarp();
+
+                const uint64_t from = max(begin, step);
+                const uint64_t to = min(end, step + kStreamStep);
+                for (uint64_t e = from; e < to; ++e) { s += products[e - step]; }
+
+                __syncwarp();
+            }
+
+            if (live) {
                 const double wi = ct / (s + nz * a_noise);
-                w[group + lane] = wi;
+                w[i] = wi;
                 noise_acc += nz * wi;
             }
 
-            group += 32;
             begin = next_begin;
             end = next_end;
             nz = next_nz;
             ct = next_ct;
-            s = 0;
-
-            next_begin = next_end = 0;
-            next_nz = next_ct = 0;
-            if (group + 32 + lane < wrow_hi) {
-                next_begin = row_ptr[group + 32 + lane];
-                next_end = row_ptr[group + 32 + lane + 1];
-                next_nz = noise[group + 32 + lane];
-                next_ct = cnt[group + 32 + lane];
-            }
-        };
-
-        for (uint32_t k = 0; k < n_blocks; ++k) {
-
-            // (the stage refilled here was used up in the previous round)
-            if (k + kStreamStages - 1 < n_blocks) { issue(first_block + static_cast<uint64_t>(k + kStreamStages - 1) * kStreamStep, (k + kStreamStages - 1) % kStreamStages); }
-            streamCommit();
-            streamWait<kStreamStages - 1>();
-            __syncwarp();
-
-            StreamStage & st = ring[k % kStreamStages];
-            const uint64_t bs = first_block + static_cast<uint64_t>(k) * kStreamStep;
-            const uint64_t be = min(bs + kStreamStep, E1);
-
-            // products in place: all gathers of the stage under way together
-            double v[kStreamStep / 32];
-            uint32_t x[kStreamStep / 32];
-
-            #pragma unroll
-            for (uint32_t u = 0; u < kStreamStep / 32; ++u) {
-                const uint64_t e = bs + u * 32 + lane;
-                const bool mine = e >= E0 && e < E1;
-                x[u] = mine ? st.col[u * 32 + lane] : 0u;
-                v[u] = mine ? st.val[u * 32 + lane] : 0.0;
-            }
-
-            double g[kStreamStep / 32];
-
-            #pragma unroll
-            for (uint32_t u = 0; u < kStreamStep / 32; ++u) { g[u] = a[x[u]]; }
-
-            #pragma unroll
-            for (uint32_t u = 0; u < kStreamStep / 32; ++u) { st.val[u * 32 + lane] = v[u] * g[u]; }
-
-            __syncwarp();
-
-            // every lane adds the products of its own read class, in entry order; a group whose last entry is in this
-            // stage is closed, the next one may begin in the same stage
-            while (group < wrow_hi) {
-
-                const uint64_t from = max(begin, bs);
-                const uint64_t to = min(end, be);
-                for (uint64_t e = from; e < to; ++e) { s += st.val[e - bs]; }
-
-                const uint32_t last = min(31u, wrow_hi - 1 - group);
-                const uint64_t group_end = __shfl_sync(0xffffffffu, end, last);
-                if (group_end > be) { break; }
-
-                finish_group();
-            }
-
-            __syncwarp();
         }
-
-        // (read classes without entries after the warp's last entry, or a range without any entry)
-        while (group < wrow_hi) { finish_group(); }
 
         const double cta_noise = blockSum(noise_acc, red);
         if (tid == 0) { sa.partial[cta] = cta_noise; }
