@@ -13,9 +13,15 @@
 // triangle of tiles only) and, when the tiles alone would not fill the GPU, into row ranges as well; one 256-thread CTA per
 // (tile, row range). The CTA stages the 64 columns of its tile 32 read classes at a time in shared memory (coalesced
 // column reads, 0.5 B of L2 traffic per log) and every thread owns 4 pairs: one column read serves 32 pairs, and the
-// kernel is bound by the fp64 log, not by memory. Sums run over the read classes in order, 32 at a time,
-// the partial sums added with compensation: the result is within an ulp or two of the exact sum whatever the number of
-// read classes (the reference's own Eigen reduction is no closer), and deterministic.
+// kernel is bound by arithmetic, not by memory. A log per term is what the reference spends
+// (G (G + 1) / 2 x M of them); here sum_r count_r log(x_r) is taken as log(prod_r x_r^count_r): every x_r is split into
+// exponent and mantissa (integer operations), the exponents are added as integers (exact), the mantissas in [1, 2)
+// multiplied into a running product that is renormalised every 32 read classes, and ONE log is taken per pair and row
+// range at the end: ll = ln2 * (sum of exponents) + log(product). The product of n mantissas carries a relative error of
+// at most n x 1.1e-16 (1.8e-12 for 16,384 read classes, typically its square root), i.e. an absolute error on ll below
+// what one rounding of a sum of that size costs (ulp(1e5) = 1.5e-11). Read classes whose count is not an integer in
+// 1..31, and values that are zero, denormal or not finite, take the plain count * log(x) route (a row-uniform branch).
+// Deterministic.
 // Scan: boundedScanKernel, one CTA per cluster: exclusive prefix maximum in pair order, test, compaction.
 
 #include <cfloat>
@@ -62,23 +68,35 @@ __device__ __forceinline__ void pairOfIndex(const uint32_t G, const uint32_t ind
 
 constexpr uint32_t kPairTile = 32;        // pairs per tile side
 constexpr uint32_t kPairRowChunk = 32;    // read classes staged at a time
-constexpr int kPairThreads = 256;         // 32 first groups x 8 threads, each thread 4 second groups
+constexpr int kPairThreads = 128;         // 16 x 8 threads, each 2 first groups x 4 second groups
+constexpr uint32_t kPairMaxSplitRows = 16384;   // read classes per work item at most: the exponent sums are 32-bit (31 x 2046 x 16384 < 2^31)
 
 struct PairTileArgs {
 
     BoundedArgs b;
     const uint4 * items;               // work items: x = cluster, y = tile row | tile column << 16, z = row range, w = row ranges of the tile;
                                        // the row ranges of a tile are adjacent items
-    uint32_t rows_per_split;           // read classes per row range (multiple of kPairRowChunk)
+    uint32_t rows_per_split;           // read classes per row range (multiple of kPairRowChunk, at most kPairMaxSplitRows)
     double * partial;                  // [n_items x 1024] when rows are split, else NULL
-    unsigned long long * log_count;    // logs evaluated (for the roofline)
+    unsigned long long * log_count;    // terms evaluated (pairs x read classes: for the roofline)
 };
+
+// this thread's pairs: first groups i0 and i0 + 16, second groups j0, j0 + 8, j0 + 16, j0 + 24 (positions in `order`);
+// pair (a, q) of thread t sits at t * 8 + a * 4 + q of a tile's partial sums
+__device__ __forceinline__ void pairsOfThread(const uint32_t tid, const uint32_t ti, const uint32_t tj, uint32_t * i0, uint32_t * j0) {
+    *i0 = ti * kPairTile + (tid >> 3);
+    *j0 = tj * kPairTile + (tid & 7);
+}
 
 __global__ void __launch_bounds__(kPairThreads) pairTileKernel(const PairTileArgs args) {
 
-    __shared__ double col_s[2 * kPairTile][kPairRowChunk + 1];   // [column of the tile][read class]: 32 first, then 32 second groups
+    // [read class][column of the tile]: 32 first, then 32 second groups. A thread's four second groups lie 8 apart, so the
+    // eight threads that share its first groups read consecutive words: no bank conflicts (pitch 65).
+    __shared__ double col_s[kPairRowChunk][2 * kPairTile + 1];
     __shared__ double noise_s[kPairRowChunk];
     __shared__ double count_s[kPairRowChunk];
+    __shared__ uint32_t power_s[kPairRowChunk];
+    __shared__ uint32_t odd_s;
 
     const BoundedArgs & b = args.b;
 
@@ -105,58 +123,186 @@ __global__ void __launch_bounds__(kPairThreads) pairTileKernel(const PairTileArg
     const uint32_t row_begin = split * args.rows_per_split;
     const uint32_t row_end = min(rows, row_begin + args.rows_per_split);
 
-    // this thread's pairs: first group i, second groups j0 .. j0 + 3 (positions in `order`)
     const uint32_t li = tid >> 3;
-    const uint32_t lj = (tid & 7) * 4;
-    const uint32_t i = ti * kPairTile + li;
-    const uint32_t j0 = tj * kPairTile + lj;
+    const uint32_t lj = tid & 7;
+    uint32_t i0, j0;
+    pairsOfThread(tid, ti, tj, &i0, &j0);
 
-    double acc[4] = {0, 0, 0, 0};
-    double comp[4] = {0, 0, 0, 0};
+    // per pair: product of mantissas, sum of (biased) exponents, and the sum of the terms taken by log
+    double product[2][4];
+    int32_t exponent[2][4];
+    double slow[2][4];
+
+    #pragma unroll
+    for (uint32_t a = 0; a < 2; ++a) {
+        #pragma unroll
+        for (uint32_t q = 0; q < 4; ++q) {
+            product[a][q] = 1.0;
+            exponent[a][q] = 0;
+            slow[a][q] = 0;
+        }
+    }
+
+    // one term: x = m 2^e -> the exponent to the sum, the mantissa (in [1, 2)) into the product
+    auto take = [](const double prob, double * prod, int32_t * exp_sum) {
+        const int32_t hi = __double2hiint(prob);
+        *exp_sum += hi >> 20;
+        const double mantissa = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(prob));
+        *prod *= mantissa;
+        return mantissa;
+    };
+
+    if (tid == 0) { odd_s = 0; }
+    __syncthreads();
 
     for (uint32_t base = row_begin; base < row_end; base += kPairRowChunk) {
 
         const uint32_t n_chunk = min(kPairRowChunk, row_end - base);
 
+        // Kind of read class `lane`, and its place in the staged chunk: first the ones whose count is 1, then counts 2..31,
+        // then the ones that take a log — counts that are not small integers, and read classes whose noise is not a
+        // normal positive number (with it, noise + a / 2 + b / 2 is one as well for finite a, b >= 0: the fast loops need
+        // no test per term). Every warp works this out for itself.
+        const bool live = lane < n_chunk;
+        const double cnt = live ? counts[base + lane] : 0.0;
+        const double nz = live ? noise[base + lane] : 1.0;
+        const bool fast = live && cnt >= 1.0 && cnt <= 31.0 && cnt == floor(cnt) && nz >= DBL_MIN && nz <= DBL_MAX;
+        const bool once = fast && cnt == 1.0;
+
+        const uint32_t m_once = __ballot_sync(0xffffffffu, once);
+        const uint32_t m_more = __ballot_sync(0xffffffffu, fast && !once);
+        const uint32_t m_slow = __ballot_sync(0xffffffffu, live && !fast);
+        const uint32_t below = (1u << lane) - 1u;
+        const uint32_t n_once = __popc(m_once), n_more = __popc(m_more);
+
+        uint32_t slot = n_chunk + (lane - n_chunk);   // (lanes past the chunk keep their place)
+        if (once) { slot = __popc(m_once & below); }
+        else if (fast) { slot = n_once + __popc(m_more & below); }
+        else if (live) { slot = n_once + n_more + __popc(m_slow & below); }
+
+        const uint32_t power_total = __reduce_add_sync(0xffffffffu, fast ? static_cast<uint32_t>(cnt) : 0u);
+
         __syncthreads();   // the previous chunk has been consumed
 
-        // stage: warp w loads columns w, w + 8, ..: lane = read class (coalesced), padded rows against bank conflicts
+        // stage: warp w loads columns w, w + 4, ..: lane = read class (coalesced)
         for (uint32_t k = warp; k < 2 * kPairTile; k += kPairThreads / 32) {
             const uint32_t pos = (k < kPairTile ? ti * kPairTile + k : tj * kPairTile + (k - kPairTile));
             double v = 0;
-            if (pos < G && lane < n_chunk) { v = matrix[static_cast<uint64_t>(order[pos]) * rows + base + lane]; }
-            col_s[k][lane] = v;
+            if (pos < G && live) { v = matrix[static_cast<uint64_t>(order[pos]) * rows + base + lane]; }
+            col_s[slot][k] = v;
+            // (anything but a finite value >= 0: from here on this CTA takes the log of every term, like the reference)
+            if (!(v >= 0.0 && v <= DBL_MAX)) { odd_s = 1; }
         }
-        if (tid < kPairRowChunk) {
-            noise_s[tid] = tid < n_chunk ? noise[base + tid] : 1.0;
-            count_s[tid] = tid < n_chunk ? counts[base + tid] : 0.0;   // padding rows add count 0 * log(1)
+        if (warp == 0) {
+            noise_s[slot] = nz;
+            count_s[slot] = cnt;
+            power_s[slot] = fast ? static_cast<uint32_t>(cnt) : 0u;
         }
 
         __syncthreads();
 
-        double sum[4] = {0, 0, 0, 0};
+        const bool odd = odd_s != 0;
+        const uint32_t n1 = odd ? 0u : n_once;
+        const uint32_t n2 = odd ? 0u : n_once + n_more;
 
+        // read classes seen once
         #pragma unroll 2
-        for (uint32_t r = 0; r < kPairRowChunk; ++r) {
+        for (uint32_t r = 0; r < n1; ++r) {
 
             // noise + col_first / 2 + col_second / 2, in the reference's order
-            const double first = noise_s[r] + col_s[li][r] / 2.0;
-            const double cnt = count_s[r];
+            const double nzr = noise_s[r];
+            const double first0 = nzr + col_s[r][li] / 2.0;
+            const double first1 = nzr + col_s[r][li + 16] / 2.0;
 
             #pragma unroll
             for (uint32_t q = 0; q < 4; ++q) {
-                const double prob = first + col_s[kPairTile + lj + q][r] / 2.0;
-                sum[q] = fma(cnt, log(prob), sum[q]);
+                const double second = col_s[r][kPairTile + lj + 8 * q];
+                take(first0 + second / 2.0, &product[0][q], &exponent[0][q]);
+                take(first1 + second / 2.0, &product[1][q], &exponent[1][q]);
             }
         }
 
-        // compensated addition of the chunk's sums
+        // read classes seen 2..31 times: x^count from the squares of the mantissa
+        for (uint32_t r = n1; r < n2; ++r) {
+
+            const uint32_t power = power_s[r];
+            const double nzr = noise_s[r];
+            const double first0 = nzr + col_s[r][li] / 2.0;
+            const double first1 = nzr + col_s[r][li + 16] / 2.0;
+
+            #pragma unroll
+            for (uint32_t q = 0; q < 4; ++q) {
+
+                const double second = col_s[r][kPairTile + lj + 8 * q];
+
+                #pragma unroll
+                for (uint32_t a = 0; a < 2; ++a) {
+
+                    const double prob = (a == 0 ? first0 : first1) + second / 2.0;
+                    const int32_t hi = __double2hiint(prob);
+                    exponent[a][q] += static_cast<int32_t>(power) * (hi >> 20);
+
+                    const double mantissa = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(prob));
+                    double square = mantissa * mantissa;
+                    double factor = (power & 1u) ? mantissa : 1.0;
+                    if (power & 2u) { factor *= square; }
+
+                    if (power >= 4) {
+                        square *= square;
+                        if (power & 4u) { factor *= square; }
+                        if (power >= 8) {
+                            square *= square;
+                            if (power & 8u) { factor *= square; }
+                            if (power >= 16) {
+                                square *= square;
+                                factor *= square;
+                            }
+                        }
+                    }
+
+                    product[a][q] *= factor;
+                }
+            }
+        }
+
+        // the terms that take a log
+        for (uint32_t r = n2; r < n_chunk; ++r) {
+
+            const double weight = count_s[r];
+            const double nzr = noise_s[r];
+            const double first0 = nzr + col_s[r][li] / 2.0;
+            const double first1 = nzr + col_s[r][li + 16] / 2.0;
+
+            #pragma unroll
+            for (uint32_t q = 0; q < 4; ++q) {
+                const double second = col_s[r][kPairTile + lj + 8 * q];
+                slow[0][q] = fma(weight, log(first0 + second / 2.0), slow[0][q]);
+                slow[1][q] = fma(weight, log(first1 + second / 2.0), slow[1][q]);
+            }
+        }
+
+        // renormalise (the products grew by at most 2^(31 x 32)) and take the bias of the chunk's exponents off
+        const int32_t bias = odd ? 0 : static_cast<int32_t>(1023u * power_total);
+
+        #pragma unroll
+        for (uint32_t a = 0; a < 2; ++a) {
+            #pragma unroll
+            for (uint32_t q = 0; q < 4; ++q) {
+                const int32_t hi = __double2hiint(product[a][q]);
+                exponent[a][q] += (hi >> 20) - 1023 - bias;
+                product[a][q] = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(product[a][q]));
+            }
+        }
+    }
+
+    // ln2 in two pieces (the high one has 21 zero bits at the end: its product with the exponent sum is exact up to 2^21)
+    double acc[2][4];
+    #pragma unroll
+    for (uint32_t a = 0; a < 2; ++a) {
         #pragma unroll
         for (uint32_t q = 0; q < 4; ++q) {
-            const double y = sum[q] - comp[q];
-            const double t = acc[q] + y;
-            comp[q] = (t - acc[q]) - y;
-            acc[q] = t;
+            const double e = static_cast<double>(exponent[a][q]);
+            acc[a][q] = fma(e, 6.93147180369123816490e-01, fma(e, 1.90821492927058770002e-10, log(product[a][q]) + slow[a][q]));
         }
     }
 
@@ -168,26 +314,35 @@ __global__ void __launch_bounds__(kPairThreads) pairTileKernel(const PairTileArg
 
     if (args.partial) {
 
-        double * out = args.partial + item * (kPairTile * kPairTile) + tid * 4;
+        double * out = args.partial + item * (kPairTile * kPairTile) + tid * 8;
         #pragma unroll
-        for (uint32_t q = 0; q < 4; ++q) { out[q] = acc[q]; }
+        for (uint32_t a = 0; a < 2; ++a) {
+            #pragma unroll
+            for (uint32_t q = 0; q < 4; ++q) { out[a * 4 + q] = acc[a][q]; }
+        }
         return;
     }
 
-    if (i >= G) { return; }
-
     const uint64_t p0 = b.pair_offset[c];
-    const uint32_t a = order[i];
-    const uint64_t row_start = static_cast<uint64_t>(i) * G - (static_cast<uint64_t>(i) * (i - 1)) / 2;
 
     #pragma unroll
-    for (uint32_t q = 0; q < 4; ++q) {
-        const uint32_t j = j0 + q;
-        if (j < G && j >= i) {
-            const uint32_t bb = order[j];
-            const uint64_t p = p0 + row_start + (j - i);
-            b.cand_loglik[p] = acc[q];
-            b.pair_ll[p] = acc[q] + (b.log_freq[g0 + a] + b.log_freq[g0 + bb] + (a == bb ? 0.0 : 0.6931471805599453));
+    for (uint32_t a = 0; a < 2; ++a) {
+
+        const uint32_t i = i0 + 16 * a;
+        if (i >= G) { continue; }
+
+        const uint32_t ga = order[i];
+        const uint64_t row_start = static_cast<uint64_t>(i) * G - (static_cast<uint64_t>(i) * (i - 1)) / 2;
+
+        #pragma unroll
+        for (uint32_t q = 0; q < 4; ++q) {
+            const uint32_t j = j0 + 8 * q;
+            if (j < G && j >= i) {
+                const uint32_t gb = order[j];
+                const uint64_t p = p0 + row_start + (j - i);
+                b.cand_loglik[p] = acc[a][q];
+                b.pair_ll[p] = acc[a][q] + (b.log_freq[g0 + ga] + b.log_freq[g0 + gb] + (ga == gb ? 0.0 : 0.6931471805599453));
+            }
         }
     }
 }
@@ -212,32 +367,37 @@ __global__ void __launch_bounds__(kPairThreads) pairCombineKernel(const PairTile
     const uint32_t ti = what.y & 0xffffu, tj = what.y >> 16;
 
     const uint32_t tid = threadIdx.x;
-    const uint32_t i = ti * kPairTile + (tid >> 3);
-    const uint32_t j0 = tj * kPairTile + (tid & 7) * 4;
-
-    if (i >= G) { return; }
+    uint32_t i0, j0;
+    pairsOfThread(tid, ti, tj, &i0, &j0);
 
     const uint64_t p0 = b.pair_offset[c];
-    const uint32_t a = order[i];
-    const uint64_t row_start = static_cast<uint64_t>(i) * G - (static_cast<uint64_t>(i) * (i - 1)) / 2;
 
-    for (uint32_t q = 0; q < 4; ++q) {
+    for (uint32_t a = 0; a < 2; ++a) {
 
-        const uint32_t j = j0 + q;
-        if (j >= G || j < i) { continue; }
+        const uint32_t i = i0 + 16 * a;
+        if (i >= G) { continue; }
 
-        double acc = 0, comp = 0;
-        for (uint32_t sp = 0; sp < n_splits; ++sp) {
-            const double y = args.partial[(item + sp) * (kPairTile * kPairTile) + tid * 4 + q] - comp;
-            const double t = acc + y;
-            comp = (t - acc) - y;
-            acc = t;
+        const uint32_t ga = order[i];
+        const uint64_t row_start = static_cast<uint64_t>(i) * G - (static_cast<uint64_t>(i) * (i - 1)) / 2;
+
+        for (uint32_t q = 0; q < 4; ++q) {
+
+            const uint32_t j = j0 + 8 * q;
+            if (j >= G || j < i) { continue; }
+
+            double acc = 0, comp = 0;
+            for (uint32_t sp = 0; sp < n_splits; ++sp) {
+                const double y = args.partial[(item + sp) * (kPairTile * kPairTile) + tid * 8 + a * 4 + q] - comp;
+                const double t = acc + y;
+                comp = (t - acc) - y;
+                acc = t;
+            }
+
+            const uint32_t gb = order[j];
+            const uint64_t p = p0 + row_start + (j - i);
+            b.cand_loglik[p] = acc;
+            b.pair_ll[p] = acc + (b.log_freq[g0 + ga] + b.log_freq[g0 + gb] + (ga == gb ? 0.0 : 0.6931471805599453));
         }
-
-        const uint32_t bb = order[j];
-        const uint64_t p = p0 + row_start + (j - i);
-        b.cand_loglik[p] = acc;
-        b.pair_ll[p] = acc + (b.log_freq[g0 + a] + b.log_freq[g0 + bb] + (a == bb ? 0.0 : 0.6931471805599453));
     }
 }
 
@@ -566,6 +726,9 @@ extern "C" int rpvg_b200_grouped_bounded_pairs(rpvg_b200_ctx * ctx, rpvg_b200_gr
                 rows_per_split = static_cast<uint32_t>((most_rows + splits - 1) / splits);
                 rows_per_split = std::max(8 * kPairRowChunk, ((rows_per_split + kPairRowChunk - 1) / kPairRowChunk) * kPairRowChunk);
             }
+
+            rows_per_split = std::min(rows_per_split, kPairMaxSplitRows);
+            rows_per_split = ((rows_per_split + kPairRowChunk - 1) / kPairRowChunk) * kPairRowChunk;
 
             std::vector<uint4> items;
             items.reserve(tiles.size());

@@ -42,7 +42,9 @@ struct BatchArena {
 
     // all clusters at once, filled in parallel over stretches of read classes (a cluster may hold most of the batch: the
     // unit of work is 256 read classes, not a cluster)
-    void build(rpvg_b200_ctx * ctx, const vector<const vector<ReadPathProbabilities> *> & members, const vector<uint32_t> & num_paths) {
+    // (sorted = false: the entries of a read class stay in the order of its groups — enough for the dense matrices of
+    // the haplotypes model, which are filled by a scatter)
+    void build(rpvg_b200_ctx * ctx, const vector<const vector<ReadPathProbabilities> *> & members, const vector<uint32_t> & num_paths, const bool sorted = true) {
 
         const size_t n = members.size();
 
@@ -112,14 +114,59 @@ struct BatchArena {
                 uint64_t e = row_ptr[r];
                 const auto & groups = probs[i].pathProbs();
 
-                if (groups.size() == 1 && is_sorted(groups.front().second.begin(), groups.front().second.end())) {
+                if (!sorted || (groups.size() == 1 && is_sorted(groups.front().second.begin(), groups.front().second.end()))) {
 
-                    for (auto & path: groups.front().second) {
-                        col[e] = path;
-                        prob[e] = groups.front().first;
-                        ++e;
+                    for (auto & path_probs: groups) {
+                        const double p = path_probs.first;
+                        for (auto & path: path_probs.second) {
+                            col[e] = path;
+                            prob[e] = p;
+                            ++e;
+                        }
                     }
                     continue;
+                }
+
+                // several groups, each ascending (the usual case): merged by always taking the smallest head
+                if (groups.size() <= 8) {
+
+                    const uint32_t * head[8];
+                    const uint32_t * tail[8];
+                    double value[8];
+                    size_t k = 0;
+                    bool ascending = true;
+
+                    for (auto & path_probs: groups) {
+                        ascending = ascending && is_sorted(path_probs.second.begin(), path_probs.second.end());
+                        if (path_probs.second.empty()) { continue; }
+                        head[k] = path_probs.second.data();
+                        tail[k] = head[k] + path_probs.second.size();
+                        value[k] = path_probs.first;
+                        ++k;
+                    }
+
+                    if (ascending) {
+
+                        while (k > 0) {
+
+                            size_t best = 0;
+                            for (size_t g = 1; g < k; ++g) {
+                                if (*head[g] < *head[best]) { best = g; }
+                            }
+
+                            col[e] = *head[best];
+                            prob[e] = value[best];
+                            ++e;
+
+                            if (++head[best] == tail[best]) {
+                                --k;
+                                head[best] = head[k];
+                                tail[best] = tail[k];
+                                value[best] = value[k];
+                            }
+                        }
+                        continue;
+                    }
                 }
 
                 row.clear();
@@ -146,6 +193,24 @@ struct BatchArena {
 
 }
 
+namespace {
+
+// stage times on stderr when RPVG_B200_BATCH_TRACE is set
+struct BatchTrace {
+
+    const bool on = getenv("RPVG_B200_BATCH_TRACE") != nullptr;
+    chrono::steady_clock::time_point last = chrono::steady_clock::now();
+
+    void lap(const char * what) {
+        if (!on) { return; }
+        const auto now = chrono::steady_clock::now();
+        cerr << "[rpvg_b200 batch] " << what << ": " << chrono::duration<double, milli>(now - last).count() << " ms" << endl;
+        last = now;
+    }
+};
+
+}
+
 void PathEstimator::runPosteriorRounds(rpvg_b200_ctx * ctx, rpvg_b200_grouped * resident, const vector<uint64_t> & group_offset, vector<GroupPosteriorPlan> * plans, const vector<PathClusterEstimates *> & outs) const {
 
     const size_t n = plans->size();
@@ -153,6 +218,8 @@ void PathEstimator::runPosteriorRounds(rpvg_b200_ctx * ctx, rpvg_b200_grouped * 
 
     const bool bounded = plans->front().bounded;
     for (auto & plan: *plans) { plan.device_pairs = bounded; }
+
+    BatchTrace trace;
 
     // round 1: the first request of every plan (Full: all multisets; Bounded: the single groups)
     {
@@ -179,6 +246,8 @@ void PathEstimator::runPosteriorRounds(rpvg_b200_ctx * ctx, rpvg_b200_grouped * 
             (void) more;
         }
     }
+
+    trace.lap("posteriors: round 1 (marginals / all sets)");
 
     if (!bounded) { return; }
 
@@ -207,11 +276,15 @@ void PathEstimator::runPosteriorRounds(rpvg_b200_ctx * ctx, rpvg_b200_grouped * 
         fatalBatch(ctx, "rpvg_b200_grouped_bounded_pairs");
     }
 
+    trace.lap("posteriors: pairs on the device");
+
     #pragma omp parallel for schedule(dynamic, 8)
     for (size_t k = 0; k < n; ++k) {
         const uint64_t c0 = cand_offset[k];
         finishBoundedPathGroupPosteriors(&(*plans)[k], outs[k], cand_offset[k + 1] - c0, cand_pair ? cand_pair + c0 : nullptr, cand_loglik ? cand_loglik + c0 : nullptr);
     }
+
+    trace.lap("posteriors: walk over the candidates");
 }
 
 void PathEstimator::estimateBatch(const vector<PathClusterEstimates *> & estimates, const vector<const vector<ReadPathProbabilities> *> & cluster_probs, const vector<mt19937 *> & rngs) {
@@ -571,6 +644,8 @@ void PathEstimator::posteriorsBatch(const vector<PathClusterEstimates *> & estim
 
     const size_t n = members.size();
 
+    BatchTrace trace;
+
     BatchArena arena;
     {
         vector<const vector<ReadPathProbabilities> *> member_probs;
@@ -579,8 +654,10 @@ void PathEstimator::posteriorsBatch(const vector<PathClusterEstimates *> & estim
             member_probs.push_back(cluster_probs[i]);
             member_paths.push_back(estimates[i]->paths.size());
         }
-        arena.build(threadContext(), member_probs, member_paths);
+        arena.build(threadContext(), member_probs, member_paths, false);
     }
+
+    trace.lap("haplotypes: flatten");
 
     const vector<uint64_t> & path_offset = arena.path_offset;
     vector<GroupPosteriorPlan> plans(n);
@@ -602,7 +679,11 @@ void PathEstimator::posteriorsBatch(const vector<PathClusterEstimates *> & estim
     // the dense matrices (rows x paths of every cluster, as denseMatrix makes them) are built on the device
     rpvg_b200_clusters clusters = arena.view();
     rpvg_b200_grouped * resident = nullptr;
+    trace.lap("haplotypes: plans");
+
     if (rpvg_b200_grouped_raw(ctx, &clusters, &resident) != RPVG_B200_OK) { fatalBatch(ctx, "rpvg_b200_grouped_raw"); }
+
+    trace.lap("haplotypes: upload + dense matrices");
 
     vector<PathClusterEstimates *> outs(n);
     for (size_t k = 0; k < n; ++k) { outs[k] = estimates[members[k]]; }
