@@ -136,6 +136,11 @@ int rpvg_b200_group_loglik(rpvg_b200_ctx * ctx, const rpvg_b200_loglik_problems 
  * not by HBM (no counterpart in the reference; MEASURED_PEAKS.json has no such figure). */
 int rpvg_b200_log_peak(rpvg_b200_ctx * ctx, double * logs_per_second);
 
+/* Micro-benchmark: fp64 fused multiply-adds per second (independent chains, no memory traffic). The pair kernel of
+ * rpvg_b200_grouped_bounded_pairs spends two fp64 instructions per term (the sum noise + a / 2 + b / 2 and the product it
+ * goes into) instead of a log: half of this figure is its roofline (no counterpart in the reference). */
+int rpvg_b200_fp64_peak(rpvg_b200_ctx * ctx, double * fma_per_second);
+
 /* ---- read-class collapse ----
  * rowSortProbabilityMatrix + readCollapseProbabilityMatrix (rpvg:src/path_estimator.cpp:13-31,197-259) for a batch of
  * problems: rows of a normalised probability matrix (sparse: entries with problem-local column indices ascending, an

@@ -14,14 +14,17 @@
 // (tile, row range). The CTA stages the 64 columns of its tile 32 read classes at a time in shared memory (coalesced
 // column reads, 0.5 B of L2 traffic per log) and every thread owns 4 pairs: one column read serves 32 pairs, and the
 // kernel is bound by arithmetic, not by memory. A log per term is what the reference spends
-// (G (G + 1) / 2 x M of them); here sum_r count_r log(x_r) is taken as log(prod_r x_r^count_r): every x_r is split into
-// exponent and mantissa (integer operations), the exponents are added as integers (exact), the mantissas in [1, 2)
-// multiplied into a running product that is renormalised every 32 read classes, and ONE log is taken per pair and row
-// range at the end: ll = ln2 * (sum of exponents) + log(product). The product of n mantissas carries a relative error of
-// at most n x 1.1e-16 (1.8e-12 for 16,384 read classes, typically its square root), i.e. an absolute error on ll below
-// what one rounding of a sum of that size costs (ulp(1e5) = 1.5e-11). Read classes whose count is not an integer in
-// 1..31, and values that are zero, denormal or not finite, take the plain count * log(x) route (a row-uniform branch).
-// Deterministic.
+// (G (G + 1) / 2 x M of them); here sum_r count_r log(x_r) is taken as log(prod_r x_r^count_r). Every read class has a
+// power of two s_r = 2^-k_r that brings all its terms below 1 (from the reference's own row maximum, which the bound
+// kernels need anyway): the scaled terms are multiplied into a running product per pair (scaling by a power of two is
+// exact), sum_r count_r k_r is the same integer for all pairs, and the products are renormalised (exponent moved to an
+// integer sum) whenever the smallest value they could have reached nears the end of the double range. ONE log per pair
+// and row range at the end: ll = ln2 * (sum of exponents) + log(product). A term costs two fp64 instructions instead of
+// the ~50 of a log. The product of n factors carries a relative error of at most n x 1.1e-16 (1.8e-12 for 16,384 read
+// classes, typically its square root), i.e. an absolute error on ll below what one rounding of a sum of that size
+// costs (ulp(1e5) = 1.5e-11). Read classes whose count is not an integer in 1..31, whose values span too many binary
+// orders or are negative or not finite take the count * log(x) route (a row-uniform branch). The columns of the next 32
+// read classes are fetched by asynchronous copies while a chunk is worked on. Deterministic.
 // Scan: boundedScanKernel, one CTA per cluster: exclusive prefix maximum in pair order, test, compaction.
 
 #include <cfloat>
@@ -78,6 +81,7 @@ struct PairTileArgs {
                                        // the row ranges of a tile are adjacent items
     uint32_t rows_per_split;           // read classes per row range (multiple of kPairRowChunk, at most kPairMaxSplitRows)
     double * partial;                  // [n_items x 1024] when rows are split, else NULL
+    const double * row_max;            // per read class: largest column / 2 (pairRowMaxKernel)
     unsigned long long * log_count;    // terms evaluated (pairs x read classes: for the roofline)
 };
 
@@ -88,15 +92,89 @@ __device__ __forceinline__ void pairsOfThread(const uint32_t tid, const uint32_t
     *j0 = tj * kPairTile + (tid & 7);
 }
 
-__global__ void __launch_bounds__(kPairThreads) pairTileKernel(const PairTileArgs args) {
+// log(x) for the terms that keep their log (counts that are not small integers): x = m 2^k with m in [1/sqrt2, sqrt2),
+// log m = 2 atanh(s), s = (m - 1) / (m + 1), |s| <= 0.1716, by its power series up to s^21 (the next term is below 1e-17);
+// the quotient from the hardware's reciprocal seed and two Newton steps plus a correction of the quotient itself. About
+// 30 instructions against the ~100 issue slots of the library's log, to 1-2 ulp of the result. Anything but a normal
+// positive number goes to the library.
+__device__ __forceinline__ double pairLog(const double x) {
 
+    const int32_t hi = __double2hiint(x);
+    if (static_cast<uint32_t>(hi - 0x00100000) >= 0x7fe00000u) { return log(x); }
+
+    // mantissa in [1, 2); above sqrt2 it is halved and the exponent goes up by one
+    int32_t k = (hi >> 20) - 1023;
+    int32_t mhi = (hi & 0x000fffff) | 0x3ff00000;
+    if (mhi >= 0x3ff6a09f) {   // high word of sqrt2, rounded up
+        mhi -= 0x00100000;
+        k += 1;
+    }
+    const double m = __hiloint2double(mhi, __double2loint(x));
+
+    const double f = m - 1.0;
+    const double d = m + 1.0;
+
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+    r = fma(r, fma(-d, r, 1.0), r);
+    r = fma(r, fma(-d, r, 1.0), r);
+
+    double q = f * r;
+    q = fma(r, fma(-d, q, f), q);   // q = f / d to the last bit or two
+
+    const double z = q * q;
+    double p = 2.0 / 21.0;
+    p = fma(p, z, 2.0 / 19.0);
+    p = fma(p, z, 2.0 / 17.0);
+    p = fma(p, z, 2.0 / 15.0);
+    p = fma(p, z, 2.0 / 13.0);
+    p = fma(p, z, 2.0 / 11.0);
+    p = fma(p, z, 2.0 / 9.0);
+    p = fma(p, z, 2.0 / 7.0);
+    p = fma(p, z, 2.0 / 5.0);
+    p = fma(p, z, 2.0 / 3.0);
+
+    // 2 q + q z p, with what the rounding of q lost put back: f - q d is exact enough in one fma
+    const double tail = fma(q * z, p, 2.0 * r * fma(-d, q, f));
+    const double kd = static_cast<double>(k);
+    return fma(kd, 6.93147180369123816490e-01, fma(kd, 1.90821492927058770002e-10, tail + 2.0 * q) );
+}
+
+// t^P for the small counts that are most of the repeated read classes
+template <uint32_t P>
+__device__ __forceinline__ double pairPower(const double t) {
+    if (P == 2) { return t * t; }
+    if (P == 3) { return t * t * t; }
+    const double t2 = t * t;
+    if (P == 4) { return t2 * t2; }
+    if (P == 5) { return t2 * t2 * t; }
+    return t2 * t2 * t2;   // 6
+}
+
+// One staged chunk: 32 read classes of the tile's 64 columns, and what the loops need to know about each read class
+struct PairStage {
     // [read class][column of the tile]: 32 first, then 32 second groups. A thread's four second groups lie 8 apart, so the
     // eight threads that share its first groups read consecutive words: no bank conflicts (pitch 65).
-    __shared__ double col_s[kPairRowChunk][2 * kPairTile + 1];
-    __shared__ double noise_s[kPairRowChunk];
-    __shared__ double count_s[kPairRowChunk];
-    __shared__ uint32_t power_s[kPairRowChunk];
-    __shared__ uint32_t odd_s;
+    double col[kPairRowChunk][2 * kPairTile + 1];
+    double noise[kPairRowChunk];      // noise of the read class, times its scale on the fast routes
+    double half[kPairRowChunk];       // scale / 2 (1 / 2 for the read classes that take logs)
+    double count[kPairRowChunk];
+    int32_t floor_[kPairRowChunk];    // count x binary orders the scaled terms of the read class can lie below 1
+    uint32_t power[kPairRowChunk];
+};
+
+// 8 bytes global -> shared without a register in between
+__device__ __forceinline__ void pairCopy8(void * dst, const void * src) {
+    const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(dst));
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"(d), "l"(src) : "memory");
+}
+
+__global__ void __launch_bounds__(kPairThreads) pairTileKernel(const PairTileArgs args) {
+
+    // two stages: the columns of the next 32 read classes are on their way (asynchronous copies) while this chunk is
+    // worked on
+    __shared__ PairStage stages[2];
+    __shared__ uint64_t column_s[2 * kPairTile];   // offset of every column of the tile in the matrix; ~0: past the last group
 
     const BoundedArgs & b = args.b;
 
@@ -115,6 +193,7 @@ __global__ void __launch_bounds__(kPairThreads) pairTileKernel(const PairTileArg
     const double * matrix = b.matrix + b.matrix_offset[c];
     const double * noise = b.noise + r0;
     const double * counts = b.counts + r0;
+    const double * row_max = args.row_max + r0;
     const uint32_t * order = b.order + g0;
 
     const uint32_t ti = what.y & 0xffffu, tj = what.y >> 16;
@@ -128,10 +207,17 @@ __global__ void __launch_bounds__(kPairThreads) pairTileKernel(const PairTileArg
     uint32_t i0, j0;
     pairsOfThread(tid, ti, tj, &i0, &j0);
 
-    // per pair: product of mantissas, sum of (biased) exponents, and the sum of the terms taken by log
+    if (tid < 2 * kPairTile) {
+        const uint32_t pos = (tid < kPairTile ? ti * kPairTile + tid : tj * kPairTile + (tid - kPairTile));
+        column_s[tid] = pos < G ? static_cast<uint64_t>(order[pos]) * rows : ~0ull;
+    }
+
+    // per pair: the running product, the exponents taken out of it, and the sum of the terms taken by log; for all pairs
+    // alike: sum of count x k over the read classes of the fast routes
     double product[2][4];
     int32_t exponent[2][4];
     double slow[2][4];
+    double common_exponent = 0;
 
     #pragma unroll
     for (uint32_t a = 0; a < 2; ++a) {
@@ -143,111 +229,198 @@ __global__ void __launch_bounds__(kPairThreads) pairTileKernel(const PairTileArg
         }
     }
 
-    // one term: x = m 2^e -> the exponent to the sum, the mantissa (in [1, 2)) into the product
-    auto take = [](const double prob, double * prod, int32_t * exp_sum) {
-        const int32_t hi = __double2hiint(prob);
-        *exp_sum += hi >> 20;
-        const double mantissa = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(prob));
-        *prod *= mantissa;
-        return mantissa;
+    // binary orders the products may have lost since they were last brought back to [1, 2)
+    int32_t depth = 0;
+    constexpr int32_t kDepthLimit = 900;
+
+    auto renormalise = [&]() {
+        #pragma unroll
+        for (uint32_t a = 0; a < 2; ++a) {
+            #pragma unroll
+            for (uint32_t q = 0; q < 4; ++q) {
+                const int32_t hi = __double2hiint(product[a][q]);
+                exponent[a][q] += (hi >> 20) - 1023;
+                product[a][q] = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(product[a][q]));
+            }
+        }
+        depth = 0;
     };
 
-    if (tid == 0) { odd_s = 0; }
-    __syncthreads();
+    // what a warp knows about read class `lane` of a chunk before it sends for its columns
+    struct Meta { double count, noise, top; };
 
-    for (uint32_t base = row_begin; base < row_end; base += kPairRowChunk) {
+    auto load_meta = [&](const uint32_t base) {
+        Meta m = {0.0, 1.0, 1.0};
+        if (base < row_end && base + lane < row_end) {
+            m.count = counts[base + lane];
+            m.noise = noise[base + lane];
+            m.top = m.noise + 2.0 * row_max[base + lane];   // (NaN where the read class holds a value that is not finite and >= 0)
+        }
+        return m;
+    };
 
+    // the chunk's split into the three routes, and sum of count x k over its fast read classes
+    struct Plan { uint32_t n_once, n_more; double shift; };
+
+    // Sends for the columns of the chunk at `base` into stage `buffer`; the read classes are placed by route: first the
+    // ones whose count is 1, then counts 2..31, then the ones that take a log. A fast read class has noise and
+    // noise + 2 x (largest column / 2) normal positive numbers: all its terms lie between the two. Scale 2^-k brings the
+    // upper one into [1/2, 1); the lower one then sits `orders` binary orders below 1 at most. Every warp works the
+    // placement out for itself.
+    auto send = [&](const uint32_t base, const uint32_t buffer, const Meta & m) {
+
+        PairStage & st = stages[buffer];
         const uint32_t n_chunk = min(kPairRowChunk, row_end - base);
-
-        // Kind of read class `lane`, and its place in the staged chunk: first the ones whose count is 1, then counts 2..31,
-        // then the ones that take a log — counts that are not small integers, and read classes whose noise is not a
-        // normal positive number (with it, noise + a / 2 + b / 2 is one as well for finite a, b >= 0: the fast loops need
-        // no test per term). Every warp works this out for itself.
         const bool live = lane < n_chunk;
-        const double cnt = live ? counts[base + lane] : 0.0;
-        const double nz = live ? noise[base + lane] : 1.0;
-        const bool fast = live && cnt >= 1.0 && cnt <= 31.0 && cnt == floor(cnt) && nz >= DBL_MIN && nz <= DBL_MAX;
-        const bool once = fast && cnt == 1.0;
+
+        const int32_t top_order = (__double2hiint(m.top) >> 20) - 1023;
+        const int32_t low_order = (__double2hiint(m.noise) >> 20) - 1023;
+        const int32_t orders = top_order + 1 - low_order;
+
+        const bool fast = live && m.count >= 1.0 && m.count <= 31.0 && m.count == floor(m.count) && m.noise >= DBL_MIN && m.top <= 1e300 && m.top >= m.noise &&
+                          orders * static_cast<int32_t>(m.count) <= kDepthLimit / 4;
+        const bool once = fast && m.count == 1.0;
 
         const uint32_t m_once = __ballot_sync(0xffffffffu, once);
         const uint32_t m_more = __ballot_sync(0xffffffffu, fast && !once);
         const uint32_t m_slow = __ballot_sync(0xffffffffu, live && !fast);
         const uint32_t below = (1u << lane) - 1u;
-        const uint32_t n_once = __popc(m_once), n_more = __popc(m_more);
 
-        uint32_t slot = n_chunk + (lane - n_chunk);   // (lanes past the chunk keep their place)
+        Plan plan;
+        plan.n_once = __popc(m_once);
+        plan.n_more = __popc(m_more);
+
+        uint32_t slot = lane;   // (lanes past the chunk keep their place)
         if (once) { slot = __popc(m_once & below); }
-        else if (fast) { slot = n_once + __popc(m_more & below); }
-        else if (live) { slot = n_once + n_more + __popc(m_slow & below); }
+        else if (fast) { slot = plan.n_once + __popc(m_more & below); }
+        else if (live) { slot = plan.n_once + plan.n_more + __popc(m_slow & below); }
 
-        const uint32_t power_total = __reduce_add_sync(0xffffffffu, fast ? static_cast<uint32_t>(cnt) : 0u);
+        // (sum over the fast read classes of the chunk, the same in every lane: count x k are small integers, exact)
+        double shift = fast ? m.count * static_cast<double>(top_order + 1) : 0.0;
+        #pragma unroll
+        for (int off = 16; off > 0; off >>= 1) { shift += __shfl_xor_sync(0xffffffffu, shift, off); }
+        plan.shift = shift;
 
-        __syncthreads();   // the previous chunk has been consumed
-
-        // stage: warp w loads columns w, w + 4, ..: lane = read class (coalesced)
+        // warp w sends for columns w, w + 4, ..: lane = read class (coalesced)
         for (uint32_t k = warp; k < 2 * kPairTile; k += kPairThreads / 32) {
-            const uint32_t pos = (k < kPairTile ? ti * kPairTile + k : tj * kPairTile + (k - kPairTile));
-            double v = 0;
-            if (pos < G && live) { v = matrix[static_cast<uint64_t>(order[pos]) * rows + base + lane]; }
-            col_s[slot][k] = v;
-            // (anything but a finite value >= 0: from here on this CTA takes the log of every term, like the reference)
-            if (!(v >= 0.0 && v <= DBL_MAX)) { odd_s = 1; }
+            const uint64_t column = column_s[k];
+            if (live && column != ~0ull) { pairCopy8(&st.col[slot][k], matrix + column + base + lane); }
+            else { st.col[slot][k] = 0.0; }
         }
+
         if (warp == 0) {
-            noise_s[slot] = nz;
-            count_s[slot] = cnt;
-            power_s[slot] = fast ? static_cast<uint32_t>(cnt) : 0u;
+            // scale = 2^-(top_order + 1)
+            const double scale = fast ? __hiloint2double((1023 - (top_order + 1)) << 20, 0) : 1.0;
+            st.noise[slot] = m.noise * scale;
+            st.half[slot] = 0.5 * scale;
+            st.count[slot] = m.count;
+            st.floor_[slot] = fast ? orders * static_cast<int32_t>(m.count) : 0;
+            st.power[slot] = fast ? static_cast<uint32_t>(m.count) : 0u;
         }
 
-        __syncthreads();
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        return plan;
+    };
 
-        const bool odd = odd_s != 0;
-        const uint32_t n1 = odd ? 0u : n_once;
-        const uint32_t n2 = odd ? 0u : n_once + n_more;
+    __syncthreads();   // column_s
 
-        // read classes seen once
-        #pragma unroll 2
-        for (uint32_t r = 0; r < n1; ++r) {
+    Plan plan = send(row_begin, 0, load_meta(row_begin));
+    Meta ahead = load_meta(row_begin + kPairRowChunk);
 
-            // noise + col_first / 2 + col_second / 2, in the reference's order
-            const double nzr = noise_s[r];
-            const double first0 = nzr + col_s[r][li] / 2.0;
-            const double first1 = nzr + col_s[r][li + 16] / 2.0;
+    uint32_t buffer = 0;
+
+    for (uint32_t base = row_begin; base < row_end; base += kPairRowChunk, buffer ^= 1u) {
+
+        const uint32_t n_chunk = min(kPairRowChunk, row_end - base);
+
+        // the next chunk into the other stage (its last readers passed the barrier at the end of the previous round)
+        Plan next_plan = {0, 0, 0.0};
+        if (base + kPairRowChunk < row_end) {
+            next_plan = send(base + kPairRowChunk, buffer ^ 1u, ahead);
+            ahead = load_meta(base + 2 * kPairRowChunk);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
+
+        __syncthreads();   // this chunk is in, for everybody
+
+        const PairStage & st = stages[buffer];
+        const uint32_t n1 = plan.n_once;
+        const uint32_t n2 = plan.n_once + plan.n_more;
+        common_exponent += plan.shift;
+
+        // term of a pair = (noise + first / 2) + second / 2 in the reference's order, scaled by the read class's power of two
+        // (exactly): fma(second, scale / 2, fma(first, scale / 2, noise x scale))
+
+        // read classes seen once, four at a time (each is at most a quarter of the depth limit deep)
+        auto once_row = [&](const uint32_t r) {
+
+            const double hs = st.half[r];
+            const double nzr = st.noise[r];
+            const double first0 = fma(st.col[r][li], hs, nzr);
+            const double first1 = fma(st.col[r][li + 16], hs, nzr);
 
             #pragma unroll
             for (uint32_t q = 0; q < 4; ++q) {
-                const double second = col_s[r][kPairTile + lj + 8 * q];
-                take(first0 + second / 2.0, &product[0][q], &exponent[0][q]);
-                take(first1 + second / 2.0, &product[1][q], &exponent[1][q]);
+                const double second = st.col[r][kPairTile + lj + 8 * q];
+                product[0][q] *= fma(second, hs, first0);
+                product[1][q] *= fma(second, hs, first1);
             }
+        };
+
+        uint32_t r = 0;
+
+        for (; r + 4 <= n1; r += 4) {
+
+            const int32_t deeper = (st.floor_[r] + st.floor_[r + 1]) + (st.floor_[r + 2] + st.floor_[r + 3]);
+            if (depth + deeper > kDepthLimit) { renormalise(); }
+            depth += deeper;
+
+            once_row(r);
+            once_row(r + 1);
+            once_row(r + 2);
+            once_row(r + 3);
         }
 
-        // read classes seen 2..31 times: x^count from the squares of the mantissa
-        for (uint32_t r = n1; r < n2; ++r) {
+        for (; r < n1; ++r) {
+            if (depth + st.floor_[r] > kDepthLimit) { renormalise(); }
+            depth += st.floor_[r];
+            once_row(r);
+        }
 
-            const uint32_t power = power_s[r];
-            const double nzr = noise_s[r];
-            const double first0 = nzr + col_s[r][li] / 2.0;
-            const double first1 = nzr + col_s[r][li + 16] / 2.0;
+        // read classes seen 2..31 times: x^count, by a product for the smallest counts, from the squares otherwise
+        for (; r < n2; ++r) {
 
-            #pragma unroll
-            for (uint32_t q = 0; q < 4; ++q) {
+            if (depth + st.floor_[r] > kDepthLimit) { renormalise(); }
+            depth += st.floor_[r];
 
-                const double second = col_s[r][kPairTile + lj + 8 * q];
+            const uint32_t power = st.power[r];
+            const double hs = st.half[r];
+            const double nzr = st.noise[r];
+            const double first0 = fma(st.col[r][li], hs, nzr);
+            const double first1 = fma(st.col[r][li + 16], hs, nzr);
 
+            auto each_term = [&](auto raise) {
                 #pragma unroll
-                for (uint32_t a = 0; a < 2; ++a) {
+                for (uint32_t q = 0; q < 4; ++q) {
+                    const double second = st.col[r][kPairTile + lj + 8 * q];
+                    product[0][q] *= raise(fma(second, hs, first0));
+                    product[1][q] *= raise(fma(second, hs, first1));
+                }
+            };
 
-                    const double prob = (a == 0 ? first0 : first1) + second / 2.0;
-                    const int32_t hi = __double2hiint(prob);
-                    exponent[a][q] += static_cast<int32_t>(power) * (hi >> 20);
-
-                    const double mantissa = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(prob));
-                    double square = mantissa * mantissa;
-                    double factor = (power & 1u) ? mantissa : 1.0;
-                    if (power & 2u) { factor *= square; }
-
-                    if (power >= 4) {
+            switch (power) {
+                case 2: each_term([](const double t) { return pairPower<2>(t); }); break;
+                case 3: each_term([](const double t) { return pairPower<3>(t); }); break;
+                case 4: each_term([](const double t) { return pairPower<4>(t); }); break;
+                case 5: each_term([](const double t) { return pairPower<5>(t); }); break;
+                case 6: each_term([](const double t) { return pairPower<6>(t); }); break;
+                default:
+                    each_term([power](const double t) {
+                        double square = t * t;
+                        double factor = (power & 1u) ? t : 1.0;
+                        if (power & 2u) { factor *= square; }
                         square *= square;
                         if (power & 4u) { factor *= square; }
                         if (power >= 8) {
@@ -258,42 +431,33 @@ __global__ void __launch_bounds__(kPairThreads) pairTileKernel(const PairTileArg
                                 factor *= square;
                             }
                         }
-                    }
-
-                    product[a][q] *= factor;
-                }
+                        return factor;
+                    });
             }
         }
 
-        // the terms that take a log
-        for (uint32_t r = n2; r < n_chunk; ++r) {
+        // the terms that take a log (unscaled: half = 1 / 2)
+        for (; r < n_chunk; ++r) {
 
-            const double weight = count_s[r];
-            const double nzr = noise_s[r];
-            const double first0 = nzr + col_s[r][li] / 2.0;
-            const double first1 = nzr + col_s[r][li + 16] / 2.0;
+            const double weight = st.count[r];
+            const double nzr = st.noise[r];
+            const double first0 = nzr + st.col[r][li] / 2.0;
+            const double first1 = nzr + st.col[r][li + 16] / 2.0;
 
             #pragma unroll
             for (uint32_t q = 0; q < 4; ++q) {
-                const double second = col_s[r][kPairTile + lj + 8 * q];
-                slow[0][q] = fma(weight, log(first0 + second / 2.0), slow[0][q]);
-                slow[1][q] = fma(weight, log(first1 + second / 2.0), slow[1][q]);
+                const double second = st.col[r][kPairTile + lj + 8 * q];
+                slow[0][q] = fma(weight, pairLog(first0 + second / 2.0), slow[0][q]);
+                slow[1][q] = fma(weight, pairLog(first1 + second / 2.0), slow[1][q]);
             }
         }
 
-        // renormalise (the products grew by at most 2^(31 x 32)) and take the bias of the chunk's exponents off
-        const int32_t bias = odd ? 0 : static_cast<int32_t>(1023u * power_total);
+        plan = next_plan;
 
-        #pragma unroll
-        for (uint32_t a = 0; a < 2; ++a) {
-            #pragma unroll
-            for (uint32_t q = 0; q < 4; ++q) {
-                const int32_t hi = __double2hiint(product[a][q]);
-                exponent[a][q] += (hi >> 20) - 1023 - bias;
-                product[a][q] = __hiloint2double((hi & 0x000fffff) | 0x3ff00000, __double2loint(product[a][q]));
-            }
-        }
+        __syncthreads();   // the stage may be refilled
     }
+
+    renormalise();
 
     // ln2 in two pieces (the high one has 21 zero bits at the end: its product with the exponent sum is exact up to 2^21)
     double acc[2][4];
@@ -301,7 +465,7 @@ __global__ void __launch_bounds__(kPairThreads) pairTileKernel(const PairTileArg
     for (uint32_t a = 0; a < 2; ++a) {
         #pragma unroll
         for (uint32_t q = 0; q < 4; ++q) {
-            const double e = static_cast<double>(exponent[a][q]);
+            const double e = common_exponent + static_cast<double>(exponent[a][q]);
             acc[a][q] = fma(e, 6.93147180369123816490e-01, fma(e, 1.90821492927058770002e-10, log(product[a][q]) + slow[a][q]));
         }
     }
@@ -417,10 +581,17 @@ __global__ void pairRowMaxKernel(const BoundedArgs b, const uint32_t n_clusters,
     const uint32_t G = static_cast<uint32_t>(b.group_offset[c + 1] - b.group_offset[c]);
     const double * matrix = b.matrix + b.matrix_offset[c];
 
-    double best = matrix[local];
-    for (uint32_t g = 1; g < G; ++g) { best = fmax(best, matrix[static_cast<uint64_t>(g) * rows + local]); }
+    // (a read class that holds anything but finite values >= 0 gets NaN: the pair kernel then takes the plain log of its
+    // terms, like the reference, and the bound of every row of pairs it is in compares false: nothing is ruled out)
+    double best = 0;
+    bool plain = true;
+    for (uint32_t g = 0; g < G; ++g) {
+        const double v = matrix[static_cast<uint64_t>(g) * rows + local];
+        plain = plain && v >= 0.0 && v <= DBL_MAX;
+        best = fmax(best, v);
+    }
 
-    row_max[r] = best / 2.0;
+    row_max[r] = plain ? best / 2.0 : __longlong_as_double(0x7ff8000000000000ll);
 }
 
 // optimal log-likelihood of any pair whose first group is order[i]: one warp per (cluster, i)
@@ -756,6 +927,7 @@ extern "C" int rpvg_b200_grouped_bounded_pairs(rpvg_b200_ctx * ctx, rpvg_b200_gr
             tile_args.rows_per_split = rows_per_split;
             tile_args.partial = split_rows ? reinterpret_cast<double *>(wave + pad(16 * items.size())) : nullptr;
             tile_args.log_count = d_log_count;
+            tile_args.row_max = d_row_max;
 
             if (err == cudaSuccess) {
 

@@ -37,7 +37,8 @@ int rpvgCollapseDevice(rpvg_b200_ctx * ctx, CollapseRows rows, uint32_t * d_row_
 
     collapseBoundaryKernel<<<grid, 256, 0, s>>>(rows, d_sorted, prob_precision, d_sorted_class);
     RPVG_LAUNCHED(ctx);
-    collapseStretchKernel<<<grid, 256, 0, s>>>(rows, d_sorted, prob_precision, d_sorted_class);
+    collapseStretchKernel<<<static_cast<unsigned>((rows.n_rows + kCollapseStretchThreads - 1) / kCollapseStretchThreads), kCollapseStretchThreads, 0, s>>>(rows, d_sorted, prob_precision,
+                                                                                                                                                        d_sorted_class);
     RPVG_LAUNCHED(ctx);
     collapseIndexKernel<<<rows.n_problems, kCollapseIndexThreads, 0, s>>>(rows, d_sorted_class, d_n_classes);
     RPVG_LAUNCHED(ctx);

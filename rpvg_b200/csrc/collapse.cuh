@@ -161,9 +161,8 @@ __device__ __forceinline__ bool collapseWithinPrecision(const CollapseRows & row
 // meet: if it differs from its predecessor by at least twice the precision in some column, then (triangle inequality) it
 // differs from the predecessor's representative by more than the precision, and from the predecessor itself too — it
 // starts a class whatever happened before. Pass 1 marks these certain starts (one thread per adjacent pair of rows);
-// pass 2 walks every stretch between two certain starts with the exact sequential rule (one thread per stretch: in real
-// data nearly every start is a certain one, or the rows are duplicates within the precision, so the stretches are short
-// or cheap); pass 3 numbers the classes (one CTA per problem). The result is the sequential scan's, bit for bit.
+// pass 2 walks every stretch between two certain starts with the exact sequential rule (a warp per stretch, the lanes
+// sharing out the columns of each comparison); pass 3 numbers the classes (one CTA per problem). The result is the sequential scan's, bit for bit.
 
 // true iff some column (absent = 0) or the noise value of rows a and b differ by at least `distance`
 __device__ __forceinline__ bool collapseFartherThan(const CollapseRows & rows, const uint32_t a, const uint32_t b, const double distance) {
@@ -202,25 +201,97 @@ static __global__ void collapseBoundaryKernel(const CollapseRows rows, const uin
     flag[s] = start ? 1u : 0u;
 }
 
-// pass 2: the thread of a certain start walks its stretch (up to the next certain start or the end of the problem) with
-// the sequential rule; rows that become representatives inside the stretch get flag 2
-static __global__ void collapseStretchKernel(const CollapseRows rows, const uint32_t * __restrict__ sorted, const double prob_precision, uint32_t * flag) {
+// pass 2: every stretch (from a certain start up to the next one or the end of the problem) is walked with the
+// sequential rule; rows that become representatives inside the stretch get flag 2. A warp takes 32 positions, and the
+// stretches that begin there and are longer than one row one after the other, all lanes on one comparison: the lanes
+// share out the entries of the row, look each column up in the representative (binary search in its sorted columns) and
+// vote. A column the representative has and the row lacks differs by the representative's own value: the
+// representative's entries that are at least the precision are counted once, and all of them must have found a partner.
+// Same predicate as collapseWithinPrecision, entry for entry.
+constexpr int kCollapseStretchThreads = 128;
 
-    const uint64_t s = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
-    if (s >= rows.n_rows || flag[s] != 1u) { return; }
+static __global__ void __launch_bounds__(kCollapseStretchThreads) collapseStretchKernel(const CollapseRows rows, const uint32_t * __restrict__ sorted, const double prob_precision,
+                                                                                        uint32_t * flag) {
 
-    uint32_t rep = sorted[s];
-    const uint64_t s1 = rows.problem_row_offset[rows.row_problem[rep] + 1];
+    const uint32_t lane = threadIdx.x & 31;
+    const uint64_t first = ((blockIdx.x * static_cast<uint64_t>(kCollapseStretchThreads) + threadIdx.x) >> 5) * 32;
+    const uint64_t s = first + lane;
 
-    for (uint64_t t = s + 1; t < s1; ++t) {
+    // (flag[] holds 0 / 1 from pass 1; a 2 is only ever written inside the writer's own stretch)
+    bool head = false;
+    uint64_t stretch_end = 0;
+    if (s < rows.n_rows && flag[s] == 1u) {
+        stretch_end = rows.problem_row_offset[rows.row_problem[sorted[s]] + 1];
+        head = s + 1 < stretch_end && flag[s + 1] != 1u;
+    }
 
-        if (flag[t] == 1u) { break; }   // written by pass 1 only; this thread alone writes inside its stretch
+    uint32_t heads = __ballot_sync(0xffffffffu, head);
 
-        const uint32_t row = sorted[t];
-        if (!collapseWithinPrecision(rows, rep, row, prob_precision)) {
-            rep = row;
-            flag[t] = 2u;
+    while (heads != 0) {
+
+        const int src = __ffs(heads) - 1;
+        heads &= heads - 1;
+
+        const uint64_t s0 = first + src;
+        const uint64_t s1 = __shfl_sync(0xffffffffu, stretch_end, src);
+
+        uint32_t rep = sorted[s0];
+        uint64_t a0 = 0, a1 = 0;
+        uint32_t rep_large = 0;
+        bool rep_loaded = false;
+
+        for (uint64_t t = s0 + 1; t < s1; ++t) {
+
+            if (flag[t] == 1u) { break; }
+
+            if (!rep_loaded) {
+                a0 = rows.row_ptr[rep];
+                a1 = rows.row_ptr[rep + 1];
+                uint32_t large = 0;
+                for (uint64_t e = a0 + lane; e < a1; e += 32) { large += fabs(rows.val[e]) >= prob_precision ? 1u : 0u; }
+                rep_large = __reduce_add_sync(0xffffffffu, large);
+                rep_loaded = true;
+            }
+
+            const uint32_t row = sorted[t];
+            const uint64_t b0 = rows.row_ptr[row], b1 = rows.row_ptr[row + 1];
+
+            bool differs = false;
+            uint32_t partners = 0;
+
+            for (uint64_t base = b0; base < b1; base += 32) {
+
+                const uint64_t e = base + lane;
+                if (e < b1) {
+
+                    const uint32_t column = rows.col[e];
+                    uint64_t lo = a0, hi = a1;
+                    while (lo < hi) {
+                        const uint64_t mid = (lo + hi) >> 1;
+                        if (rows.col[mid] < column) { lo = mid + 1; } else { hi = mid; }
+                    }
+
+                    double of_rep = 0;
+                    if (lo < a1 && rows.col[lo] == column) {
+                        of_rep = rows.val[lo];
+                        partners += fabs(of_rep) >= prob_precision ? 1u : 0u;
+                    }
+                    if (fabs(of_rep - rows.val[e]) >= prob_precision) { differs = true; }
+                }
+            }
+
+            differs = __any_sync(0xffffffffu, differs);
+            if (!differs) { differs = __reduce_add_sync(0xffffffffu, partners) != rep_large; }
+            if (!differs) { differs = !(fabs(rows.noise[rep] - rows.noise[row]) < prob_precision); }
+
+            if (differs) {
+                rep = row;
+                rep_loaded = false;
+                if (lane == 0) { flag[t] = 2u; }
+            }
         }
+
+        __syncwarp();
     }
 }
 

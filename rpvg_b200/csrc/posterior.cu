@@ -348,9 +348,30 @@ __global__ void logPeakKernel(const uint32_t iterations, const double seed, doub
 
 }
 
-extern "C" int rpvg_b200_log_peak(rpvg_b200_ctx * ctx, double * logs_per_second) {
+namespace {
 
-    if (!ctx || !logs_per_second) { return RPVG_B200_ERR_INVALID; }
+// Every thread runs 8 independent chains of fused multiply-adds: the fp64 pipe alone.
+__global__ void fmaPeakKernel(const uint32_t iterations, const double seed, double * __restrict__ sink) {
+
+    double x[8];
+    #pragma unroll
+    for (int q = 0; q < 8; ++q) { x[q] = seed + 1e-3 * (threadIdx.x * 8 + q) + 1e-6 * blockIdx.x; }
+
+    const double a = 1.0 - 1e-9, b = 1e-9;
+
+    for (uint32_t it = 0; it < iterations; ++it) {
+        #pragma unroll
+        for (int q = 0; q < 8; ++q) { x[q] = fma(x[q], a, b); }
+    }
+
+    const double total = ((x[0] + x[1]) + (x[2] + x[3])) + ((x[4] + x[5]) + (x[6] + x[7]));
+    if (total == 12345.678) { sink[0] = total; }   // never true: keeps the loop alive
+}
+
+// best of three timed launches (after one warm-up) of a kernel<<<grid, 256>>>(iterations, seed, sink); returns
+// per_thread * iterations * threads / seconds
+template <typename Kernel>
+int peakOf(rpvg_b200_ctx * ctx, Kernel kernel, const uint32_t iterations, const double per_thread, const char * name, double * per_second) {
 
     RPVG_CUDA(ctx, cudaSetDevice(ctx->device));
     cudaStream_t s = ctx->stream;
@@ -362,29 +383,42 @@ extern "C" int rpvg_b200_log_peak(rpvg_b200_ctx * ctx, double * logs_per_second)
     cudaError_t err = cudaEventCreate(&ev0);
     if (err == cudaSuccess) { err = cudaEventCreate(&ev1); }
 
-    const uint32_t iterations = 2000;
     const unsigned grid = 8u * static_cast<unsigned>(ctx->num_sms), block = 256;
     double best = 0;
 
     for (int rep = 0; rep < 4 && err == cudaSuccess; ++rep) {   // first repetition = warm-up
 
         cudaEventRecord(ev0, s);
-        logPeakKernel<<<grid, block, 0, s>>>(iterations, 0.5, d_sink);
+        kernel<<<grid, block, 0, s>>>(iterations, 0.5, d_sink);
         ctx->launches++;
         cudaEventRecord(ev1, s);
         err = cudaEventSynchronize(ev1);
 
         float ms = 0;
         if (err == cudaSuccess) { err = cudaEventElapsedTime(&ms, ev0, ev1); }
-        if (err == cudaSuccess && rep > 0 && ms > 0) { best = std::max(best, 4.0 * iterations * grid * block / (ms * 1e-3)); }
+        if (err == cudaSuccess && rep > 0 && ms > 0) { best = std::max(best, per_thread * iterations * grid * block / (ms * 1e-3)); }
     }
 
     if (ev0) { cudaEventDestroy(ev0); }
     if (ev1) { cudaEventDestroy(ev1); }
     cudaFreeAsync(d_sink, s);
 
-    if (err != cudaSuccess) { return rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("rpvg_b200_log_peak: ") + cudaGetErrorString(err)); }
+    if (err != cudaSuccess) { return rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string(name) + ": " + cudaGetErrorString(err)); }
 
-    *logs_per_second = best;
+    *per_second = best;
     return RPVG_B200_OK;
+}
+
+}
+
+extern "C" int rpvg_b200_fp64_peak(rpvg_b200_ctx * ctx, double * fma_per_second) {
+
+    if (!ctx || !fma_per_second) { return RPVG_B200_ERR_INVALID; }
+    return peakOf(ctx, fmaPeakKernel, 20000, 8.0, "rpvg_b200_fp64_peak", fma_per_second);
+}
+
+extern "C" int rpvg_b200_log_peak(rpvg_b200_ctx * ctx, double * logs_per_second) {
+
+    if (!ctx || !logs_per_second) { return RPVG_B200_ERR_INVALID; }
+    return peakOf(ctx, logPeakKernel, 2000, 4.0, "rpvg_b200_log_peak", logs_per_second);
 }

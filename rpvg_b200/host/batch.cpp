@@ -510,8 +510,22 @@ void NestedPathAbundanceEstimator::estimateBatch(const vector<PathClusterEstimat
     // this thread)
     lap("A flatten");
 
-    #pragma omp parallel for schedule(dynamic, 8)
-    for (size_t k = 0; k < items.size(); ++k) { items[k].source_groups = findPathSourceGroups(estimates[items[k].index]->paths); }
+    // (the cost is the number of haplotype ids a cluster's paths carry: the largest clusters go first, one at a time)
+    {
+        vector<pair<uint64_t, uint32_t> > by_cost(items.size());
+        for (size_t k = 0; k < items.size(); ++k) {
+            uint64_t ids = 0;
+            for (auto & path: estimates[items[k].index]->paths) { ids += path.source_ids.size(); }
+            by_cost[k] = make_pair(ids, static_cast<uint32_t>(k));
+        }
+        sort(by_cost.begin(), by_cost.end(), [](const pair<uint64_t, uint32_t> & a, const pair<uint64_t, uint32_t> & b) { return a.first > b.first || (a.first == b.first && a.second < b.second); });
+
+        #pragma omp parallel for schedule(dynamic, 1)
+        for (size_t q = 0; q < by_cost.size(); ++q) {
+            const size_t k = by_cost[q].second;
+            items[k].source_groups = findPathSourceGroups(estimates[items[k].index]->paths);
+        }
+    }
 
     auto * ctx = threadContext();
     rpvg_b200_clusters clusters = arena.view();
