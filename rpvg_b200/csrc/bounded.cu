@@ -156,8 +156,8 @@ struct PairStage {
     // [read class][column of the tile]: 32 first, then 32 second groups. A thread's four second groups lie 8 apart, so the
     // eight threads that share its first groups read consecutive words: no bank conflicts (pitch 65).
     double col[kPairRowChunk][2 * kPairTile + 1];
-    double noise[kPairRowChunk];      // noise of the read class, times its scale on the fast routes
-    double half[kPairRowChunk];       // scale / 2 (1 / 2 for the read classes that take logs)
+    double2 noise_half[kPairRowChunk];   // x: noise of the read class, times its scale on the fast routes; y: scale / 2 (1 / 2
+                                         // for the read classes that take logs) — one 16-byte load
     double count[kPairRowChunk];
     int32_t floor_[kPairRowChunk];    // count x binary orders the scaled terms of the read class can lie below 1
     uint32_t power[kPairRowChunk];
@@ -311,8 +311,7 @@ __global__ void __launch_bounds__(kPairThreads) pairTileKernel(const PairTileArg
         if (warp == 0) {
             // scale = 2^-(top_order + 1)
             const double scale = fast ? __hiloint2double((1023 - (top_order + 1)) << 20, 0) : 1.0;
-            st.noise[slot] = m.noise * scale;
-            st.half[slot] = 0.5 * scale;
+            st.noise_half[slot] = make_double2(m.noise * scale, 0.5 * scale);
             st.count[slot] = m.count;
             st.floor_[slot] = fast ? orders * static_cast<int32_t>(m.count) : 0;
             st.power[slot] = fast ? static_cast<uint32_t>(m.count) : 0u;
@@ -356,8 +355,9 @@ __global__ void __launch_bounds__(kPairThreads) pairTileKernel(const PairTileArg
         // read classes seen once, four at a time (each is at most a quarter of the depth limit deep)
         auto once_row = [&](const uint32_t r) {
 
-            const double hs = st.half[r];
-            const double nzr = st.noise[r];
+            const double2 nh = st.noise_half[r];
+            const double hs = nh.y;
+            const double nzr = nh.x;
             const double first0 = fma(st.col[r][li], hs, nzr);
             const double first1 = fma(st.col[r][li + 16], hs, nzr);
 
@@ -396,8 +396,9 @@ __global__ void __launch_bounds__(kPairThreads) pairTileKernel(const PairTileArg
             depth += st.floor_[r];
 
             const uint32_t power = st.power[r];
-            const double hs = st.half[r];
-            const double nzr = st.noise[r];
+            const double2 nh = st.noise_half[r];
+            const double hs = nh.y;
+            const double nzr = nh.x;
             const double first0 = fma(st.col[r][li], hs, nzr);
             const double first1 = fma(st.col[r][li + 16], hs, nzr);
 
@@ -440,7 +441,7 @@ __global__ void __launch_bounds__(kPairThreads) pairTileKernel(const PairTileArg
         for (; r < n_chunk; ++r) {
 
             const double weight = st.count[r];
-            const double nzr = st.noise[r];
+            const double nzr = st.noise_half[r].x;
             const double first0 = nzr + st.col[r][li] / 2.0;
             const double first1 = nzr + st.col[r][li + 16] / 2.0;
 
@@ -551,7 +552,17 @@ __global__ void __launch_bounds__(kPairThreads) pairCombineKernel(const PairTile
 
             double acc = 0, comp = 0;
             for (uint32_t sp = 0; sp < n_splits; ++sp) {
-                const double y = args.partial[(item + sp) * (kPairTile * kPairTile) + tid * 8 + a * 4 + q] - comp;
+
+                const double part = args.partial[(item + sp) * (kPairTile * kPairTile) + tid * 8 + a * 4 + q];
+
+                // (a row range with a zero term is -inf: plain addition, the compensation would turn it into NaN)
+                if (!(fabs(part) <= DBL_MAX) || !(fabs(acc) <= DBL_MAX)) {
+                    acc += part;
+                    comp = 0;
+                    continue;
+                }
+
+                const double y = part - comp;
                 const double t = acc + y;
                 comp = (t - acc) - y;
                 acc = t;
@@ -889,7 +900,7 @@ extern "C" int rpvg_b200_grouped_bounded_pairs(rpvg_b200_ctx * ctx, rpvg_b200_gr
             uint32_t most_rows = 0;
             for (auto & t: tiles) { most_rows = std::max(most_rows, n_classes[t.x]); }
 
-            const uint64_t want_items = 4ull * static_cast<uint64_t>(ctx->num_sms);
+            const uint64_t want_items = 32ull * static_cast<uint64_t>(ctx->num_sms);
             uint32_t rows_per_split = std::max(most_rows, kPairRowChunk);
 
             if (tiles.size() < want_items) {
