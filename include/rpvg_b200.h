@@ -131,9 +131,9 @@ typedef struct {
 
 int rpvg_b200_group_loglik(rpvg_b200_ctx * ctx, const rpvg_b200_loglik_problems * problems, double * loglik);
 
-/* Micro-benchmark: fp64 log() evaluations per second this GPU sustains with the instruction mix of the log-likelihood
- * kernels and no memory traffic (a few milliseconds). The denominator of their roofline: they are bound by the fp64 log,
- * not by HBM (no counterpart in the reference; MEASURED_PEAKS.json has no such figure). */
+/* Micro-benchmark: fp64 log() evaluations per second this GPU sustains (a log, an add and a fused multiply-add per
+ * evaluation, no memory traffic; a few milliseconds). The bound of every kernel that takes a log per term, as the
+ * reference's formulation does (no counterpart in the reference; MEASURED_PEAKS.json has no such figure). */
 int rpvg_b200_log_peak(rpvg_b200_ctx * ctx, double * logs_per_second);
 
 /* Micro-benchmark: fp64 fused multiply-adds per second (independent chains, no memory traffic). The pair kernel of
@@ -230,8 +230,9 @@ int rpvg_b200_grouped_upload(rpvg_b200_ctx * ctx, const rpvg_b200_loglik_problem
  * out fail the exact test as well and never hold the running maximum. */
 int rpvg_b200_grouped_bounded_pairs(rpvg_b200_ctx * ctx, rpvg_b200_grouped * grouped, const uint64_t * group_offset, const uint32_t * order, const double * log_freq,
                                     double min_log_diff, const uint64_t ** cand_offset, const uint32_t ** cand_pair, const double ** cand_loglik);
-/* Device time (CUDA events around the pair kernels) and number of log evaluations (pairs x read classes) summed over the
- * rpvg_b200_grouped_bounded_pairs calls made on this handle: what bench.py's log-throughput roofline is computed from. */
+/* Device time (CUDA events around the pair kernels) and number of terms (pairs x read classes: a log each in the
+ * reference's formulation) summed over the rpvg_b200_grouped_bounded_pairs calls made on this handle: what bench.py's
+ * roofline of the pair kernel is computed from. */
 int rpvg_b200_grouped_pair_stats(const rpvg_b200_grouped * grouped, double * kernel_ms, double * log_evaluations);
 void rpvg_b200_grouped_free(rpvg_b200_ctx * ctx, rpvg_b200_grouped * grouped);
 
