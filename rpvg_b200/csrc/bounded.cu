@@ -28,6 +28,9 @@
 // Scan: boundedScanKernel, one CTA per cluster: exclusive prefix maximum in pair order, test, compaction.
 
 #include <cfloat>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <string>
 #include <vector>
 
@@ -838,6 +841,17 @@ extern "C" int rpvg_b200_grouped_bounded_pairs(rpvg_b200_ctx * ctx, rpvg_b200_gr
     uint32_t * d_out_pair = reinterpret_cast<uint32_t *>(take(4 * NP));
     double * d_out_loglik = d_pair_ll;   // free once the first kernel is through
 
+    // stage times on stderr when RPVG_B200_BATCH_TRACE is set (each lap synchronises the stream: tracing only)
+    const bool trace = std::getenv("RPVG_B200_BATCH_TRACE") != nullptr;
+    auto lap_from = std::chrono::steady_clock::now();
+    auto lap = [&](const char * what) {
+        if (!trace) { return; }
+        cudaStreamSynchronize(s);
+        const auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "[rpvg_b200 pairs] %s: %.3f ms\n", what, std::chrono::duration<double, std::milli>(now - lap_from).count());
+        lap_from = now;
+    };
+
     cudaError_t err = cudaMemcpyAsync(d_pair_offset, pair_offset.data(), 8 * (C + 1), cudaMemcpyHostToDevice, s);
     if (err == cudaSuccess) { err = cudaMemcpyAsync(d_order, order, 4 * G, cudaMemcpyHostToDevice, s); }
     if (err == cudaSuccess) { err = cudaMemcpyAsync(d_log_freq, log_freq, 8 * G, cudaMemcpyHostToDevice, s); }
@@ -976,6 +990,8 @@ extern "C" int rpvg_b200_grouped_bounded_pairs(rpvg_b200_ctx * ctx, rpvg_b200_gr
                 err = cudaGetLastError();
             }
 
+            lap("row maxima, bounds, fill");
+
             // wave 1: tile row 0 of every cluster
             std::vector<uint4> tiles;
             for (uint32_t c = 0; c < C; ++c) {
@@ -983,6 +999,7 @@ extern "C" int rpvg_b200_grouped_bounded_pairs(rpvg_b200_ctx * ctx, rpvg_b200_gr
                 for (uint32_t tj = 0; tj < side; ++tj) { tiles.push_back(make_uint4(c, tj << 16, 0, 1)); }
             }
             run_wave(tiles);
+            lap("wave 1");
 
             if (err == cudaSuccess) {
                 pairHeadMaxKernel<<<C, kBoundedThreads, 0, s>>>(args, kPairTile, d_head_max);
@@ -992,6 +1009,8 @@ extern "C" int rpvg_b200_grouped_bounded_pairs(rpvg_b200_ctx * ctx, rpvg_b200_gr
             if (err == cudaSuccess) { err = cudaMemcpyAsync(bound.data(), d_bound, 8 * G, cudaMemcpyDeviceToHost, s); }
             if (err == cudaSuccess) { err = cudaMemcpyAsync(head_max.data(), d_head_max, 8 * static_cast<size_t>(C), cudaMemcpyDeviceToHost, s); }
             if (err == cudaSuccess) { err = cudaStreamSynchronize(s); }
+
+            lap("head maxima to the host");
 
             // wave 2: the other tile rows that hold a first group still in reach
             tiles.clear();
@@ -1009,6 +1028,7 @@ extern "C" int rpvg_b200_grouped_bounded_pairs(rpvg_b200_ctx * ctx, rpvg_b200_gr
                 }
             }
             run_wave(tiles);
+            lap("wave 2");
 
             if (err == cudaSuccess) {
                 boundedScanKernel<<<C, kScanThreads, 0, s>>>(args);
@@ -1030,6 +1050,8 @@ extern "C" int rpvg_b200_grouped_bounded_pairs(rpvg_b200_ctx * ctx, rpvg_b200_gr
         if (ev1) { cudaEventDestroy(ev1); }
         if (extra) { cudaFreeAsync(extra, s); }
     }
+
+    lap("scan");
 
     if (err == cudaSuccess) { err = cudaMemcpyAsync(n_candidates.data(), d_n_candidates, 4 * C, cudaMemcpyDeviceToHost, s); }
     if (err == cudaSuccess) { err = cudaStreamSynchronize(s); }
@@ -1059,6 +1081,8 @@ extern "C" int rpvg_b200_grouped_bounded_pairs(rpvg_b200_ctx * ctx, rpvg_b200_gr
 
         if (err == cudaSuccess) { err = cudaStreamSynchronize(s); }
     }
+
+    lap("candidates to the host");
 
     cudaFreeAsync(base, s);
 

@@ -146,6 +146,88 @@ vector<vector<uint32_t> > NestedPathAbundanceEstimator::findPathGroups(const vec
 // group whose count is its multiplicity. Groups come out in the hash map's iteration order (of their first haplotype).
 pair<vector<vector<uint32_t> >, vector<uint32_t> > NestedPathAbundanceEstimator::findPathSourceGroups(const vector<PathInfo> & paths) const {
 
+    // The reference's map from haplotype id to the paths that carry it (rpvg:src/path_abundance_estimator.cpp:495-504:
+    // emplace + push_back per (path, id)) is only ever walked in its iteration order, which depends on the sequence of
+    // insertions alone, i.e. on the order in which the ids are first met — not on the mapped type. So the lists are
+    // gathered in one flat array by counting (no hashing and no allocation per (path, id) pair: a 1000GP-scale batch has
+    // millions of them), and a map from id to id receives every id once, in first-met order: same keys in the same
+    // sequence, same order of iteration.
+    // (the id sets are walked once, in their own order; everything after that runs over a flat copy)
+    size_t n_pairs = 0;
+    for (auto & path: paths) { n_pairs += path.source_ids.size(); }
+
+    vector<uint32_t> pair_id;
+    vector<uint32_t> pair_path;
+    pair_id.reserve(n_pairs);
+    pair_path.reserve(n_pairs);
+
+    uint32_t max_id = 0;
+    for (size_t i = 0; i < paths.size(); ++i) {
+        for (auto & id: paths[i].source_ids) {
+            max_id = max(max_id, id);
+            pair_id.push_back(id);
+            pair_path.push_back(static_cast<uint32_t>(i));
+        }
+    }
+
+    pair<vector<vector<uint32_t> >, vector<uint32_t> > path_source_groups;
+
+    if (n_pairs > 0 && static_cast<size_t>(max_id) <= 64 * n_pairs + 1024) {
+
+        vector<uint32_t> begin(static_cast<size_t>(max_id) + 2, 0);
+        vector<uint32_t> first_met;
+
+        for (auto id: pair_id) {
+            if (begin[id + 1]++ == 0) { first_met.push_back(id); }
+        }
+
+        for (size_t id = 0; id + 1 < begin.size(); ++id) { begin[id + 1] += begin[id]; }
+
+        vector<uint32_t> flat(n_pairs);
+        {
+            vector<uint32_t> cursor(begin.begin(), begin.end() - 1);
+            for (size_t k = 0; k < n_pairs; ++k) { flat[cursor[pair_id[k]]++] = pair_path[k]; }
+        }
+
+        rpvg_b200_host::hash_map<uint32_t, uint32_t> id_order;
+        for (auto id: first_met) { id_order.emplace(id, id); }
+
+        // One pass instead of the reference's comparison of every list with every later one: a group is emitted when its
+        // path list is first met in the map's iteration order, every later haplotype with that list adds one to its count.
+        // (lists are compared through a 64-bit hash first; its map is only looked up, never walked)
+        std::unordered_map<uint64_t, vector<uint32_t> > groups_of_hash;
+
+        for (auto it = id_order.begin(); it != id_order.end(); ++it) {
+
+            const uint32_t * list = flat.data() + begin[it->first];
+            const size_t len = begin[it->first + 1] - begin[it->first];
+
+            uint64_t h = 1469598103934665603ull ^ len;
+            for (size_t k = 0; k < len; ++k) { h = (h ^ list[k]) * 1099511628211ull; }
+
+            auto & candidates = groups_of_hash[h];
+            bool found = false;
+
+            for (auto g: candidates) {
+                const auto & have = path_source_groups.first[g];
+                if (have.size() == len && equal(have.begin(), have.end(), list)) {
+                    path_source_groups.second[g]++;
+                    found = true;
+                    break;
+                }
+            }
+
+            if (!found) {
+                candidates.push_back(static_cast<uint32_t>(path_source_groups.first.size()));
+                path_source_groups.first.emplace_back(list, list + len);
+                path_source_groups.second.emplace_back(1);
+            }
+        }
+
+        return path_source_groups;
+    }
+
+    // (ids too sparse for a table: the reference's own sequence of operations)
     rpvg_b200_host::hash_map<uint32_t, vector<uint32_t> > source_id_paths;
 
     for (size_t i = 0; i < paths.size(); ++i) {
@@ -155,10 +237,6 @@ pair<vector<vector<uint32_t> >, vector<uint32_t> > NestedPathAbundanceEstimator:
         }
     }
 
-    // The reference compares every haplotype's list with every later one (quadratic in the haplotype ids of the cluster:
-    // ~5,000 at 1000GP scale). The same groups in the same order come out of one pass: a group is emitted when its path
-    // list is first met in the map's iteration order, every later haplotype with that list adds one to its count.
-    pair<vector<vector<uint32_t> >, vector<uint32_t> > path_source_groups;
     rpvg_b200_host::hash_map<vector<uint32_t>, uint32_t> group_of_list;
 
     for (auto it = source_id_paths.begin(); it != source_id_paths.end(); ++it) {
