@@ -78,7 +78,7 @@ def run(args, rank, local_rank, world, ClockSampler, host_threads):
     arena, cfg, what = build_config(args.config, args.scale)
     nested = cfg.model == loader.MODEL_HAPLOTYPE_TRANSCRIPTS
     config = {"workload": what if args.scale == 1.0 else f"DEBUG scale={args.scale}: {what}", "clusters": arena.n_clusters, "paths": arena.n_paths,
-              "read_classes": arena.n_reads, "sharding": f"clusters dealt to {world} rank(s) by LPT on path non-zeros, no collective",
+              "read_classes": arena.n_reads, "sharding": f"clusters dealt to {world} rank(s) by LPT on the model's cost (pairs x read classes, or path non-zeros), no collective",
               "l2": "inputs come from host memory every step (nothing stays resident between steps)"}
     metric, unit = "inference_stage_reads_per_second", "reads/s"
     cost = dense_cost(arena, nested)
@@ -129,9 +129,17 @@ def run(args, rank, local_rank, world, ClockSampler, host_threads):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
+    # torchrun sets OMP_NUM_THREADS=1 for its workers: the host stages of estimateBatch (flatten, haplotype groups, plans)
+    # are OpenMP loops, every rank gets its share of the cores (read when the harness library brings in the OpenMP runtime)
+    if world > 1:
+        os.environ["OMP_NUM_THREADS"] = str(max(1, host_threads() // world))
+
     harness = loader.load_harness(os.path.join(ROOT, "tests", "_build", "libharness_b200.so"))
+    harness.harness_set_threads(max(1, host_threads() // world))
+    # clusters dealt by the cost of the model: pairs x read classes for the haplotype models, path non-zeros otherwise
     nnz = np.diff(arena.row_ptr[arena.read_offset.astype(np.int64)].astype(np.int64)).astype(np.float64) + 1
-    mine = [int(c) for c in multi_gpu.lpt_partition(nnz, world)[rank]]
+    weight = cost + nnz if (nested or cfg.model == loader.MODEL_HAPLOTYPES) else nnz
+    mine = [int(c) for c in multi_gpu.lpt_partition(weight, world)[rank]]
 
     def barrier():
         if world > 1:

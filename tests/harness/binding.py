@@ -46,6 +46,8 @@ def make_config(model, group_size=2, min_hap_prob=0.001, infer_collapsed=True, u
 def _bind_harness(l):
     l.harness_impl_name.restype = C.c_char_p
     l.harness_max_threads.restype = C.c_int32
+    l.harness_set_threads.argtypes = [C.c_int32]
+    l.harness_set_threads.restype = None
     l.harness_estimator_create.restype = C.c_void_p
     l.harness_estimator_create.argtypes = [C.POINTER(HarnessConfig)]
     l.harness_estimator_destroy.argtypes = [C.c_void_p]

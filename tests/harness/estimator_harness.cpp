@@ -153,6 +153,12 @@ int32_t harness_max_threads(void) {
     return omp_get_max_threads();
 }
 
+// Host threads of the calls that follow (launchers such as torchrun export OMP_NUM_THREADS=1 to their workers).
+void harness_set_threads(int32_t num_threads) {
+
+    if (num_threads > 0) { omp_set_num_threads(num_threads); }
+}
+
 // The factory of main.cpp:766-788.
 void * harness_estimator_create(const HarnessConfig * cfg) {
 

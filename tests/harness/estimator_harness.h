@@ -99,6 +99,7 @@ const HarnessResult * harness_result_view(void * handle);
 void harness_result_free(void * handle);
 
 int32_t harness_max_threads(void);
+void harness_set_threads(int32_t num_threads);
 
 #ifdef HARNESS_REFERENCE
 /* ---- kernel-level oracles: the reference's protected members, called one by one ---- */
