@@ -87,11 +87,16 @@ __global__ void coverWeightsKernel(uint64_t n_paths, const uint64_t * __restrict
 // the counts are kept up to date instead: a read class is zeroed exactly once, and when it is, its count is taken off
 // every column that holds it (the entries of its row). All sums are sums of integers below 2^53 — exact in fp64 whatever
 // the order, atomics included — so the scores, and with them the picks, are the reference's. Work: O(entries + picks x N).
-__global__ void __launch_bounds__(kCoverThreads) coverKernel(const uint64_t * __restrict__ read_offset, const uint64_t * __restrict__ path_offset,
-                                                             const uint64_t * __restrict__ row_ptr, const uint32_t * __restrict__ col,
-                                                             const uint64_t * __restrict__ col_ptr, const uint32_t * __restrict__ csc_row,
-                                                             const double * __restrict__ weight, double * uncovered, double * covered, uint8_t * __restrict__ in_cover,
-                                                             const uint32_t * __restrict__ error) {
+// The picks of a cluster are sequential and each is a scan over its paths: the clusters with many paths (`list`, or all
+// when it is NULL) get a CTA of 1024 threads, the others one of 256.
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS) coverKernel(const uint64_t * __restrict__ read_offset, const uint64_t * __restrict__ path_offset,
+                                                       const uint64_t * __restrict__ row_ptr, const uint32_t * __restrict__ col,
+                                                       const uint64_t * __restrict__ col_ptr, const uint32_t * __restrict__ csc_row,
+                                                       const double * __restrict__ weight, double * uncovered, double * covered, uint8_t * __restrict__ in_cover,
+                                                       const uint32_t * __restrict__ error, const uint32_t * __restrict__ list) {
+
+    constexpr int kCoverThreads = THREADS;   // (shadows the small kernels' constant)
 
     __shared__ double best_score[kCoverThreads / 32];
     __shared__ uint32_t best_index[kCoverThreads / 32];
@@ -100,7 +105,7 @@ __global__ void __launch_bounds__(kCoverThreads) coverKernel(const uint64_t * __
 
     if (*error) { return; }
 
-    const uint32_t c = blockIdx.x;
+    const uint32_t c = list ? list[blockIdx.x] : blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int num_warps = kCoverThreads / 32;
 
@@ -140,7 +145,9 @@ __global__ void __launch_bounds__(kCoverThreads) coverKernel(const uint64_t * __
         uint32_t index = 0xffffffffu;
 
         for (uint32_t j = tid; j < N; j += kCoverThreads) {   // ascending j per thread: its first maximum stays
-            const double s = covered[p0 + j] / weight[p0 + j];
+            const double count = covered[p0 + j];
+            if (!(count > 0)) { continue; }   // (0 / weight is never above the score the scan starts from: most paths, soon)
+            const double s = count / weight[p0 + j];
             if (s > score) {
                 score = s;
                 index = j;
@@ -164,16 +171,22 @@ __global__ void __launch_bounds__(kCoverThreads) coverKernel(const uint64_t * __
         }
         __syncthreads();
 
-        if (tid == 0) {
-            double s = 0;
-            uint32_t best = 0xffffffffu;
-            for (int wi = 0; wi < num_warps; ++wi) {
-                if (best_index[wi] != 0xffffffffu && (best == 0xffffffffu || best_score[wi] > s || (best_score[wi] == s && best_index[wi] < best))) {
-                    s = best_score[wi];
-                    best = best_index[wi];
+        if (warp == 0) {
+
+            double s = lane < num_warps ? best_score[lane] : 0.0;
+            uint32_t best = lane < num_warps ? best_index[lane] : 0xffffffffu;
+
+            #pragma unroll
+            for (int off = 16; off > 0; off >>= 1) {
+                const double other_score = __shfl_xor_sync(0xffffffffu, s, off);
+                const uint32_t other_index = __shfl_xor_sync(0xffffffffu, best, off);
+                if (other_index != 0xffffffffu && (best == 0xffffffffu || other_score > s || (other_score == s && other_index < best))) {
+                    s = other_score;
+                    best = other_index;
                 }
             }
-            pick_shared = static_cast<int>(best);
+
+            if (lane == 0) { pick_shared = static_cast<int>(best); }
         }
         __syncthreads();
 
@@ -289,7 +302,37 @@ extern "C" int rpvg_b200_path_cover(rpvg_b200_ctx * ctx, const rpvg_b200_cluster
     if (err == cudaSuccess) {
         coverColumnPointerKernel<<<static_cast<unsigned>((P + 1 + 255) / 256), 256, 0, s>>>(P, Z, d_key_out, d_col_ptr);
         coverWeightsKernel<<<static_cast<unsigned>((P + 255) / 256), 256, 0, s>>>(P, d_col_ptr, d_idx_out, d_entry_row, d_prob, d_cnt, d_csc_row, d_weight);
-        coverKernel<<<C, kCoverThreads, 0, s>>>(d_read_offset, d_path_offset, d_row_ptr, d_col, d_col_ptr, d_csc_row, d_weight, d_cnt, d_covered, d_in_cover, d_error);
+        // clusters of many paths on CTAs of 1024 threads (first: they take longest), the others on CTAs of 256
+        std::vector<uint32_t> wide, narrow;
+        for (uint32_t c = 0; c < C; ++c) { (cl->path_offset[c + 1] - cl->path_offset[c] >= 512 ? wide : narrow).push_back(c); }
+
+        uint32_t * d_list = nullptr;
+        err = cudaMallocFromPoolAsync(reinterpret_cast<void **>(&d_list), 4 * static_cast<size_t>(C), ctx->pool, s);
+        if (err == cudaSuccess && !wide.empty()) { err = cudaMemcpyAsync(d_list, wide.data(), 4 * wide.size(), cudaMemcpyHostToDevice, s); }
+        if (err == cudaSuccess && !narrow.empty()) { err = cudaMemcpyAsync(d_list + wide.size(), narrow.data(), 4 * narrow.size(), cudaMemcpyHostToDevice, s); }
+
+        // (the narrow ones on a side stream beside the wide ones: a few CTAs of 1024 threads do not fill the GPU)
+        cudaStream_t side = (!wide.empty() && !narrow.empty() && !ctx->side_streams.empty()) ? ctx->side_streams[0] : s;
+
+        if (err == cudaSuccess && side != s) {
+            cudaEventRecord(ctx->fork_event, s);
+            cudaStreamWaitEvent(side, ctx->fork_event, 0);
+        }
+        if (err == cudaSuccess && !wide.empty()) {
+            coverKernel<1024><<<static_cast<unsigned>(wide.size()), 1024, 0, s>>>(d_read_offset, d_path_offset, d_row_ptr, d_col, d_col_ptr, d_csc_row, d_weight, d_cnt, d_covered, d_in_cover,
+                                                                                  d_error, d_list);
+            ctx->launches++;
+        }
+        if (err == cudaSuccess && !narrow.empty()) {
+            coverKernel<kCoverThreads><<<static_cast<unsigned>(narrow.size()), kCoverThreads, 0, side>>>(d_read_offset, d_path_offset, d_row_ptr, d_col, d_col_ptr, d_csc_row, d_weight, d_cnt,
+                                                                                                         d_covered, d_in_cover, d_error, d_list + wide.size());
+        }
+        if (err == cudaSuccess && side != s) {
+            cudaEventRecord(ctx->join_events[0], side);
+            cudaStreamWaitEvent(s, ctx->join_events[0], 0);
+        }
+        if (err == cudaSuccess) { err = cudaStreamSynchronize(s); }   // (the lists are host vectors)
+        if (d_list) { cudaFreeAsync(d_list, s); }
         ctx->launches += 3;
         err = cudaGetLastError();
     }
@@ -420,7 +463,11 @@ extern "C" int rpvg_b200_weighted_path_cover(rpvg_b200_ctx * ctx, uint32_t n_rea
     if (err == cudaSuccess) {
         coverColumnPointerKernel<<<static_cast<unsigned>((P + 1 + 255) / 256), 256, 0, s>>>(P, Z, d_key_out, d_col_ptr);
         if (Z > 0) { coverGivenColumnsKernel<<<static_cast<unsigned>((Z + 255) / 256), 256, 0, s>>>(Z, d_idx_out, d_entry_row, d_csc_row); }
-        coverKernel<<<1, kCoverThreads, 0, s>>>(d_read_offset, d_path_offset, d_row_ptr, d_col, d_col_ptr, d_csc_row, d_weight, d_cnt, d_covered, d_in_cover, d_error);
+        if (n_paths >= 512) {
+            coverKernel<1024><<<1, 1024, 0, s>>>(d_read_offset, d_path_offset, d_row_ptr, d_col, d_col_ptr, d_csc_row, d_weight, d_cnt, d_covered, d_in_cover, d_error, nullptr);
+        } else {
+            coverKernel<kCoverThreads><<<1, kCoverThreads, 0, s>>>(d_read_offset, d_path_offset, d_row_ptr, d_col, d_col_ptr, d_csc_row, d_weight, d_cnt, d_covered, d_in_cover, d_error, nullptr);
+        }
         ctx->launches += 3;
         err = cudaGetLastError();
     }
