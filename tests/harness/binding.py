@@ -48,6 +48,8 @@ def _bind_harness(l):
     l.harness_max_threads.restype = C.c_int32
     l.harness_set_threads.argtypes = [C.c_int32]
     l.harness_set_threads.restype = None
+    l.harness_source_groups.argtypes = [C.c_uint32] + [C.c_void_p] * 5
+    l.harness_source_groups.restype = C.c_uint32
     l.harness_estimator_create.restype = C.c_void_p
     l.harness_estimator_create.argtypes = [C.POINTER(HarnessConfig)]
     l.harness_estimator_destroy.argtypes = [C.c_void_p]
@@ -193,3 +195,19 @@ def harness_estimate_batched(lib_, config: HarnessConfig, arena, cluster_ids=Non
         lib_.harness_estimator_destroy(est)
 
 
+
+
+def harness_source_groups(lib, id_lists):
+    """findPathSourceGroups of the haplotype-transcripts class on paths carrying the given haplotype ids (one list per path,
+    inserted in list order). Returns (groups: list of path-index lists in output order, counts)."""
+    n = len(id_lists)
+    id_ptr = np.zeros(n + 1, dtype=np.uint64)
+    id_ptr[1:] = np.cumsum([len(x) for x in id_lists])
+    ids = np.asarray([i for x in id_lists for i in x], dtype=np.uint32)
+    total = max(1, int(id_ptr[-1]))
+    group_ptr = np.zeros(total + 1, dtype=np.uint64)
+    group_paths = np.zeros(total, dtype=np.uint32)
+    group_counts = np.zeros(total, dtype=np.uint32)
+    g = lib.harness_source_groups(n, id_ptr.ctypes.data, ids.ctypes.data if ids.size else None, group_ptr.ctypes.data, group_paths.ctypes.data, group_counts.ctypes.data)
+    groups = [[int(p) for p in group_paths[int(group_ptr[k]):int(group_ptr[k + 1])]] for k in range(g)]
+    return groups, [int(c) for c in group_counts[:g]]

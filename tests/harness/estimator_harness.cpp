@@ -159,6 +159,32 @@ void harness_set_threads(int32_t num_threads) {
     if (num_threads > 0) { omp_set_num_threads(num_threads); }
 }
 
+// findPathSourceGroups of the haplotype-transcripts class (a host routine: no device involved), on paths that carry the
+// given haplotype ids, inserted in the given order.
+uint32_t harness_source_groups(uint32_t n_paths, const uint64_t * id_ptr, const uint32_t * ids, uint64_t * out_group_ptr, uint32_t * out_group_paths, uint32_t * out_group_counts) {
+
+    vector<PathInfo> paths;
+    paths.reserve(n_paths);
+
+    for (uint32_t p = 0; p < n_paths; ++p) {
+        paths.emplace_back("path" + to_string(p));
+        for (uint64_t k = id_ptr[p]; k < id_ptr[p + 1]; ++k) { paths.back().source_ids.insert(ids[k]); }
+        paths.back().source_count = static_cast<uint32_t>(paths.back().source_ids.size());
+    }
+
+    NestedPathAbundanceEstimator estimator(2, 0.01, true, false, 100, 0.001, 0, 1, 1e-8);
+    const auto groups = estimator.findPathSourceGroups(paths);
+
+    out_group_ptr[0] = 0;
+    for (size_t g = 0; g < groups.first.size(); ++g) {
+        for (size_t k = 0; k < groups.first[g].size(); ++k) { out_group_paths[out_group_ptr[g] + k] = groups.first[g][k]; }
+        out_group_ptr[g + 1] = out_group_ptr[g] + groups.first[g].size();
+        out_group_counts[g] = groups.second[g];
+    }
+
+    return static_cast<uint32_t>(groups.first.size());
+}
+
 // The factory of main.cpp:766-788.
 void * harness_estimator_create(const HarnessConfig * cfg) {
 

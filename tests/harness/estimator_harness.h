@@ -101,6 +101,12 @@ void harness_result_free(void * handle);
 int32_t harness_max_threads(void);
 void harness_set_threads(int32_t num_threads);
 
+/* NestedPathAbundanceEstimator::findPathSourceGroups (rpvg:src/path_abundance_estimator.cpp:493-546; host only): path p
+ * carries the haplotype ids ids[id_ptr[p] .. id_ptr[p + 1]), inserted in that order. Groups in the order they come out:
+ * out_group_ptr [n_groups + 1] into out_group_paths (sized for the sum of all list lengths: at most the number of ids),
+ * out_group_counts [n_groups]. Returns n_groups. */
+uint32_t harness_source_groups(uint32_t n_paths, const uint64_t * id_ptr, const uint32_t * ids, uint64_t * out_group_ptr, uint32_t * out_group_paths, uint32_t * out_group_counts);
+
 #ifdef HARNESS_REFERENCE
 /* ---- kernel-level oracles: the reference's protected members, called one by one ---- */
 
