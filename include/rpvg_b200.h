@@ -301,6 +301,12 @@ typedef struct rpvg_b200_read_records {
 int rpvg_b200_merge_read_records(rpvg_b200_ctx * ctx, const rpvg_b200_read_records * records, double prob_precision, uint32_t * n_merged, uint32_t * record_class,
                                  uint32_t * merged_rep, uint32_t * merged_count);
 
+/* rpvg_b200_grouped_raw (the raw dense matrices of the haplotypes model, constructProbabilityMatrix,
+ * rpvg:src/path_estimator.cpp:55-77) from the read records as ReadPathProbabilities::pathProbs() holds them — a
+ * probability and the paths that share it — instead of the expanded arena: a third of the bytes cross the host link.
+ * path_offset [n_clusters + 1]: paths of every cluster. */
+int rpvg_b200_grouped_raw_records(rpvg_b200_ctx * ctx, const rpvg_b200_read_records * records, const uint64_t * path_offset, rpvg_b200_grouped ** grouped);
+
 /* ---- per-read path probabilities: the step right before the estimators' boundary ----
  * ReadPathProbabilities::addPathProbs (rpvg:src/read_path_probabilities.cpp:74-221) with calcAlignPathLogProbs (:39-67)
  * for all reads of a batch of clusters. Read r (of the cluster whose read_offset range holds it) owns the alignment paths

@@ -498,6 +498,148 @@ extern "C" int rpvg_b200_grouped_raw(rpvg_b200_ctx * ctx, const rpvg_b200_cluste
     return RPVG_B200_OK;
 }
 
+namespace {
+
+// one thread per read record: the probability of each of its groups scattered to the group's paths in the zero-filled
+// dense block of its cluster
+__global__ void rawRecordRowsKernel(const uint32_t n_clusters, const uint64_t n_reads, const uint64_t * __restrict__ read_offset, const uint64_t * __restrict__ path_offset,
+                                    const uint64_t * __restrict__ matrix_offset, const uint64_t * __restrict__ group_ptr, const double * __restrict__ group_prob,
+                                    const uint64_t * __restrict__ id_ptr, const uint32_t * __restrict__ ids, const uint32_t * __restrict__ count, double * __restrict__ matrix,
+                                    double * __restrict__ counts, uint32_t * __restrict__ rows_of_cluster) {
+
+    const uint64_t r = blockIdx.x * static_cast<uint64_t>(blockDim.x) + threadIdx.x;
+    if (r >= n_reads) { return; }
+
+    const uint32_t c = clusterOf(read_offset, n_clusters, r);
+    const uint64_t rows = read_offset[c + 1] - read_offset[c];
+    const uint64_t num_paths = path_offset[c + 1] - path_offset[c];
+    const uint64_t local = r - read_offset[c];
+
+    double * row = matrix + matrix_offset[c] + local;
+
+    for (uint64_t g = group_ptr[r]; g < group_ptr[r + 1]; ++g) {
+        const double p = group_prob[g];
+        for (uint64_t k = id_ptr[g]; k < id_ptr[g + 1]; ++k) {
+            const uint32_t j = ids[k];
+            if (j < num_paths) { row[j * rows] = p; }
+        }
+    }
+
+    counts[r] = static_cast<double>(count[r]);
+    if (local == 0) { rows_of_cluster[c] = static_cast<uint32_t>(rows); }
+}
+
+}
+
+// rpvg_b200_grouped_raw from read records as ReadPathProbabilities holds them (a probability and the paths that share
+// it): a third of the bytes of the expanded arena go over the host link.
+extern "C" int rpvg_b200_grouped_raw_records(rpvg_b200_ctx * ctx, const rpvg_b200_read_records * rec, const uint64_t * path_offset, rpvg_b200_grouped ** out) {
+
+    if (!ctx || !rec || !path_offset || !out) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "NULL argument"); }
+    *out = nullptr;
+    if (rec->n_clusters == 0) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "no clusters"); }
+    if (!rec->read_offset || !rec->group_ptr || !rec->id_ptr || !rec->noise || !rec->count) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "rpvg_b200_grouped_raw_records: NULL array"); }
+
+    const uint32_t C = rec->n_clusters;
+    const uint64_t R = rec->read_offset[C];
+    if (R == 0 || rec->read_offset[0] != 0 || path_offset[0] != 0) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "rpvg_b200_grouped_raw_records: no read records, or offsets that do not start at 0"); }
+
+    const uint64_t NG = rec->group_ptr[R];
+    if (rec->group_ptr[0] != 0 || rec->id_ptr[0] != 0) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "rpvg_b200_grouped_raw_records: pointers must start at 0"); }
+    for (uint64_t r = 0; r < R; ++r) {
+        if (rec->group_ptr[r + 1] < rec->group_ptr[r]) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "rpvg_b200_grouped_raw_records: group_ptr decreases"); }
+    }
+    for (uint64_t g = 0; g < NG; ++g) {
+        if (rec->id_ptr[g + 1] < rec->id_ptr[g]) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "rpvg_b200_grouped_raw_records: id_ptr decreases"); }
+    }
+    const uint64_t Z = rec->id_ptr[NG];
+    if ((NG > 0 && !rec->group_prob) || (Z > 0 && !rec->ids)) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "rpvg_b200_grouped_raw_records: NULL array"); }
+
+    std::vector<uint64_t> matrix_offset(C + 1, 0);
+    for (uint32_t c = 0; c < C; ++c) {
+        if (rec->read_offset[c + 1] < rec->read_offset[c] || path_offset[c + 1] < path_offset[c]) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "rpvg_b200_grouped_raw_records: offsets decrease"); }
+        const uint64_t rows = rec->read_offset[c + 1] - rec->read_offset[c];
+        const uint64_t num_paths = path_offset[c + 1] - path_offset[c];
+        if (rows == 0) { return rpvgFail(ctx, RPVG_B200_ERR_INVALID, "rpvg_b200_grouped_raw_records: a cluster has no read records"); }
+        if (num_paths >= 0xffffffffull) { return rpvgFail(ctx, RPVG_B200_ERR_LIMIT, "rpvg_b200_grouped_raw_records: too many paths in a cluster"); }
+        matrix_offset[c + 1] = matrix_offset[c] + rows * num_paths;
+    }
+
+    const uint64_t MX = matrix_offset[C];
+    if (R >= 0xffffffffull || MX >= (uint64_t(1) << 33)) { return rpvgFail(ctx, RPVG_B200_ERR_LIMIT, "dense matrices too large for one call (rows x paths)"); }
+
+    RPVG_CUDA(ctx, cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+
+    auto pad = [](size_t b) { return (b + 255) & ~size_t(255); };
+    const size_t bytes = 3 * pad(8 * (C + 1)) + pad(8 * (R + 1)) + pad(8 * NG) + pad(8 * (NG + 1)) + pad(4 * Z) + 2 * pad(8 * R) + pad(4 * R) + pad(8 * MX) + pad(4 * C) + 4096;
+
+    char * base = nullptr;
+    RPVG_CUDA(ctx, cudaMallocFromPoolAsync(reinterpret_cast<void **>(&base), bytes, ctx->pool, s));
+
+    size_t used = 0;
+    auto take = [&](size_t b) { char * q = base + used; used += pad(b); return q; };
+
+    uint64_t * d_read_offset = reinterpret_cast<uint64_t *>(take(8 * (C + 1)));
+    uint64_t * d_path_offset = reinterpret_cast<uint64_t *>(take(8 * (C + 1)));
+    uint64_t * d_matrix_offset = reinterpret_cast<uint64_t *>(take(8 * (C + 1)));
+    uint64_t * d_group_ptr = reinterpret_cast<uint64_t *>(take(8 * (R + 1)));
+    double * d_group_prob = reinterpret_cast<double *>(take(8 * NG));
+    uint64_t * d_id_ptr = reinterpret_cast<uint64_t *>(take(8 * (NG + 1)));
+    uint32_t * d_ids = reinterpret_cast<uint32_t *>(take(4 * Z));
+    double * d_noise = reinterpret_cast<double *>(take(8 * R));
+    double * d_counts = reinterpret_cast<double *>(take(8 * R));
+    uint32_t * d_count = reinterpret_cast<uint32_t *>(take(4 * R));
+    double * d_matrix = reinterpret_cast<double *>(take(8 * MX));
+    uint32_t * d_rows = reinterpret_cast<uint32_t *>(take(4 * C));
+
+    cudaError_t err = cudaSuccess;
+    auto up = [&](void * dst, const void * src, size_t n) {
+        if (err == cudaSuccess && n > 0) { err = cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, s); }
+    };
+
+    up(d_read_offset, rec->read_offset, 8 * (C + 1));
+    up(d_path_offset, path_offset, 8 * (C + 1));
+    up(d_matrix_offset, matrix_offset.data(), 8 * (C + 1));
+    up(d_group_ptr, rec->group_ptr, 8 * (R + 1));
+    up(d_group_prob, rec->group_prob, 8 * NG);
+    up(d_id_ptr, rec->id_ptr, 8 * (NG + 1));
+    up(d_ids, rec->ids, 4 * Z);
+    up(d_noise, rec->noise, 8 * R);
+    up(d_count, rec->count, 4 * R);
+
+    if (err == cudaSuccess) { err = cudaMemsetAsync(d_matrix, 0, 8 * MX, s); }
+
+    if (err == cudaSuccess) {
+        rawRecordRowsKernel<<<static_cast<unsigned>((R + 255) / 256), 256, 0, s>>>(C, R, d_read_offset, d_path_offset, d_matrix_offset, d_group_ptr, d_group_prob, d_id_ptr, d_ids, d_count,
+                                                                                  d_matrix, d_counts, d_rows);
+        ctx->launches++;
+        err = cudaGetLastError();
+    }
+
+    if (err == cudaSuccess) { err = cudaStreamSynchronize(s); }   // matrix_offset and the caller's arrays may go away
+
+    if (err != cudaSuccess) {
+        cudaFreeAsync(base, s);
+        return rpvgFail(ctx, RPVG_B200_ERR_CUDA, std::string("rpvg_b200_grouped_raw_records: ") + cudaGetErrorString(err));
+    }
+
+    auto * grouped = new rpvg_b200_grouped();
+    grouped->n_clusters = C;
+    grouped->base = base;
+    grouped->d_matrix = d_matrix;
+    grouped->d_noise = d_noise;
+    grouped->d_counts = d_counts;
+    grouped->d_row_offset = d_read_offset;
+    grouped->d_group_offset = d_path_offset;
+    grouped->d_matrix_offset = d_matrix_offset;
+    grouped->d_n_classes = d_rows;
+    grouped->h_rows_total = R;
+    *out = grouped;
+
+    return RPVG_B200_OK;
+}
+
 extern "C" void rpvg_b200_grouped_free(rpvg_b200_ctx * ctx, rpvg_b200_grouped * grouped) {
 
     if (!grouped) { return; }

@@ -11,6 +11,7 @@
 #include <cassert>
 #include <chrono>
 #include <cstdlib>
+#include <cstring>
 #include <iostream>
 #include <memory>
 #include <numeric>
@@ -194,6 +195,109 @@ struct BatchArena {
 }
 
 namespace {
+
+// Many clusters as read records (rpvg_b200_read_records): every pair<double, vector<uint32_t>> stays a probability and its
+// list of paths — what the dense matrices of the haplotypes model are filled from. A third of the arena's bytes.
+struct BatchRecords {
+
+    vector<uint64_t> read_offset = {0}, path_offset = {0};
+
+    // in page-locked memory of the thread's context (rpvg_b200_pinned_scratch)
+    uint64_t * group_ptr = nullptr, * id_ptr = nullptr;
+    uint32_t * ids = nullptr, * count = nullptr;
+    double * group_prob = nullptr, * noise = nullptr;
+
+    void build(rpvg_b200_ctx * ctx, const vector<const vector<ReadPathProbabilities> *> & members, const vector<uint32_t> & num_paths) {
+
+        const size_t n = members.size();
+
+        read_offset.assign(1, 0);
+        path_offset.assign(1, 0);
+
+        for (size_t k = 0; k < n; ++k) {
+            read_offset.push_back(read_offset.back() + members[k]->size());
+            path_offset.push_back(path_offset.back() + num_paths[k]);
+        }
+
+        const uint64_t R = read_offset.back();
+
+        struct Stretch { uint32_t cluster; uint32_t begin, end; };
+        constexpr uint32_t kStretchRows = 256;
+
+        vector<Stretch> stretches;
+        for (size_t k = 0; k < n; ++k) {
+            const uint32_t m = members[k]->size();
+            for (uint32_t b = 0; b < m; b += kStretchRows) { stretches.push_back({static_cast<uint32_t>(k), b, min(m, b + kStretchRows)}); }
+        }
+
+        group_ptr = static_cast<uint64_t *>(rpvg_b200_pinned_scratch(ctx, 0, sizeof(uint64_t) * (R + 1)));
+        noise = static_cast<double *>(rpvg_b200_pinned_scratch(ctx, 3, sizeof(double) * (R + 1)));
+        count = static_cast<uint32_t *>(rpvg_b200_pinned_scratch(ctx, 4, sizeof(uint32_t) * (R + 1)));
+        if (!group_ptr || !noise || !count) { fatalBatch(ctx, "rpvg_b200_pinned_scratch"); }
+
+        vector<uint64_t> first_id(R + 1, 0);
+
+        // pass 1: groups and ids of every record
+        #pragma omp parallel for schedule(dynamic, 4)
+        for (size_t q = 0; q < stretches.size(); ++q) {
+
+            const auto & st = stretches[q];
+            const auto & probs = *members[st.cluster];
+            uint64_t r = read_offset[st.cluster] + st.begin;
+
+            for (uint32_t i = st.begin; i < st.end; ++i, ++r) {
+                uint64_t e = 0;
+                for (auto & path_probs: probs[i].pathProbs()) { e += path_probs.second.size(); }
+                group_ptr[r + 1] = probs[i].pathProbs().size();
+                first_id[r + 1] = e;
+                noise[r] = probs[i].noiseProb();
+                count[r] = probs[i].readCount();
+            }
+        }
+
+        group_ptr[0] = 0;
+        for (uint64_t r = 0; r < R; ++r) {
+            group_ptr[r + 1] += group_ptr[r];
+            first_id[r + 1] += first_id[r];
+        }
+
+        const uint64_t NG = group_ptr[R], Z = first_id[R];
+
+        group_prob = static_cast<double *>(rpvg_b200_pinned_scratch(ctx, 2, sizeof(double) * (NG + 1)));
+        id_ptr = static_cast<uint64_t *>(rpvg_b200_pinned_scratch(ctx, 5, sizeof(uint64_t) * (NG + 1)));
+        ids = static_cast<uint32_t *>(rpvg_b200_pinned_scratch(ctx, 1, sizeof(uint32_t) * (Z + 1)));
+        if (!group_prob || !id_ptr || !ids) { fatalBatch(ctx, "rpvg_b200_pinned_scratch"); }
+
+        // pass 2: the groups as they are
+        #pragma omp parallel for schedule(dynamic, 4)
+        for (size_t q = 0; q < stretches.size(); ++q) {
+
+            const auto & st = stretches[q];
+            const auto & probs = *members[st.cluster];
+            uint64_t r = read_offset[st.cluster] + st.begin;
+
+            for (uint32_t i = st.begin; i < st.end; ++i, ++r) {
+
+                uint64_t g = group_ptr[r];
+                uint64_t e = first_id[r];
+
+                for (auto & path_probs: probs[i].pathProbs()) {
+                    group_prob[g] = path_probs.first;
+                    id_ptr[g] = e;
+                    if (!path_probs.second.empty()) { memcpy(ids + e, path_probs.second.data(), sizeof(uint32_t) * path_probs.second.size()); }
+                    e += path_probs.second.size();
+                    ++g;
+                }
+            }
+        }
+
+        id_ptr[NG] = Z;
+    }
+
+    rpvg_b200_read_records view() const {
+        return rpvg_b200_read_records{static_cast<uint32_t>(read_offset.size() - 1), read_offset.data(), group_ptr, group_prob, id_ptr, ids, noise, count};
+    }
+};
 
 // stage times on stderr when RPVG_B200_BATCH_TRACE is set
 struct BatchTrace {
@@ -660,7 +764,7 @@ void PathEstimator::posteriorsBatch(const vector<PathClusterEstimates *> & estim
 
     BatchTrace trace;
 
-    BatchArena arena;
+    BatchRecords arena;
     {
         vector<const vector<ReadPathProbabilities> *> member_probs;
         vector<uint32_t> member_paths;
@@ -668,7 +772,7 @@ void PathEstimator::posteriorsBatch(const vector<PathClusterEstimates *> & estim
             member_probs.push_back(cluster_probs[i]);
             member_paths.push_back(estimates[i]->paths.size());
         }
-        arena.build(threadContext(), member_probs, member_paths, false);
+        arena.build(threadContext(), member_probs, member_paths);
     }
 
     trace.lap("haplotypes: flatten");
@@ -691,11 +795,11 @@ void PathEstimator::posteriorsBatch(const vector<PathClusterEstimates *> & estim
     auto * ctx = threadContext();
 
     // the dense matrices (rows x paths of every cluster, as denseMatrix makes them) are built on the device
-    rpvg_b200_clusters clusters = arena.view();
+    rpvg_b200_read_records records = arena.view();
     rpvg_b200_grouped * resident = nullptr;
     trace.lap("haplotypes: plans");
 
-    if (rpvg_b200_grouped_raw(ctx, &clusters, &resident) != RPVG_B200_OK) { fatalBatch(ctx, "rpvg_b200_grouped_raw"); }
+    if (rpvg_b200_grouped_raw_records(ctx, &records, path_offset.data(), &resident) != RPVG_B200_OK) { fatalBatch(ctx, "rpvg_b200_grouped_raw_records"); }
 
     trace.lap("haplotypes: upload + dense matrices");
 
