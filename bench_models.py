@@ -175,7 +175,9 @@ def run(args, rank, local_rank, world, ClockSampler, host_threads):
                 "ms_per_step": 1e3 * max_seconds / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic", "config": config, "clocks": clocks, "inference_stage_wall_ms": 1e3 * max_seconds / args.steps,
                 "e2e": {"value": value, "unit": unit, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8 * arena.n_paths,
-                        "ms_per_step": 1e3 * max_seconds / args.steps, "note": "estimateBatch takes and fills host objects: the value is end to end by construction"},
+                        "ms_per_step": 1e3 * max_seconds / args.steps,
+                        "note": "estimateBatch takes and fills host objects: the value is end to end by construction; h2d bytes = the expanded arena (the "
+                                "haplotypes model sends its read records unexpanded, about a third of that)"},
                 "gpu_launches": None}
 
         if args.config == "c4":
